@@ -1,0 +1,70 @@
+"""ctypes binding of libfunasr_b200.so (the C-ABI in include/funasr_b200.h).
+
+No torch types cross the boundary: tensors are passed as raw device pointers, sizes as ints
+and the stream as an opaque handle.  There is NO CPU or PyTorch fallback: if the library is
+missing or a call fails, a RuntimeError is raised.
+"""
+import ctypes
+import os
+from ctypes import c_float, c_int, c_int64, c_uint32, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfunasr_b200.so")
+
+_P = c_void_p
+_I = c_int
+_F = c_float
+
+# name -> argument types (all return int unless noted); mirrors include/funasr_b200.h
+SIGNATURES = {
+    "fb200_fbank": [_P, _P, _P, _I, _I, _P, _I, _I, _I, _P, _I, _F, _F, _P, _P],
+    "fb200_lfr_cmvn": [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P, _P, _F, _I, _P, _I, _P],
+    "fb200_scale_add_pe": [_P, _I, _P, _I, _I, _I, _P, _F, _P, _I, _P],
+    "fb200_layernorm": [_P, _I, _I, _I, _P, _P, _F, _P, _I, _P, _I, _I, _P, _I, _P],
+    "fb200_split_rows": [_P, _I, _I, _I, _P, _I, _P],
+    "fb200_fsmn": [_P, _I, _P, _I, _I, _I, _P, _I, _P, _I, _P, _I, _P],
+    "fb200_gemm": [_P, _I, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P, _I, _P, _I, _P, _I, _I, _P],
+    "fb200_split_weight": [_P, _I, _I, _P, _I, _P],
+    "fb200_attention": [_P, _I, _P, _I, _P, _I, _P, _P, _I, _I, _I, _I, _I, _F, _P, _I, _P, _I, _P],
+    "fb200_cif_alpha": [_P, _I, _P, _I, _I, _I, _P, _P, _F, _F, _P, _P],
+    "fb200_cif_scan": [_P, _P, _I, _F, _P, _P, _P, _P, _P],
+    "fb200_cif_integrate": [_P, _I, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P, _I, _P],
+    "fb200_argmax_logprob": [_P, _I, _I, _I, _P, _P, _P],
+    "fb200_ctc_collapse": [_P, _P, _I, c_uint32, _I, _P, _P, _P],
+}
+EXPORTS = sorted(list(SIGNATURES) + ["fb200_version", "fb200_last_error", "fb200_launch_count"])
+
+_lib = None
+
+
+def load():
+    """Load the shared library (building it is `__graft_entry__.build()` / `python -m funasr_b200.build`)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            "funasr_b200: %s not found -- the CUDA extension is not built and there is no fallback path. "
+            "Run `python -m funasr_b200.build`." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, args in SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = c_int
+    lib.fb200_version.restype = c_int
+    lib.fb200_last_error.restype = ctypes.c_char_p
+    lib.fb200_launch_count.argtypes = [c_int]
+    lib.fb200_launch_count.restype = ctypes.c_longlong
+    _lib = lib
+    return lib
+
+
+def call(name, *args):
+    lib = load()
+    rc = getattr(lib, name)(*args)
+    if rc != 0:
+        raise RuntimeError("%s failed (%d): %s" % (name, rc, lib.fb200_last_error().decode()))
+
+
+def launch_count(reset: bool = False) -> int:
+    return int(load().fb200_launch_count(1 if reset else 0))

@@ -1,0 +1,80 @@
+// Shared helpers for the funasr_b200 kernels (sm_100a only).
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/funasr_b200.h"
+
+namespace fb200 {
+
+void set_error(const char* fmt, ...);
+void count_launch(int n = 1);
+
+#define FB_CHECK_ARG(cond, ...)          \
+  do {                                   \
+    if (!(cond)) {                       \
+      fb200::set_error(__VA_ARGS__);     \
+      return FB200_EINVAL;               \
+    }                                    \
+  } while (0)
+
+#define FB_CHECK_LAUNCH(name)                                                        \
+  do {                                                                               \
+    cudaError_t e_ = cudaGetLastError();                                             \
+    if (e_ != cudaSuccess) {                                                         \
+      fb200::set_error("%s: launch failed: %s", name, cudaGetErrorString(e_));       \
+      return FB200_ECUDA;                                                            \
+    }                                                                                \
+    fb200::count_launch();                                                           \
+  } while (0)
+
+constexpr int kWarp = 32;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// x ~= hi + mid + lo with each part a bf16 (round-to-nearest); hi+mid+lo carries 24 mantissa bits.
+__device__ __forceinline__ void split3(float x, __nv_bfloat16& hi, __nv_bfloat16& mid, __nv_bfloat16& lo) {
+  hi = __float2bfloat16_rn(x);
+  float r = x - __bfloat162float(hi);
+  mid = __float2bfloat16_rn(r);
+  r -= __bfloat162float(mid);
+  lo = __float2bfloat16_rn(r);
+}
+
+// Store `x` into a split operand row: part p at column p*kp + col.
+__device__ __forceinline__ void store_split(__nv_bfloat16* row, int kp, int col, float x, int nparts) {
+  if (nparts == 1) {
+    row[col] = __float2bfloat16_rn(x);
+  } else {
+    __nv_bfloat16 h, m, l;
+    split3(x, h, m, l);
+    row[col] = h;
+    row[kp + col] = m;
+    row[2 * kp + col] = l;
+  }
+}
+
+__host__ __device__ __forceinline__ int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+// Sequence index of packed row r: largest b with cu[b] <= r (cu has batch+1 entries).
+__device__ __forceinline__ int find_seq(const int32_t* __restrict__ cu, int batch, int r) {
+  int lo = 0, hi = batch;  // invariant: cu[lo] <= r < cu[hi]
+  while (hi - lo > 1) {
+    int mid = (lo + hi) >> 1;
+    if (__ldg(cu + mid) <= r) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+}  // namespace fb200

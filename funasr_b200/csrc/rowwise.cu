@@ -1,0 +1,214 @@
+// Row-wise HBM-bound kernels: LayerNorm (fp32 and/or bf16 split-operand output), operand
+// splitting, FSMN depthwise conv with per-sequence zero halos.
+#include "common.cuh"
+
+namespace fb200 {
+
+constexpr int kLnWarps = 4;
+
+// One warp per row, the row lives in registers (NV float4 per lane), two-pass mean/variance
+// like torch.nn.LayerNorm.  dim % 4 == 0, dim <= NV*128.
+template <int NV>
+__global__ void __launch_bounds__(kLnWarps * 32)
+layernorm_kernel(const float* __restrict__ x, int ld_x, int rows, int dim, const float* __restrict__ gamma,
+                 const float* __restrict__ beta, float eps, float* __restrict__ out_f32, int ld_f32,
+                 __nv_bfloat16* __restrict__ out_split, int nparts, int halo,
+                 const int32_t* __restrict__ cu_rows, int batch) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * kLnWarps + warp;
+  if (row >= rows) return;
+  const int nvec = dim >> 2;
+  const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * ld_x);
+  float4 v[NV];
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int idx = lane + i * 32;
+    v[i] = idx < nvec ? xr[idx] : make_float4(0.f, 0.f, 0.f, 0.f);
+    s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+  }
+  const float mean = warp_sum(s) / (float)dim;
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int idx = lane + i * 32;
+    if (idx < nvec) {
+      const float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
+      q += (a * a + b * b) + (c * c + d * d);
+    }
+  }
+  const float rstd = rsqrtf(warp_sum(q) / (float)dim + eps);
+
+  int out_row = row;
+  if (halo) out_row = row + 1 + find_seq(cu_rows, batch, row);
+  const int kp = round_up(dim, 64);
+  __nv_bfloat16* srow = out_split ? out_split + (size_t)out_row * (nparts * kp) : nullptr;
+#pragma unroll
+  for (int i = 0; i < NV; ++i) {
+    const int idx = lane + i * 32;
+    if (idx < nvec) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(gamma) + idx);
+      const float4 b = __ldg(reinterpret_cast<const float4*>(beta) + idx);
+      float4 y;
+      y.x = (v[i].x - mean) * rstd * g.x + b.x;
+      y.y = (v[i].y - mean) * rstd * g.y + b.y;
+      y.z = (v[i].z - mean) * rstd * g.z + b.z;
+      y.w = (v[i].w - mean) * rstd * g.w + b.w;
+      if (out_f32) reinterpret_cast<float4*>(out_f32 + (size_t)row * ld_f32)[idx] = y;
+      if (srow) {
+        const float yy[4] = {y.x, y.y, y.z, y.w};
+        __nv_bfloat16 p[3][4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (nparts == 1) p[0][u] = __float2bfloat16_rn(yy[u]);
+          else split3(yy[u], p[0][u], p[1][u], p[2][u]);
+        }
+        for (int pp = 0; pp < nparts; ++pp)
+          *reinterpret_cast<uint2*>(srow + pp * kp + idx * 4) = *reinterpret_cast<uint2*>(p[pp]);
+      }
+    }
+  }
+  if (srow) {  // zero the K padding
+    for (int c = dim + lane; c < kp; c += 32)
+      for (int pp = 0; pp < nparts; ++pp) srow[pp * kp + c] = __float2bfloat16_rn(0.f);
+  }
+}
+
+// fp32 [rows, dim] -> bf16 split [rows, nparts*Kp]; one thread per (row, column of Kp).
+__global__ void split_rows_kernel(const float* __restrict__ x, int ld_x, int rows, int dim,
+                                  __nv_bfloat16* __restrict__ out, int nparts) {
+  const int kp = round_up(dim, 64);
+  const size_t total = (size_t)rows * kp;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / kp), c = (int)(i - (size_t)r * kp);
+    const float val = c < dim ? x[(size_t)r * ld_x + c] : 0.f;
+    store_split(out + (size_t)r * nparts * kp, kp, c, val, nparts);
+  }
+}
+
+constexpr int kFsmnRows = 16;
+constexpr int kFsmnMaxK = 32;
+
+// out[r, c] = sum_j w[c, j] * v[r + j - left, c] (inside the sequence of r) + v[r, c] (+ res[r, c]).
+// One CTA = kFsmnRows consecutive packed rows x all channels; a thread owns 4 channels.
+// KS > 0: compile-time tap count (weights in registers); KS == 0: runtime `ksize_rt`.
+template <int KS>
+__global__ void fsmn_kernel(const float* __restrict__ v, int ld_v, const int32_t* __restrict__ cu_rows, int batch,
+                            int total_rows, int dim, const float* __restrict__ weight, int ksize_rt,
+                            const float* __restrict__ res, int ld_res, float* __restrict__ out, int ld_out) {
+  const int ksize = KS > 0 ? KS : ksize_rt;
+  constexpr int KW = KS > 0 ? KS : 1;
+  __shared__ int s_beg[kFsmnRows], s_end[kFsmnRows];
+  const int r0 = blockIdx.x * kFsmnRows;
+  if (threadIdx.x < kFsmnRows) {
+    const int r = r0 + threadIdx.x;
+    if (r < total_rows) {
+      const int b = find_seq(cu_rows, batch, r);
+      s_beg[threadIdx.x] = cu_rows[b];
+      s_end[threadIdx.x] = cu_rows[b + 1];
+    }
+  }
+  __syncthreads();
+  const int left = (ksize - 1) / 2;
+  for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) {
+    float w[4][KW];
+    if (KS > 0) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int j = 0; j < KW; ++j) w[u][j] = __ldg(weight + (size_t)(c + u) * ksize + j);
+    }
+    for (int i = 0; i < kFsmnRows; ++i) {
+      const int r = r0 + i;
+      if (r >= total_rows) break;
+      const int beg = s_beg[i], end = s_end[i];
+      float4 acc = *reinterpret_cast<const float4*>(v + (size_t)r * ld_v + c);
+      if (res) {
+        const float4 rr = *reinterpret_cast<const float4*>(res + (size_t)r * ld_res + c);
+        acc.x += rr.x; acc.y += rr.y; acc.z += rr.z; acc.w += rr.w;
+      }
+      float4 conv = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int j = 0; j < (KS > 0 ? KS : kFsmnMaxK); ++j) {
+        if (KS == 0 && j >= ksize) break;
+        const int rr = r + j - left;
+        if (rr >= beg && rr < end) {
+          const float4 x = *reinterpret_cast<const float4*>(v + (size_t)rr * ld_v + c);
+          float w0, w1, w2, w3;
+          if (KS > 0) {
+            w0 = w[0][j % KW]; w1 = w[1][j % KW]; w2 = w[2][j % KW]; w3 = w[3][j % KW];
+          } else {
+            w0 = __ldg(weight + (size_t)(c + 0) * ksize + j); w1 = __ldg(weight + (size_t)(c + 1) * ksize + j);
+            w2 = __ldg(weight + (size_t)(c + 2) * ksize + j); w3 = __ldg(weight + (size_t)(c + 3) * ksize + j);
+          }
+          conv.x = fmaf(w0, x.x, conv.x);
+          conv.y = fmaf(w1, x.y, conv.y);
+          conv.z = fmaf(w2, x.z, conv.z);
+          conv.w = fmaf(w3, x.w, conv.w);
+        }
+      }
+      acc.x += conv.x; acc.y += conv.y; acc.z += conv.z; acc.w += conv.w;
+      *reinterpret_cast<float4*>(out + (size_t)r * ld_out + c) = acc;
+    }
+  }
+}
+
+}  // namespace fb200
+
+using namespace fb200;
+
+extern "C" __attribute__((visibility("default"))) int fb200_layernorm(const float* x, int ld_x, int rows, int dim, const float* gamma, const float* beta,
+                               float eps, float* out_f32, int ld_f32, void* out_split, int nparts, int halo,
+                               const int32_t* cu_rows, int batch, void* stream) {
+  FB_CHECK_ARG(dim % 4 == 0 && dim <= 2048 && ld_x % 4 == 0, "layernorm: dim %d / ld %d unsupported", dim, ld_x);
+  FB_CHECK_ARG(out_f32 == nullptr || ld_f32 % 4 == 0, "layernorm: ld_f32 must be a multiple of 4");
+  FB_CHECK_ARG(nparts == 1 || nparts == 3, "layernorm: nparts must be 1 or 3");
+  FB_CHECK_ARG(!halo || (cu_rows != nullptr && batch > 0), "layernorm: halo output needs cu_rows");
+  if (rows == 0) return FB200_OK;
+  const int grid = (rows + kLnWarps - 1) / kLnWarps;
+  cudaStream_t st = (cudaStream_t)stream;
+  __nv_bfloat16* sp = (__nv_bfloat16*)out_split;
+#define LN_LAUNCH(NV)                                                                                            \
+  layernorm_kernel<NV><<<grid, kLnWarps * 32, 0, st>>>(x, ld_x, rows, dim, gamma, beta, eps, out_f32, ld_f32, sp, \
+                                                       nparts, halo, cu_rows, batch)
+  if (dim <= 512) LN_LAUNCH(4);
+  else if (dim <= 640) LN_LAUNCH(5);
+  else LN_LAUNCH(16);
+#undef LN_LAUNCH
+  FB_CHECK_LAUNCH("layernorm");
+  return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_split_rows(const float* x, int ld_x, int rows, int dim, void* out_split, int nparts,
+                                void* stream) {
+  FB_CHECK_ARG(nparts == 1 || nparts == 3, "split_rows: nparts must be 1 or 3");
+  if (rows == 0) return FB200_OK;
+  const size_t total = (size_t)rows * round_up(dim, 64);
+  int grid = (int)((total + 255) / 256);
+  if (grid > 148 * 16) grid = 148 * 16;
+  split_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, ld_x, rows, dim, (__nv_bfloat16*)out_split, nparts);
+  FB_CHECK_LAUNCH("split_rows");
+  return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts, void* stream) {
+  return fb200_split_rows(w, k, n, k, out_split, nparts, stream);
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_fsmn(const float* v, int ld_v, const int32_t* cu_rows, int batch, int total_rows, int dim,
+                          const float* weight, int ksize, const float* residual, int ld_res, float* out, int ld_out,
+                          void* stream) {
+  FB_CHECK_ARG(dim % 4 == 0 && ld_v % 4 == 0 && ld_out % 4 == 0, "fsmn: dim/ld must be multiples of 4");
+  FB_CHECK_ARG(ksize >= 1 && ksize <= kFsmnMaxK, "fsmn: ksize %d unsupported", ksize);
+  FB_CHECK_ARG(residual == nullptr || ld_res % 4 == 0, "fsmn: ld_res must be a multiple of 4");
+  if (total_rows == 0) return FB200_OK;
+  const int grid = (total_rows + kFsmnRows - 1) / kFsmnRows;
+  if (ksize == 11)
+    fsmn_kernel<11><<<grid, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight, ksize,
+                                                            residual, ld_res, out, ld_out);
+  else
+    fsmn_kernel<0><<<grid, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight, ksize,
+                                                           residual, ld_res, out, ld_out);
+  FB_CHECK_LAUNCH("fsmn");
+  return FB200_OK;
+}

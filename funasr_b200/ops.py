@@ -1,0 +1,144 @@
+"""Thin torch-facing wrappers over the C-ABI (include/funasr_b200.h).
+
+torch is used for device memory and the current stream only; every function here enqueues
+hand-written CUDA kernels from libfunasr_b200.so and raises if the library is unavailable.
+Naming: `cu_*` are int32 prefix-sum tensors on the device ([batch + 1]).
+"""
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+BK = 64  # K padding of split operands
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(t: torch.Tensor, dtype, name: str):
+    if not t.is_cuda:
+        raise RuntimeError("funasr_b200.%s: tensor must live on a CUDA device (no CPU fallback)" % name)
+    if t.dtype != dtype:
+        raise RuntimeError("funasr_b200.%s: expected %s, got %s" % (name, dtype, t.dtype))
+    return t
+
+
+def round_up(x: int, m: int = BK) -> int:
+    return (x + m - 1) // m * m
+
+
+def split_width(k: int, nparts: int) -> int:
+    return nparts * round_up(k)
+
+
+def fbank(wave, cu_samples, cu_frames, total_frames, window, mel_bank, frame_shift=160, nfft=512,
+          upscale=32768.0, preemph=0.97, out=None):
+    _chk(wave, torch.float32, "fbank")
+    _chk(cu_samples, torch.int64, "fbank")
+    _chk(cu_frames, torch.int32, "fbank")
+    n_mels = mel_bank.shape[0]
+    if out is None:
+        out = torch.empty(total_frames, n_mels, dtype=torch.float32, device=wave.device)
+    _lib.call("fb200_fbank", _p(wave), _p(cu_samples), _p(cu_frames), cu_frames.numel() - 1, total_frames,
+              _p(window), window.numel(), frame_shift, nfft, _p(mel_bank), n_mels, upscale, preemph, _p(out),
+              _stream())
+    return out
+
+
+def lfr_cmvn(fb, cu_frames, cu_rows, total_rows, lfr_m=7, lfr_n=6, shift=None, scale=None, pe_inv=None,
+             pe_scale=1.0, row_skip=0, out=None):
+    n_mels = fb.shape[1]
+    if out is None:
+        out = torch.empty(total_rows, n_mels * lfr_m, dtype=torch.float32, device=fb.device)
+    _lib.call("fb200_lfr_cmvn", _p(fb), _p(cu_frames), _p(cu_rows), cu_rows.numel() - 1, total_rows, n_mels,
+              lfr_m, lfr_n, _p(shift), _p(scale), _p(pe_inv), pe_scale, row_skip, _p(out), out.stride(0), _stream())
+    return out
+
+
+def scale_add_pe(x, cu_rows, pe_inv, scale, out=None):
+    _chk(x, torch.float32, "scale_add_pe")
+    if out is None:
+        out = torch.empty_like(x)
+    _lib.call("fb200_scale_add_pe", _p(x), x.stride(0), _p(cu_rows), cu_rows.numel() - 1, x.shape[0], x.shape[1],
+              _p(pe_inv), scale, _p(out), out.stride(0), _stream())
+    return out
+
+
+def layernorm(x, gamma, beta, eps, out_f32=None, out_split=None, nparts=1, halo=False, cu_rows=None, rows=None):
+    """x fp32 [rows, dim] (row stride allowed).  Writes out_f32 and/or out_split (preallocated)."""
+    _chk(x, torch.float32, "layernorm")
+    rows = x.shape[0] if rows is None else rows
+    batch = 0 if cu_rows is None else cu_rows.numel() - 1
+    _lib.call("fb200_layernorm", _p(x), x.stride(0), rows, x.shape[1], _p(gamma), _p(beta), eps, _p(out_f32),
+              0 if out_f32 is None else out_f32.stride(0), _p(out_split), nparts, 1 if halo else 0, _p(cu_rows),
+              batch, _stream())
+
+
+def split_rows(x, nparts, out=None):
+    _chk(x, torch.float32, "split_rows")
+    rows, dim = x.shape
+    if out is None:
+        out = torch.empty(rows, split_width(dim, nparts), dtype=torch.bfloat16, device=x.device)
+    _lib.call("fb200_split_rows", _p(x), x.stride(0), rows, dim, _p(out), nparts, _stream())
+    return out
+
+
+def fsmn(v, cu_rows, weight, out, residual=None, rows=None):
+    """v fp32 [rows, dim] view (row stride allowed); weight fp32 [dim, k]; out fp32 [rows, dim]."""
+    rows = v.shape[0] if rows is None else rows
+    _lib.call("fb200_fsmn", _p(v), v.stride(0), _p(cu_rows), cu_rows.numel() - 1, rows, v.shape[1], _p(weight),
+              weight.shape[-1], _p(residual), 0 if residual is None else residual.stride(0), _p(out), out.stride(0),
+              _stream())
+    return out
+
+
+def gemm(a_split, a_parts, w_split, w_parts, m, n, k, bias=None, relu=False, res1=None, res2=None, out_f32=None,
+         out_split=None, out_parts=1, taps=1, impl=0, a_rows=None):
+    """C[m, n] = A . W^T (+bias)(relu)(+res1)(+res2) over bf16 split operands (tcgen05)."""
+    _chk(a_split, torch.bfloat16, "gemm")
+    _chk(w_split, torch.bfloat16, "gemm")
+    a_rows = a_split.shape[0] if a_rows is None else a_rows
+    _lib.call("fb200_gemm", _p(a_split), a_rows, a_parts, _p(w_split), w_parts, m, n, k, taps, _p(bias),
+              1 if relu else 0, _p(res1), 0 if res1 is None else res1.stride(0), _p(res2),
+              0 if res2 is None else res2.stride(0), _p(out_f32), 0 if out_f32 is None else out_f32.stride(0),
+              _p(out_split), out_parts, impl, _stream())
+
+
+def attention(q, k, v, cu_q, cu_kv, max_q, heads, scale, out_f32=None, out_split=None, nparts=1, q_rows=None):
+    """q, k, v: fp32 2-D views (row stride allowed) with heads*128 columns."""
+    q_rows = q.shape[0] if q_rows is None else q_rows
+    _lib.call("fb200_attention", _p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(cu_q), _p(cu_kv),
+              cu_q.numel() - 1, q_rows, max_q, heads, q.shape[1] // heads, scale, _p(out_f32),
+              0 if out_f32 is None else out_f32.stride(0), _p(out_split), nparts, _stream())
+
+
+def cif_alpha(conv_relu, cu_rows, total_rows, w, b, alphas, smooth=1.0, noise=0.0):
+    _lib.call("fb200_cif_alpha", _p(conv_relu), conv_relu.stride(0), _p(cu_rows), cu_rows.numel() - 1, total_rows,
+              conv_relu.shape[1], _p(w), _p(b), smooth, noise, _p(alphas), _stream())
+
+
+def cif_scan(alphas, cu_rows, tail, token_num, fire_pos, fire_rem, fires=None):
+    _lib.call("fb200_cif_scan", _p(alphas), _p(cu_rows), cu_rows.numel() - 1, tail, _p(token_num), _p(fire_pos),
+              _p(fire_rem), _p(fires), _stream())
+
+
+def cif_integrate(hidden, alphas, cu_rows, cu_tok, total_tok, tail, fire_pos, fire_rem, embeds):
+    _lib.call("fb200_cif_integrate", _p(hidden), hidden.stride(0), _p(alphas), _p(cu_rows), _p(cu_tok),
+              cu_rows.numel() - 1, total_tok, hidden.shape[1], tail, _p(fire_pos), _p(fire_rem), _p(embeds),
+              embeds.stride(0), _stream())
+
+
+def argmax_logprob(logits, vocab, ids, score=None, rows=None):
+    rows = logits.shape[0] if rows is None else rows
+    _lib.call("fb200_argmax_logprob", _p(logits), logits.stride(0), rows, vocab, _p(ids), _p(score), _stream())
+
+
+def ctc_collapse(ids, cu_rows, drop_mask, collapse, out_ids, out_len):
+    _lib.call("fb200_ctc_collapse", _p(ids), _p(cu_rows), cu_rows.numel() - 1, drop_mask, 1 if collapse else 0,
+              _p(out_ids), _p(out_len), _stream())

@@ -1,0 +1,198 @@
+/*
+ * funasr_b200 -- C-ABI of the B200-native (sm_100a) kernels behind FunASR's batched offline
+ * non-autoregressive recognition path (WavFrontend -> SANMEncoder -> CifPredictorV2 ->
+ * ParaformerSANMDecoder -> greedy / CTC greedy).
+ *
+ * Boundary rules:
+ *   - plain pointers and sizes only; every pointer is DEVICE memory unless named `h_`;
+ *   - the caller owns every buffer (inputs, outputs, workspaces); the library never allocates
+ *     or frees device memory and keeps no mutable global state but a thread-local error string;
+ *   - all work is enqueued on the caller's `stream` (a cudaStream_t passed as void*); no call
+ *     synchronises the device;
+ *   - return 0 on success, a negative FB200_E* code otherwise; text via fb200_last_error().
+ *
+ * Data layout: utterances are PACKED, never padded.  Row r of a packed matrix belongs to the
+ * utterance b with cu_rows[b] <= r < cu_rows[b+1] (int32 prefix sums, cu_rows[0] = 0).  This is
+ * the reference's batch_size=1 semantics (funasr/auto/auto_model.py:185-187) for a whole batch.
+ *
+ * "Split operand" (dense contractions): a GEMM operand X[rows, K] is stored as bf16
+ * [rows, nparts * Kp], Kp = K rounded up to 64, part p in columns [p*Kp, (p+1)*Kp):
+ *   nparts = 1: bf16(X)                       (throughput mode)
+ *   nparts = 3: X ~= hi + mid + lo, each bf16 (fp32-parity mode; 6 cross terms on tcgen05)
+ * Padding columns are zero.
+ *
+ * Each entry point names the reference code it replaces (paths relative to the reference root).
+ */
+#ifndef FUNASR_B200_H_
+#define FUNASR_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FB200_OK 0
+#define FB200_EINVAL (-1)    /* bad shape / argument */
+#define FB200_ECUDA (-2)     /* CUDA runtime or driver error */
+#define FB200_EUNSUPPORTED (-3)
+
+#define FB200_VERSION 100
+
+int fb200_version(void);
+const char* fb200_last_error(void);
+/* Number of kernels launched by this thread through the library since the last reset. */
+long long fb200_launch_count(int reset);
+
+/* ------------------------------------------------------------------ frontend --------- */
+
+/* Kaldi fbank, replaces torchaudio.compliance.kaldi.fbank as called by WavFrontend.forward
+ * (funasr/frontends/wav_frontend.py:127-143): frames of `frame_len` samples every `frame_shift`,
+ * snip_edges, x32768 upscale (`upscale`), DC removal, pre-emphasis 0.97, window table,
+ * zero-pad to `nfft`, |rfft|^2, mel filterbank [n_mels, nfft/2+1], log(max(., FLT_EPSILON)).
+ *   wave        f32 [total_samples]   packed waveforms
+ *   cu_samples  i64 [batch+1]         sample offsets
+ *   cu_frames   i32 [batch+1]         frame offsets (frames_b = 1 + (N_b - frame_len)/frame_shift)
+ *   window      f32 [frame_len]
+ *   mel_bank    f32 [n_mels, nfft/2+1]
+ *   out         f32 [total_frames, n_mels]
+ */
+int fb200_fbank(const float* wave, const int64_t* cu_samples, const int32_t* cu_frames, int batch,
+                int total_frames, const float* window, int frame_len, int frame_shift, int nfft,
+                const float* mel_bank, int n_mels, float upscale, float preemph, float* out,
+                void* stream);
+
+/* LFR stacking + CMVN (+ optional encoder prologue), replaces apply_lfr / apply_cmvn
+ * (funasr/frontends/wav_frontend.py:41-74) and, when `pe_inv_timescales` != NULL, the
+ * `xs_pad * sqrt(d)` + SinusoidalPositionEncoder prologue of SANMEncoder.forward
+ * (funasr/models/sanm/encoder.py:378,397; funasr/models/transformer/embedding.py:383-413).
+ *   out[row, n_mels*j + c] = (fbank[clamp(lfr_n*i - (lfr_m-1)/2 + j, 0, F-1), c] + shift) * scale
+ *   cmvn_shift / cmvn_scale  f32 [n_mels*lfr_m] or NULL
+ *   pe_inv_timescales        f32 [n_mels*lfr_m/2] or NULL; position = i + 1 + pos_offset
+ *   out f32 [total_rows, ld_out] (ld_out >= n_mels*lfr_m), row = cu_rows[b] + row_offset_in_seq + i
+ * `row_skip` rows at the head of every sequence are left untouched (SenseVoice prompt frames).
+ */
+int fb200_lfr_cmvn(const float* fbank, const int32_t* cu_frames, const int32_t* cu_rows, int batch,
+                   int total_rows, int n_mels, int lfr_m, int lfr_n, const float* cmvn_shift,
+                   const float* cmvn_scale, const float* pe_inv_timescales, float pe_scale,
+                   int row_skip, float* out, int ld_out, void* stream);
+
+/* Encoder prologue alone for callers that hand over features: out = x*scale + PE(pos = i+1). */
+int fb200_scale_add_pe(const float* x, int ld_x, const int32_t* cu_rows, int batch, int total_rows,
+                       int dim, const float* pe_inv_timescales, float scale, float* out, int ld_out,
+                       void* stream);
+
+/* ------------------------------------------------------------------ row-wise ops ------ */
+
+/* LayerNorm over the last dim, replaces funasr/models/transformer/layer_norm.py:13-39
+ * (eps 1e-12) and the SenseVoice copy (eps 1e-5).  Outputs (either may be NULL):
+ *   out_f32   f32  [rows, ld_f32]
+ *   out_split bf16 split operand [rows_out, nparts*Kp]; row r is written at
+ *             r + (halo ? 1 + seq(r) : 0): `halo` interleaves one untouched (zero) row before
+ *             every sequence and after the last, for the k=3 CIF convolution.
+ */
+int fb200_layernorm(const float* x, int ld_x, int rows, int dim, const float* gamma,
+                    const float* beta, float eps, float* out_f32, int ld_f32, void* out_split,
+                    int nparts, int halo, const int32_t* cu_rows, int batch, void* stream);
+
+/* fp32 [rows, dim] -> bf16 split operand (no normalisation). */
+int fb200_split_rows(const float* x, int ld_x, int rows, int dim, void* out_split, int nparts,
+                     void* stream);
+
+/* FSMN memory block: depthwise conv1d over time, kernel `ksize`, zero halo PER SEQUENCE, plus
+ * identity: out = conv(v) + v (+ residual).  Replaces MultiHeadedAttentionSANM.forward_fsmn
+ * (funasr/models/sanm/attention.py:207-223) and MultiHeadedAttentionSANMDecoder.forward
+ * (:499-547).  weight f32 [dim, ksize] (= Conv1d weight [dim,1,ksize]); left pad (ksize-1)/2.
+ */
+int fb200_fsmn(const float* v, int ld_v, const int32_t* cu_rows, int batch, int total_rows, int dim,
+               const float* weight, int ksize, const float* residual, int ld_res, float* out,
+               int ld_out, void* stream);
+
+/* ------------------------------------------------------------------ dense contractions - */
+
+/* C = A . W^T over split operands on tcgen05 (TMA -> smem -> UMMA, fp32 accumulators in TMEM).
+ * Replaces every nn.Linear on the path and the k=3 Conv1d of CifPredictorV2:
+ *   linear_q_k_v / linear_out (funasr/models/sanm/attention.py:225-252,290),
+ *   w_1 / w_2 (funasr/models/transformer/positionwise_feed_forward.py:14-34,
+ *              funasr/models/sanm/positionwise_feed_forward.py:12-33),
+ *   linear_q / linear_k_v (attention.py:631-662), output_layer (paraformer/decoder.py:404),
+ *   cif_conv1d (paraformer/cif_predictor.py:190,213), ctc_lo (funasr/models/ctc/ctc.py:173-197).
+ *   a        bf16 split [a_rows, a_parts*Kp]
+ *   w        bf16 split [n, w_parts*Kp] (per tap: [taps][n, w_parts*Kp], tap stride = n*w_parts*Kp)
+ *   taps     1 for a Linear; 3 for the CIF conv: tap j reads A row (m + j) (halo layout)
+ *   terms    cross terms summed: a_parts=w_parts=1 -> 1; 3x3 parts -> 6 (hi.hi, hi.mid, mid.hi,
+ *            hi.lo, lo.hi, mid.mid) accumulated small-to-large
+ *   epilogue y = acc + bias[n]; if relu y = max(y,0); y += res1[m, :] + res2[m, :]
+ *   outputs  out_f32 [m, ld_out] and/or out_split (bf16 split, out_parts parts, Kp = n up to 64)
+ * impl: 0 = tcgen05 (product path), 1 = SIMT fp32 check kernel (same operands, for bring-up tests).
+ */
+int fb200_gemm(const void* a, int a_rows, int a_parts, const void* w, int w_parts, int m, int n,
+               int k, int taps, const float* bias, int relu, const float* res1, int ld_res1,
+               const float* res2, int ld_res2, float* out_f32, int ld_out, void* out_split,
+               int out_parts, int impl, void* stream);
+
+/* fp32 weight [n, k] -> bf16 split [n, nparts*Kp] (done once at load). */
+int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts, void* stream);
+
+/* ------------------------------------------------------------------ attention ---------- */
+
+/* softmax(q k^T * scale) v per utterance and head, var-len, streaming softmax (scores never
+ * materialised).  Replaces MultiHeadedAttentionSANM.forward_attention
+ * (funasr/models/sanm/attention.py:254-311) when cu_q == cu_kv, and
+ * MultiHeadedAttentionCrossAtt (attention.py:664-717) otherwise.
+ *   q f32 [q_rows, ld_q], k / v f32 [kv_rows, ld_k / ld_v], heads * head_dim columns each
+ *   out: f32 [q_rows, ld_out] and/or bf16 split [q_rows, nparts*Kp]
+ */
+int fb200_attention(const float* q, int ld_q, const float* k, int ld_k, const float* v, int ld_v,
+                    const int32_t* cu_q, const int32_t* cu_kv, int batch, int q_rows, int max_q,
+                    int heads, int head_dim, float scale, float* out_f32, int ld_out,
+                    void* out_split, int nparts, void* stream);
+
+/* ------------------------------------------------------------------ CIF predictor ------ */
+
+/* alpha = sigmoid(relu_conv[m, :] . w + b) * smooth - noise, clamped at 0; rows are in the halo
+ * layout of the conv GEMM (row m = r + seq(r)); writes alphas in PACKED order [total_rows].
+ * Replaces cif_output + sigmoid (funasr/models/paraformer/cif_predictor.py:216-219). */
+int fb200_cif_alpha(const float* conv_relu, int ld, const int32_t* cu_rows, int batch, int total_rows,
+                    int dim, const float* w, const float* b, float smooth, float noise, float* alphas,
+                    void* stream);
+
+/* Integrate-and-fire scan per utterance: tail_threshold appended at index T_b
+ * (tail_process_fn, cif_predictor.py:346-370), prefix sum in fp64 rounded to fp32, fire where
+ * floor crosses (cif_wo_hidden_v1, :668-693).
+ *   token_num  i32 [batch]    floor(sum alphas incl. tail)
+ *   fire_pos   i32 [total_rows + batch] packed per utterance at cu_rows[b] + b: frame index of the
+ *              k-th fire (index T_b = the appended zero frame)
+ *   fire_rem   f32 same layout: frac(fires) at the fire (`remains`, cif_v1 :718)
+ *   fires      f32 [total_rows + batch] or NULL: the reference's `fires`/cif_peak row (T_b+1 each)
+ */
+int fb200_cif_scan(const float* alphas, const int32_t* cu_rows, int batch, float tail_threshold,
+                   int32_t* token_num, int32_t* fire_pos, float* fire_rem, float* fires, void* stream);
+
+/* frames: embeds[cu_tok[b] + k, :] = sum_{t in (t_{k-1}, t_k]} alpha_t h_t + rem_{k-1} h_{t_{k-1}}
+ * - rem_k h_{t_k}  (cif_v1, cif_predictor.py:696-735); cu_tok = prefix sum of token_num. */
+int fb200_cif_integrate(const float* hidden, int ld_h, const float* alphas, const int32_t* cu_rows,
+                        const int32_t* cu_tok, int batch, int total_tok, int dim, float tail_threshold,
+                        const int32_t* fire_pos, const float* fire_rem, float* embeds, int ld_e,
+                        void* stream);
+
+/* ------------------------------------------------------------------ decoding ----------- */
+
+/* Per row: id = argmax(logits), score = max(log_softmax) -- the greedy branch of
+ * Paraformer.inference (funasr/models/paraformer/model.py:541-546) / CTC.argmax
+ * (funasr/models/ctc/ctc.py:186-197). */
+int fb200_argmax_logprob(const float* logits, int ld, int rows, int vocab, int32_t* ids, float* score,
+                         void* stream);
+
+/* CTC greedy collapse per utterance: unique_consecutive then drop ids < n_drop... drop set is
+ * {blank} (SenseVoiceSmall, funasr/models/sense_voice/model.py:895-906) or {0,1,2} given as a
+ * bit mask over ids 0..31 (funasr/models/ctc/model.py:243-247).  out_ids packed at cu_rows[b],
+ * out_len i32 [batch]. */
+int fb200_ctc_collapse(const int32_t* ids, const int32_t* cu_rows, int batch, uint32_t drop_mask,
+                       int collapse_repeats, int32_t* out_ids, int32_t* out_len, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FUNASR_B200_H_ */
