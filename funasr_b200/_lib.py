@@ -32,7 +32,10 @@ SIGNATURES = {
     "fb200_argmax_logprob": [_P, _I, _I, _I, _P, _P, _P],
     "fb200_ctc_collapse": [_P, _P, _I, c_uint32, _I, _P, _P, _P],
 }
-EXPORTS = sorted(list(SIGNATURES) + ["fb200_version", "fb200_last_error", "fb200_launch_count"])
+EXPORTS = sorted(list(SIGNATURES) + ["fb200_version", "fb200_last_error", "fb200_launch_count",
+                  "fb200_profile_enable", "fb200_profile_read"])
+PROFILE_KINDS = ["fbank", "lfr_cmvn", "scale_add_pe", "layernorm", "split_rows", "fsmn", "gemm", "attention",
+                 "cif_alpha", "cif_scan", "cif_integrate", "argmax_logprob", "ctc_collapse"]
 
 _lib = None
 
@@ -55,6 +58,11 @@ def load():
     lib.fb200_last_error.restype = ctypes.c_char_p
     lib.fb200_launch_count.argtypes = [c_int]
     lib.fb200_launch_count.restype = ctypes.c_longlong
+    lib.fb200_profile_enable.argtypes = [c_int]
+    lib.fb200_profile_enable.restype = c_int
+    lib.fb200_profile_read.argtypes = [c_int, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong),
+                                       ctypes.POINTER(ctypes.c_double), c_int]
+    lib.fb200_profile_read.restype = c_int
     _lib = lib
     return lib
 
@@ -68,3 +76,21 @@ def call(name, *args):
 
 def launch_count(reset: bool = False) -> int:
     return int(load().fb200_launch_count(1 if reset else 0))
+
+
+def profile_enable(on: bool) -> None:
+    load().fb200_profile_enable(1 if on else 0)
+
+
+def profile_read(reset: bool = True) -> dict:
+    """{kind: {"ms": summed device ms, "calls": n, "work": algorithmic bytes or FLOPs}} for this thread."""
+    lib = load()
+    out = {}
+    for i, name in enumerate(PROFILE_KINDS):
+        ms, calls, work = ctypes.c_double(), ctypes.c_longlong(), ctypes.c_double()
+        rc = lib.fb200_profile_read(i, ctypes.byref(ms), ctypes.byref(calls), ctypes.byref(work), 1 if reset else 0)
+        if rc != 0:
+            raise RuntimeError("fb200_profile_read failed (%d): %s" % (rc, lib.fb200_last_error().decode()))
+        if calls.value:
+            out[name] = {"ms": ms.value, "calls": int(calls.value), "work": work.value}
+    return out

@@ -186,6 +186,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_attention(const floa
   FB_CHECK_ARG(out_split == nullptr || nparts == 1 || nparts == 3, "attention: nparts must be 1 or 3");
   FB_CHECK_ARG(batch > 0 && batch <= 65535 && heads > 0, "attention: batch %d / heads %d out of range", batch, heads);
   if (q_rows == 0 || max_q == 0) return FB200_OK;
+  ProfScope prof(kProfAttention, stream, 0.0);
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kAttnSmem);

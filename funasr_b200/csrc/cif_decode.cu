@@ -179,6 +179,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_cif_alpha(const floa
                                void* stream) {
   FB_CHECK_ARG(batch > 0 && dim > 0, "cif_alpha: bad batch/dim");
   if (total_rows == 0) return FB200_OK;
+  ProfScope prof(kProfCifAlpha, stream, (double)total_rows * (dim + 1) * 4.0);
   cif_alpha_kernel<<<(total_rows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(conv_relu, ld, cu_rows, batch, total_rows,
                                                                           dim, w, b, smooth, noise, alphas);
   FB_CHECK_LAUNCH("cif_alpha");
@@ -188,6 +189,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_cif_alpha(const floa
 extern "C" __attribute__((visibility("default"))) int fb200_cif_scan(const float* alphas, const int32_t* cu_rows, int batch, float tail_threshold,
                               int32_t* token_num, int32_t* fire_pos, float* fire_rem, float* fires, void* stream) {
   FB_CHECK_ARG(batch > 0, "cif_scan: bad batch");
+  ProfScope prof(kProfCifScan, stream, 0.0);
   cif_scan_kernel<<<(batch + 3) / 4, 128, 0, (cudaStream_t)stream>>>(alphas, cu_rows, batch, tail_threshold, token_num,
                                                                     fire_pos, fire_rem, fires);
   FB_CHECK_LAUNCH("cif_scan");
@@ -200,6 +202,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_cif_integrate(const 
                                    void* stream) {
   FB_CHECK_ARG(dim % 4 == 0 && ld_h % 4 == 0 && ld_e % 4 == 0, "cif_integrate: dim/ld must be multiples of 4");
   if (total_tok == 0) return FB200_OK;
+  ProfScope prof(kProfCifIntegrate, stream, (double)total_tok * dim * 4.0);
   cif_integrate_kernel<<<total_tok, 128, 0, (cudaStream_t)stream>>>(hidden, ld_h, alphas, cu_rows, cu_tok, batch, dim,
                                                                    tail_threshold, fire_pos, fire_rem, embeds, ld_e);
   FB_CHECK_LAUNCH("cif_integrate");
@@ -210,6 +213,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_argmax_logprob(const
                                     void* stream) {
   FB_CHECK_ARG(vocab > 0 && ld >= vocab, "argmax: bad vocab/ld");
   if (rows == 0) return FB200_OK;
+  ProfScope prof(kProfArgmax, stream, (double)rows * vocab * 4.0);
   argmax_logprob_kernel<<<rows, 256, 0, (cudaStream_t)stream>>>(logits, ld, vocab, ids, score);
   FB_CHECK_LAUNCH("argmax_logprob");
   return FB200_OK;
@@ -218,6 +222,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_argmax_logprob(const
 extern "C" __attribute__((visibility("default"))) int fb200_ctc_collapse(const int32_t* ids, const int32_t* cu_rows, int batch, uint32_t drop_mask,
                                   int collapse_repeats, int32_t* out_ids, int32_t* out_len, void* stream) {
   FB_CHECK_ARG(batch > 0, "ctc_collapse: bad batch");
+  ProfScope prof(kProfCtc, stream, 0.0);
   ctc_collapse_kernel<<<(batch + 3) / 4, 128, 0, (cudaStream_t)stream>>>(ids, cu_rows, batch, drop_mask,
                                                                         collapse_repeats, out_ids, out_len);
   FB_CHECK_LAUNCH("ctc_collapse");

@@ -12,6 +12,21 @@ namespace fb200 {
 void set_error(const char* fmt, ...);
 void count_launch(int n = 1);
 
+// Times one entry point with CUDA events on the caller's stream when fb200_profile_enable(1)
+// was called by this thread; `work` is the algorithmic bytes or FLOPs of the call.
+enum ProfKind {
+  kProfFbank = 0, kProfLfr, kProfPe, kProfLayerNorm, kProfSplit, kProfFsmn, kProfGemm, kProfAttention,
+  kProfCifAlpha, kProfCifScan, kProfCifIntegrate, kProfArgmax, kProfCtc, kProfKinds
+};
+class ProfScope {
+ public:
+  ProfScope(int kind, void* stream, double work);
+  ~ProfScope();
+ private:
+  bool active_;
+  void* stream_;
+};
+
 #define FB_CHECK_ARG(cond, ...)          \
   do {                                   \
     if (!(cond)) {                       \

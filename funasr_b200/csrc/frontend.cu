@@ -179,6 +179,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_fbank(const float* w
   FB_CHECK_ARG(frame_len > 0 && frame_len <= nfft, "fbank: frame_len %d > nfft %d", frame_len, nfft);
   FB_CHECK_ARG(n_mels > 0 && n_mels <= kMaxMel, "fbank: n_mels %d unsupported", n_mels);
   if (total_frames == 0) return FB200_OK;
+  ProfScope prof(kProfFbank, stream, 4.0 * (double)total_frames * (frame_shift + n_mels));
   int log2n = 0;
   while ((1 << log2n) < nfft) ++log2n;
   int grid = (total_frames + kFbankWarps - 1) / kFbankWarps;
@@ -199,6 +200,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_lfr_cmvn(const float
   FB_CHECK_ARG((cmvn_shift == nullptr) == (cmvn_scale == nullptr), "lfr_cmvn: shift/scale must come together");
   FB_CHECK_ARG(ld_out >= n_mels * lfr_m, "lfr_cmvn: ld_out too small");
   if (total_rows == 0) return FB200_OK;
+  ProfScope prof(kProfLfr, stream, 4.0 * (double)total_rows * n_mels * (lfr_n + lfr_m));
   lfr_cmvn_kernel<<<total_rows, 160, 0, (cudaStream_t)stream>>>(fbank, cu_frames, cu_rows, batch, n_mels, lfr_m,
                                                                lfr_n, cmvn_shift, cmvn_scale, pe_inv_timescales,
                                                                pe_scale, row_skip, out, ld_out);
@@ -211,6 +213,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_scale_add_pe(const f
                                   void* stream) {
   FB_CHECK_ARG(dim % 2 == 0, "scale_add_pe: dim must be even");
   if (total_rows == 0) return FB200_OK;
+  ProfScope prof(kProfPe, stream, 8.0 * (double)total_rows * dim);
   scale_add_pe_kernel<<<total_rows, 256, 0, (cudaStream_t)stream>>>(x, ld_x, cu_rows, batch, dim,
                                                                    pe_inv_timescales, scale, out, ld_out);
   FB_CHECK_LAUNCH("scale_add_pe");

@@ -369,6 +369,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_gemm(const void* a, 
   FB_CHECK_ARG(out_f32 != nullptr || out_split != nullptr, "gemm: no output");
   FB_CHECK_ARG(out_split == nullptr || out_parts == 1 || out_parts == 3, "gemm: out_parts must be 1 or 3");
   if (m == 0) return FB200_OK;
+  ProfScope prof(kProfGemm, stream, 2.0 * (double)m * n * k * taps);
   GemmParams p;
   p.m = m;
   p.n = n;

@@ -40,8 +40,25 @@ layernorm_kernel(const float* __restrict__ x, int ld_x, int rows, int dim, const
   const float rstd = rsqrtf(warp_sum(q) / (float)dim + eps);
 
   int out_row = row;
-  if (halo) out_row = row + 1 + find_seq(cu_rows, batch, row);
   const int kp = round_up(dim, 64);
+  if (halo) {
+    const int b = find_seq(cu_rows, batch, row);
+    out_row = row + 1 + b;
+    // the zero rows of the halo layout are owned by the first row of each sequence (the row
+    // before it) and by the very last row (the row after it)
+    if (out_split) {
+      const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+      const int nv16 = nparts * kp / 8;
+      if (row == __ldg(cu_rows + b)) {
+        uint4* zr = reinterpret_cast<uint4*>(out_split + (size_t)(out_row - 1) * (nparts * kp));
+        for (int c = lane; c < nv16; c += 32) zr[c] = z;
+      }
+      if (row == rows - 1) {
+        uint4* zr = reinterpret_cast<uint4*>(out_split + (size_t)(out_row + 1) * (nparts * kp));
+        for (int c = lane; c < nv16; c += 32) zr[c] = z;
+      }
+    }
+  }
   __nv_bfloat16* srow = out_split ? out_split + (size_t)out_row * (nparts * kp) : nullptr;
 #pragma unroll
   for (int i = 0; i < NV; ++i) {
@@ -165,6 +182,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_layernorm(const floa
   FB_CHECK_ARG(nparts == 1 || nparts == 3, "layernorm: nparts must be 1 or 3");
   FB_CHECK_ARG(!halo || (cu_rows != nullptr && batch > 0), "layernorm: halo output needs cu_rows");
   if (rows == 0) return FB200_OK;
+  ProfScope prof(kProfLayerNorm, stream, (double)rows * dim * (4.0 + (out_f32 ? 4.0 : 0.0) + (out_split ? 2.0 * nparts : 0.0)));
   const int grid = (rows + kLnWarps - 1) / kLnWarps;
   cudaStream_t st = (cudaStream_t)stream;
   __nv_bfloat16* sp = (__nv_bfloat16*)out_split;
@@ -183,6 +201,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_split_rows(const flo
                                 void* stream) {
   FB_CHECK_ARG(nparts == 1 || nparts == 3, "split_rows: nparts must be 1 or 3");
   if (rows == 0) return FB200_OK;
+  ProfScope prof(kProfSplit, stream, (double)rows * dim * (4.0 + 2.0 * nparts));
   const size_t total = (size_t)rows * round_up(dim, 64);
   int grid = (int)((total + 255) / 256);
   if (grid > 148 * 16) grid = 148 * 16;
@@ -202,6 +221,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_fsmn(const float* v,
   FB_CHECK_ARG(ksize >= 1 && ksize <= kFsmnMaxK, "fsmn: ksize %d unsupported", ksize);
   FB_CHECK_ARG(residual == nullptr || ld_res % 4 == 0, "fsmn: ld_res must be a multiple of 4");
   if (total_rows == 0) return FB200_OK;
+  ProfScope prof(kProfFsmn, stream, (double)total_rows * dim * 4.0 * (residual ? 3.0 : 2.0));
   const int grid = (total_rows + kFsmnRows - 1) / kFsmnRows;
   if (ksize == 11)
     fsmn_kernel<11><<<grid, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight, ksize,

