@@ -373,16 +373,17 @@ class ParaformerEngine:
             self.decoder = DecoderPack(state_dict, self.device, heads=heads, nparts=self.nparts)
 
     # ---- stage-level entry points (also used by the parity tests) ------------------------------
-    def upload(self, waves: Sequence[np.ndarray]) -> Tuple[torch.Tensor, List[int]]:
-        """Pack host waveforms into one pinned buffer and copy it to the device (one H2D)."""
+    def upload(self, waves: Sequence) -> Tuple[torch.Tensor, List[int]]:
+        """Copy host waveforms (numpy arrays or torch CPU tensors, ideally pinned) into one packed
+        device buffer -- one async H2D per utterance on the current stream."""
         lens = [int(w.shape[0]) for w in waves]
-        host = torch.empty(sum(lens), dtype=torch.float32, pin_memory=True)
+        dev = torch.empty(sum(lens), dtype=torch.float32, device=self.device)
         o = 0
-        hv = host.numpy()
         for w, n in zip(waves, lens):
-            hv[o: o + n] = w
+            src = torch.from_numpy(w) if isinstance(w, np.ndarray) else w
+            dev[o: o + n].copy_(src, non_blocking=True)
             o += n
-        return host.to(self.device, non_blocking=True), lens
+        return dev, lens
 
     def forward_packed(self, wave: torch.Tensor, lens: Sequence[int], taps: Optional[dict] = None):
         """Device-resident packed waveforms -> (ids i32 [L] device, logp, token_num list)."""
