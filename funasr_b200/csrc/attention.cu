@@ -183,7 +183,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_attention(const floa
   FB_CHECK_ARG(ld_q % 4 == 0 && ld_k % 4 == 0 && ld_v % 4 == 0, "attention: leading dims must be multiples of 4");
   FB_CHECK_ARG(out_f32 != nullptr || out_split != nullptr, "attention: no output");
   FB_CHECK_ARG(out_f32 == nullptr || ld_out % 4 == 0, "attention: ld_out must be a multiple of 4");
-  FB_CHECK_ARG(out_split == nullptr || nparts == 1 || nparts == 3, "attention: nparts must be 1 or 3");
+  FB_CHECK_ARG(out_split == nullptr || (nparts >= 1 && nparts <= 3), "attention: nparts must be 1, 2 or 3");
   FB_CHECK_ARG(batch > 0 && batch <= 65535 && heads > 0, "attention: batch %d / heads %d out of range", batch, heads);
   if (q_rows == 0 || max_q == 0) return FB200_OK;
   ProfScope prof(kProfAttention, stream, 0.0);

@@ -67,17 +67,26 @@ __device__ __forceinline__ void split3(float x, __nv_bfloat16& hi, __nv_bfloat16
   lo = __float2bfloat16_rn(r);
 }
 
-// Store `x` into a split operand row: part p at column p*kp + col.
+// Store `x` into a split operand row: part p at column p*kp + col (nparts = 1, 2 or 3).
 __device__ __forceinline__ void store_split(__nv_bfloat16* row, int kp, int col, float x, int nparts) {
-  if (nparts == 1) {
-    row[col] = __float2bfloat16_rn(x);
-  } else {
-    __nv_bfloat16 h, m, l;
-    split3(x, h, m, l);
-    row[col] = h;
+  const __nv_bfloat16 h = __float2bfloat16_rn(x);
+  row[col] = h;
+  if (nparts > 1) {
+    float r = x - __bfloat162float(h);
+    const __nv_bfloat16 m = __float2bfloat16_rn(r);
     row[kp + col] = m;
-    row[2 * kp + col] = l;
+    if (nparts > 2) row[2 * kp + col] = __float2bfloat16_rn(r - __bfloat162float(m));
   }
+}
+
+// Four consecutive values -> 8-byte stores into each part (col % 4 == 0).
+__device__ __forceinline__ void store_split4(__nv_bfloat16* row, int kp, int col, const float (&y)[4], int nparts) {
+  __nv_bfloat16 part[3][4];
+#pragma unroll
+  for (int u = 0; u < 4; ++u) split3(y[u], part[0][u], part[1][u], part[2][u]);
+  *reinterpret_cast<uint2*>(row + col) = *reinterpret_cast<uint2*>(part[0]);
+  if (nparts > 1) *reinterpret_cast<uint2*>(row + kp + col) = *reinterpret_cast<uint2*>(part[1]);
+  if (nparts > 2) *reinterpret_cast<uint2*>(row + 2 * kp + col) = *reinterpret_cast<uint2*>(part[2]);
 }
 
 __host__ __device__ __forceinline__ int round_up(int x, int m) { return (x + m - 1) / m * m; }

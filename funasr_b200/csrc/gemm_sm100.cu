@@ -1,9 +1,18 @@
-// Dense contraction C = A . W^T over bf16 split operands on the 5th-gen tensor cores:
-//   TMA (cp.async.bulk.tensor, 128B swizzle) -> shared memory ring -> tcgen05.mma (one elected
-//   thread, fp32 accumulators in TMEM) -> tcgen05.ld -> fused epilogue (bias / ReLU / two
-//   residual addends / fp32 and bf16-split outputs).
-// fp32-parity mode runs the 6 cross terms of the 3-way bf16 split as extra K iterations of the
-// same accumulator (small terms first), so no separate accumulation pass exists.
+// Dense contraction C = A . W^T over bf16 split operands on the 5th-gen tensor cores.
+//
+//   persistent CTAs (one per SM), warp-specialised:
+//     warp 0      TMA producer   cp.async.bulk.tensor (128B swizzle) -> shared-memory stage ring
+//     warp 1      MMA issuer     tcgen05.mma kind::f16, one elected thread, fp32 accumulators in TMEM
+//     warps 2..5  epilogue       tcgen05.ld -> smem transpose -> coalesced bias/ReLU/residual/stores
+//   two TMEM accumulator buffers (2 x BN columns) so the epilogue of tile i overlaps the MMAs of
+//   tile i+1.
+//
+// Split operands: a stage holds ALL parts (hi, mid[, lo]) of the A and W k-block, and every cross
+// term of the split is issued against that one stage -- the tiles are fetched once from L2 for
+// 3 (or 6) tensor-core passes, which is what keeps the fp32-parity mode off the L2 roof.
+//   NP = 1: bf16                      1 term
+//   NP = 2: hi + mid (16-bit mant.)   3 terms  hi.mid, mid.hi, hi.hi        ("bf16x3")
+//   NP = 3: hi + mid + lo             6 terms  + mid.mid, hi.lo, lo.hi
 // A SIMT fp32 kernel over the SAME operands and epilogue is kept for bring-up tests (impl=1).
 #include <cuda.h>
 
@@ -13,13 +22,15 @@ namespace fb200 {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // bf16 elements = 128 bytes = one swizzle row
-constexpr int kStages = 4;
-constexpr int kGemmThreads = 192;  // warp0 TMA, warp1 MMA + TMEM alloc, warps 2..5 epilogue
+constexpr int kGemmThreads = 192;
+constexpr int kEpiPitch = 36;  // floats per staged row (32 + 4: conflict-free 128-bit accesses)
+constexpr int kMaxTerms = 6;
 
 struct GemmParams {
   int m, n, k_blocks, kp_a, kp_w;
   int taps, nterms;
-  int term_a[6], term_b[6];
+  int term_a[kMaxTerms], term_b[kMaxTerms];
+  int tiles_m, tiles_n;
   const float* bias;
   int relu;
   const float* res1;
@@ -41,6 +52,9 @@ __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
@@ -60,8 +74,8 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > 4000000000ll) {
-      printf("fb200 gemm: mbarrier wait timed out (block %d,%d thread %d bar %u parity %u)\n", blockIdx.x, blockIdx.y,
-             threadIdx.x, bar, parity);
+      printf("fb200 gemm: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x,
+             bar, parity);
       __trap();
     }
   }
@@ -115,79 +129,58 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
-// ---------------------------------------------------------------- shared epilogue -------
-// 32 consecutive output columns [col0, col0+32) of row `row`.
-__device__ __forceinline__ void epilogue_store32(const GemmParams& p, int row, int col0, float* acc) {
+// y = acc (+bias)(relu)(+res1)(+res2) for one output element (scalar path shared with the SIMT kernel)
+__device__ __forceinline__ float epilogue_value(const GemmParams& p, int row, int col, float acc) {
+  float y = acc;
+  if (p.bias) y += __ldg(p.bias + col);
+  if (p.relu) y = fmaxf(y, 0.f);
+  if (p.res1) y += p.res1[(size_t)row * p.ld_res1 + col];
+  if (p.res2) y += p.res2[(size_t)row * p.ld_res2 + col];
+  return y;
+}
+__device__ __forceinline__ void epilogue_store_scalar(const GemmParams& p, int row, int col, float acc) {
   if (row >= p.m) return;
-#pragma unroll
-  for (int j = 0; j < 32; ++j) {
-    const int col = col0 + j;
-    if (col < p.n) {
-      float y = acc[j];
-      if (p.bias) y += __ldg(p.bias + col);
-      if (p.relu) y = fmaxf(y, 0.f);
-      if (p.res1) y += p.res1[(size_t)row * p.ld_res1 + col];
-      if (p.res2) y += p.res2[(size_t)row * p.ld_res2 + col];
-      acc[j] = y;
-    } else {
-      acc[j] = 0.f;
-    }
-  }
-  if (p.out_f32) {
-    float* o = p.out_f32 + (size_t)row * p.ld_out + col0;
-    if (col0 + 32 <= p.n && (p.ld_out & 3) == 0) {
-#pragma unroll
-      for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
-    } else {
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < p.n) o[j] = acc[j];
-    }
-  }
-  if (p.out_split) {
-    // padding columns n..out_kp are written as zero (acc was zeroed above)
-    __nv_bfloat16* o = p.out_split + (size_t)row * (p.out_parts * p.out_kp);
-    if (col0 + 32 <= p.out_kp) {
-      __nv_bfloat16 h[32], mi[32], lo[32];
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        if (p.out_parts == 1) h[j] = __float2bfloat16_rn(acc[j]);
-        else split3(acc[j], h[j], mi[j], lo[j]);
-      }
-#pragma unroll
-      for (int j = 0; j < 32; j += 8) {
-        *reinterpret_cast<uint4*>(o + col0 + j) = *reinterpret_cast<uint4*>(h + j);
-        if (p.out_parts == 3) {
-          *reinterpret_cast<uint4*>(o + p.out_kp + col0 + j) = *reinterpret_cast<uint4*>(mi + j);
-          *reinterpret_cast<uint4*>(o + 2 * p.out_kp + col0 + j) = *reinterpret_cast<uint4*>(lo + j);
-        }
-      }
-    } else {
-      for (int j = 0; j < 32; ++j)
-        if (col0 + j < p.out_kp) store_split(o, p.out_kp, col0 + j, acc[j], p.out_parts);
-    }
+  if (col < p.n) {
+    const float y = epilogue_value(p, row, col, acc);
+    if (p.out_f32) p.out_f32[(size_t)row * p.ld_out + col] = y;
+    if (p.out_split) store_split(p.out_split + (size_t)row * (p.out_parts * p.out_kp), p.out_kp, col, y, p.out_parts);
+  } else if (p.out_split && col < p.out_kp) {  // zero padding columns of a split output
+    store_split(p.out_split + (size_t)row * (p.out_parts * p.out_kp), p.out_kp, col, 0.f, p.out_parts);
   }
 }
 
+// Cross terms of the split, smallest products first (hi = 0, mid = 1, lo = 2).
+template <int NP> __host__ __device__ constexpr int term_count() { return NP == 1 ? 1 : NP == 2 ? 3 : 6; }
+template <int NP> __host__ __device__ constexpr int term_a(int t) {
+  return NP == 1 ? 0 : NP == 2 ? (t == 1 ? 1 : 0) : (t == 0 ? 1 : t == 2 ? 2 : t == 4 ? 1 : 0);
+}
+template <int NP> __host__ __device__ constexpr int term_b(int t) {
+  return NP == 1 ? 0 : NP == 2 ? (t == 0 ? 1 : 0) : (t == 0 ? 1 : t == 1 ? 2 : t == 3 ? 1 : 0);
+}
+
 // ---------------------------------------------------------------- tcgen05 kernel --------
-template <int BN>
+template <int NP, int BN, int STAGES>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     const GemmParams p) {
-  constexpr uint32_t kABytes = BM * BK * 2;
-  constexpr uint32_t kBBytes = BN * BK * 2;
-  constexpr uint32_t kStageBytes = kABytes + kBBytes;
+  constexpr uint32_t kAPart = BM * BK * 2;
+  constexpr uint32_t kBPart = BN * BK * 2;
+  constexpr uint32_t kStageBytes = NP * (kAPart + kBPart);
+  constexpr uint32_t kEpiBytes = 4 * 32 * kEpiPitch * 4;
+  constexpr uint32_t kTmemCols = 2 * BN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B needs 1024 B alignment
-  const uint32_t bar_base = smem_base + kStages * kStageBytes;
-  // barriers: full[kStages], empty[kStages], tmem_full; then the TMEM base address slot
+  const uint32_t epi_base = smem_base + STAGES * kStageBytes;
+  const uint32_t bar_base = epi_base + kEpiBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
-  const uint32_t tmem_full_bar = bar_base + 8u * (2 * kStages);
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kStages + 1);
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * BM;
-  const int iters = p.taps * p.nterms * p.k_blocks;
+  const int total_tiles = p.tiles_m * p.tiles_n;
+  const int k_iters = p.taps * p.k_blocks;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -195,15 +188,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   }
   if (warp == 1) {
     if (lane == 0) {
-      for (int s = 0; s < kStages; ++s) {
+      for (int s = 0; s < STAGES; ++s) {
         mbar_init(full_bar(s), 1);
         mbar_init(empty_bar(s), 1);
       }
-      mbar_init(tmem_full_bar, 1);
+      for (int a = 0; a < 2; ++a) {
+        mbar_init(tfull_bar(a), 1);
+        mbar_init(tempty_bar(a), 4);  // one arrival per epilogue warp
+      }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)BN));
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(kTmemCols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
   }
   tcgen05_fence_before();
@@ -215,206 +211,141 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer =====
       int it = 0;
-      for (int tap = 0; tap < p.taps; ++tap)
-        for (int t = 0; t < p.nterms; ++t)
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+        for (int tap = 0; tap < p.taps; ++tap)
           for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
-            const int s = it % kStages;
-            const uint32_t ph = (uint32_t)(it / kStages) & 1u;
+            const int s = it % STAGES;
+            const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
             mbar_wait(empty_bar(s), ph ^ 1u);
             mbar_expect_tx(full_bar(s), kStageBytes);
             const uint32_t sa = smem_base + s * kStageBytes;
-            tma_load_2d(sa, &map_a, p.term_a[t] * p.kp_a + kb * BK, m0 + tap, full_bar(s));
-            tma_load_2d(sa + kABytes, &map_w, p.term_b[t] * p.kp_w + kb * BK, tap * p.n + n0, full_bar(s));
+#pragma unroll
+            for (int pa = 0; pa < NP; ++pa)
+              tma_load_2d(sa + pa * kAPart, &map_a, pa * p.kp_a + kb * BK, m0 + tap, full_bar(s));
+#pragma unroll
+            for (int pb = 0; pb < NP; ++pb)
+              tma_load_2d(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK, tap * p.n + n0, full_bar(s));
           }
+      }
     }
   } else if (warp == 1) {
     if (lane == 0) {  // ===== MMA issuer =====
       constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
-      for (int it = 0; it < iters; ++it) {
-        const int s = it % kStages;
-        const uint32_t ph = (uint32_t)(it / kStages) & 1u;
-        mbar_wait(full_bar(s), ph);
+      int it = 0, tl = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tl) {
+        const int acc = tl & 1;
+        mbar_wait(tempty_bar(acc), (((uint32_t)tl >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
         tcgen05_fence_after();
-        const uint32_t sa = smem_base + s * kStageBytes;
+        const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
+        for (int j = 0; j < k_iters; ++j, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+          mbar_wait(full_bar(s), ph);
+          tcgen05_fence_after();
+          const uint32_t sa = smem_base + s * kStageBytes;
+          const uint32_t sb = sa + NP * kAPart;
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          const uint64_t da = umma_desc_sw128(sa + k * 32);
-          const uint64_t db = umma_desc_sw128(sa + kABytes + k * 32);
-          umma_bf16(tmem_base, da, db, idesc, (it > 0 || k > 0) ? 1u : 0u);
+          for (int t = 0; t < term_count<NP>(); ++t) {
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = umma_desc_sw128(sa + term_a<NP>(t) * kAPart + k * 32);
+              const uint64_t db = umma_desc_sw128(sb + term_b<NP>(t) * kBPart + k * 32);
+              umma_bf16(tmem_d, da, db, idesc, (j > 0 || t > 0 || k > 0) ? 1u : 0u);
+            }
+          }
+          umma_commit(empty_bar(s));  // frees the smem stage once these MMAs retire
         }
-        umma_commit(empty_bar(s));  // frees the smem slot once these MMAs retire
+        umma_commit(tfull_bar(acc));
       }
-      umma_commit(tmem_full_bar);
     }
   } else {  // ===== epilogue warps 2..5: TMEM lane group = warp % 4 =====
     const int lg = warp & 3;
-    mbar_wait(tmem_full_bar, 0);
-    tcgen05_fence_after();
-    const int row = m0 + lg * 32 + lane;
+    float* stage = reinterpret_cast<float*>(smem_raw + (epi_base - smem_u32(smem_raw))) + (warp - 2) * 32 * kEpiPitch;
+    const int ncols = p.out_split ? p.out_kp : p.n;
+    const bool vec_ok = (p.n & 3) == 0 && (!p.out_f32 || (p.ld_out & 3) == 0) && (!p.res1 || (p.ld_res1 & 3) == 0) &&
+                        (!p.res2 || (p.ld_res2 & 3) == 0);
+    const int rr0 = lane >> 3, cc = (lane & 7) * 4;
+    int tl = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tl) {
+      const int acc = tl & 1;
+      const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+      mbar_wait(tfull_bar(acc), ((uint32_t)tl >> 1) & 1u);
+      tcgen05_fence_after();
+      const int row_base = m0 + lg * 32;
 #pragma unroll 1
-    for (int c = 0; c < BN; c += 32) {
-      uint32_t r[32];
-      tmem_ld32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)c, r);
-      if (n0 + c < p.n || (p.out_split && n0 + c < p.out_kp))
-        epilogue_store32(p, row, n0 + c, reinterpret_cast<float*>(r));
+      for (int c = 0; c < BN; c += 32) {
+        const int col = n0 + c + cc;
+        const bool live = n0 + c < ncols;  // warp-uniform
+        // residual prefetch for this chunk (coalesced: 8 lanes cover 128 B of one row)
+        float4 rv[8];
+        const bool vec = vec_ok && col + 3 < p.n;
+        if (live && p.res1 && vec) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int row = row_base + i * 4 + rr0;
+            rv[i] = row < p.m ? *reinterpret_cast<const float4*>(p.res1 + (size_t)row * p.ld_res1 + col)
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * BN + c), r);
+        if (c + 32 >= BN) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
+          tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(acc));
+        }
+        if (!live) continue;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(stage + lane * kEpiPitch + j * 4) =
+              make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
+                          __uint_as_float(r[4 * j + 3]));
+        __syncwarp();
+        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (vec && p.bias) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = i * 4 + rr0;
+          const int row = row_base + rr;
+          const float4 a4 = *reinterpret_cast<const float4*>(stage + rr * kEpiPitch + cc);
+          if (row >= p.m) continue;
+          if (vec) {
+            float y[4] = {a4.x + bv.x, a4.y + bv.y, a4.z + bv.z, a4.w + bv.w};
+            if (p.relu) {
+#pragma unroll
+              for (int u = 0; u < 4; ++u) y[u] = fmaxf(y[u], 0.f);
+            }
+            if (p.res1) {
+              y[0] += rv[i].x; y[1] += rv[i].y; y[2] += rv[i].z; y[3] += rv[i].w;
+            }
+            if (p.res2) {
+              const float4 q = *reinterpret_cast<const float4*>(p.res2 + (size_t)row * p.ld_res2 + col);
+              y[0] += q.x; y[1] += q.y; y[2] += q.z; y[3] += q.w;
+            }
+            if (p.out_f32)
+              *reinterpret_cast<float4*>(p.out_f32 + (size_t)row * p.ld_out + col) = make_float4(y[0], y[1], y[2], y[3]);
+            if (p.out_split)
+              store_split4(p.out_split + (size_t)row * (p.out_parts * p.out_kp), p.out_kp, col, y, p.out_parts);
+          } else {
+            epilogue_store_scalar(p, row, col + 0, a4.x);
+            epilogue_store_scalar(p, row, col + 1, a4.y);
+            epilogue_store_scalar(p, row, col + 2, a4.z);
+            epilogue_store_scalar(p, row, col + 3, a4.w);
+          }
+        }
+        __syncwarp();
+      }
     }
   }
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
     __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)BN));
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
   }
-}
-
-// ---------------------------------------------------------------- SIMT check kernel -----
-// Same operands, same term list, same epilogue; fp32 FFMA.  One thread = one row x 32 columns.
-__global__ void gemm_simt_kernel(const __nv_bfloat16* __restrict__ a, int a_rows, int lda,
-                                 const __nv_bfloat16* __restrict__ w, int ldw, const GemmParams p) {
-  const int row = blockIdx.y * blockDim.x + threadIdx.x;
-  const int col0 = blockIdx.x * 32;
-  float acc[32];
-#pragma unroll
-  for (int j = 0; j < 32; ++j) acc[j] = 0.f;
-  if (row < p.m) {
-    for (int tap = 0; tap < p.taps; ++tap) {
-      const int ar = row + tap;
-      if (ar >= a_rows) continue;
-      for (int t = 0; t < p.nterms; ++t) {
-        const __nv_bfloat16* ap = a + (size_t)ar * lda + p.term_a[t] * p.kp_a;
-        for (int k = 0; k < p.k_blocks * BK; ++k) {
-          const float av = __bfloat162float(ap[k]);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int col = col0 + j;
-            if (col < p.n)
-              acc[j] = fmaf(av, __bfloat162float(w[((size_t)tap * p.n + col) * ldw + p.term_b[t] * p.kp_w + k]), acc[j]);
-          }
-        }
-      }
-    }
-  }
-  epilogue_store32(p, row, col0, acc);
-}
-
-// ---------------------------------------------------------------- host side -------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (fn == nullptr) {
-    void* ptr = nullptr;
-    cudaDriverEntryPointQueryResult q;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
-        q == cudaDriverEntryPointSuccess)
-      fn = (EncodeTiledFn)ptr;
-  }
-  return fn;
-}
-
-// 2-D bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128-byte swizzle, zero OOB fill.
-static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
-  EncodeTiledFn fn = get_encode_fn();
-  if (fn == nullptr) {
-    set_error("gemm: cuTensorMapEncodeTiled entry point not available");
-    return FB200_ECUDA;
-  }
-  cuuint64_t dims[2] = {cols, rows};
-  cuuint64_t strides[1] = {cols * 2};
-  cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    set_error("gemm: cuTensorMapEncodeTiled failed (%d) rows=%llu cols=%llu", (int)r, (unsigned long long)rows,
-              (unsigned long long)cols);
-    return FB200_ECUDA;
-  }
-  return FB200_OK;
-}
-
-template <int BN>
-static int launch_tcgen05(const CUtensorMap& ma, const CUtensorMap& mw, const GemmParams& p, cudaStream_t st) {
-  constexpr size_t smem = kStages * (BM * BK * 2 + BN * BK * 2) + 1024 + 256;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaError_t e = cudaFuncSetAttribute(gemm_tcgen05_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) {
-      set_error("gemm: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-      return FB200_ECUDA;
-    }
-    attr_set = true;
-  }
-  const int ncols = p.out_split ? p.out_kp : p.n;  // split outputs also own their zero padding columns
-  dim3 grid((ncols + BN - 1) / BN, (p.m + BM - 1) / BM);
-  gemm_tcgen05_kernel<BN><<<grid, kGemmThreads, smem, st>>>(ma, mw, p);
-  return FB200_OK;
 }
 
 }  // namespace fb200
 
-using namespace fb200;
-
-extern "C" __attribute__((visibility("default"))) int fb200_gemm(const void* a, int a_rows, int a_parts, const void* w, int w_parts, int m, int n, int k,
-                          int taps, const float* bias, int relu, const float* res1, int ld_res1, const float* res2,
-                          int ld_res2, float* out_f32, int ld_out, void* out_split, int out_parts, int impl,
-                          void* stream) {
-  FB_CHECK_ARG(m >= 0 && n > 0 && k > 0, "gemm: bad shape m=%d n=%d k=%d", m, n, k);
-  FB_CHECK_ARG((a_parts == 1 || a_parts == 3) && (w_parts == 1 || w_parts == 3), "gemm: parts must be 1 or 3");
-  FB_CHECK_ARG(taps >= 1 && taps <= 3, "gemm: taps %d unsupported", taps);
-  FB_CHECK_ARG(a_rows >= m + taps - 1 || taps == 1, "gemm: a_rows %d too small for m=%d taps=%d", a_rows, m, taps);
-  FB_CHECK_ARG(out_f32 != nullptr || out_split != nullptr, "gemm: no output");
-  FB_CHECK_ARG(out_split == nullptr || out_parts == 1 || out_parts == 3, "gemm: out_parts must be 1 or 3");
-  if (m == 0) return FB200_OK;
-  ProfScope prof(kProfGemm, stream, 2.0 * (double)m * n * k * taps);
-  GemmParams p;
-  p.m = m;
-  p.n = n;
-  p.kp_a = p.kp_w = round_up(k, BK);
-  p.k_blocks = p.kp_a / BK;
-  p.taps = taps;
-  if (a_parts == 3 && w_parts == 3) {
-    // hi=0, mid=1, lo=2; smallest products first so the fp32 accumulator keeps their bits
-    const int ta[6] = {1, 0, 2, 0, 1, 0}, tb[6] = {1, 2, 0, 1, 0, 0};
-    p.nterms = 6;
-    for (int i = 0; i < 6; ++i) p.term_a[i] = ta[i], p.term_b[i] = tb[i];
-  } else {
-    FB_CHECK_ARG(a_parts == 1 && w_parts == 1, "gemm: mixed split counts (%d, %d) unsupported", a_parts, w_parts);
-    p.nterms = 1;
-    for (int i = 0; i < 6; ++i) p.term_a[i] = p.term_b[i] = 0;
-  }
-  p.bias = bias;
-  p.relu = relu;
-  p.res1 = res1;
-  p.ld_res1 = ld_res1;
-  p.res2 = res2;
-  p.ld_res2 = ld_res2;
-  p.out_f32 = out_f32;
-  p.ld_out = ld_out;
-  p.out_split = (__nv_bfloat16*)out_split;
-  p.out_parts = out_split ? out_parts : 0;
-  p.out_kp = out_split ? round_up(n, BK) : 0;
-  cudaStream_t st = (cudaStream_t)stream;
-  const int lda = a_parts * p.kp_a, ldw = w_parts * p.kp_w;
-
-  if (impl == 1) {
-    const int ncols = p.out_split ? p.out_kp : n;
-    dim3 grid((ncols + 31) / 32, (m + 127) / 128);
-    gemm_simt_kernel<<<grid, 128, 0, st>>>((const __nv_bfloat16*)a, a_rows, lda, (const __nv_bfloat16*)w, ldw, p);
-    FB_CHECK_LAUNCH("gemm_simt");
-    return FB200_OK;
-  }
-  FB_CHECK_ARG(impl == 0, "gemm: impl %d unknown", impl);
-  CUtensorMap ma, mw;
-  int rc = make_map(&ma, a, (uint64_t)a_rows, (uint64_t)lda, BM);
-  if (rc) return rc;
-  rc = make_map(&mw, w, (uint64_t)taps * n, (uint64_t)ldw, 128);
-  if (rc) return rc;
-  rc = launch_tcgen05<128>(ma, mw, p, st);
-  if (rc) return rc;
-  FB_CHECK_LAUNCH("gemm_tcgen05");
-  return FB200_OK;
-}
+#include "gemm_host.inc"

@@ -74,14 +74,7 @@ layernorm_kernel(const float* __restrict__ x, int ld_x, int rows, int dim, const
       if (out_f32) reinterpret_cast<float4*>(out_f32 + (size_t)row * ld_f32)[idx] = y;
       if (srow) {
         const float yy[4] = {y.x, y.y, y.z, y.w};
-        __nv_bfloat16 p[3][4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          if (nparts == 1) p[0][u] = __float2bfloat16_rn(yy[u]);
-          else split3(yy[u], p[0][u], p[1][u], p[2][u]);
-        }
-        for (int pp = 0; pp < nparts; ++pp)
-          *reinterpret_cast<uint2*>(srow + pp * kp + idx * 4) = *reinterpret_cast<uint2*>(p[pp]);
+        store_split4(srow, kp, idx * 4, yy, nparts);
       }
     }
   }
@@ -179,7 +172,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_layernorm(const floa
                                const int32_t* cu_rows, int batch, void* stream) {
   FB_CHECK_ARG(dim % 4 == 0 && dim <= 2048 && ld_x % 4 == 0, "layernorm: dim %d / ld %d unsupported", dim, ld_x);
   FB_CHECK_ARG(out_f32 == nullptr || ld_f32 % 4 == 0, "layernorm: ld_f32 must be a multiple of 4");
-  FB_CHECK_ARG(nparts == 1 || nparts == 3, "layernorm: nparts must be 1 or 3");
+  FB_CHECK_ARG(nparts >= 1 && nparts <= 3, "layernorm: nparts must be 1, 2 or 3");
   FB_CHECK_ARG(!halo || (cu_rows != nullptr && batch > 0), "layernorm: halo output needs cu_rows");
   if (rows == 0) return FB200_OK;
   ProfScope prof(kProfLayerNorm, stream, (double)rows * dim * (4.0 + (out_f32 ? 4.0 : 0.0) + (out_split ? 2.0 * nparts : 0.0)));
@@ -199,7 +192,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_layernorm(const floa
 
 extern "C" __attribute__((visibility("default"))) int fb200_split_rows(const float* x, int ld_x, int rows, int dim, void* out_split, int nparts,
                                 void* stream) {
-  FB_CHECK_ARG(nparts == 1 || nparts == 3, "split_rows: nparts must be 1 or 3");
+  FB_CHECK_ARG(nparts >= 1 && nparts <= 3, "split_rows: nparts must be 1, 2 or 3");
   if (rows == 0) return FB200_OK;
   ProfScope prof(kProfSplit, stream, (double)rows * dim * (4.0 + 2.0 * nparts));
   const size_t total = (size_t)rows * round_up(dim, 64);

@@ -13,8 +13,9 @@ Stages (reference call stack):
   predict    funasr/models/paraformer/cif_predictor.py:202-253, :346-370, :668-735
   decode     funasr/models/paraformer/decoder.py:359-411 + greedy pick paraformer/model.py:527-565
 
-precision = "fp32": every dense contraction runs the 3-way bf16 split (6 tcgen05 cross terms,
-fp32 accumulate) -- parity mode.  precision = "bf16": single bf16 operands -- throughput mode.
+precision = "fp32": every dense contraction runs on a 2-way bf16 split of both operands (hi + mid,
+16 mantissa bits; 3 tcgen05 cross terms, fp32 accumulate) -- parity mode.  "fp32x6": 3-way split,
+6 terms (24 mantissa bits).  "bf16": single bf16 operands -- throughput mode.
 """
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -354,17 +355,20 @@ class ParaformerEngine:
     host float32 waveforms in, token-id lists out.  One instance per process / GPU."""
 
     DROP_IDS = (0, 1, 2)  # blank, sos, eos (model.py:561-565)
+    # bf16 parts per dense-contraction operand: fp32 = hi + mid (3 tcgen05 terms, "bf16x3"),
+    # fp32x6 = hi + mid + lo (6 terms), bf16 = plain bf16 operands
+    PRECISIONS = {"fp32": 2, "fp32x6": 3, "bf16": 1}
 
     def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp32",
                  cmvn: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, window: str = "hamming", heads: int = 4,
                  max_rows: int = 16384):
-        if precision not in ("fp32", "bf16"):
-            raise ValueError("precision must be 'fp32' or 'bf16'")
+        if precision not in self.PRECISIONS:
+            raise ValueError("precision must be one of %s" % sorted(self.PRECISIONS))
         if not torch.cuda.is_available():
             raise RuntimeError("funasr_b200: no CUDA device -- this path has no CPU fallback")
         self.device = torch.device(device)
         self.precision = precision
-        self.nparts = 3 if precision == "fp32" else 1
+        self.nparts = self.PRECISIONS[precision]
         self.max_rows = max_rows
         with torch.cuda.device(self.device):
             self.frontend = FrontendPack(self.device, cmvn=cmvn, window=window)

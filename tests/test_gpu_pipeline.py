@@ -29,6 +29,11 @@ def eng_fp32(paraformer_sd, cmvn):
 
 
 @pytest.fixture(scope="module")
+def eng_fp32x6(paraformer_sd, cmvn):
+    return engine.ParaformerEngine(paraformer_sd, DEV, "fp32x6", cmvn=cmvn)
+
+
+@pytest.fixture(scope="module")
 def eng_bf16(paraformer_sd, cmvn):
     return engine.ParaformerEngine(paraformer_sd, DEV, "bf16", cmvn=cmvn)
 
@@ -117,3 +122,25 @@ def test_launch_counter_counts_kernels(eng_fp32):
     eng_fp32.forward_packed(wave, lens)
     n = _lib.launch_count()
     assert n > 400  # 50 encoder layers x 8 kernels + predictor + 16 decoder layers
+
+
+def test_fp32x6_mode_matches_reference_golden(golden_dir, eng_fp32x6):
+    g = np.load(os.path.join(golden_dir, "transcripts.npz"))
+    lens = g["num_samples"].tolist()
+    waves = [synth.synth_waveform(100 + i, n) for i, n in enumerate(lens)]
+    out = eng_fp32x6.recognize(waves)
+    for i in range(len(lens)):
+        assert out[i] == g["ids_%d" % i].tolist(), "utterance %d" % i
+
+
+def test_fp32_mode_error_budget_is_reported(golden_dir, eng_fp32, eng_fp32x6):
+    """Encoder max-relative error of both parity modes against the reference (budget 1e-3)."""
+    g = np.load(os.path.join(golden_dir, "stages_10s.npz"))
+    for name, eng in (("fp32 (3 terms)", eng_fp32), ("fp32x6 (6 terms)", eng_fp32x6)):
+        wave, lens = eng.upload([synth.synth_waveform(11, 160000)])
+        taps = {}
+        eng.forward_packed(wave, lens, taps=taps)
+        err = rel(taps["enc"], g["enc"])
+        print("%s: encoder max-rel error %.3e, alpha max abs %.3e" % (
+            name, err, float((taps["alphas"].cpu() - torch.from_numpy(g["alphas"][:-1])).abs().max())))
+        assert err < 1e-3
