@@ -17,6 +17,7 @@
 #include <cuda.h>
 
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 namespace fb200 {
 
@@ -38,96 +39,10 @@ struct GemmParams {
   const float* res2;
   int ld_res2;
   float* out_f32;
-  int ld_out;
+  int ld_out, f32_col0;  // out_f32 holds columns [f32_col0, n) only
   __nv_bfloat16* out_split;
   int out_parts, out_kp;
 };
-
-// ---------------------------------------------------------------- PTX wrappers ----------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t"
-      "}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok;
-}
-// Bounded wait: a pipeline bug must trap (reported as a CUDA error), never hang the GPU box.
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000ll) {
-      printf("fb200 gemm: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x,
-             bar, parity);
-      __trap();
-    }
-  }
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-      "l"(map), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
-                                          uint32_t accumulate) {
-  asm volatile(
-      "{\n\t"
-      ".reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t"
-      "}" ::"r"(tmem_d),
-      "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-// K-major operand tile, 128-byte swizzle: rows are 128 B, 8-row atoms are 1024 B apart.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);  // start address
-  d |= (uint64_t)1 << 16;                        // leading byte offset (unused for swizzled K-major)
-  d |= (uint64_t)(1024 >> 4) << 32;              // stride byte offset
-  d |= (uint64_t)1 << 46;                        // descriptor version (sm_100)
-  d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
-  return d;
-}
-// kind::f16 instruction descriptor: bf16 x bf16 -> fp32, both operands K-major.
-__host__ __device__ constexpr uint32_t umma_idesc_bf16(int m, int n) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
 
 // y = acc (+bias)(relu)(+res1)(+res2) for one output element (scalar path shared with the SIMT kernel)
 __device__ __forceinline__ float epilogue_value(const GemmParams& p, int row, int col, float acc) {
@@ -142,7 +57,7 @@ __device__ __forceinline__ void epilogue_store_scalar(const GemmParams& p, int r
   if (row >= p.m) return;
   if (col < p.n) {
     const float y = epilogue_value(p, row, col, acc);
-    if (p.out_f32) p.out_f32[(size_t)row * p.ld_out + col] = y;
+    if (p.out_f32 && col >= p.f32_col0) p.out_f32[(size_t)row * p.ld_out + col - p.f32_col0] = y;
     if (p.out_split) store_split(p.out_split + (size_t)row * (p.out_parts * p.out_kp), p.out_kp, col, y, p.out_parts);
   } else if (p.out_split && col < p.out_kp) {  // zero padding columns of a split output
     store_split(p.out_split + (size_t)row * (p.out_parts * p.out_kp), p.out_kp, col, 0.f, p.out_parts);
@@ -323,8 +238,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               const float4 q = *reinterpret_cast<const float4*>(p.res2 + (size_t)row * p.ld_res2 + col);
               y[0] += q.x; y[1] += q.y; y[2] += q.z; y[3] += q.w;
             }
-            if (p.out_f32)
-              *reinterpret_cast<float4*>(p.out_f32 + (size_t)row * p.ld_out + col) = make_float4(y[0], y[1], y[2], y[3]);
+            if (p.out_f32 && col >= p.f32_col0)
+              *reinterpret_cast<float4*>(p.out_f32 + (size_t)row * p.ld_out + col - p.f32_col0) =
+                  make_float4(y[0], y[1], y[2], y[3]);
             if (p.out_split)
               store_split4(p.out_split + (size_t)row * (p.out_parts * p.out_kp), p.out_kp, col, y, p.out_parts);
           } else {

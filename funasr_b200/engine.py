@@ -175,14 +175,14 @@ class EncoderPack:
         r, np_, d = x.shape[0], self.nparts, self.d
         xs = ws["xs"] if ly.din == d else ws["xs0"]
         ops.layernorm(x, ly.norm1.g, ly.norm1.b, self.eps, out_split=xs, nparts=np_)
-        qkv = ws["qkv"]
-        ops.gemm(xs, np_, ly.qkv.w, np_, r, 3 * d, ly.din, bias=ly.qkv.bias, out_f32=qkv)
-        v = qkv[:, 2 * d:]
+        qkv, v = ws["qkv"], ws["v"]  # q | k | v as a bf16 split for the attention UMMAs; v also in fp32 for the FSMN
+        ops.gemm(xs, np_, ly.qkv.w, np_, r, 3 * d, ly.din, bias=ly.qkv.bias, out_f32=v, f32_col0=2 * d, out_split=qkv,
+                 out_parts=np_)
         mem = ws["mem"]
         ops.fsmn(v, cu_rows, ly.fsmn, mem, residual=x if ly.din == d else None)  # conv(v) + v (+ x)
         ctx = ws["xs"]
-        ops.attention(qkv[:, :d], qkv[:, d: 2 * d], v, cu_rows, cu_rows, max_t, self.heads,
-                      float(d // self.heads) ** -0.5, out_split=ctx, nparts=np_)
+        ops.attention(qkv, 0, 3 * d, qkv, d, qkv, 2 * d, 3 * d, np_, cu_rows, cu_rows, max_t, self.heads,
+                      float(d // self.heads) ** -0.5, out_split=ctx)
         x1 = ws["x1"]
         ops.gemm(ctx, np_, ly.out.w, np_, r, d, d, bias=ly.out.bias, res1=mem, out_f32=x1)
         ops.layernorm(x1, ly.norm2.g, ly.norm2.b, self.eps, out_split=ws["xs"], nparts=np_)
@@ -199,7 +199,8 @@ class EncoderPack:
             "xs0": torch.empty(r, ops.split_width(self.din, np_), dtype=bf, device=dev),
             "xs": torch.empty(r, ops.split_width(d, np_), dtype=bf, device=dev),
             "h": torch.empty(r, ops.split_width(self.ff, np_), dtype=bf, device=dev),
-            "qkv": torch.empty(r, 3 * d, dtype=torch.float32, device=dev),
+            "qkv": torch.empty(r, ops.split_width(3 * d, np_), dtype=bf, device=dev),
+            "v": torch.empty(r, d, dtype=torch.float32, device=dev),
             "mem": torch.empty(r, d, dtype=torch.float32, device=dev),
             "x0": torch.empty(r, d, dtype=torch.float32, device=dev),
             "x1": torch.empty(r, d, dtype=torch.float32, device=dev),
@@ -306,14 +307,14 @@ class DecoderPack:
         bf = torch.bfloat16
         if enc_split is None:
             enc_split = ops.split_rows(enc, np_)
-        kv = torch.empty(r, self.kv.n, dtype=torch.float32, device=dev)
-        ops.gemm(enc_split, np_, self.kv.w, np_, r, self.kv.n, d, bias=self.kv.bias, out_f32=kv)
+        kv = torch.empty(r, ops.split_width(self.kv.n, np_), dtype=bf, device=dev)
+        ops.gemm(enc_split, np_, self.kv.w, np_, r, self.kv.n, d, bias=self.kv.bias, out_split=kv, out_parts=np_)
+        qs = torch.empty(l, ops.split_width(d, np_), dtype=bf, device=dev)
         xs = torch.empty(l, ops.split_width(d, np_), dtype=bf, device=dev)
         hs = torch.empty(l, ops.split_width(self.ff, np_), dtype=bf, device=dev)
         h = torch.empty(l, self.ff, dtype=torch.float32, device=dev)
         t = torch.empty(l, d, dtype=torch.float32, device=dev)
         n2 = torch.empty(l, d, dtype=torch.float32, device=dev)
-        q = torch.empty(l, d, dtype=torch.float32, device=dev)
         bufs = [torch.empty(l, d, dtype=torch.float32, device=dev) for _ in range(2)]
         x = embeds
         for li, ly in enumerate(self.layers):
@@ -330,12 +331,10 @@ class DecoderPack:
             ops.fsmn(n2, cu_tok, ly.fsmn, y, residual=x)  # x + conv(n2) + n2
             if ly.has_src:
                 ops.layernorm(y, ly.norm3.g, ly.norm3.b, eps, out_split=xs, nparts=np_)
-                ops.gemm(xs, np_, ly.q.w, np_, l, d, d, bias=ly.q.bias, out_f32=q)
+                ops.gemm(xs, np_, ly.q.w, np_, l, d, d, bias=ly.q.bias, out_split=qs, out_parts=np_)
                 j = self.src_index[li]
-                k_ = kv[:, j * 2 * d: j * 2 * d + d]
-                v_ = kv[:, j * 2 * d + d: (j + 1) * 2 * d]
-                ops.attention(q, k_, v_, cu_tok, cu_rows, max_l, self.heads, float(d // self.heads) ** -0.5,
-                              out_split=xs, nparts=np_)
+                ops.attention(qs, 0, d, kv, j * 2 * d, kv, j * 2 * d + d, self.kv.n, np_, cu_tok, cu_rows, max_l,
+                              self.heads, float(d // self.heads) ** -0.5, out_split=xs)
                 xo = bufs[0] if y is not bufs[0] else bufs[1]
                 ops.gemm(xs, np_, ly.out.w, np_, l, d, d, bias=ly.out.bias, res1=y, out_f32=xo)
                 x = xo

@@ -99,23 +99,30 @@ def fsmn(v, cu_rows, weight, out, residual=None, rows=None):
 
 
 def gemm(a_split, a_parts, w_split, w_parts, m, n, k, bias=None, relu=False, res1=None, res2=None, out_f32=None,
-         out_split=None, out_parts=1, taps=1, impl=0, a_rows=None):
-    """C[m, n] = A . W^T (+bias)(relu)(+res1)(+res2) over bf16 split operands (tcgen05)."""
+         out_split=None, out_parts=1, taps=1, impl=0, a_rows=None, f32_col0=0):
+    """C[m, n] = A . W^T (+bias)(relu)(+res1)(+res2) over bf16 split operands (tcgen05).
+    `out_f32` receives columns [f32_col0, n) only (column c at c - f32_col0)."""
     _chk(a_split, torch.bfloat16, "gemm")
     _chk(w_split, torch.bfloat16, "gemm")
     a_rows = a_split.shape[0] if a_rows is None else a_rows
     _lib.call("fb200_gemm", _p(a_split), a_rows, a_parts, _p(w_split), w_parts, m, n, k, taps, _p(bias),
               1 if relu else 0, _p(res1), 0 if res1 is None else res1.stride(0), _p(res2),
               0 if res2 is None else res2.stride(0), _p(out_f32), 0 if out_f32 is None else out_f32.stride(0),
-              _p(out_split), out_parts, impl, _stream())
+              f32_col0, _p(out_split), out_parts, impl, _stream())
 
 
-def attention(q, k, v, cu_q, cu_kv, max_q, heads, scale, out_f32=None, out_split=None, nparts=1, q_rows=None):
-    """q, k, v: fp32 2-D views (row stride allowed) with heads*128 columns."""
+def attention(q, q_col0, q_ps, k, k_col0, v, v_col0, kv_ps, nparts, cu_q, cu_kv, max_q, heads, scale, out_f32=None,
+              out_split=None, out_parts=None, impl=0, q_rows=None, kv_rows=None, head_dim=128):
+    """q / k / v: bf16 split matrices; head h of part p starts at column col0 + p * part_stride + h * head_dim."""
+    _chk(q, torch.bfloat16, "attention")
+    _chk(k, torch.bfloat16, "attention")
+    _chk(v, torch.bfloat16, "attention")
     q_rows = q.shape[0] if q_rows is None else q_rows
-    _lib.call("fb200_attention", _p(q), q.stride(0), _p(k), k.stride(0), _p(v), v.stride(0), _p(cu_q), _p(cu_kv),
-              cu_q.numel() - 1, q_rows, max_q, heads, q.shape[1] // heads, scale, _p(out_f32),
-              0 if out_f32 is None else out_f32.stride(0), _p(out_split), nparts, _stream())
+    kv_rows = k.shape[0] if kv_rows is None else kv_rows
+    _lib.call("fb200_attention", _p(q), q.stride(0), q_col0, q_ps, _p(k), k.stride(0), k_col0, _p(v), v.stride(0),
+              v_col0, kv_ps, nparts, _p(cu_q), _p(cu_kv), cu_q.numel() - 1, q_rows, kv_rows, max_q, heads, head_dim,
+              scale, _p(out_f32), 0 if out_f32 is None else out_f32.stride(0), _p(out_split),
+              nparts if out_parts is None else out_parts, impl, _stream())
 
 
 def cif_alpha(conv_relu, cu_rows, total_rows, w, b, alphas, smooth=1.0, noise=0.0):

@@ -18,7 +18,8 @@
  * "Split operand" (dense contractions): a GEMM operand X[rows, K] is stored as bf16
  * [rows, nparts * Kp], Kp = K rounded up to 64, part p in columns [p*Kp, (p+1)*Kp):
  *   nparts = 1: bf16(X)                       (throughput mode)
- *   nparts = 3: X ~= hi + mid + lo, each bf16 (fp32-parity mode; 6 cross terms on tcgen05)
+ *   nparts = 2: X ~= hi + mid, each bf16      (fp32-parity mode "bf16x3": 3 cross terms on tcgen05)
+ *   nparts = 3: X ~= hi + mid + lo            (6 cross terms; check mode)
  * Padding columns are zero.
  *
  * Each entry point names the reference code it replaces (paths relative to the reference root).
@@ -136,13 +137,14 @@ int fb200_fsmn(const float* v, int ld_v, const int32_t* cu_rows, int batch, int 
  *   terms    cross terms summed: a_parts=w_parts=1 -> 1; 3x3 parts -> 6 (hi.hi, hi.mid, mid.hi,
  *            hi.lo, lo.hi, mid.mid) accumulated small-to-large
  *   epilogue y = acc + bias[n]; if relu y = max(y,0); y += res1[m, :] + res2[m, :]
- *   outputs  out_f32 [m, ld_out] and/or out_split (bf16 split, out_parts parts, Kp = n up to 64)
+ *   outputs  out_f32 [m, ld_out] holding columns [f32_col0, n) (column c at c - f32_col0), and/or
+ *            out_split (bf16 split, out_parts parts, Kp = n up to 64)
  * impl: 0 = tcgen05 (product path), 1 = SIMT fp32 check kernel (same operands, for bring-up tests).
  */
 int fb200_gemm(const void* a, int a_rows, int a_parts, const void* w, int w_parts, int m, int n,
                int k, int taps, const float* bias, int relu, const float* res1, int ld_res1,
-               const float* res2, int ld_res2, float* out_f32, int ld_out, void* out_split,
-               int out_parts, int impl, void* stream);
+               const float* res2, int ld_res2, float* out_f32, int ld_out, int f32_col0,
+               void* out_split, int out_parts, int impl, void* stream);
 
 /* fp32 weight [n, k] -> bf16 split [n, nparts*Kp] (done once at load). */
 int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts, void* stream);
@@ -150,16 +152,22 @@ int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts
 /* ------------------------------------------------------------------ attention ---------- */
 
 /* softmax(q k^T * scale) v per utterance and head, var-len, streaming softmax (scores never
- * materialised).  Replaces MultiHeadedAttentionSANM.forward_attention
- * (funasr/models/sanm/attention.py:254-311) when cu_q == cu_kv, and
- * MultiHeadedAttentionCrossAtt (attention.py:664-717) otherwise.
- *   q f32 [q_rows, ld_q], k / v f32 [kv_rows, ld_k / ld_v], heads * head_dim columns each
- *   out: f32 [q_rows, ld_out] and/or bf16 split [q_rows, nparts*Kp]
+ * materialised) on tcgen05: S = Q K^T and O = P V as UMMAs over TMA-staged tiles, fp32
+ * accumulators in TMEM.  Replaces MultiHeadedAttentionSANM.forward_attention
+ * (funasr/models/sanm/attention.py:254-311) when cu_q == cu_kv, and MultiHeadedAttentionCrossAtt
+ * (attention.py:664-717) otherwise.
+ *   q, k, v   bf16 split matrices (as written by fb200_gemm's out_split): [q_rows, ld_q] and
+ *             [kv_rows, ld_k / ld_v]; head h of part p starts at column
+ *             {q,k,v}_col0 + p * {q,kv}_part_stride + h * head_dim.  k and v may be one matrix.
+ *   nparts    1 (bf16) or 2 (hi + mid: 3 cross terms per contraction); 3 runs the SIMT kernel
+ *   out       f32 [q_rows, ld_out] and/or bf16 split [q_rows, out_parts * Kp], Kp = heads*head_dim
+ * impl: 0 = tcgen05 (product path), 1 = SIMT fp32 check kernel over the same operands.
  */
-int fb200_attention(const float* q, int ld_q, const float* k, int ld_k, const float* v, int ld_v,
-                    const int32_t* cu_q, const int32_t* cu_kv, int batch, int q_rows, int max_q,
-                    int heads, int head_dim, float scale, float* out_f32, int ld_out,
-                    void* out_split, int nparts, void* stream);
+int fb200_attention(const void* q, int ld_q, int q_col0, int q_part_stride, const void* k, int ld_k,
+                    int k_col0, const void* v, int ld_v, int v_col0, int kv_part_stride, int nparts,
+                    const int32_t* cu_q, const int32_t* cu_kv, int batch, int q_rows, int kv_rows,
+                    int max_q, int heads, int head_dim, float scale, float* out_f32, int ld_out,
+                    void* out_split, int out_parts, int impl, void* stream);
 
 /* ------------------------------------------------------------------ CIF predictor ------ */
 
