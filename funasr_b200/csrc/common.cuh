@@ -79,14 +79,28 @@ __device__ __forceinline__ void store_split(__nv_bfloat16* row, int kp, int col,
   }
 }
 
-// Four consecutive values -> 8-byte stores into each part (col % 4 == 0).
+// Four consecutive values -> 8-byte stores into each part (col % 4 == 0); packed conversions.
 __device__ __forceinline__ void store_split4(__nv_bfloat16* row, int kp, int col, const float (&y)[4], int nparts) {
-  __nv_bfloat16 part[3][4];
-#pragma unroll
-  for (int u = 0; u < 4; ++u) split3(y[u], part[0][u], part[1][u], part[2][u]);
-  *reinterpret_cast<uint2*>(row + col) = *reinterpret_cast<uint2*>(part[0]);
-  if (nparts > 1) *reinterpret_cast<uint2*>(row + kp + col) = *reinterpret_cast<uint2*>(part[1]);
-  if (nparts > 2) *reinterpret_cast<uint2*>(row + 2 * kp + col) = *reinterpret_cast<uint2*>(part[2]);
+  const __nv_bfloat162 h01 = __floats2bfloat162_rn(y[0], y[1]), h23 = __floats2bfloat162_rn(y[2], y[3]);
+  uint2 pk;
+  pk.x = *reinterpret_cast<const uint32_t*>(&h01);
+  pk.y = *reinterpret_cast<const uint32_t*>(&h23);
+  *reinterpret_cast<uint2*>(row + col) = pk;
+  if (nparts > 1) {
+    const float r0 = y[0] - __low2float(h01), r1 = y[1] - __high2float(h01);
+    const float r2 = y[2] - __low2float(h23), r3 = y[3] - __high2float(h23);
+    const __nv_bfloat162 m01 = __floats2bfloat162_rn(r0, r1), m23 = __floats2bfloat162_rn(r2, r3);
+    pk.x = *reinterpret_cast<const uint32_t*>(&m01);
+    pk.y = *reinterpret_cast<const uint32_t*>(&m23);
+    *reinterpret_cast<uint2*>(row + kp + col) = pk;
+    if (nparts > 2) {
+      const __nv_bfloat162 l01 = __floats2bfloat162_rn(r0 - __low2float(m01), r1 - __high2float(m01));
+      const __nv_bfloat162 l23 = __floats2bfloat162_rn(r2 - __low2float(m23), r3 - __high2float(m23));
+      pk.x = *reinterpret_cast<const uint32_t*>(&l01);
+      pk.y = *reinterpret_cast<const uint32_t*>(&l23);
+      *reinterpret_cast<uint2*>(row + 2 * kp + col) = pk;
+    }
+  }
 }
 
 __host__ __device__ __forceinline__ int round_up(int x, int m) { return (x + m - 1) / m * m; }

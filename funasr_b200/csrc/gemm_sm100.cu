@@ -24,7 +24,7 @@ namespace fb200 {
 constexpr int BM = 128;
 constexpr int BK = 64;  // bf16 elements = 128 bytes = one swizzle row
 constexpr int kGemmThreads = 192;
-constexpr int kEpiPitch = 36;  // floats per staged row (32 + 4: conflict-free 128-bit accesses)
+constexpr int kEpiWarpBytes = 8192;  // per epilogue warp: fp32 box 32x32 (4 KB, SW128) + 2 bf16 part boxes 32x32 (2 KB each, SW64)
 constexpr int kMaxTerms = 6;
 
 struct GemmParams {
@@ -36,24 +36,21 @@ struct GemmParams {
   int relu;
   const float* res1;
   int ld_res1;
-  const float* res2;
-  int ld_res2;
   float* out_f32;
   int ld_out, f32_col0;  // out_f32 holds columns [f32_col0, n) only
   __nv_bfloat16* out_split;
   int out_parts, out_kp;
 };
 
-// y = acc (+bias)(relu)(+res1)(+res2) for one output element (scalar path shared with the SIMT kernel)
+// y = acc (+bias)(relu)(+res1) for one output element (scalar path shared with the SIMT kernel)
 __device__ __forceinline__ float epilogue_value(const GemmParams& p, int row, int col, float acc) {
   float y = acc;
   if (p.bias) y += __ldg(p.bias + col);
   if (p.relu) y = fmaxf(y, 0.f);
   if (p.res1) y += p.res1[(size_t)row * p.ld_res1 + col];
-  if (p.res2) y += p.res2[(size_t)row * p.ld_res2 + col];
   return y;
 }
-__device__ __forceinline__ void epilogue_store_scalar(const GemmParams& p, int row, int col, float acc) {
+__device__ __noinline__ void epilogue_store_scalar(const GemmParams& p, int row, int col, float acc) {
   if (row >= p.m) return;
   if (col < p.n) {
     const float y = epilogue_value(p, row, col, acc);
@@ -77,11 +74,12 @@ template <int NP> __host__ __device__ constexpr int term_b(int t) {
 template <int NP, int BN, int STAGES>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
+                    const __grid_constant__ CUtensorMap map_f32, const __grid_constant__ CUtensorMap map_split,
                     const GemmParams p) {
   constexpr uint32_t kAPart = BM * BK * 2;
   constexpr uint32_t kBPart = BN * BK * 2;
   constexpr uint32_t kStageBytes = NP * (kAPart + kBPart);
-  constexpr uint32_t kEpiBytes = 4 * 32 * kEpiPitch * 4;
+  constexpr uint32_t kEpiBytes = 4 * kEpiWarpBytes;
   constexpr uint32_t kTmemCols = 2 * BN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B needs 1024 B alignment
@@ -100,6 +98,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_f32) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_split) : "memory");
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -174,85 +174,127 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         umma_commit(tfull_bar(acc));
       }
     }
-  } else {  // ===== epilogue warps 2..5: TMEM lane group = warp % 4 =====
+  } else {  // ===== epilogue warps 2..5: TMEM lane group = warp % 4, lane = output row =====
+    // TMEM -> registers -> (bias, ReLU, residual, bf16 split) -> swizzled smem boxes -> TMA stores.
+    // The TMA engine does the address generation, coalescing and edge clipping; the warp only
+    // touches each value once, which keeps this issue-bound branch short.
     const int lg = warp & 3;
-    float* stage = reinterpret_cast<float*>(smem_raw + (epi_base - smem_u32(smem_raw))) + (warp - 2) * 32 * kEpiPitch;
-    const int ncols = p.out_split ? p.out_kp : p.n;
-    const bool vec_ok = (p.n & 3) == 0 && (!p.out_f32 || (p.ld_out & 3) == 0) && (!p.res1 || (p.ld_res1 & 3) == 0) &&
-                        (!p.res2 || (p.ld_res2 & 3) == 0);
-    const int rr0 = lane >> 3, cc = (lane & 7) * 4;
+    const uint32_t fbuf = epi_base + (uint32_t)(warp - 2) * kEpiWarpBytes;  // 32 rows x 128 B, SWIZZLE_128B
+    const uint32_t sbuf = fbuf + 4096u;                                     // per part: 32 rows x 64 B, SWIZZLE_64B
+    const int m = p.m, n = p.n, f32_col0 = p.f32_col0, out_parts = p.out_parts, out_kp = p.out_kp;
+    const float* __restrict__ bias = p.bias;
+    const float* __restrict__ res1 = p.res1;
+    const bool has_f32 = p.out_f32 != nullptr, has_split = p.out_split != nullptr;
+    const float lo = p.relu ? 0.f : -INFINITY;
+    const int ncols = has_split ? out_kp : n;
+    const uint32_t sw128 = (uint32_t)(lane & 7), sw64 = (uint32_t)((lane >> 1) & 3);
     int tl = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tl) {
       const int acc = tl & 1;
       const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
       mbar_wait(tfull_bar(acc), ((uint32_t)tl >> 1) & 1u);
       tcgen05_fence_after();
-      const int row_base = m0 + lg * 32;
+      const int row = m0 + lg * 32 + lane;
+      const bool row_ok = row < m;
 #pragma unroll 1
       for (int c = 0; c < BN; c += 32) {
-        const int col = n0 + c + cc;
-        const bool live = n0 + c < ncols;  // warp-uniform
-        // residual prefetch for this chunk (coalesced: 8 lanes cover 128 B of one row)
-        float4 rv[8];
-        const bool vec = vec_ok && col + 3 < p.n;
-        if (live && p.res1 && vec) {
+        const int col0 = n0 + c;
+        const bool live = col0 < ncols;    // warp-uniform
+        const bool full = col0 + 32 <= n;  // warp-uniform: no column guard needed
+        float y[32];
+        {
+          uint32_t r[32];
+          tmem_ld32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * BN + c), r);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int row = row_base + i * 4 + rr0;
-            rv[i] = row < p.m ? *reinterpret_cast<const float4*>(p.res1 + (size_t)row * p.ld_res1 + col)
-                              : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
+          for (int j = 0; j < 32; ++j) y[j] = __uint_as_float(r[j]);
         }
-        uint32_t r[32];
-        tmem_ld32(tmem_base + ((uint32_t)(lg * 32) << 16) + (uint32_t)(acc * BN + c), r);
         if (c + 32 >= BN) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
           tcgen05_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty_bar(acc));
         }
         if (!live) continue;
+        if (bias != nullptr) {
+          if (full) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(stage + lane * kEpiPitch + j * 4) =
-              make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]),
-                          __uint_as_float(r[4 * j + 3]));
-        __syncwarp();
-        float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (vec && p.bias) bv = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int rr = i * 4 + rr0;
-          const int row = row_base + rr;
-          const float4 a4 = *reinterpret_cast<const float4*>(stage + rr * kEpiPitch + cc);
-          if (row >= p.m) continue;
-          if (vec) {
-            float y[4] = {a4.x + bv.x, a4.y + bv.y, a4.z + bv.z, a4.w + bv.w};
-            if (p.relu) {
-#pragma unroll
-              for (int u = 0; u < 4; ++u) y[u] = fmaxf(y[u], 0.f);
+            for (int j = 0; j < 8; ++j) {
+              const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col0) + j);
+              y[4 * j] += b4.x; y[4 * j + 1] += b4.y; y[4 * j + 2] += b4.z; y[4 * j + 3] += b4.w;
             }
-            if (p.res1) {
-              y[0] += rv[i].x; y[1] += rv[i].y; y[2] += rv[i].z; y[3] += rv[i].w;
-            }
-            if (p.res2) {
-              const float4 q = *reinterpret_cast<const float4*>(p.res2 + (size_t)row * p.ld_res2 + col);
-              y[0] += q.x; y[1] += q.y; y[2] += q.z; y[3] += q.w;
-            }
-            if (p.out_f32 && col >= p.f32_col0)
-              *reinterpret_cast<float4*>(p.out_f32 + (size_t)row * p.ld_out + col - p.f32_col0) =
-                  make_float4(y[0], y[1], y[2], y[3]);
-            if (p.out_split)
-              store_split4(p.out_split + (size_t)row * (p.out_parts * p.out_kp), p.out_kp, col, y, p.out_parts);
           } else {
-            epilogue_store_scalar(p, row, col + 0, a4.x);
-            epilogue_store_scalar(p, row, col + 1, a4.y);
-            epilogue_store_scalar(p, row, col + 2, a4.z);
-            epilogue_store_scalar(p, row, col + 3, a4.w);
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < n) y[j] += __ldg(bias + col0 + j);
           }
         }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], lo);
+        if (res1 != nullptr && row_ok) {
+          const float* rp = res1 + (size_t)row * p.ld_res1 + col0;
+          if (full && (p.ld_res1 & 3) == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const float4 q = *(reinterpret_cast<const float4*>(rp) + j);
+              y[4 * j] += q.x; y[4 * j + 1] += q.y; y[4 * j + 2] += q.z; y[4 * j + 3] += q.w;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < n) y[j] += rp[j];
+          }
+        }
+        if (!full) {  // columns >= n: zero (they are the K padding of a split output; fp32 ones are clipped)
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (col0 + j >= n) y[j] = 0.f;
+        }
+        // the boxes of the previous chunk must have been read by the TMA engine before they are overwritten
+        if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
+        const bool do_f32 = has_f32 && col0 >= f32_col0;
+        if (do_f32) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(fbuf + (uint32_t)lane * 128u + ((uint32_t)j ^ sw128) * 16u),
+                         "f"(y[4 * j]), "f"(y[4 * j + 1]), "f"(y[4 * j + 2]), "f"(y[4 * j + 3])
+                         : "memory");
+        }
+        if (has_split) {
+#pragma unroll
+          for (int pp = 0; pp < 2; ++pp) {
+            if (pp < out_parts) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint32_t w[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  const int j = q * 8 + u * 2;
+                  const __nv_bfloat162 h = __floats2bfloat162_rn(y[j], y[j + 1]);
+                  w[u] = *reinterpret_cast<const uint32_t*>(&h);
+                  y[j] -= __low2float(h);  // residual feeds the next part
+                  y[j + 1] -= __high2float(h);
+                }
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(sbuf + (uint32_t)pp * 2048u + (uint32_t)lane * 64u + ((uint32_t)q ^ sw64) * 16u),
+                             "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3])
+                             : "memory");
+              }
+            }
+          }
+        }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          const int r0 = m0 + lg * 32;
+          if (do_f32) tma_store_2d(&map_f32, fbuf, col0 - f32_col0, r0);
+          if (has_split) {
+            tma_store_2d(&map_split, sbuf, col0, r0);
+            if (out_parts > 1) tma_store_2d(&map_split, sbuf + 2048u, out_kp + col0, r0);
+          }
+          asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
       }
     }
+    if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tcgen05_fence_before();
   __syncthreads();

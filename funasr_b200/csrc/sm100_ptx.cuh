@@ -32,13 +32,13 @@ __device__ __forceinline__ uint32_t mbar_try_wait(uint32_t bar, uint32_t parity)
   return ok;
 }
 // Bounded wait: a pipeline bug must trap (reported as a CUDA error), never hang the GPU box.
+// try_wait suspends in hardware for a while per call; the bound is a spin count, not a clock read.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
+  uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 4000000000ll) {
-      printf("fb200: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x,
-             bar, parity);
+    if (++spins == (1u << 26)) {
+      printf("fb200: mbarrier wait timed out (block %d thread %d bar %u parity %u)\n", blockIdx.x, threadIdx.x, bar,
+             parity);
       __trap();
     }
   }
@@ -109,9 +109,20 @@ __device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t smem_addr, uint3
 // kind::f16 instruction descriptor with the B operand MN-major (A stays K-major).
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_bmn(int m, int n) { return umma_idesc_bf16(m, n) | (1u << 16); }
 
-// 2-D bf16 row-major [rows, cols] tensor, box = [box_rows, 64 cols], 128-byte swizzle, zero OOB fill
-// (defined in gemm_sm100.cu).
-int make_tma_map_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows);
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(map), "r"(src),
+               "r"(c0), "r"(c1)
+               : "memory");
+}
+
+// 2-D row-major tensor map (defined in gemm_sm100.cu): `cols` valid columns of `elem_bytes`-wide
+// elements, row pitch `ld` elements, box = [box_rows, box_cols]; swizzle_bytes 128 or 64.
+int make_tma_map(CUtensorMap* map, const void* base, int elem_bytes, uint64_t rows, uint64_t cols, uint64_t ld,
+                 uint32_t box_cols, uint32_t box_rows, int swizzle_bytes);
+// bf16 [rows, cols] operand tile map: box = [box_rows, 64 cols], 128-byte swizzle, zero OOB fill.
+inline int make_tma_map_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  return make_tma_map(map, base, 2, rows, cols, cols, 64, box_rows, 128);
+}
 int sm_count();
 
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }

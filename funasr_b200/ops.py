@@ -98,17 +98,16 @@ def fsmn(v, cu_rows, weight, out, residual=None, rows=None):
     return out
 
 
-def gemm(a_split, a_parts, w_split, w_parts, m, n, k, bias=None, relu=False, res1=None, res2=None, out_f32=None,
+def gemm(a_split, a_parts, w_split, w_parts, m, n, k, bias=None, relu=False, res1=None, out_f32=None,
          out_split=None, out_parts=1, taps=1, impl=0, a_rows=None, f32_col0=0):
-    """C[m, n] = A . W^T (+bias)(relu)(+res1)(+res2) over bf16 split operands (tcgen05).
+    """C[m, n] = A . W^T (+bias)(relu)(+res1) over bf16 split operands (tcgen05).
     `out_f32` receives columns [f32_col0, n) only (column c at c - f32_col0)."""
     _chk(a_split, torch.bfloat16, "gemm")
     _chk(w_split, torch.bfloat16, "gemm")
     a_rows = a_split.shape[0] if a_rows is None else a_rows
     _lib.call("fb200_gemm", _p(a_split), a_rows, a_parts, _p(w_split), w_parts, m, n, k, taps, _p(bias),
-              1 if relu else 0, _p(res1), 0 if res1 is None else res1.stride(0), _p(res2),
-              0 if res2 is None else res2.stride(0), _p(out_f32), 0 if out_f32 is None else out_f32.stride(0),
-              f32_col0, _p(out_split), out_parts, impl, _stream())
+              1 if relu else 0, _p(res1), 0 if res1 is None else res1.stride(0), _p(out_f32),
+              0 if out_f32 is None else out_f32.stride(0), f32_col0, _p(out_split), out_parts, impl, _stream())
 
 
 def attention(q, q_col0, q_ps, k, k_col0, v, v_col0, kv_ps, nparts, cu_q, cu_kv, max_q, heads, scale, out_f32=None,

@@ -136,15 +136,15 @@ int fb200_fsmn(const float* v, int ld_v, const int32_t* cu_rows, int batch, int 
  *   taps     1 for a Linear; 3 for the CIF conv: tap j reads A row (m + j) (halo layout)
  *   terms    cross terms summed: a_parts=w_parts=1 -> 1; 3x3 parts -> 6 (hi.hi, hi.mid, mid.hi,
  *            hi.lo, lo.hi, mid.mid) accumulated small-to-large
- *   epilogue y = acc + bias[n]; if relu y = max(y,0); y += res1[m, :] + res2[m, :]
- *   outputs  out_f32 [m, ld_out] holding columns [f32_col0, n) (column c at c - f32_col0), and/or
+ *   epilogue y = acc + bias[n]; if relu y = max(y,0); y += res1[m, :]
+ *   outputs  out_f32 [m, ld_out] holding columns [f32_col0, n) (column c at c - f32_col0; f32_col0 % 32 == 0), and/or
  *            out_split (bf16 split, out_parts parts, Kp = n up to 64)
  * impl: 0 = tcgen05 (product path), 1 = SIMT fp32 check kernel (same operands, for bring-up tests).
  */
 int fb200_gemm(const void* a, int a_rows, int a_parts, const void* w, int w_parts, int m, int n,
                int k, int taps, const float* bias, int relu, const float* res1, int ld_res1,
-               const float* res2, int ld_res2, float* out_f32, int ld_out, int f32_col0,
-               void* out_split, int out_parts, int impl, void* stream);
+               float* out_f32, int ld_out, int f32_col0, void* out_split, int out_parts, int impl,
+               void* stream);
 
 /* fp32 weight [n, k] -> bf16 split [n, nparts*Kp] (done once at load). */
 int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts, void* stream);
