@@ -22,6 +22,9 @@ SIGNATURES = {
     "fb200_scale_add_pe": [_P, _I, _P, _I, _I, _I, _P, _F, _P, _I, _P],
     "fb200_layernorm": [_P, _I, _I, _I, _P, _P, _F, _P, _I, _P, _I, _I, _P, _I, _P],
     "fb200_split_rows": [_P, _I, _I, _I, _P, _I, _P],
+    "fb200_split_rows_halo": [_P, _I, _I, _I, _P, _I, _P, _I, _P],
+    "fb200_pack_rows": [_P, ctypes.c_longlong, _I, _P, _I, _I, _I, _P, _I, _P],
+    "fb200_unpack_rows": [_P, _I, _P, _I, _I, _I, _F, _P, _P],
     "fb200_fsmn": [_P, _I, _P, _I, _I, _I, _P, _I, _P, _I, _P, _I, _P],
     "fb200_gemm": [_P, _I, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
     "fb200_split_weight": [_P, _I, _I, _P, _I, _P],

@@ -85,14 +85,24 @@ layernorm_kernel(const float* __restrict__ x, int ld_x, int rows, int dim, const
 }
 
 // fp32 [rows, dim] -> bf16 split [rows, nparts*Kp]; one thread per (row, column of Kp).
+// cu_rows != NULL: halo layout (row r lands at r + 1 + seq(r); the interleaved rows are zeroed).
 __global__ void split_rows_kernel(const float* __restrict__ x, int ld_x, int rows, int dim,
-                                  __nv_bfloat16* __restrict__ out, int nparts) {
+                                  __nv_bfloat16* __restrict__ out, int nparts, const int32_t* __restrict__ cu_rows,
+                                  int batch) {
   const int kp = round_up(dim, 64);
   const size_t total = (size_t)rows * kp;
+  const size_t ld = (size_t)nparts * kp;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int r = (int)(i / kp), c = (int)(i - (size_t)r * kp);
     const float val = c < dim ? x[(size_t)r * ld_x + c] : 0.f;
-    store_split(out + (size_t)r * nparts * kp, kp, c, val, nparts);
+    size_t orow = r;
+    if (cu_rows != nullptr) {
+      const int b = find_seq(cu_rows, batch, r);
+      orow = (size_t)r + 1 + b;
+      if (r == __ldg(cu_rows + b)) store_split(out + (orow - 1) * ld, kp, c, 0.f, nparts);
+      if (r == rows - 1) store_split(out + (orow + 1) * ld, kp, c, 0.f, nparts);
+    }
+    store_split(out + orow * ld, kp, c, val, nparts);
   }
 }
 
@@ -163,9 +173,66 @@ __global__ void fsmn_kernel(const float* __restrict__ v, int ld_v, const int32_t
   }
 }
 
+// padded [batch, max_len, dim] <-> packed [sum len, dim]; one CTA per row, float4 per thread.
+__global__ void pack_rows_kernel(const float* __restrict__ padded, long long batch_stride, int row_stride,
+                                 const int32_t* __restrict__ cu_rows, int batch, int dim,
+                                 float* __restrict__ packed, int ld_packed) {
+  __shared__ int s_b;
+  const int r = blockIdx.x;
+  if (threadIdx.x == 0) s_b = find_seq(cu_rows, batch, r);
+  __syncthreads();
+  const int b = s_b, t = r - cu_rows[b];
+  const float* src = padded + (size_t)b * batch_stride + (size_t)t * row_stride;
+  for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4)
+    *reinterpret_cast<float4*>(packed + (size_t)r * ld_packed + c) = *reinterpret_cast<const float4*>(src + c);
+}
+
+__global__ void unpack_rows_kernel(const float* __restrict__ packed, int ld_packed, const int32_t* __restrict__ cu_rows,
+                                   int max_len, int dim, float pad_value, float* __restrict__ padded) {
+  const int b = blockIdx.y, t = blockIdx.x;
+  const int beg = cu_rows[b], len = cu_rows[b + 1] - beg;
+  float* dst = padded + ((size_t)b * max_len + t) * dim;
+  if (t < len) {
+    const float* src = packed + (size_t)(beg + t) * ld_packed;
+    for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4)
+      *reinterpret_cast<float4*>(dst + c) = *reinterpret_cast<const float4*>(src + c);
+  } else {
+    const float4 pv = make_float4(pad_value, pad_value, pad_value, pad_value);
+    for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) *reinterpret_cast<float4*>(dst + c) = pv;
+  }
+}
+
 }  // namespace fb200
 
 using namespace fb200;
+
+extern "C" __attribute__((visibility("default"))) int fb200_pack_rows(const float* padded, long long batch_stride,
+                                                                       int row_stride, const int32_t* cu_rows, int batch,
+                                                                       int total_rows, int dim, float* packed,
+                                                                       int ld_packed, void* stream) {
+  FB_CHECK_ARG(dim % 4 == 0 && row_stride % 4 == 0 && batch_stride % 4 == 0 && ld_packed % 4 == 0,
+               "pack_rows: dim and strides must be multiples of 4");
+  if (total_rows == 0) return FB200_OK;
+  ProfScope prof(kProfSplit, stream, 8.0 * (double)total_rows * dim);
+  pack_rows_kernel<<<total_rows, 128, 0, (cudaStream_t)stream>>>(padded, batch_stride, row_stride, cu_rows, batch, dim,
+                                                                 packed, ld_packed);
+  FB_CHECK_LAUNCH("pack_rows");
+  return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_unpack_rows(const float* packed, int ld_packed,
+                                                                         const int32_t* cu_rows, int batch, int max_len,
+                                                                         int dim, float pad_value, float* padded,
+                                                                         void* stream) {
+  FB_CHECK_ARG(dim % 4 == 0 && ld_packed % 4 == 0, "unpack_rows: dim and ld must be multiples of 4");
+  FB_CHECK_ARG(batch > 0 && batch <= 65535, "unpack_rows: batch %d out of range", batch);
+  if (max_len == 0) return FB200_OK;
+  ProfScope prof(kProfSplit, stream, 8.0 * (double)batch * max_len * dim);
+  unpack_rows_kernel<<<dim3(max_len, batch), 128, 0, (cudaStream_t)stream>>>(packed, ld_packed, cu_rows, max_len, dim,
+                                                                             pad_value, padded);
+  FB_CHECK_LAUNCH("unpack_rows");
+  return FB200_OK;
+}
 
 extern "C" __attribute__((visibility("default"))) int fb200_layernorm(const float* x, int ld_x, int rows, int dim, const float* gamma, const float* beta,
                                float eps, float* out_f32, int ld_f32, void* out_split, int nparts, int halo,
@@ -190,17 +257,31 @@ extern "C" __attribute__((visibility("default"))) int fb200_layernorm(const floa
   return FB200_OK;
 }
 
-extern "C" __attribute__((visibility("default"))) int fb200_split_rows(const float* x, int ld_x, int rows, int dim, void* out_split, int nparts,
-                                void* stream) {
+static int split_rows_impl(const float* x, int ld_x, int rows, int dim, void* out_split, int nparts,
+                           const int32_t* cu_rows, int batch, void* stream) {
   FB_CHECK_ARG(nparts >= 1 && nparts <= 3, "split_rows: nparts must be 1, 2 or 3");
   if (rows == 0) return FB200_OK;
   ProfScope prof(kProfSplit, stream, (double)rows * dim * (4.0 + 2.0 * nparts));
   const size_t total = (size_t)rows * round_up(dim, 64);
   int grid = (int)((total + 255) / 256);
   if (grid > 148 * 16) grid = 148 * 16;
-  split_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, ld_x, rows, dim, (__nv_bfloat16*)out_split, nparts);
+  split_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, ld_x, rows, dim, (__nv_bfloat16*)out_split, nparts,
+                                                            cu_rows, batch);
   FB_CHECK_LAUNCH("split_rows");
   return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_split_rows(const float* x, int ld_x, int rows, int dim,
+                                                                        void* out_split, int nparts, void* stream) {
+  return split_rows_impl(x, ld_x, rows, dim, out_split, nparts, nullptr, 0, stream);
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_split_rows_halo(const float* x, int ld_x, int rows, int dim,
+                                                                             void* out_split, int nparts,
+                                                                             const int32_t* cu_rows, int batch,
+                                                                             void* stream) {
+  FB_CHECK_ARG(cu_rows != nullptr && batch > 0, "split_rows_halo: cu_rows / batch missing");
+  return split_rows_impl(x, ld_x, rows, dim, out_split, nparts, cu_rows, batch, stream);
 }
 
 extern "C" __attribute__((visibility("default"))) int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts, void* stream) {

@@ -1,0 +1,322 @@
+"""Drop-in modules behind the reference's registry (funasr/register.py:57-65, last registration
+wins) for the batched offline Paraformer path.
+
+Each class keeps the reference class's name, constructor keywords, `forward` signature, return
+tuple and state_dict keys, so `AutoModel(model="Paraformer", ...)` builds them
+by string key and `load_pretrained_model(strict=True)` loads a reference checkpoint unchanged:
+
+    WavFrontend            funasr/frontends/wav_frontend.py:78-158
+    SANMEncoder            funasr/models/sanm/encoder.py:188-430
+    CifPredictorV2         funasr/models/paraformer/cif_predictor.py:172-253
+    ParaformerSANMDecoder  funasr/models/paraformer/decoder.py:224-411
+
+The modules exchange the reference's PADDED tensors ([B, T, D] + lengths) at their boundaries;
+inside, rows are packed (fb200_pack_rows), run through the CUDA kernels with batch-1 semantics per
+utterance, and unpacked again.  There is no CPU path: a forward on CPU tensors raises.
+
+`install()` registers the classes into `funasr.register.tables` under the original keys.
+"""
+from typing import Dict, List, Optional, Tuple
+
+import torch
+from torch import nn
+
+from . import engine, ops, params, tables
+
+PRECISION = "fp32"  # module-level default; override per module with `precision=` or set_precision()
+
+
+def set_precision(name: str) -> None:
+    global PRECISION
+    if name not in engine.ParaformerEngine.PRECISIONS:
+        raise ValueError("precision must be one of %s" % sorted(engine.ParaformerEngine.PRECISIONS))
+    PRECISION = name
+
+
+def _require_cuda(t: torch.Tensor, who: str) -> None:
+    if not t.is_cuda:
+        raise RuntimeError("funasr_b200.%s: input lives on %s -- this path runs on a CUDA device only (no CPU "
+                           "fallback); build the model with device='cuda'" % (who, t.device))
+
+
+class _ParamTree(nn.Module):
+    """Holds parameters under the reference's dotted names (e.g. `encoders.3.self_attn.linear_out.weight`)
+    so state_dict()/load_state_dict() round-trip reference checkpoints.  Values start as the torch
+    default init of the reference layers' shapes."""
+
+    def _declare(self, shapes: Dict[str, Tuple[int, ...]], prefix: str) -> None:
+        for name, shape in shapes.items():
+            assert name.startswith(prefix)
+            parts = name[len(prefix):].split(".")
+            mod = self
+            for p in parts[:-1]:
+                if p not in mod._modules:
+                    mod.add_module(p, nn.Module())
+                mod = mod._modules[p]
+            t = torch.empty(*shape)
+            leaf = parts[-1]
+            is_norm = any(s.startswith("norm") or s in ("after_norm", "tp_norm") for s in parts[:-1])
+            if is_norm:
+                nn.init.ones_(t) if leaf == "weight" else nn.init.zeros_(t)
+            elif "embed" in parts and leaf == "weight":
+                nn.init.normal_(t)
+            else:
+                wshape = shapes.get(name[: -len(leaf)] + "weight", shape) if leaf == "bias" else shape
+                fan_in = 1
+                for s in wshape[1:]:
+                    fan_in *= s
+                bound = 1.0 / max(float(fan_in), 1.0) ** 0.5
+                nn.init.uniform_(t, -bound, bound)
+            mod.register_parameter(leaf, nn.Parameter(t))
+        self._pack = None
+        self._pack_key = None
+
+    def _state_key(self):
+        return tuple((p.data_ptr(), p._version, str(p.device)) for p in self.parameters())
+
+    def _packed(self, build):
+        """Cache of the kernels' weight pack (bf16 splits etc.), rebuilt when parameters change."""
+        key = (self._state_key(), PRECISION if getattr(self, "precision", None) is None else self.precision)
+        if self._pack is None or self._pack_key != key:
+            self._pack = build()
+            self._pack_key = key
+        return self._pack
+
+    @property
+    def _nparts(self) -> int:
+        prec = PRECISION if getattr(self, "precision", None) is None else self.precision
+        return engine.ParaformerEngine.PRECISIONS[prec]
+
+    def _sd(self, prefix: str) -> Dict[str, torch.Tensor]:
+        return {prefix + k: v.detach() for k, v in self.state_dict().items()}
+
+
+def _lengths_list(lengths) -> List[int]:
+    if isinstance(lengths, torch.Tensor):
+        return [int(v) for v in lengths.detach().cpu().tolist()]  # one [B] D2H, like make_pad_mask's tolist()
+    return [int(v) for v in lengths]
+
+
+class WavFrontend(nn.Module):
+    """funasr/frontends/wav_frontend.py:78-158, on the GPU for the whole batch at once.
+
+    `forward(input [B, Nmax], input_lengths) -> (feats [B, Tmax, n_mels*lfr_m] f32 on the CUDA
+    device, feats_lens [B] int64 on the host)`.  `input` may be a host tensor (it is copied to the
+    device here: the path's one H2D) or already on the device.  dither != 0 adds N(0, dither^2)
+    noise per sample (Kaldi draws it per frame element; parity is defined at dither = 0)."""
+
+    def __init__(self, cmvn_file: str = None, fs: int = 16000, window: str = "hamming", n_mels: int = 80,
+                 frame_length: int = 25, frame_shift: int = 10, filter_length_min: int = -1,
+                 filter_length_max: int = -1, lfr_m: int = 1, lfr_n: int = 1, dither: float = 1.0,
+                 snip_edges: bool = True, upsacle_samples: bool = True, device=None, **kwargs):
+        super().__init__()
+        if not snip_edges:
+            raise ValueError("funasr_b200.WavFrontend: snip_edges=False is not supported")
+        self.fs, self.window, self.n_mels = fs, window, n_mels
+        self.frame_length, self.frame_shift = frame_length, frame_shift
+        self.filter_length_min, self.filter_length_max = filter_length_min, filter_length_max
+        self.lfr_m, self.lfr_n = lfr_m, lfr_n
+        self.cmvn_file, self.dither, self.snip_edges, self.upsacle_samples = cmvn_file, dither, snip_edges, upsacle_samples
+        self.cmvn = None if cmvn_file is None else tables.load_cmvn(cmvn_file)
+        self.device = device
+        self._pack = None
+
+    def output_size(self) -> int:
+        return self.n_mels * self.lfr_m
+
+    def _frontend(self, dev) -> engine.FrontendPack:
+        if self._pack is None or self._pack.device != dev:
+            self._pack = engine.FrontendPack(dev, cmvn=self.cmvn, window=self.window, n_mels=self.n_mels,
+                                             lfr_m=self.lfr_m, lfr_n=self.lfr_n, fs=self.fs,
+                                             frame_length=self.frame_length, frame_shift=self.frame_shift,
+                                             upscale=self.upsacle_samples)
+        return self._pack
+
+    def forward(self, input: torch.Tensor, input_lengths, **kwargs) -> Tuple[torch.Tensor, torch.Tensor]:
+        if not torch.cuda.is_available():
+            raise RuntimeError("funasr_b200.WavFrontend: no CUDA device (this path has no CPU fallback)")
+        dev = input.device if input.is_cuda else torch.device(self.device or ("cuda:%d" % torch.cuda.current_device()))
+        lens = _lengths_list(input_lengths)
+        fe = self._frontend(dev)
+        with torch.cuda.device(dev):
+            wave = torch.empty(sum(lens), dtype=torch.float32, device=dev)
+            o = 0
+            for b, n in enumerate(lens):
+                wave[o: o + n].copy_(input[b, :n], non_blocking=True)
+                o += n
+            if self.dither != 0.0:
+                wave.add_(torch.randn_like(wave), alpha=float(self.dither) / (fe.upscale if fe.upscale > 1 else 1.0))
+            feats, cu_rows, rows = fe.run(wave, lens)
+            out = ops.unpack_rows(feats, cu_rows, max(rows))
+        return out, torch.as_tensor(rows, dtype=torch.int64)
+
+
+class SANMEncoder(_ParamTree):
+    """funasr/models/sanm/encoder.py:188-430 (`input_layer="pe"`, SAN-M self-attention, pre-norm)."""
+
+    def __init__(self, input_size: int, output_size: int = 256, attention_heads: int = 4, linear_units: int = 2048,
+                 num_blocks: int = 6, dropout_rate: float = 0.1, positional_dropout_rate: float = 0.1,
+                 attention_dropout_rate: float = 0.0, input_layer: Optional[str] = "conv2d", pos_enc_class=None,
+                 normalize_before: bool = True, concat_after: bool = False, positionwise_layer_type: str = "linear",
+                 positionwise_conv_kernel_size: int = 1, padding_idx: int = -1, interctc_layer_idx: List[int] = [],
+                 interctc_use_conditioning: bool = False, kernel_size: int = 11, sanm_shfit: int = 0,
+                 lora_list: List[str] = None, lora_rank: int = 8, lora_alpha: int = 16, lora_dropout: float = 0.1,
+                 selfattention_layer_type: str = "sanm", tf2torch_tensor_name_prefix_torch: str = "encoder",
+                 tf2torch_tensor_name_prefix_tf: str = "seq2seq/encoder", precision: Optional[str] = None, **kwargs):
+        super().__init__()
+        unsupported = []
+        if input_layer != "pe":
+            unsupported.append("input_layer=%r (only 'pe')" % (input_layer,))
+        if selfattention_layer_type != "sanm" or positionwise_layer_type != "linear":
+            unsupported.append("attention/positionwise layer types other than sanm/linear")
+        if not normalize_before or concat_after or interctc_layer_idx or lora_list:
+            unsupported.append("post-norm / concat_after / interctc / lora")
+        if sanm_shfit != 0:
+            unsupported.append("sanm_shfit != 0")
+        if output_size // attention_heads != 128:
+            unsupported.append("head dim %d (128 only)" % (output_size // attention_heads))
+        if unsupported:
+            raise NotImplementedError("funasr_b200.SANMEncoder does not support: " + "; ".join(unsupported))
+        self._output_size, self.heads, self.precision = output_size, attention_heads, precision
+        self.interctc_layer_idx, self.interctc_use_conditioning, self.conditioning_layer = [], False, None
+        self._declare(params.sanm_encoder_shapes(input_size, output_size, linear_units, num_blocks, kernel_size, ""), "")
+
+    def output_size(self) -> int:
+        return self._output_size
+
+    def _enc(self, dev) -> engine.EncoderPack:
+        return self._packed(lambda: engine.EncoderPack(self._sd("encoder."), dev, heads=self.heads, eps=1e-12,
+                                                       nparts=self._nparts))
+
+    def forward(self, xs_pad: torch.Tensor, ilens: torch.Tensor, prev_states: torch.Tensor = None, ctc=None):
+        _require_cuda(xs_pad, "SANMEncoder")
+        lens = _lengths_list(ilens)
+        dev = xs_pad.device
+        with torch.cuda.device(dev):
+            cu_rows = tables.cu_from_lengths(lens, torch.int32, dev)
+            enc = self._enc(dev)
+            x = ops.pack_rows(xs_pad.float(), cu_rows, sum(lens))
+            x = enc.prologue(x, cu_rows)
+            y = enc.run(x, cu_rows, max(lens))
+            out = ops.unpack_rows(y, cu_rows, xs_pad.shape[1])
+        olens = torch.as_tensor(lens, dtype=torch.int64, device=dev)  # masks.squeeze(1).sum(1)
+        return out, olens, None
+
+
+class CifPredictorV2(_ParamTree):
+    """funasr/models/paraformer/cif_predictor.py:172-253 at inference (no target labels)."""
+
+    def __init__(self, idim, l_order, r_order, threshold=1.0, dropout=0.1, smooth_factor=1.0, noise_threshold=0,
+                 tail_threshold=0.0, tf2torch_tensor_name_prefix_torch="predictor",
+                 tf2torch_tensor_name_prefix_tf="seq2seq/cif", tail_mask=True, precision: Optional[str] = None, **kwargs):
+        super().__init__()
+        if l_order != 1 or r_order != 1:
+            raise NotImplementedError("funasr_b200.CifPredictorV2: only l_order = r_order = 1")
+        if tail_threshold <= 0.0 or not tail_mask:
+            raise NotImplementedError("funasr_b200.CifPredictorV2: tail_threshold > 0 with tail_mask is required")
+        self.threshold, self.smooth_factor, self.noise_threshold = threshold, smooth_factor, noise_threshold
+        self.tail_threshold, self.tail_mask, self.precision, self.idim = tail_threshold, tail_mask, precision, idim
+        self._declare(params.cif_predictor_shapes(idim, l_order, r_order, ""), "")
+
+    def _pred(self, dev) -> engine.PredictorPack:
+        return self._packed(lambda: engine.PredictorPack(self._sd("predictor."), dev, nparts=self._nparts,
+                                                         smooth_factor=self.smooth_factor,
+                                                         noise_threshold=self.noise_threshold,
+                                                         tail_threshold=self.tail_threshold))
+
+    def forward(self, hidden, target_label=None, mask=None, ignore_id=-1, mask_chunk_predictor=None,
+                target_label_length=None):
+        _require_cuda(hidden, "CifPredictorV2")
+        if target_label is not None or target_label_length is not None or mask_chunk_predictor is not None:
+            raise NotImplementedError("funasr_b200.CifPredictorV2: training-time arguments are not supported")
+        b, t, d = hidden.shape
+        dev = hidden.device
+        lens = [t] * b if mask is None else _lengths_list(mask.reshape(b, -1).sum(-1))
+        with torch.cuda.device(dev):
+            cu_rows = tables.cu_from_lengths(lens, torch.int32, dev)
+            pred = self._pred(dev)
+            h = ops.pack_rows(hidden.float(), cu_rows, sum(lens))
+            halo = ops.split_rows_halo(h, self._nparts, cu_rows)
+            out = pred.run(h, halo, cu_rows, b, want_fires=True)
+            tok = out["token_num"]
+            lmax = max(tok) if tok else 0
+            embeds = ops.unpack_rows(out["embeds"], out["cu_tok"], lmax) if lmax > 0 else hidden.new_zeros(b, 0, d)
+            # alphas / cif_peak in the reference's padded [B, T + 1] layout (tail frame at index len_b)
+            alphas = hidden.new_zeros(b, t + 1)
+            peaks = hidden.new_zeros(b, t + 1)
+            a, f = out["alphas"], out["fires"]
+            o = 0
+            for i, n in enumerate(lens):
+                alphas[i, :n] = a[o: o + n]
+                alphas[i, n] = self.tail_threshold
+                peaks[i, : n + 1] = f[o + i: o + i + n + 1]
+                o += n
+        token_num = torch.as_tensor(tok, dtype=torch.float32, device=dev)
+        return embeds, token_num, alphas, peaks
+
+
+class ParaformerSANMDecoder(_ParamTree):
+    """funasr/models/paraformer/decoder.py:224-411: `forward(hs_pad, hlens, ys_in_pad, ys_in_lens)`
+    -> (logits [B, Lmax, V], olens)."""
+
+    def __init__(self, vocab_size: int, encoder_output_size: int, attention_heads: int = 4, linear_units: int = 2048,
+                 num_blocks: int = 6, dropout_rate: float = 0.1, positional_dropout_rate: float = 0.1,
+                 self_attention_dropout_rate: float = 0.0, src_attention_dropout_rate: float = 0.0,
+                 input_layer: str = "embed", use_output_layer: bool = True, wo_input_layer: bool = False,
+                 pos_enc_class=None, normalize_before: bool = True, concat_after: bool = False, att_layer_num: int = 6,
+                 kernel_size: int = 21, sanm_shfit: int = 0, lora_list: List[str] = None, lora_rank: int = 8,
+                 lora_alpha: int = 16, lora_dropout: float = 0.1, chunk_multiply_factor: tuple = (1,),
+                 tf2torch_tensor_name_prefix_torch: str = "decoder",
+                 tf2torch_tensor_name_prefix_tf: str = "seq2seq/decoder", precision: Optional[str] = None, **kwargs):
+        super().__init__()
+        if not normalize_before or concat_after or lora_list or not use_output_layer:
+            raise NotImplementedError("funasr_b200.ParaformerSANMDecoder: post-norm / concat_after / lora / no output layer")
+        if sanm_shfit not in (0, None):
+            raise NotImplementedError("funasr_b200.ParaformerSANMDecoder: sanm_shfit=%r (centred FSMN only)" % (sanm_shfit,))
+        if encoder_output_size // attention_heads != 128:
+            raise NotImplementedError("funasr_b200.ParaformerSANMDecoder: head dim 128 only")
+        self.heads, self.precision, self.vocab_size = attention_heads, precision, vocab_size
+        self._declare(params.paraformer_decoder_shapes(vocab_size, encoder_output_size, linear_units, att_layer_num,
+                                                       num_blocks, kernel_size, ""), "")
+
+    def _dec(self, dev) -> engine.DecoderPack:
+        return self._packed(lambda: engine.DecoderPack(self._sd("decoder."), dev, heads=self.heads, eps=1e-12,
+                                                       nparts=self._nparts))
+
+    def forward(self, hs_pad, hlens, ys_in_pad, ys_in_lens, chunk_mask=None, return_hidden: bool = False,
+                return_both: bool = False):
+        _require_cuda(hs_pad, "ParaformerSANMDecoder")
+        if chunk_mask is not None or return_hidden or return_both:
+            raise NotImplementedError("funasr_b200.ParaformerSANMDecoder: chunk_mask / return_hidden are not supported")
+        dev = hs_pad.device
+        rows, toks = _lengths_list(hlens), _lengths_list(ys_in_lens)
+        with torch.cuda.device(dev):
+            cu_rows = tables.cu_from_lengths(rows, torch.int32, dev)
+            cu_tok = tables.cu_from_lengths(toks, torch.int32, dev)
+            dec = self._dec(dev)
+            enc = ops.pack_rows(hs_pad.float(), cu_rows, sum(rows))
+            emb = ops.pack_rows(ys_in_pad.float(), cu_tok, sum(toks))
+            _, _, logits = dec.run(enc, cu_rows, emb, cu_tok, max(toks) if toks else 0, want_logits=True)
+            out = ops.unpack_rows(logits, cu_tok, ys_in_pad.shape[1])
+        return out, torch.as_tensor(toks, dtype=torch.int64, device=dev)
+
+
+DROPIN_CLASSES = {
+    ("frontend_classes", "WavFrontend"): WavFrontend,
+    ("frontend_classes", "wav_frontend"): WavFrontend,
+    ("encoder_classes", "SANMEncoder"): SANMEncoder,
+    ("predictor_classes", "CifPredictorV2"): CifPredictorV2,
+    ("decoder_classes", "ParaformerSANMDecoder"): ParaformerSANMDecoder,
+}
+
+
+def install(tables_obj=None) -> List[str]:
+    """Re-register the drop-in classes under the reference's keys (`import funasr` must have run, so
+    the reference's own registrations are already in place and ours come last)."""
+    if tables_obj is None:
+        from funasr.register import tables as tables_obj  # noqa: WPS433 (the host application's registry)
+    done = []
+    for (table, key), cls in DROPIN_CLASSES.items():
+        getattr(tables_obj, table)[key] = cls
+        done.append("%s[%s]" % (table, key))
+    return done

@@ -89,6 +89,40 @@ def split_rows(x, nparts, out=None):
     return out
 
 
+def pack_rows(padded, cu_rows, total_rows, out=None):
+    """padded fp32 [B, Tmax, D] (any batch/row strides, unit column stride) -> packed [sum T, D]."""
+    _chk(padded, torch.float32, "pack_rows")
+    if padded.stride(2) != 1:
+        padded = padded.contiguous()
+    dim = padded.shape[2]
+    if out is None:
+        out = torch.empty(total_rows, dim, dtype=torch.float32, device=padded.device)
+    _lib.call("fb200_pack_rows", _p(padded), padded.stride(0), padded.stride(1), _p(cu_rows), cu_rows.numel() - 1,
+              total_rows, dim, _p(out), out.stride(0), _stream())
+    return out
+
+
+def unpack_rows(packed, cu_rows, max_len, pad_value=0.0, dim=None):
+    """packed fp32 [sum T, >= D] -> dense padded [B, max_len, D]."""
+    _chk(packed, torch.float32, "unpack_rows")
+    dim = packed.shape[1] if dim is None else dim
+    batch = cu_rows.numel() - 1
+    out = torch.empty(batch, max_len, dim, dtype=torch.float32, device=packed.device)
+    _lib.call("fb200_unpack_rows", _p(packed), packed.stride(0), _p(cu_rows), batch, max_len, dim, pad_value, _p(out),
+              _stream())
+    return out
+
+
+def split_rows_halo(x, nparts, cu_rows):
+    """fp32 [R, D] -> bf16 split in the CIF conv's halo layout [R + B + 1, nparts * Kp]."""
+    _chk(x, torch.float32, "split_rows_halo")
+    rows, dim = x.shape
+    batch = cu_rows.numel() - 1
+    out = torch.empty(rows + batch + 1, split_width(dim, nparts), dtype=torch.bfloat16, device=x.device)
+    _lib.call("fb200_split_rows_halo", _p(x), x.stride(0), rows, dim, _p(out), nparts, _p(cu_rows), batch, _stream())
+    return out
+
+
 def fsmn(v, cu_rows, weight, out, residual=None, rows=None):
     """v fp32 [rows, dim] view (row stride allowed); weight fp32 [dim, k]; out fp32 [rows, dim]."""
     rows = v.shape[0] if rows is None else rows

@@ -112,6 +112,19 @@ int fb200_layernorm(const float* x, int ld_x, int rows, int dim, const float* ga
 /* fp32 [rows, dim] -> bf16 split operand (no normalisation). */
 int fb200_split_rows(const float* x, int ld_x, int rows, int dim, void* out_split, int nparts,
                      void* stream);
+/* Same, into the halo layout of fb200_layernorm (rows + batch + 1 output rows, interleaved zero
+ * rows written by the kernel): the input of the CIF conv for callers that hold encoder output. */
+int fb200_split_rows_halo(const float* x, int ld_x, int rows, int dim, void* out_split, int nparts,
+                          const int32_t* cu_rows, int batch, void* stream);
+
+/* Layout adapters for callers that hold the reference's padded tensors (pad_sequence layout,
+ * funasr/frontends/wav_frontend.py:157): padded f32 [batch, max_len, dim] <-> packed [sum len, dim].
+ * pack: row t of utterance b is read at padded + b*batch_stride + t*row_stride (elements).
+ * unpack: writes a dense [batch, max_len, dim]; rows t >= len_b are filled with pad_value. */
+int fb200_pack_rows(const float* padded, long long batch_stride, int row_stride, const int32_t* cu_rows,
+                    int batch, int total_rows, int dim, float* packed, int ld_packed, void* stream);
+int fb200_unpack_rows(const float* packed, int ld_packed, const int32_t* cu_rows, int batch, int max_len,
+                      int dim, float pad_value, float* padded, void* stream);
 
 /* FSMN memory block: depthwise conv1d over time, kernel `ksize`, zero halo PER SEQUENCE, plus
  * identity: out = conv(v) + v (+ residual).  Replaces MultiHeadedAttentionSANM.forward_fsmn

@@ -1,0 +1,141 @@
+"""Drop-in boundary: the classes registered under the reference's keys keep its constructor
+keywords, state_dict keys and forward contracts.  CPU part: registry + checkpoint compatibility
+(against the UNMODIFIED reference when /root/reference is present).  GPU part: the reference's call
+sequence of Paraformer.inference (funasr/models/paraformer/model.py:486-546) driven through the
+drop-in modules with PADDED batches, compared with the oracle's batch-1 results."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from funasr_b200 import dropin, params, synth
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(HERE, "golden"))
+from ref_loader import reference_available  # noqa: E402
+
+ENC = dict(output_size=512, attention_heads=4, linear_units=2048, num_blocks=50, dropout_rate=0.1,
+           positional_dropout_rate=0.1, attention_dropout_rate=0.1, input_layer="pe", pos_enc_class="SinusoidalPositionEncoder",
+           normalize_before=True, kernel_size=11, sanm_shfit=0, selfattention_layer_type="sanm")
+DEC = dict(attention_heads=4, linear_units=2048, num_blocks=16, dropout_rate=0.1, positional_dropout_rate=0.1,
+           self_attention_dropout_rate=0.1, src_attention_dropout_rate=0.1, att_layer_num=16, kernel_size=11, sanm_shfit=0)
+PRED = dict(idim=512, threshold=1.0, l_order=1, r_order=1, tail_threshold=0.45)
+
+
+def test_state_dict_keys_are_the_reference_inventory():
+    enc = dropin.SANMEncoder(560, **ENC)
+    dec = dropin.ParaformerSANMDecoder(8404, 512, **DEC)
+    pred = dropin.CifPredictorV2(**PRED)
+    got = {"encoder." + k: tuple(v.shape) for k, v in enc.state_dict().items()}
+    got.update({"decoder." + k: tuple(v.shape) for k, v in dec.state_dict().items()})
+    got.update({"predictor." + k: tuple(v.shape) for k, v in pred.state_dict().items()})
+    assert got == dict(params.paraformer_large_shapes())
+    assert enc.output_size() == 512
+
+
+def test_unsupported_configurations_raise():
+    with pytest.raises(NotImplementedError):
+        dropin.SANMEncoder(560, **dict(ENC, input_layer="conv2d"))
+    with pytest.raises(NotImplementedError):
+        dropin.CifPredictorV2(512, 2, 1, tail_threshold=0.45)
+    with pytest.raises(NotImplementedError):
+        dropin.ParaformerSANMDecoder(8404, 512, **dict(DEC, sanm_shfit=5))
+
+
+def test_forward_on_cpu_fails_loudly():
+    enc = dropin.SANMEncoder(560, **dict(ENC, num_blocks=2))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        enc(torch.zeros(1, 8, 560), torch.tensor([8]))
+
+
+@pytest.mark.skipif(not reference_available(), reason="reference tree not present (GPU box)")
+def test_registers_into_reference_tables_and_loads_reference_checkpoint(tmp_path):
+    import yaml
+    from ref_loader import REFERENCE_ROOT, import_reference
+
+    import_reference()
+    from funasr import AutoModel
+    from funasr.register import tables
+
+    cfg = yaml.safe_load(open(os.path.join(REFERENCE_ROOT, "funasr/models/paraformer/template.yaml")))
+    cfg["tokenizer_conf"]["token_list"] = synth.synth_token_list(8404)
+    cfg["frontend_conf"]["dither"] = 0.0
+    cfg["specaug"] = None
+    for k in ("encoder_conf", "decoder_conf"):
+        cfg[k]["num_blocks"] = 2  # keep the CPU test small; shapes per layer are the full ones
+    cfg["decoder_conf"]["att_layer_num"] = 2
+    ref = AutoModel(**cfg, device="cpu", disable_update=True, disable_pbar=True)
+    ref_sd = ref.model.state_dict()
+    saved = {k: dict(getattr(tables, k)) for k in ("frontend_classes", "encoder_classes", "predictor_classes", "decoder_classes")}
+    try:
+        done = dropin.install()
+        assert "encoder_classes[SANMEncoder]" in done
+        ours = AutoModel(**cfg, device="cpu", disable_update=True, disable_pbar=True)
+        assert type(ours.model.encoder) is dropin.SANMEncoder
+        assert type(ours.model.decoder) is dropin.ParaformerSANMDecoder
+        assert type(ours.model.predictor) is dropin.CifPredictorV2
+        assert type(ours.kwargs["frontend"]) is dropin.WavFrontend
+        assert ours.kwargs["frontend"].output_size() == 560
+        mine = ours.model.state_dict()
+        assert set(mine.keys()) == set(ref_sd.keys())
+        assert all(mine[k].shape == ref_sd[k].shape for k in ref_sd)
+        ours.model.load_state_dict(ref_sd, strict=True)  # a reference checkpoint loads unchanged
+        with pytest.raises(RuntimeError, match="no CUDA device|no CPU fallback"):
+            ours.generate(input=synth.synth_waveform(0, 16000))
+    finally:
+        for k, v in saved.items():
+            getattr(tables, k).clear()
+            getattr(tables, k).update(v)
+
+
+# ---------------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+def test_reference_call_sequence_through_dropin_modules_matches_oracle(paraformer_sd, cmvn, tmp_path):
+    from oracle import paraformer_oracle as O
+
+    dev = torch.device("cuda:0")
+    shift, scale = synth.synth_cmvn()
+    cmvn_file = str(tmp_path / "am.mvn")
+    synth.write_cmvn_file(cmvn_file, shift, scale)
+    frontend = dropin.WavFrontend(cmvn_file=cmvn_file, fs=16000, window="hamming", n_mels=80, frame_length=25,
+                                  frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0)
+    enc = dropin.SANMEncoder(560, **ENC).to(dev)
+    pred = dropin.CifPredictorV2(**PRED).to(dev)
+    dec = dropin.ParaformerSANMDecoder(8404, 512, **DEC).to(dev)
+    enc.load_state_dict({k[len("encoder."):]: v for k, v in paraformer_sd.items() if k.startswith("encoder.")}, strict=True)
+    pred.load_state_dict({k[len("predictor."):]: v for k, v in paraformer_sd.items() if k.startswith("predictor.")}, strict=True)
+    dec.load_state_dict({k[len("decoder."):]: v for k, v in paraformer_sd.items() if k.startswith("decoder.")}, strict=True)
+
+    lens = [32000, 51234, 16000 * 4]
+    waves = [torch.from_numpy(synth.synth_waveform(200 + i, n)) for i, n in enumerate(lens)]
+    # extract_fbank (funasr/utils/load_utils.py:207-216): pad_sequence -> frontend(data, lens)
+    data = torch.nn.utils.rnn.pad_sequence(waves, batch_first=True)
+    speech, speech_lengths = frontend(data, torch.tensor(lens, dtype=torch.int32))
+    speech_lengths = speech_lengths.to(dev)
+    # Paraformer.encode (model.py:239-266)
+    encoder_out, encoder_out_lens, _ = enc(speech, speech_lengths)
+    # calc_predictor (model.py:268-276)
+    t = encoder_out.shape[1]
+    mask = (torch.arange(t, device=dev)[None, :] < encoder_out_lens[:, None]).float()[:, None, :]
+    embeds, token_num, alphas, peaks = pred(encoder_out, None, mask, ignore_id=-1)
+    pre_token_length = token_num.round().long()
+    # cal_decoder_with_predictor (model.py:278-285)
+    logits, _ = dec(encoder_out, encoder_out_lens, embeds, pre_token_length)
+    decoder_out = torch.log_softmax(logits, dim=-1)
+    for i, w in enumerate(waves):
+        taps = {}
+        want = O.recognize(w, paraformer_sd, cmvn, taps=taps)
+        n_tok = int(pre_token_length[i])
+        assert n_tok == taps["token_num"]
+        am_scores = decoder_out[i, :n_tok]
+        yseq = am_scores.argmax(dim=-1).tolist()
+        assert [v for v in yseq if v not in (0, 1, 2)] == want
+        ti = int(encoder_out_lens[i])
+        ref_enc = taps["enc"]
+        err = float((encoder_out[i, :ti].cpu() - ref_enc).abs().max() / ref_enc.abs().max())
+        assert err < 1e-3
+        assert float(encoder_out[i, ti:].abs().max()) == 0.0 if ti < t else True
+        assert float((alphas[i, : ti + 1].cpu() - taps["alphas"]).abs().max()) < 1e-4
+        assert float((peaks[i, : ti + 1].cpu() - taps["fires"]).abs().max()) < 1e-3
