@@ -3,7 +3,7 @@
 //   persistent CTAs (one per SM), warp-specialised:
 //     warp 0      TMA producer   cp.async.bulk.tensor (128B swizzle) -> shared-memory stage ring
 //     warp 1      MMA issuer     tcgen05.mma kind::f16, one elected thread, fp32 accumulators in TMEM
-//     warps 2..5  epilogue       tcgen05.ld -> smem transpose -> coalesced bias/ReLU/residual/stores
+//     warps 2..5  epilogue       tcgen05.ld -> bias/ReLU/residual/bf16 split -> swizzled smem boxes -> TMA stores
 //   two TMEM accumulator buffers (2 x BN columns) so the epilogue of tile i overlaps the MMAs of
 //   tile i+1.
 //

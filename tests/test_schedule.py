@@ -1,0 +1,72 @@
+"""Host-side sharding/batching logic and the transcript gather (gloo, world_size 2, CPU)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from funasr_b200 import schedule, synth, tables
+
+
+def test_encoder_rows_matches_frontend_tables():
+    for n in [0, 399, 400, 559, 560, 16000, 32491, 160000, 480000]:
+        f = tables.num_frames(n)
+        assert schedule.encoder_rows(n) == tables.num_lfr_rows(f)
+
+
+def test_shards_partition_and_balance():
+    lens = synth.synth_durations(1024).tolist()
+    for world in (1, 2, 4, 8):
+        parts = schedule.shard(lens, world)
+        flat = sorted(i for p in parts for i in p)
+        assert flat == list(range(1024))
+        loads = [sum(schedule.cost(schedule.encoder_rows(lens[i])) for i in p) for p in parts]
+        assert max(loads) / (sum(loads) / world) < 1.01  # LPT: within 1 % of perfect balance
+        assert schedule.shard(lens, world) == parts  # deterministic: every rank derives the same plan
+
+
+def test_batches_respect_row_budget_and_drop_empty():
+    lens = [399, 16000, 480000, 32000, 100, 160000]
+    b = schedule.batches(lens, range(len(lens)), max_rows=600)
+    flat = [i for x in b for i in x]
+    assert sorted(flat) == [1, 2, 3, 5]
+    for x in b:
+        rows = sum(schedule.encoder_rows(lens[i]) for i in x)
+        assert rows <= 600 or len(x) == 1
+    assert flat[0] == 2  # longest first
+
+
+class _FakeEngine:
+    """Stands in for ParaformerEngine on CPU: 'token ids' are a function of the waveform only."""
+
+    def recognize(self, waves):
+        return [[int(w.shape[0]) % 97, int(abs(float(w[0])) * 1e6) % 89] for w in waves]
+
+
+def _worker(rank, world, port, lens, out_path):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    waves = [synth.synth_waveform(i, n) for i, n in enumerate(lens)]
+    got = schedule.recognize_sharded(_FakeEngine(), waves, rank, world)
+    if rank == 0:
+        torch.save(got, out_path)
+    else:
+        assert got is None
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_recognize_sharded_two_ranks_gloo(tmp_path):
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    lens = [16000, 24000, 700, 52000, 8000, 31000, 399]
+    out_path = str(tmp_path / "out.pt")
+    mp.spawn(_worker, args=(2, port, lens, out_path), nprocs=2, join=True)
+    got = torch.load(out_path)
+    waves = [synth.synth_waveform(i, n) for i, n in enumerate(lens)]
+    assert got == _FakeEngine().recognize(waves)
