@@ -5,10 +5,13 @@
 //   (funasr/models/sanm/attention.py:309) never exists.
 //     warp 4      TMA producer + tcgen05.mma issuer (one elected thread)
 //     warps 0..3  softmax: thread r owns query row r = TMEM lane r
-//   per key tile j:   S_j = Q K_j^T          tcgen05, Q and K K-major (d contiguous)      -> TMEM
-//                     P_j = exp2(S_j c - m)  registers, written as a bf16 split A operand  -> smem
-//                     O_j = P_j V_j          tcgen05, V MN-major (as it lies in memory)    -> TMEM
-//                     o   = o * corr + O_j   registers (fp32 running output, 128 per thread)
+//   per key tile j:   S_j = Q K_j^T          tcgen05, Q and K K-major (d contiguous)      -> TMEM (2 buffers)
+//                     P_j = exp2(S_j c - m)  registers, written as a bf16 split A operand  -> smem (2 buffers)
+//                     O  += P_j V_j          tcgen05, V MN-major (as it lies in memory)    -> TMEM (accumulates)
+//   S, K and P are double-buffered so the tensor pipe runs S_{j+1} / P.V_{j-1} while the softmax
+//   warps work on tile j.  O stays in TMEM for the whole row block; the running maximum `m` is only
+//   raised (and O, l rescaled through tcgen05.ld/st) when a tile's maximum exceeds it by more than
+//   2^8 -- softmax is invariant to the shift, so the result is unchanged (lazy rescale).
 //   Operands are bf16 splits (hi [+ mid]) like the GEMM's: NP = 2 issues the 3 cross terms against
 //   the same shared-memory tiles (fp32-parity mode), NP = 1 is plain bf16.
 // A SIMT fp32 kernel over the SAME split operands is kept as impl = 1 (bring-up check, and the
@@ -24,6 +27,7 @@ constexpr int TQ = 128;   // query rows per CTA
 constexpr int TK = 64;    // key/value rows per tile
 constexpr int HD = 128;   // head dim
 constexpr int kAttnThreads = 160;
+constexpr float kRescaleThreshold = 8.0f;  // log2 units
 
 struct AttnParams {
   int q_col0, q_ps, k_col0, v_col0, kv_ps;  // column offsets / part strides (elements)
@@ -53,10 +57,12 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
   constexpr uint32_t kQBytes = NP * 2 * kQBlk, kKBytes = NP * 2 * kKBlk, kPBytes = NP * TQ * 128;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t q_sm = base, k_sm = q_sm + kQBytes, v_sm = k_sm + kKBytes, p_sm = v_sm + kKBytes;
-  const uint32_t bar_base = p_sm + kPBytes;
-  const uint32_t bar_q = bar_base, bar_k = bar_base + 8, bar_v = bar_base + 16, bar_s = bar_base + 24,
-                 bar_p = bar_base + 32, bar_o = bar_base + 40, tmem_slot = bar_base + 48;
+  const uint32_t q_sm = base, k_sm = q_sm + kQBytes, v_sm = k_sm + 2 * kKBytes, p_sm = v_sm + kKBytes;
+  const uint32_t bar_base = p_sm + 2 * kPBytes;
+  const uint32_t bar_q = bar_base, bar_v = bar_base + 8, bar_o = bar_base + 16, tmem_slot = bar_base + 24;
+  auto bar_k = [&](int i) { return bar_base + 32u + 8u * i; };
+  auto bar_s = [&](int i) { return bar_base + 48u + 8u * i; };
+  auto bar_p = [&](int i) { return bar_base + 64u + 8u * i; };
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
   if (warp == 4) {
@@ -65,11 +71,13 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_k) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&map_v) : "memory");
       mbar_init(bar_q, 1);
-      mbar_init(bar_k, 1);
       mbar_init(bar_v, 1);
-      mbar_init(bar_s, 1);
-      mbar_init(bar_p, 128);
       mbar_init(bar_o, 1);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(bar_k(i), 1);
+        mbar_init(bar_s(i), 1);
+        mbar_init(bar_p(i), 128);
+      }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -81,19 +89,21 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
   tcgen05_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
-  const uint32_t tmem_s = tmem_base, tmem_o = tmem_base + 128u;
+  const uint32_t tmem_o = tmem_base + 128u;                  // O: columns [128, 256)
+  auto tmem_s = [&](int i) { return tmem_base + 64u * i; };  // S buffers: columns [0, 64) and [64, 128)
 
   if (warp == 4) {
     if (lane == 0) {
       const int hcol = head * HD;
-      auto load_k = [&](int j) {
-        mbar_expect_tx(bar_k, kKBytes);
+      auto load_k = [&](int j) {  // tile j -> K buffer j & 1
+        const int i = j & 1;
+        mbar_expect_tx(bar_k(i), kKBytes);
 #pragma unroll
         for (int pp = 0; pp < NP; ++pp)
 #pragma unroll
           for (int kb = 0; kb < 2; ++kb)
-            tma_load_2d(k_sm + (pp * 2 + kb) * kKBlk, &map_k, p.k_col0 + pp * p.kv_ps + hcol + kb * 64,
-                        kv_beg + j * TK, bar_k);
+            tma_load_2d(k_sm + i * kKBytes + (pp * 2 + kb) * kKBlk, &map_k, p.k_col0 + pp * p.kv_ps + hcol + kb * 64,
+                        kv_beg + j * TK, bar_k(i));
       };
       auto load_v = [&](int j) {
         mbar_expect_tx(bar_v, kKBytes);
@@ -106,7 +116,9 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
       };
       constexpr uint32_t idesc_s = umma_idesc_bf16(TQ, TK);
       constexpr uint32_t idesc_o = umma_idesc_bf16_bmn(TQ, HD);
-      auto issue_s = [&]() {  // S = Q K^T, all cross terms of the split
+      auto issue_s = [&](int j) {  // S_j = Q K_j^T into S buffer j & 1, all cross terms of the split
+        const int i = j & 1;
+        mbar_wait(bar_k(i), ((uint32_t)j >> 1) & 1u);
         tcgen05_fence_after();
 #pragma unroll
         for (int t = 0; t < (NP == 1 ? 1 : 3); ++t) {
@@ -115,10 +127,11 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
           for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
             for (int k4 = 0; k4 < 4; ++k4)
-              umma_bf16(tmem_s, umma_desc_sw128(q_sm + (ta * 2 + kb) * kQBlk + k4 * 32),
-                        umma_desc_sw128(k_sm + (tb * 2 + kb) * kKBlk + k4 * 32), idesc_s, (t | kb | k4) ? 1u : 0u);
+              umma_bf16(tmem_s(i), umma_desc_sw128(q_sm + (ta * 2 + kb) * kQBlk + k4 * 32),
+                        umma_desc_sw128(k_sm + i * kKBytes + (tb * 2 + kb) * kKBlk + k4 * 32), idesc_s,
+                        (t | kb | k4) ? 1u : 0u);
         }
-        umma_commit(bar_s);
+        umma_commit(bar_s(i));
       };
       mbar_expect_tx(bar_q, kQBytes);
 #pragma unroll
@@ -127,117 +140,36 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
         for (int kb = 0; kb < 2; ++kb)
           tma_load_2d(q_sm + (pp * 2 + kb) * kQBlk, &map_q, p.q_col0 + pp * p.q_ps + hcol + kb * 64, q_beg + q0, bar_q);
       load_k(0);
+      if (ntiles > 1) load_k(1);
       load_v(0);
       mbar_wait(bar_q, 0);
-      mbar_wait(bar_k, 0);
-      issue_s();
+      issue_s(0);
+      if (ntiles > 1) issue_s(1);
       for (int j = 0; j < ntiles; ++j) {
-        const uint32_t ph = (uint32_t)j & 1u;
-        mbar_wait(bar_s, ph);  // S_j done: the K tile is free
-        if (j + 1 < ntiles) load_k(j + 1);
-        mbar_wait(bar_p, ph);  // P_j in shared memory, S_j consumed
-        mbar_wait(bar_v, ph);
+        const int i = j & 1;
+        const uint32_t ph2 = ((uint32_t)j >> 1) & 1u;
+        mbar_wait(bar_s(i), ph2);  // S_j done: K buffer i is free for tile j + 2
+        if (j + 2 < ntiles) load_k(j + 2);
+        mbar_wait(bar_p(i), ph2);  // P_j in shared memory, S buffer i consumed, O rescaled if needed
+        mbar_wait(bar_v, (uint32_t)j & 1u);
         tcgen05_fence_after();
 #pragma unroll
         for (int t = 0; t < (NP == 1 ? 1 : 3); ++t) {
           const int ta = NP == 1 ? 0 : (t == 1 ? 1 : 0), tb = NP == 1 ? 0 : (t == 0 ? 1 : 0);
 #pragma unroll
           for (int k4 = 0; k4 < 4; ++k4)  // 16 key rows per MMA = two 8-row groups of the V tile
-            umma_bf16(tmem_o, umma_desc_sw128(p_sm + ta * (TQ * 128) + k4 * 32),
+            umma_bf16(tmem_o, umma_desc_sw128(p_sm + i * kPBytes + ta * (TQ * 128) + k4 * 32),
                       umma_desc_sw128_mn(v_sm + tb * 2 * kKBlk + k4 * 2048, p.v_lbo, p.v_sbo), idesc_o,
-                      (t | k4) ? 1u : 0u);
+                      (j | t | k4) ? 1u : 0u);
         }
         umma_commit(bar_o);
-        if (j + 1 < ntiles) {
-          mbar_wait(bar_k, ph ^ 1u);
-          issue_s();  // overlaps the softmax warps' accumulation of O_j
-        }
-        mbar_wait(bar_o, ph);  // O_j done: the V and P tiles are free
+        if (j + 2 < ntiles) issue_s(j + 2);  // queued behind P.V_j; overlaps the softmax of tile j + 1
+        mbar_wait(bar_o, (uint32_t)j & 1u);  // P.V_j done: the V tile and P buffer i are free
         if (j + 1 < ntiles) load_v(j + 1);
       }
     }
   } else {
-    const int r = warp * 32 + lane;  // query row within the tile = TMEM lane
-    const uint32_t lane_off = (uint32_t)(warp * 32) << 16;
-    float o[HD];
-#pragma unroll
-    for (int i = 0; i < HD; ++i) o[i] = 0.f;
-    float m_run = -INFINITY, l_run = 0.f;
-    const float c = p.scale_log2e;
-    for (int j = 0; j < ntiles; ++j) {
-      const uint32_t ph = (uint32_t)j & 1u;
-      const int valid = min(TK, kv_len - j * TK);
-      mbar_wait(bar_s, ph);
-      tcgen05_fence_after();
-      uint32_t s[32];
-      float mx = -INFINITY;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        tmem_ld32(tmem_s + lane_off + h * 32, s);
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (h * 32 + i < valid) mx = fmaxf(mx, __uint_as_float(s[i]));
-      }
-      const float m_new = fmaxf(m_run, mx * c);
-      const float corr = exp2f(m_run - m_new);  // exp2(-inf) = 0 on the first tile
-      float sum = 0.f;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        tmem_ld32(tmem_s + lane_off + h * 32, s);
-#pragma unroll
-        for (int c8 = 0; c8 < 4; ++c8) {  // 8 key columns = one 16-byte chunk of the P row per part
-          __nv_bfloat16 hi[8], mid[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int col = h * 32 + c8 * 8 + u;
-            const float pv = col < valid ? exp2f(__uint_as_float(s[c8 * 8 + u]) * c - m_new) : 0.f;
-            sum += pv;
-            hi[u] = __float2bfloat16_rn(pv);
-            mid[u] = __float2bfloat16_rn(pv - __bfloat162float(hi[u]));
-          }
-          const int chunk = h * 4 + c8;
-          const uint32_t off = (uint32_t)(r >> 3) * 1024u + (uint32_t)(r & 7) * 128u + (uint32_t)((chunk ^ (r & 7)) * 16);
-          const uint4 hv = *reinterpret_cast<uint4*>(hi);
-          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_sm + off), "r"(hv.x), "r"(hv.y), "r"(hv.z), "r"(hv.w) : "memory");
-          if (NP > 1) {
-            const uint4 mv = *reinterpret_cast<uint4*>(mid);
-            asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(p_sm + (uint32_t)(TQ * 128) + off), "r"(mv.x), "r"(mv.y), "r"(mv.z), "r"(mv.w) : "memory");
-          }
-        }
-      }
-      l_run = l_run * corr + sum;
-      m_run = m_new;
-      fence_proxy_async_smem();  // make the P stores visible to the tensor core's (async proxy) reads
-      tcgen05_fence_before();
-      mbar_arrive(bar_p);
-      mbar_wait(bar_o, ph);
-      tcgen05_fence_after();
-#pragma unroll
-      for (int cb = 0; cb < HD; cb += 32) {
-        tmem_ld32(tmem_o + lane_off + cb, s);
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[cb + i] = fmaf(o[cb + i], corr, __uint_as_float(s[i]));
-      }
-    }
-    if (q0 + r < q_len) {
-      const float inv = 1.f / l_run;
-      const size_t row = (size_t)(q_beg + q0 + r);
-      const int col0 = head * HD;
-      if (p.out_f32) {
-        float* dst = p.out_f32 + row * p.ld_out + col0;
-#pragma unroll
-        for (int i = 0; i < HD; i += 4)
-          *reinterpret_cast<float4*>(dst + i) = make_float4(o[i] * inv, o[i + 1] * inv, o[i + 2] * inv, o[i + 3] * inv);
-      }
-      if (p.out_split) {
-        __nv_bfloat16* dst = p.out_split + row * (size_t)(p.out_parts * p.out_kp);
-#pragma unroll
-        for (int i = 0; i < HD; i += 4) {
-          const float y[4] = {o[i] * inv, o[i + 1] * inv, o[i + 2] * inv, o[i + 3] * inv};
-          store_split4(dst, p.out_kp, col0 + i, y, p.out_parts);
-        }
-      }
-    }
+#include "attention_softmax.inc"
   }
   tcgen05_fence_before();
   __syncthreads();

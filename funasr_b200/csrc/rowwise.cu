@@ -106,70 +106,117 @@ __global__ void split_rows_kernel(const float* __restrict__ x, int ld_x, int row
   }
 }
 
-constexpr int kFsmnRows = 16;
+constexpr int kFsmnRows = 32;   // output rows per CTA
 constexpr int kFsmnMaxK = 32;
+constexpr int kFsmnGroup = 4;   // rows fetched per step (independent loads in flight)
 
 // out[r, c] = sum_j w[c, j] * v[r + j - left, c] (inside the sequence of r) + v[r, c] (+ res[r, c]).
-// One CTA = kFsmnRows consecutive packed rows x all channels; a thread owns 4 channels.
-// KS > 0: compile-time tap count (weights in registers); KS == 0: runtime `ksize_rt`.
+// One CTA = kFsmnRows consecutive packed rows x all channels; a thread owns 4 channels and walks
+// down the rows with the last KS inputs in registers (sliding window), so every input element is
+// read once (+ a (KS-1)-row halo per CTA) instead of KS times.
 template <int KS>
-__global__ void fsmn_kernel(const float* __restrict__ v, int ld_v, const int32_t* __restrict__ cu_rows, int batch,
-                            int total_rows, int dim, const float* __restrict__ weight, int ksize_rt,
-                            const float* __restrict__ res, int ld_res, float* __restrict__ out, int ld_out) {
-  const int ksize = KS > 0 ? KS : ksize_rt;
-  constexpr int KW = KS > 0 ? KS : 1;
+__global__ void __launch_bounds__(128)
+fsmn_window_kernel(const float* __restrict__ v, int ld_v, const int32_t* __restrict__ cu_rows, int batch,
+                   int total_rows, int dim, const float* __restrict__ weight, const float* __restrict__ res,
+                   int ld_res, float* __restrict__ out, int ld_out) {
+  constexpr int LEFT = (KS - 1) / 2, RIGHT = KS - 1 - LEFT;
   __shared__ int s_beg[kFsmnRows], s_end[kFsmnRows];
   const int r0 = blockIdx.x * kFsmnRows;
   if (threadIdx.x < kFsmnRows) {
     const int r = r0 + threadIdx.x;
+    int b0 = 0, e0 = 0;
     if (r < total_rows) {
       const int b = find_seq(cu_rows, batch, r);
-      s_beg[threadIdx.x] = cu_rows[b];
-      s_end[threadIdx.x] = cu_rows[b + 1];
+      b0 = cu_rows[b];
+      e0 = cu_rows[b + 1];
     }
+    s_beg[threadIdx.x] = b0;
+    s_end[threadIdx.x] = e0;
+  }
+  __syncthreads();
+  const int nrows = min(kFsmnRows, total_rows - r0);
+  for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) {
+    float4 w[KS];
+#pragma unroll
+    for (int j = 0; j < KS; ++j)
+      w[j] = make_float4(__ldg(weight + (size_t)(c + 0) * KS + j), __ldg(weight + (size_t)(c + 1) * KS + j),
+                         __ldg(weight + (size_t)(c + 2) * KS + j), __ldg(weight + (size_t)(c + 3) * KS + j));
+    // win[j] holds input row (r - LEFT + j) while output row r is produced
+    float4 win[KS];
+    auto load_row = [&](int rr) -> float4 {
+      return (rr >= 0 && rr < total_rows) ? *reinterpret_cast<const float4*>(v + (size_t)rr * ld_v + c)
+                                          : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+#pragma unroll
+    for (int j = 1; j < KS; ++j) win[j] = load_row(r0 - LEFT + j - 1);  // rows r0-LEFT .. r0+RIGHT-1, shifted in below
+    for (int i0 = 0; i0 < nrows; i0 += kFsmnGroup) {
+      float4 nxt[kFsmnGroup], rs[kFsmnGroup];
+#pragma unroll
+      for (int g = 0; g < kFsmnGroup; ++g) {
+        nxt[g] = load_row(r0 + i0 + g + RIGHT);
+        rs[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (res != nullptr && i0 + g < nrows) rs[g] = *reinterpret_cast<const float4*>(res + (size_t)(r0 + i0 + g) * ld_res + c);
+      }
+#pragma unroll
+      for (int g = 0; g < kFsmnGroup; ++g) {
+#pragma unroll
+        for (int j = 0; j < KS - 1; ++j) win[j] = win[j + 1];
+        win[KS - 1] = nxt[g];
+        const int i = i0 + g;
+        if (i < nrows) {
+          const int r = r0 + i;
+          const int beg = s_beg[i], end = s_end[i];
+          float4 acc = win[LEFT];  // + v (the identity branch)
+          acc.x += rs[g].x; acc.y += rs[g].y; acc.z += rs[g].z; acc.w += rs[g].w;
+          float4 conv = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int j = 0; j < KS; ++j) {
+            const int rr = r - LEFT + j;
+            if (rr >= beg && rr < end) {
+              conv.x = fmaf(w[j].x, win[j].x, conv.x);
+              conv.y = fmaf(w[j].y, win[j].y, conv.y);
+              conv.z = fmaf(w[j].z, win[j].z, conv.z);
+              conv.w = fmaf(w[j].w, win[j].w, conv.w);
+            }
+          }
+          acc.x += conv.x; acc.y += conv.y; acc.z += conv.z; acc.w += conv.w;
+          *reinterpret_cast<float4*>(out + (size_t)r * ld_out + c) = acc;
+        }
+      }
+    }
+  }
+}
+
+// Generic tap count (runtime): one thread = 4 channels of one row, taps re-read through L1.
+__global__ void fsmn_generic_kernel(const float* __restrict__ v, int ld_v, const int32_t* __restrict__ cu_rows,
+                                    int batch, int total_rows, int dim, const float* __restrict__ weight, int ksize,
+                                    const float* __restrict__ res, int ld_res, float* __restrict__ out, int ld_out) {
+  __shared__ int s_beg, s_end;
+  const int r = blockIdx.x;
+  if (threadIdx.x == 0) {
+    const int b = find_seq(cu_rows, batch, r);
+    s_beg = cu_rows[b];
+    s_end = cu_rows[b + 1];
   }
   __syncthreads();
   const int left = (ksize - 1) / 2;
   for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) {
-    float w[4][KW];
-    if (KS > 0) {
-#pragma unroll
-      for (int u = 0; u < 4; ++u)
-#pragma unroll
-        for (int j = 0; j < KW; ++j) w[u][j] = __ldg(weight + (size_t)(c + u) * ksize + j);
+    float4 acc = *reinterpret_cast<const float4*>(v + (size_t)r * ld_v + c);
+    if (res) {
+      const float4 rr = *reinterpret_cast<const float4*>(res + (size_t)r * ld_res + c);
+      acc.x += rr.x; acc.y += rr.y; acc.z += rr.z; acc.w += rr.w;
     }
-    for (int i = 0; i < kFsmnRows; ++i) {
-      const int r = r0 + i;
-      if (r >= total_rows) break;
-      const int beg = s_beg[i], end = s_end[i];
-      float4 acc = *reinterpret_cast<const float4*>(v + (size_t)r * ld_v + c);
-      if (res) {
-        const float4 rr = *reinterpret_cast<const float4*>(res + (size_t)r * ld_res + c);
-        acc.x += rr.x; acc.y += rr.y; acc.z += rr.z; acc.w += rr.w;
+    for (int j = 0; j < ksize; ++j) {
+      const int rr = r + j - left;
+      if (rr >= s_beg && rr < s_end) {
+        const float4 x = *reinterpret_cast<const float4*>(v + (size_t)rr * ld_v + c);
+        acc.x = fmaf(__ldg(weight + (size_t)(c + 0) * ksize + j), x.x, acc.x);
+        acc.y = fmaf(__ldg(weight + (size_t)(c + 1) * ksize + j), x.y, acc.y);
+        acc.z = fmaf(__ldg(weight + (size_t)(c + 2) * ksize + j), x.z, acc.z);
+        acc.w = fmaf(__ldg(weight + (size_t)(c + 3) * ksize + j), x.w, acc.w);
       }
-      float4 conv = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-      for (int j = 0; j < (KS > 0 ? KS : kFsmnMaxK); ++j) {
-        if (KS == 0 && j >= ksize) break;
-        const int rr = r + j - left;
-        if (rr >= beg && rr < end) {
-          const float4 x = *reinterpret_cast<const float4*>(v + (size_t)rr * ld_v + c);
-          float w0, w1, w2, w3;
-          if (KS > 0) {
-            w0 = w[0][j % KW]; w1 = w[1][j % KW]; w2 = w[2][j % KW]; w3 = w[3][j % KW];
-          } else {
-            w0 = __ldg(weight + (size_t)(c + 0) * ksize + j); w1 = __ldg(weight + (size_t)(c + 1) * ksize + j);
-            w2 = __ldg(weight + (size_t)(c + 2) * ksize + j); w3 = __ldg(weight + (size_t)(c + 3) * ksize + j);
-          }
-          conv.x = fmaf(w0, x.x, conv.x);
-          conv.y = fmaf(w1, x.y, conv.y);
-          conv.z = fmaf(w2, x.z, conv.z);
-          conv.w = fmaf(w3, x.w, conv.w);
-        }
-      }
-      acc.x += conv.x; acc.y += conv.y; acc.z += conv.z; acc.w += conv.w;
-      *reinterpret_cast<float4*>(out + (size_t)r * ld_out + c) = acc;
     }
+    *reinterpret_cast<float4*>(out + (size_t)r * ld_out + c) = acc;
   }
 }
 
@@ -296,13 +343,12 @@ extern "C" __attribute__((visibility("default"))) int fb200_fsmn(const float* v,
   FB_CHECK_ARG(residual == nullptr || ld_res % 4 == 0, "fsmn: ld_res must be a multiple of 4");
   if (total_rows == 0) return FB200_OK;
   ProfScope prof(kProfFsmn, stream, (double)total_rows * dim * 4.0 * (residual ? 3.0 : 2.0));
-  const int grid = (total_rows + kFsmnRows - 1) / kFsmnRows;
   if (ksize == 11)
-    fsmn_kernel<11><<<grid, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight, ksize,
-                                                            residual, ld_res, out, ld_out);
+    fsmn_window_kernel<11><<<(total_rows + kFsmnRows - 1) / kFsmnRows, 128, 0, (cudaStream_t)stream>>>(
+        v, ld_v, cu_rows, batch, total_rows, dim, weight, residual, ld_res, out, ld_out);
   else
-    fsmn_kernel<0><<<grid, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight, ksize,
-                                                           residual, ld_res, out, ld_out);
+    fsmn_generic_kernel<<<total_rows, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight,
+                                                                      ksize, residual, ld_res, out, ld_out);
   FB_CHECK_LAUNCH("fsmn");
   return FB200_OK;
 }
