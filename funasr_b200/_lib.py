@@ -28,8 +28,9 @@ SIGNATURES = {
     "fb200_fsmn": [_P, _I, _P, _I, _I, _I, _P, _I, _P, _I, _P, _I, _P],
     "fb200_gemm": [_P, _I, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
     "fb200_split_weight": [_P, _I, _I, _P, _I, _P],
-    "fb200_attention": [_P, _I, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P, _I, _P,
-                        _I, _I, _P],
+    "fb200_attention_plan": [_P, _P, _I, _P, _I, _P],
+    "fb200_attention": [_P, _I, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P, _I,
+                        _P, _I, _I, _P],
     "fb200_cif_alpha": [_P, _I, _P, _I, _I, _I, _P, _P, _F, _F, _P, _P],
     "fb200_cif_scan": [_P, _P, _I, _F, _P, _P, _P, _P, _P],
     "fb200_cif_integrate": [_P, _I, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P, _I, _P],

@@ -26,7 +26,7 @@ def _stale(target: str, deps) -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "gemm_host.inc"), os.path.join(CSRC, "attention_host.inc"), os.path.join(CSRC, "attention_softmax.inc"), os.path.join(CSRC, "sm100_ptx.cuh"), os.path.join(os.path.dirname(HERE), "include", "funasr_b200.h")]
+    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "gemm_host.inc"), os.path.join(CSRC, "attention_host.inc"), os.path.join(CSRC, "attention_softmax.inc"), os.path.join(CSRC, "attention_output.inc"), os.path.join(CSRC, "sm100_ptx.cuh"), os.path.join(os.path.dirname(HERE), "include", "funasr_b200.h")]
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     objs, jobs = [], []

@@ -182,7 +182,7 @@ class EncoderPack:
         ops.fsmn(v, cu_rows, ly.fsmn, mem, residual=x if ly.din == d else None)  # conv(v) + v (+ x)
         ctx = ws["xs"]
         ops.attention(qkv, 0, 3 * d, qkv, d, qkv, 2 * d, 3 * d, np_, cu_rows, cu_rows, max_t, self.heads,
-                      float(d // self.heads) ** -0.5, out_split=ctx)
+                      float(d // self.heads) ** -0.5, out_split=ctx, plan=ws["plan"])
         x1 = ws["x1"]
         ops.gemm(ctx, np_, ly.out.w, np_, r, d, d, bias=ly.out.bias, res1=mem, out_f32=x1)
         ops.layernorm(x1, ly.norm2.g, ly.norm2.b, self.eps, out_split=ws["xs"], nparts=np_)
@@ -212,6 +212,8 @@ class EncoderPack:
         split, R + B + 1 rows) additionally receives it in the CIF conv's halo layout."""
         r = x.shape[0]
         ws = self.workspace(r)
+        # attention work list of this batch, shared by every layer (the SIMT 3-part mode needs none)
+        ws["plan"] = ops.attention_plan(cu_rows, cu_rows, r) if self.nparts < 3 else None
         for ly in self.layers:
             x = self._layer(ly, x, cu_rows, max_t, ws)
             if taps is not None:
@@ -316,6 +318,7 @@ class DecoderPack:
         t = torch.empty(l, d, dtype=torch.float32, device=dev)
         n2 = torch.empty(l, d, dtype=torch.float32, device=dev)
         bufs = [torch.empty(l, d, dtype=torch.float32, device=dev) for _ in range(2)]
+        plan = ops.attention_plan(cu_tok, cu_rows, l) if np_ < 3 else None  # one work list for all cross-attentions
         x = embeds
         for li, ly in enumerate(self.layers):
             ops.layernorm(x, ly.norm1.g, ly.norm1.b, eps, out_split=xs, nparts=np_)
@@ -334,7 +337,7 @@ class DecoderPack:
                 ops.gemm(xs, np_, ly.q.w, np_, l, d, d, bias=ly.q.bias, out_split=qs, out_parts=np_)
                 j = self.src_index[li]
                 ops.attention(qs, 0, d, kv, j * 2 * d, kv, j * 2 * d + d, self.kv.n, np_, cu_tok, cu_rows, max_l,
-                              self.heads, float(d // self.heads) ** -0.5, out_split=xs)
+                              self.heads, float(d // self.heads) ** -0.5, out_split=xs, plan=plan)
                 xo = bufs[0] if y is not bufs[0] else bufs[1]
                 ops.gemm(xs, np_, ly.out.w, np_, l, d, d, bias=ly.out.bias, res1=y, out_f32=xo)
                 x = xo

@@ -144,17 +144,28 @@ def gemm(a_split, a_parts, w_split, w_parts, m, n, k, bias=None, relu=False, res
               0 if out_f32 is None else out_f32.stride(0), f32_col0, _p(out_split), out_parts, impl, _stream())
 
 
+def attention_plan(cu_q, cu_kv, q_rows):
+    """Work list of `attention` for one (cu_q, cu_kv) pair; reuse it for every call over the same batch."""
+    batch = cu_q.numel() - 1
+    cap = q_rows // 128 + batch
+    plan = torch.empty(4 + 4 * cap, dtype=torch.int32, device=cu_q.device)
+    _lib.call("fb200_attention_plan", _p(cu_q), _p(cu_kv), batch, _p(plan), cap, _stream())
+    return plan
+
+
 def attention(q, q_col0, q_ps, k, k_col0, v, v_col0, kv_ps, nparts, cu_q, cu_kv, max_q, heads, scale, out_f32=None,
-              out_split=None, out_parts=None, impl=0, q_rows=None, kv_rows=None, head_dim=128):
+              out_split=None, out_parts=None, impl=0, q_rows=None, kv_rows=None, head_dim=128, plan=None):
     """q / k / v: bf16 split matrices; head h of part p starts at column col0 + p * part_stride + h * head_dim."""
     _chk(q, torch.bfloat16, "attention")
     _chk(k, torch.bfloat16, "attention")
     _chk(v, torch.bfloat16, "attention")
     q_rows = q.shape[0] if q_rows is None else q_rows
     kv_rows = k.shape[0] if kv_rows is None else kv_rows
+    if plan is None and impl == 0 and nparts < 3:
+        plan = attention_plan(cu_q, cu_kv, q_rows)
     _lib.call("fb200_attention", _p(q), q.stride(0), q_col0, q_ps, _p(k), k.stride(0), k_col0, _p(v), v.stride(0),
-              v_col0, kv_ps, nparts, _p(cu_q), _p(cu_kv), cu_q.numel() - 1, q_rows, kv_rows, max_q, heads, head_dim,
-              scale, _p(out_f32), 0 if out_f32 is None else out_f32.stride(0), _p(out_split),
+              v_col0, kv_ps, nparts, _p(cu_q), _p(cu_kv), _p(plan), cu_q.numel() - 1, q_rows, kv_rows, max_q, heads,
+              head_dim, scale, _p(out_f32), 0 if out_f32 is None else out_f32.stride(0), _p(out_split),
               nparts if out_parts is None else out_parts, impl, _stream())
 
 

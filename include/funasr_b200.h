@@ -164,8 +164,16 @@ int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts
 
 /* ------------------------------------------------------------------ attention ---------- */
 
+/* Work list of fb200_attention for one (cu_q, cu_kv) pair: every 128-row query block of every
+ * utterance that has keys.  Built on the device (one small kernel), reused by every attention call
+ * over the same batch (all layers).  plan: int32 [4 + 4 * capacity]; capacity >= q_rows / 128 + batch
+ * always suffices.  plan[0] = entries written, plan[1] = entries needed. */
+int fb200_attention_plan(const int32_t* cu_q, const int32_t* cu_kv, int batch, int32_t* plan,
+                         int capacity, void* stream);
+
 /* softmax(q k^T * scale) v per utterance and head, var-len, streaming softmax (scores never
- * materialised) on tcgen05: S = Q K^T and O = P V as UMMAs over TMA-staged tiles, fp32
+ * materialised) on tcgen05: a persistent grid walks the plan's (query block, head) items;
+ * S = Q K^T and O = P V as UMMAs with Q and P in tensor memory and TMA-staged K / V tiles, fp32
  * accumulators in TMEM.  Replaces MultiHeadedAttentionSANM.forward_attention
  * (funasr/models/sanm/attention.py:254-311) when cu_q == cu_kv, and MultiHeadedAttentionCrossAtt
  * (attention.py:664-717) otherwise.
@@ -173,14 +181,16 @@ int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts
  *             [kv_rows, ld_k / ld_v]; head h of part p starts at column
  *             {q,k,v}_col0 + p * {q,kv}_part_stride + h * head_dim.  k and v may be one matrix.
  *   nparts    1 (bf16) or 2 (hi + mid: 3 cross terms per contraction); 3 runs the SIMT kernel
+ *   plan      from fb200_attention_plan(cu_q, cu_kv, ...); required by impl 0, ignored by impl 1
  *   out       f32 [q_rows, ld_out] and/or bf16 split [q_rows, out_parts * Kp], Kp = heads*head_dim
  * impl: 0 = tcgen05 (product path), 1 = SIMT fp32 check kernel over the same operands.
  */
 int fb200_attention(const void* q, int ld_q, int q_col0, int q_part_stride, const void* k, int ld_k,
                     int k_col0, const void* v, int ld_v, int v_col0, int kv_part_stride, int nparts,
-                    const int32_t* cu_q, const int32_t* cu_kv, int batch, int q_rows, int kv_rows,
-                    int max_q, int heads, int head_dim, float scale, float* out_f32, int ld_out,
-                    void* out_split, int out_parts, int impl, void* stream);
+                    const int32_t* cu_q, const int32_t* cu_kv, const int32_t* plan, int batch,
+                    int q_rows, int kv_rows, int max_q, int heads, int head_dim, float scale,
+                    float* out_f32, int ld_out, void* out_split, int out_parts, int impl,
+                    void* stream);
 
 /* ------------------------------------------------------------------ CIF predictor ------ */
 

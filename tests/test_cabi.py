@@ -43,8 +43,8 @@ def test_bad_arguments_fail_loudly_without_a_gpu(lib_path):
     with pytest.raises(RuntimeError, match="parts must be 1, 2 or 3"):
         _lib.call("fb200_gemm", None, 1, 4, None, 4, 1, 1, 1, 1, None, 0, None, 0, None, 0, 0, None, 0, 0, None)
     with pytest.raises(RuntimeError, match="head_dim"):
-        _lib.call("fb200_attention", None, 8, 0, 8, None, 8, 0, None, 8, 0, 8, 1, None, None, 1, 1, 1, 1, 4, 64, 1.0, None, 0,
-                  None, 1, 0, None)
+        _lib.call("fb200_attention", None, 8, 0, 8, None, 8, 0, None, 8, 0, 8, 1, None, None, None, 1, 1, 1, 1, 4, 64, 1.0, None,
+                  0, None, 1, 0, None)
 
 
 def test_ops_refuse_cpu_tensors(lib_path):
