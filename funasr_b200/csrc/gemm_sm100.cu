@@ -70,6 +70,13 @@ template <int NP> __host__ __device__ constexpr int term_b(int t) {
   return NP == 1 ? 0 : NP == 2 ? (t == 0 ? 1 : 0) : (t == 0 ? 1 : t == 1 ? 2 : t == 3 ? 1 : 0);
 }
 
+#ifdef FB200_TRACE
+__device__ long long g_gemm_trace[3][1024];
+#define GTRACE(w, tag) do { if (blockIdx.x == 0 && gti < 511) { g_gemm_trace[w][2 * gti] = tag; g_gemm_trace[w][2 * gti + 1] = clock64(); ++gti; } } while (0)
+#else
+#define GTRACE(w, tag) do { } while (0)
+#endif
+
 // ---------------------------------------------------------------- tcgen05 kernel --------
 template <int NP, int BN, int STAGES>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -94,6 +101,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.tiles_m * p.tiles_n;
   const int k_iters = p.taps * p.k_blocks;
+#ifdef FB200_TRACE
+  int gti = 0;
+#endif
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -133,6 +143,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             const int s = it % STAGES;
             const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
             mbar_wait(empty_bar(s), ph ^ 1u);
+            GTRACE(0, 1);
             mbar_expect_tx(full_bar(s), kStageBytes);
             const uint32_t sa = smem_base + s * kStageBytes;
 #pragma unroll
@@ -151,12 +162,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tl) {
         const int acc = tl & 1;
         mbar_wait(tempty_bar(acc), (((uint32_t)tl >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
+        GTRACE(1, 10);
         tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)(acc * BN);
         for (int j = 0; j < k_iters; ++j, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
           mbar_wait(full_bar(s), ph);
+          GTRACE(1, 11);
           tcgen05_fence_after();
           const uint32_t sa = smem_base + s * kStageBytes;
           const uint32_t sb = sa + NP * kAPart;
@@ -170,6 +183,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             }
           }
           umma_commit(empty_bar(s));  // frees the smem stage once these MMAs retire
+          GTRACE(1, 12);
         }
         umma_commit(tfull_bar(acc));
       }
@@ -188,11 +202,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     const float lo = p.relu ? 0.f : -INFINITY;
     const int ncols = has_split ? out_kp : n;
     const uint32_t sw128 = (uint32_t)(lane & 7), sw64 = (uint32_t)((lane >> 1) & 3);
+    // Residual, coalesced: the warp reads the NEXT chunk's [32 rows x 32 columns] one row per instruction
+    // (rv[i] = element (row i, column `lane`), a whole 128-byte line per load) while the current chunk is
+    // processed, then turns it through the (otherwise unused) split staging box so that each lane gets its
+    // own row.  Used when no split output is produced (the residual GEMMs write fp32 only).
+    const bool res_coal = res1 != nullptr && !has_split;
+    float rv[32];
+    auto load_res = [&](int tile, int c) {
+      const int r0 = (tile / p.tiles_n) * BM + lg * 32, col = (tile % p.tiles_n) * BN + c + lane;
+      const bool col_ok = col < n;
+      const float* rp = res1 + (size_t)r0 * p.ld_res1 + col;
+#pragma unroll
+      for (int i = 0; i < 32; ++i) rv[i] = (col_ok && r0 + i < m) ? __ldg(rp + (size_t)i * p.ld_res1) : 0.f;
+    };
     int tl = 0;
+    if (res_coal && (int)blockIdx.x < total_tiles) load_res(blockIdx.x, 0);
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tl) {
       const int acc = tl & 1;
       const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
       mbar_wait(tfull_bar(acc), ((uint32_t)tl >> 1) & 1u);
+      if (warp == 2 && lane == 0) GTRACE(2, 20);
       tcgen05_fence_after();
       const int row = m0 + lg * 32 + lane;
       const bool row_ok = row < m;
@@ -229,7 +258,31 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
 #pragma unroll
         for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], lo);
-        if (res1 != nullptr && row_ok) {
+        if (res_coal) {
+          // rv -> box (128-byte swizzle, like the fp32 output box) -> this lane's row
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(sbuf + (uint32_t)i * 128u + ((((uint32_t)lane >> 2) ^ ((uint32_t)i & 7u)) * 16u) +
+                                                         ((uint32_t)lane & 3u) * 4u),
+                         "f"(rv[i])
+                         : "memory");
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float4 q;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(q.x), "=f"(q.y), "=f"(q.z), "=f"(q.w)
+                         : "r"(sbuf + (uint32_t)lane * 128u + ((uint32_t)j ^ sw128) * 16u)
+                         : "memory");
+            y[4 * j] += q.x; y[4 * j + 1] += q.y; y[4 * j + 2] += q.z; y[4 * j + 3] += q.w;
+          }
+          __syncwarp();
+          // next chunk of this tile that is live, else the first chunk of this CTA's next tile
+          if (c + 32 < BN && col0 + 32 < ncols)
+            load_res(tile, c + 32);
+          else if (tile + (int)gridDim.x < total_tiles)
+            load_res(tile + gridDim.x, 0);
+        } else if (res1 != nullptr && row_ok) {
           const float* rp = res1 + (size_t)row * p.ld_res1 + col0;
           if (full && (p.ld_res1 & 3) == 0) {
 #pragma unroll
@@ -291,6 +344,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             if (out_parts > 1) tma_store_2d(&map_split, sbuf + 2048u, out_kp + col0, r0);
           }
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          if (warp == 2) GTRACE(2, 21);
         }
       }
     }
@@ -305,5 +359,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 }
 
 }  // namespace fb200
+
+#ifdef FB200_TRACE
+extern "C" __attribute__((visibility("default"))) int fb200_debug_gemm_trace(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, fb200::g_gemm_trace, sizeof(long long) * 3072);
+}
+#endif
 
 #include "gemm_host.inc"
