@@ -78,7 +78,11 @@ __device__ long long g_gemm_trace[3][1024];
 #endif
 
 // ---------------------------------------------------------------- tcgen05 kernel --------
-template <int NP, int BN, int STAGES>
+// CL = CTAs per cluster.  The CTAs of a cluster work on CL consecutive row blocks against the SAME weight tile:
+// each loads 1/CL of the weight rows of a k-block and multicasts them to all, so a CTA pulls
+// NP * (16 KB + 32 KB / CL) from L2 per k-block instead of NP * 48 KB -- the mainloop was bound by the
+// L2 -> SM bandwidth (~41 B/clk/SM), not by the tensor pipe.
+template <int NP, int BN, int STAGES, int CL>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     const __grid_constant__ CUtensorMap map_f32, const __grid_constant__ CUtensorMap map_split,
@@ -99,8 +103,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int total_tiles = p.tiles_m * p.tiles_n;
+  // work unit = (group of CL row blocks, column block); cluster g takes units g, g + #clusters, ...; CTA rank r
+  // of the cluster takes row block group * CL + r (past the last row block it still loads / multiplies, nothing is
+  // stored: TMA clips)
+  const int cta_rank = CL > 1 ? (int)cluster_ctarank() : 0;
+  const int unit0 = blockIdx.x / CL, unit_step = gridDim.x / CL;
+  const int total_tiles = ((p.tiles_m + CL - 1) / CL) * p.tiles_n;
   const int k_iters = p.taps * p.k_blocks;
+  constexpr uint16_t kClusterMask = (uint16_t)((1u << CL) - 1u);
 #ifdef FB200_TRACE
   int gti = 0;
 #endif
@@ -115,7 +125,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     if (lane == 0) {
       for (int s = 0; s < STAGES; ++s) {
         mbar_init(full_bar(s), 1);
-        mbar_init(empty_bar(s), 1);
+        mbar_init(empty_bar(s), CL);  // one commit per CTA of the cluster: they all read what lands in this stage
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(tfull_bar(a), 1);
@@ -128,7 +138,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (CL > 1)
+    cluster_sync_all();  // the peers' barriers are initialised before anything is multicast to them
+  else
+    __syncthreads();
   tcgen05_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
@@ -136,8 +149,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   if (warp == 0) {
     if (elect_one()) {  // ===== TMA producer =====
       int it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+      for (int tile = unit0; tile < total_tiles; tile += unit_step) {
+        const int m0 = ((tile / p.tiles_n) * CL + cta_rank) * BM, n0 = (tile % p.tiles_n) * BN;
         for (int tap = 0; tap < p.taps; ++tap)
           for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
             const int s = it % STAGES;
@@ -150,8 +163,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             for (int pa = 0; pa < NP; ++pa)
               tma_load_2d(sa + pa * kAPart, &map_a, pa * p.kp_a + kb * BK, m0 + tap, full_bar(s));
 #pragma unroll
-            for (int pb = 0; pb < NP; ++pb)
-              tma_load_2d(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK, tap * p.n + n0, full_bar(s));
+            for (int pb = 0; pb < NP; ++pb) {
+              if (CL == 1) {
+                tma_load_2d(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK, tap * p.n + n0, full_bar(s));
+              } else {  // this CTA's slice of the weight rows, delivered to every CTA of the cluster
+                constexpr int kSlice = BN / CL;
+                tma_load_2d_mc(sa + NP * kAPart + pb * kBPart + cta_rank * (kSlice * BK * 2), &map_w, pb * p.kp_w + kb * BK,
+                               tap * p.n + n0 + cta_rank * kSlice, full_bar(s), kClusterMask);
+              }
+            }
           }
       }
     }
@@ -159,7 +179,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     if (elect_one()) {  // ===== MMA issuer =====
       constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
       int it = 0, tl = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tl) {
+      for (int tile = unit0; tile < total_tiles; tile += unit_step, ++tl) {
         const int acc = tl & 1;
         mbar_wait(tempty_bar(acc), (((uint32_t)tl >> 1) & 1u) ^ 1u);  // epilogue drained this buffer
         GTRACE(1, 10);
@@ -182,7 +202,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               umma_bf16(tmem_d, da, db, idesc, (j > 0 || t > 0 || k > 0) ? 1u : 0u);
             }
           }
-          umma_commit(empty_bar(s));  // frees the smem stage once these MMAs retire
+          // frees the smem stage once these MMAs retire -- in every CTA whose loads land in it
+          if (CL == 1)
+            umma_commit(empty_bar(s));
+          else
+            umma_commit_mc(empty_bar(s), kClusterMask);
           GTRACE(1, 12);
         }
         umma_commit(tfull_bar(acc));
@@ -209,17 +233,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     const bool res_coal = res1 != nullptr && !has_split;
     float rv[32];
     auto load_res = [&](int tile, int c) {
-      const int r0 = (tile / p.tiles_n) * BM + lg * 32, col = (tile % p.tiles_n) * BN + c + lane;
+      const int r0 = ((tile / p.tiles_n) * CL + cta_rank) * BM + lg * 32, col = (tile % p.tiles_n) * BN + c + lane;
       const bool col_ok = col < n;
       const float* rp = res1 + (size_t)r0 * p.ld_res1 + col;
 #pragma unroll
       for (int i = 0; i < 32; ++i) rv[i] = (col_ok && r0 + i < m) ? __ldg(rp + (size_t)i * p.ld_res1) : 0.f;
     };
     int tl = 0;
-    if (res_coal && (int)blockIdx.x < total_tiles) load_res(blockIdx.x, 0);
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tl) {
+    if (res_coal && unit0 < total_tiles) load_res(unit0, 0);
+    for (int tile = unit0; tile < total_tiles; tile += unit_step, ++tl) {
       const int acc = tl & 1;
-      const int m0 = (tile / p.tiles_n) * BM, n0 = (tile % p.tiles_n) * BN;
+      const int m0 = ((tile / p.tiles_n) * CL + cta_rank) * BM, n0 = (tile % p.tiles_n) * BN;
       mbar_wait(tfull_bar(acc), ((uint32_t)tl >> 1) & 1u);
       if (warp == 2 && lane == 0) GTRACE(2, 20);
       tcgen05_fence_after();
@@ -280,8 +304,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           // next chunk of this tile that is live, else the first chunk of this CTA's next tile
           if (c + 32 < BN && col0 + 32 < ncols)
             load_res(tile, c + 32);
-          else if (tile + (int)gridDim.x < total_tiles)
-            load_res(tile + gridDim.x, 0);
+          else if (tile + unit_step < total_tiles)
+            load_res(tile + unit_step, 0);
         } else if (res1 != nullptr && row_ok) {
           const float* rp = res1 + (size_t)row * p.ld_res1 + col0;
           if (full && (p.ld_res1 & 3) == 0) {
@@ -351,7 +375,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   }
   tcgen05_fence_before();
-  __syncthreads();
+  if (CL > 1)
+    cluster_sync_all();  // no CTA leaves while a peer may still multicast into it or arrive on its barriers
+  else
+    __syncthreads();
   if (warp == 1) {
     __syncwarp();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));

@@ -372,6 +372,8 @@ class ParaformerEngine:
         self.precision = precision
         self.nparts = self.PRECISIONS[precision]
         self.max_rows = max_rows
+        self._copy_stream = None
+        self._drop_ids = np.array(sorted(self.DROP_IDS), dtype=np.int32)
         with torch.cuda.device(self.device):
             self.frontend = FrontendPack(self.device, cmvn=cmvn, window=window)
             self.encoder = EncoderPack(state_dict, self.device, heads=heads, nparts=self.nparts)
@@ -435,16 +437,37 @@ class ParaformerEngine:
         results: List[List[int]] = [[] for _ in waves]
         scores = [0.0 for _ in waves]
         lens_all = [int(w.shape[0]) for w in waves]
-        for batch in self.plan_batches(lens_all):
-            wave, lens = self.upload([waves[i] for i in batch])
-            ids, logp, tok = self.forward_packed(wave, lens)
-            ids_h = ids.cpu().numpy()
-            logp_h = logp.cpu().numpy() if with_scores else None
-            o = 0
-            for i, n in zip(batch, tok):
-                seq = ids_h[o: o + n]
-                results[i] = [int(t) for t in seq if t not in self.DROP_IDS]
-                if with_scores:
-                    scores[i] = float(logp_h[o: o + n].sum())
-                o += n
+        batches = self.plan_batches(lens_all)
+        if not batches:
+            return (results, scores) if with_scores else results
+        with torch.cuda.device(self.device):
+            # host -> device copies of batch k + 1 run on their own stream under the kernels of batch k
+            compute = torch.cuda.current_stream()
+            if self._copy_stream is None:
+                self._copy_stream = torch.cuda.Stream(device=self.device)
+
+            def start_upload(batch):
+                with torch.cuda.stream(self._copy_stream):
+                    wave, lens = self.upload([waves[i] for i in batch])
+                    done = torch.cuda.Event()
+                    done.record(self._copy_stream)
+                return wave, lens, done
+
+            nxt = start_upload(batches[0])
+            for bi, batch in enumerate(batches):
+                wave, lens, done = nxt
+                compute.wait_event(done)
+                wave.record_stream(compute)  # allocated under the copy stream, consumed on the compute stream
+                if bi + 1 < len(batches):
+                    nxt = start_upload(batches[bi + 1])
+                ids, logp, tok = self.forward_packed(wave, lens)
+                ids_h = ids.cpu().numpy()
+                logp_h = logp.cpu().numpy() if with_scores else None
+                keep = ~np.isin(ids_h, self._drop_ids)
+                o = 0
+                for i, n in zip(batch, tok):
+                    results[i] = ids_h[o: o + n][keep[o: o + n]].tolist()
+                    if with_scores:
+                        scores[i] = float(logp_h[o: o + n].sum())
+                    o += n
         return (results, scores) if with_scores else results
