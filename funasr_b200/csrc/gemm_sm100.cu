@@ -78,17 +78,18 @@ __device__ long long g_gemm_trace[3][1024];
 #endif
 
 // ---------------------------------------------------------------- tcgen05 kernel --------
-// CL = CTAs per cluster.  The CTAs of a cluster work on CL consecutive row blocks against the SAME weight tile:
-// each loads 1/CL of the weight rows of a k-block and multicasts them to all, so a CTA pulls
-// NP * (16 KB + 32 KB / CL) from L2 per k-block instead of NP * 48 KB -- the mainloop was bound by the
-// L2 -> SM bandwidth (~41 B/clk/SM), not by the tensor pipe.
+// CL = 2: a CTA PAIR (two SMs of one TPC, tcgen05 cta_group::2) computes a [256 x BN] tile: each CTA holds its own
+// 128 rows of A and HALF of the weight rows of a k-block, the leader (rank 0) issues one M = 256 MMA that reads
+// both halves, and each CTA's tensor memory receives its 128 accumulator rows.  A CTA then takes in
+// NP * (16 KB + BN / 2 * 128 B) per k-block instead of NP * (16 KB + BN * 128 B): the mainloop was bound by
+// the ~41 B/clk an SM can take in, not by the tensor pipe -- and the smaller stage buys a third stage.
 template <int NP, int BN, int STAGES, int CL>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     const __grid_constant__ CUtensorMap map_f32, const __grid_constant__ CUtensorMap map_split,
                     const GemmParams p) {
   constexpr uint32_t kAPart = BM * BK * 2;
-  constexpr uint32_t kBPart = BN * BK * 2;
+  constexpr uint32_t kBPart = (BN / CL) * BK * 2;  // this CTA's share of the weight rows
   constexpr uint32_t kStageBytes = NP * (kAPart + kBPart);
   constexpr uint32_t kEpiBytes = 4 * kEpiWarpBytes;
   constexpr uint32_t kTmemCols = 2 * BN;
@@ -104,13 +105,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // work unit = (group of CL row blocks, column block); cluster g takes units g, g + #clusters, ...; CTA rank r
-  // of the cluster takes row block group * CL + r (past the last row block it still loads / multiplies, nothing is
+  // of the pair owns row block group * CL + r (past the last row block it still loads / multiplies, nothing is
   // stored: TMA clips)
   const int cta_rank = CL > 1 ? (int)cluster_ctarank() : 0;
   const int unit0 = blockIdx.x / CL, unit_step = gridDim.x / CL;
   const int total_tiles = ((p.tiles_m + CL - 1) / CL) * p.tiles_n;
   const int k_iters = p.taps * p.k_blocks;
   constexpr uint16_t kClusterMask = (uint16_t)((1u << CL) - 1u);
+  const bool leader = cta_rank == 0;
 #ifdef FB200_TRACE
   int gti = 0;
 #endif
@@ -124,18 +126,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   if (warp == 1) {
     if (lane == 0) {
       for (int s = 0; s < STAGES; ++s) {
-        mbar_init(full_bar(s), 1);
-        mbar_init(empty_bar(s), CL);  // one commit per CTA of the cluster: they all read what lands in this stage
+        mbar_init(full_bar(s), 1);  // a pair uses the leader's: it counts the bytes of both CTAs' loads
+        mbar_init(empty_bar(s), 1);
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(tfull_bar(a), 1);
-        mbar_init(tempty_bar(a), 4);  // one arrival per epilogue warp
+        mbar_init(tempty_bar(a), 4 * CL);  // one arrival per epilogue warp (of both CTAs, on the leader's)
       }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(kTmemCols));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    if (CL == 1) {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(kTmemCols));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(kTmemCols));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+    }
   }
   tcgen05_fence_before();
   if (CL > 1)
@@ -157,27 +164,34 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
             mbar_wait(empty_bar(s), ph ^ 1u);
             GTRACE(0, 1);
-            mbar_expect_tx(full_bar(s), kStageBytes);
             const uint32_t sa = smem_base + s * kStageBytes;
+            if (CL == 1) {
+              mbar_expect_tx(full_bar(s), kStageBytes);
 #pragma unroll
-            for (int pa = 0; pa < NP; ++pa)
-              tma_load_2d(sa + pa * kAPart, &map_a, pa * p.kp_a + kb * BK, m0 + tap, full_bar(s));
+              for (int pa = 0; pa < NP; ++pa)
+                tma_load_2d(sa + pa * kAPart, &map_a, pa * p.kp_a + kb * BK, m0 + tap, full_bar(s));
 #pragma unroll
-            for (int pb = 0; pb < NP; ++pb) {
-              if (CL == 1) {
+              for (int pb = 0; pb < NP; ++pb)
                 tma_load_2d(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK, tap * p.n + n0, full_bar(s));
-              } else {  // this CTA's slice of the weight rows, delivered to every CTA of the cluster
-                constexpr int kSlice = BN / CL;
-                tma_load_2d_mc(sa + NP * kAPart + pb * kBPart + cta_rank * (kSlice * BK * 2), &map_w, pb * p.kp_w + kb * BK,
-                               tap * p.n + n0 + cta_rank * kSlice, full_bar(s), kClusterMask);
-              }
+            } else {  // own A rows and own half of the weight rows; the bytes are counted on the leader's barrier
+              // Only the leader arms the barrier (for both CTAs' bytes): the peer's bytes may land first, the phase
+              // still cannot complete before the leader's arrival, and the peer is spared a remote arrive per stage.
+              const uint32_t lbar = leader ? full_bar(s) : mapa_shared(full_bar(s), 0);
+              if (leader) mbar_expect_tx(full_bar(s), CL * kStageBytes);
+#pragma unroll
+              for (int pa = 0; pa < NP; ++pa)
+                tma_load_2d_pair(sa + pa * kAPart, &map_a, pa * p.kp_a + kb * BK, m0 + tap, lbar);
+#pragma unroll
+              for (int pb = 0; pb < NP; ++pb)
+                tma_load_2d_pair(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK,
+                                 tap * p.n + n0 + cta_rank * (BN / CL), lbar);
             }
           }
       }
     }
   } else if (warp == 1) {
-    if (elect_one()) {  // ===== MMA issuer =====
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+    if (leader && elect_one()) {  // ===== MMA issuer (of the pair: the leader CTA) =====
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * CL, BN);
       int it = 0, tl = 0;
       for (int tile = unit0; tile < total_tiles; tile += unit_step, ++tl) {
         const int acc = tl & 1;
@@ -199,17 +213,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             for (int k = 0; k < BK / 16; ++k) {
               const uint64_t da = umma_desc_sw128(sa + term_a<NP>(t) * kAPart + k * 32);
               const uint64_t db = umma_desc_sw128(sb + term_b<NP>(t) * kBPart + k * 32);
-              umma_bf16(tmem_d, da, db, idesc, (j > 0 || t > 0 || k > 0) ? 1u : 0u);
+              if (CL == 1)
+                umma_bf16(tmem_d, da, db, idesc, (j > 0 || t > 0 || k > 0) ? 1u : 0u);
+              else
+                umma_bf16_pair(tmem_d, da, db, idesc, (j > 0 || t > 0 || k > 0) ? 1u : 0u);
             }
           }
           // frees the smem stage once these MMAs retire -- in every CTA whose loads land in it
           if (CL == 1)
             umma_commit(empty_bar(s));
           else
-            umma_commit_mc(empty_bar(s), kClusterMask);
+            umma_commit_pair(empty_bar(s), kClusterMask);
           GTRACE(1, 12);
         }
-        umma_commit(tfull_bar(acc));
+        if (CL == 1)
+          umma_commit(tfull_bar(acc));
+        else
+          umma_commit_pair(tfull_bar(acc), kClusterMask);  // each CTA's epilogue reads its own 128 rows
       }
     }
   } else {  // ===== epilogue warps 2..5: TMEM lane group = warp % 4, lane = output row =====
@@ -264,7 +284,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         if (c + 32 >= BN) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
           tcgen05_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty_bar(acc));
+          if (lane == 0) {
+            if (CL == 1)
+              mbar_arrive(tempty_bar(acc));
+            else
+              mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));  // the leader issues the MMAs of both CTAs
+          }
         }
         if (!live) continue;
         if (bias != nullptr) {
@@ -381,7 +406,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     __syncthreads();
   if (warp == 1) {
     __syncwarp();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+    if (CL == 1)
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+    else
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
   }
 }
 
