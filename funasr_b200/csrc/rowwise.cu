@@ -106,9 +106,9 @@ __global__ void split_rows_kernel(const float* __restrict__ x, int ld_x, int row
   }
 }
 
-constexpr int kFsmnRows = 32;   // output rows per CTA
+constexpr int kFsmnRows = 64;   // output rows per CTA: 18944 rows = 296 CTAs = two per SM, one wave
 constexpr int kFsmnMaxK = 32;
-constexpr int kFsmnGroup = 4;   // rows fetched per step (independent loads in flight)
+constexpr int kFsmnGroup = 8;   // rows fetched per step (independent loads in flight)
 
 // out[r, c] = sum_j w[c, j] * v[r + j - left, c] (inside the sequence of r) + v[r, c] (+ res[r, c]).
 // One CTA = kFsmnRows consecutive packed rows x all channels; a thread owns 4 channels and walks
