@@ -259,6 +259,14 @@ def main():
     h2d = int(sum(int(n) for n in durs) * 4 + sum(3 * (len(b) + 1) * 4 + (len(b) + 1) * 8 for b in batches))
     n_tok = step_resident()
     d2h = int(n_tok * 4 + len(durs) * 4)
+    # DRAM bytes per GEMM launch: one ncu pass over the same command, summarised under profiles/ (bytes, or None)
+    gemm_traffic, gemm_traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_gemm_dram.json")) as f:
+            _t = json.load(f)
+        gemm_traffic, gemm_traffic_src = _t["dram_bytes_per_launch"], "profiles/r01_gemm_dram.json (ncu dram__bytes_read+write.sum, avg over %d launches)" % _t["launches"]
+    except (OSError, KeyError, ValueError):
+        pass
     line = {
         "metric": "Paraformer-large RTFx (audio s / wall s)", "value": value, "unit": "audio_s/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_res / args.steps, "higher_is_better": True,
@@ -279,7 +287,8 @@ def main():
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": "gemm_tcgen05_kernel", "achieved": achieved,
                      "peak": pk["tf_sustained"], "unit": "TFLOP/s", "frac": achieved / pk["tf_sustained"],
-                     "traffic": None, "peak_source": pk["source"] + " (sustained bf16)",
+                     "traffic": gemm_traffic, "traffic_source": gemm_traffic_src,
+                     "peak_source": pk["source"] + " (sustained bf16)",
                      "launches": g["calls"], "avg_launch_us": 1e3 * g["ms"] / max(g["calls"], 1),
                      "share_of_step": g["ms"] / tot_ms, "tensor_terms_per_flop": terms,
                      "executed_tflops": achieved * terms},
