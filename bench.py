@@ -31,6 +31,16 @@ sys.path.insert(0, ROOT)
 
 from funasr_b200 import params, synth  # noqa: E402
 
+# The contract is ONE JSON line on stdout: everything else that libraries print there (the NCCL version banner,
+# warnings) is sent to stderr by pointing fd 1 at fd 2 for the whole run; `emit` writes to the real stdout.
+_REAL_STDOUT = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(obj) -> None:
+    os.write(_REAL_STDOUT, (json.dumps(obj) + "\n").encode())
+
+
 FRAME_S = 0.06  # audio seconds per encoder row: frame_shift 10 ms * lfr_n 6 (paraformer/model.py:491-493)
 
 
@@ -124,7 +134,7 @@ def run_reference(args):
     dt = (time.perf_counter() - t0) / args.steps
     v = secs / dt
     sample = "first %d of the %d utterances (%.1f s audio) per step, batch 1" % (len(idx), args.utts, secs)
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": "Paraformer-large RTFx (audio s / wall s)", "value": v, "unit": "audio_s/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -300,7 +310,7 @@ def main():
         line["cpu_baseline"] = {"value": v, "unit": "audio_s/s", "cores": threads, "kind": "port",
                                 "sample": "first %d of the %d utterances (%.1f s audio, %.1f s CPU), batch 1, oracle"
                                           % (n, args.utts, s, dt)}
-    print(json.dumps(line))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 
