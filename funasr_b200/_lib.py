@@ -28,6 +28,7 @@ SIGNATURES = {
     "fb200_fsmn": [_P, _I, _P, _I, _I, _I, _P, _I, _P, _I, _P, _I, _P],
     "fb200_gemm": [_P, _I, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
     "fb200_split_weight": [_P, _I, _I, _P, _I, _P],
+    "fb200_fill_head_rows": [_P, _I, _I, _P, _I, _P, _F, _P, _I, _P],
     "fb200_attention_plan": [_P, _P, _I, _P, _I, _P],
     "fb200_attention": [_P, _I, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P, _I,
                         _P, _I, _I, _P],

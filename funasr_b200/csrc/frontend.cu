@@ -166,6 +166,22 @@ __global__ void scale_add_pe_kernel(const float* __restrict__ x, int ld_x, const
   }
 }
 
+// out[cu_rows[b] + j, :] = head[j, :] * scale + PE(pos = j + 1) for the first n_head rows of every sequence.
+__global__ void fill_head_rows_kernel(const float* __restrict__ head, int n_head, int dim, const int32_t* __restrict__ cu_rows,
+                                      const float* __restrict__ inv_ts, float scale, float* __restrict__ out, int ld_out) {
+  const int b = blockIdx.x / n_head, j = blockIdx.x % n_head;
+  const size_t row = (size_t)cu_rows[b] + j;
+  const int half = dim / 2;
+  for (int c = threadIdx.x; c < dim; c += blockDim.x) {
+    float v = head[(size_t)j * dim + c] * scale;
+    if (inv_ts != nullptr) {
+      const float arg = (float)(j + 1) * __ldg(inv_ts + (c < half ? c : c - half));
+      v += c < half ? sinf(arg) : cosf(arg);
+    }
+    out[row * ld_out + c] = v;
+  }
+}
+
 }  // namespace fb200
 
 using namespace fb200;
@@ -217,5 +233,18 @@ extern "C" __attribute__((visibility("default"))) int fb200_scale_add_pe(const f
   scale_add_pe_kernel<<<total_rows, 256, 0, (cudaStream_t)stream>>>(x, ld_x, cu_rows, batch, dim,
                                                                    pe_inv_timescales, scale, out, ld_out);
   FB_CHECK_LAUNCH("scale_add_pe");
+  return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_fill_head_rows(const float* head, int n_head, int dim,
+                                                                           const int32_t* cu_rows, int batch,
+                                                                           const float* pe_inv_timescales, float scale,
+                                                                           float* out, int ld_out, void* stream) {
+  FB_CHECK_ARG(n_head > 0 && dim > 0 && dim % 2 == 0 && batch >= 0, "fill_head_rows: n_head %d dim %d batch %d", n_head, dim, batch);
+  if (batch == 0) return FB200_OK;
+  ProfScope prof(kProfPe, stream, 8.0 * (double)batch * n_head * dim);
+  fill_head_rows_kernel<<<batch * n_head, 256, 0, (cudaStream_t)stream>>>(head, n_head, dim, cu_rows, pe_inv_timescales, scale,
+                                                                         out, ld_out);
+  FB_CHECK_LAUNCH("fill_head_rows");
   return FB200_OK;
 }

@@ -203,6 +203,56 @@ class SANMEncoder(_ParamTree):
         return out, olens, None
 
 
+class SenseVoiceEncoderSmall(_ParamTree):
+    """funasr/models/sense_voice/model.py:444-585: the SAN-M stack of SANMEncoder (LayerNorm eps 1e-5) followed by
+    `tp_blocks` more blocks and `tp_norm`; `forward(xs_pad, ilens) -> (xs_pad, olens)`.  The caller
+    (SenseVoiceSmall.inference, :852-876) has already prepended the 4 query frames."""
+
+    def __init__(self, input_size: int, output_size: int = 256, attention_heads: int = 4, linear_units: int = 2048,
+                 num_blocks: int = 6, tp_blocks: int = 0, dropout_rate: float = 0.1, positional_dropout_rate: float = 0.1,
+                 attention_dropout_rate: float = 0.0, stochastic_depth_rate: float = 0.0,
+                 input_layer: Optional[str] = "conv2d", pos_enc_class=None, normalize_before: bool = True,
+                 concat_after: bool = False, positionwise_layer_type: str = "linear",
+                 positionwise_conv_kernel_size: int = 1, padding_idx: int = -1, kernel_size: int = 11, sanm_shfit: int = 0,
+                 selfattention_layer_type: str = "sanm", precision: Optional[str] = None, **kwargs):
+        super().__init__()
+        unsupported = []
+        if selfattention_layer_type != "sanm" or positionwise_layer_type != "linear":
+            unsupported.append("attention/positionwise layer types other than sanm/linear")
+        if not normalize_before or concat_after:
+            unsupported.append("post-norm / concat_after")
+        if sanm_shfit != 0:
+            unsupported.append("sanm_shfit != 0")
+        if output_size // attention_heads != 128:
+            unsupported.append("head dim %d (128 only)" % (output_size // attention_heads))
+        if unsupported:
+            raise NotImplementedError("funasr_b200.SenseVoiceEncoderSmall does not support: " + "; ".join(unsupported))
+        self._output_size, self.heads, self.precision = output_size, attention_heads, precision
+        self._declare(params.sanm_encoder_shapes(input_size, output_size, linear_units, num_blocks, kernel_size, "",
+                                                 tp_blocks=tp_blocks), "")
+
+    def output_size(self) -> int:
+        return self._output_size
+
+    def _enc(self, dev) -> engine.EncoderPack:
+        return self._packed(lambda: engine.EncoderPack(self._sd("encoder."), dev, heads=self.heads, eps=1e-5,
+                                                       nparts=self._nparts))
+
+    def forward(self, xs_pad: torch.Tensor, ilens: torch.Tensor):
+        _require_cuda(xs_pad, "SenseVoiceEncoderSmall")
+        lens = _lengths_list(ilens)
+        dev = xs_pad.device
+        with torch.cuda.device(dev):
+            cu_rows = tables.cu_from_lengths(lens, torch.int32, dev)
+            enc = self._enc(dev)
+            x = ops.pack_rows(xs_pad.float(), cu_rows, sum(lens))
+            x = enc.prologue(x, cu_rows)  # x * sqrt(d) + sinusoidal position code (:561-563)
+            y = enc.run(x, cu_rows, max(lens), tp=True)
+            out = ops.unpack_rows(y, cu_rows, xs_pad.shape[1])
+        olens = torch.as_tensor(lens, dtype=torch.int32, device=dev)  # masks.squeeze(1).sum(1).int()
+        return out, olens
+
+
 class CifPredictorV2(_ParamTree):
     """funasr/models/paraformer/cif_predictor.py:172-253 at inference (no target labels)."""
 
@@ -305,6 +355,7 @@ DROPIN_CLASSES = {
     ("frontend_classes", "WavFrontend"): WavFrontend,
     ("frontend_classes", "wav_frontend"): WavFrontend,
     ("encoder_classes", "SANMEncoder"): SANMEncoder,
+    ("encoder_classes", "SenseVoiceEncoderSmall"): SenseVoiceEncoderSmall,
     ("predictor_classes", "CifPredictorV2"): CifPredictorV2,
     ("decoder_classes", "ParaformerSANMDecoder"): ParaformerSANMDecoder,
 }

@@ -128,10 +128,13 @@ class FrontendPack:
         return frames, rows
 
     def run(self, wave: torch.Tensor, num_samples: Sequence[int], pe_scale: Optional[float] = None,
-            fbank_out: Optional[list] = None):
+            fbank_out: Optional[list] = None, row_skip: int = 0):
         """wave: packed fp32 [sum N] on the device.  Returns (feats [R, dim], cu_rows i32 dev, rows list).
-        pe_scale given: feats = cmvn(lfr(fbank)) * pe_scale + PE(pos)  (the encoder input)."""
+        pe_scale given: feats = cmvn(lfr(fbank)) * pe_scale + PE(pos)  (the encoder input).
+        row_skip > 0: every utterance gets that many extra rows at its head (counted in `rows`, positions
+        included, left for the caller to fill -- the SenseVoice prompt frames)."""
         frames, rows = self.plan(num_samples)
+        rows = [r + row_skip for r in rows]
         if min(frames) < 1:
             raise RuntimeError("funasr_b200: an utterance is shorter than one %d-sample frame" % self.frame_len)
         dev = self.device
@@ -143,7 +146,8 @@ class FrontendPack:
         if fbank_out is not None:
             fbank_out.append(fb)
         feats = ops.lfr_cmvn(fb, cu_frames, cu_rows, int(sum(rows)), self.lfr_m, self.lfr_n, self.shift, self.scale,
-                             self.pe_inv if pe_scale is not None else None, 1.0 if pe_scale is None else pe_scale)
+                             self.pe_inv if pe_scale is not None else None, 1.0 if pe_scale is None else pe_scale,
+                             row_skip=row_skip)
         return feats, cu_rows, rows
 
 
@@ -471,3 +475,104 @@ class ParaformerEngine:
                         scores[i] = float(logp_h[o: o + n].sum())
                     o += n
         return (results, scores) if with_scores else results
+
+
+class SenseVoiceEngine:
+    """SenseVoiceSmall.inference (funasr/models/sense_voice/model.py:836-906) for one GPU -- BASELINE
+    config 3: host float32 waveforms in, CTC-greedy token-id lists out.  Same frontend and SAN-M kernels
+    as the Paraformer path; differences: 4 query rows from `embed.weight` at the head of every utterance
+    (:852-876), LayerNorm eps 1e-5 (:275-287), 20 extra `tp_encoders` + `tp_norm` (:553-585), then the
+    CTC projection, per-frame argmax, unique_consecutive and blank removal (:884-906,
+    funasr/models/ctc/ctc.py:173-197)."""
+
+    LID = {"auto": 0, "zh": 3, "en": 4, "yue": 7, "ja": 11, "ko": 12, "nospeech": 13}  # model.py:642
+    TEXTNORM = {"withitn": 14, "woitn": 15}                                             # model.py:644
+    N_PROMPT = 4
+    LOGIT_ROWS = 4096  # rows of the [rows, V] logits buffer per projection call (V = 25055: 410 MB)
+
+    def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp32",
+                 cmvn: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, window: str = "hamming", heads: int = 4,
+                 max_rows: int = 16384, blank_id: int = 0):
+        if precision not in ParaformerEngine.PRECISIONS:
+            raise ValueError("precision must be one of %s" % sorted(ParaformerEngine.PRECISIONS))
+        if not torch.cuda.is_available():
+            raise RuntimeError("funasr_b200: no CUDA device -- this path has no CPU fallback")
+        if not 0 <= blank_id < 32:
+            raise ValueError("blank_id must be below 32")
+        self.device = torch.device(device)
+        self.precision = precision
+        self.nparts = ParaformerEngine.PRECISIONS[precision]
+        self.max_rows = max_rows
+        self.blank_id = blank_id
+        with torch.cuda.device(self.device):
+            self.frontend = FrontendPack(self.device, cmvn=cmvn, window=window)
+            self.encoder = EncoderPack(state_dict, self.device, heads=heads, eps=1e-5, nparts=self.nparts)
+            self.ctc = _Linear(state_dict["ctc.ctc_lo.weight"], state_dict["ctc.ctc_lo.bias"], self.nparts, self.device)
+            self.embed = _dev(state_dict["embed.weight"], self.device)
+        self._prompts: Dict[Tuple[str, str], torch.Tensor] = {}
+
+    def prompt(self, language: str = "auto", textnorm: str = "woitn") -> torch.Tensor:
+        """[language, event, emotion, text-norm] rows of the query embedding, [4, 560] on the device."""
+        key = (language, textnorm)
+        if key not in self._prompts:
+            ids = [self.LID.get(language, 0), 1, 2, self.TEXTNORM[textnorm]]
+            self._prompts[key] = self.embed[torch.tensor(ids, device=self.device)].contiguous()
+        return self._prompts[key]
+
+    def forward_packed(self, wave: torch.Tensor, lens: Sequence[int], language: str = "auto", textnorm: str = "woitn",
+                       taps: Optional[dict] = None):
+        """Device-resident packed waveforms -> (token ids i32 packed at cu_rows, counts i32 [B], cu_rows, rows)."""
+        with torch.cuda.device(self.device):
+            scale = float(self.encoder.d) ** 0.5
+            feats, cu_rows, rows = self.frontend.run(wave, lens, pe_scale=scale, row_skip=self.N_PROMPT)
+            ops.fill_head_rows(self.prompt(language, textnorm), cu_rows, feats, pe_inv=self.frontend.pe_inv, scale=scale)
+            enc = self.encoder.run(feats, cu_rows, max(rows), tp=True)
+            r, v = enc.shape[0], self.ctc.n
+            enc_split = ops.split_rows(enc, self.nparts)
+            frame_ids = torch.empty(r, dtype=torch.int32, device=self.device)
+            ld = (v + 3) // 4 * 4
+            logits = torch.empty(min(r, self.LOGIT_ROWS), ld, dtype=torch.float32, device=self.device)
+            for r0 in range(0, r, self.LOGIT_ROWS):
+                n = min(self.LOGIT_ROWS, r - r0)
+                ops.gemm(enc_split[r0: r0 + n], self.nparts, self.ctc.w, self.nparts, n, v, self.ctc.k, bias=self.ctc.bias,
+                         out_f32=logits[:n])
+                ops.argmax_logprob(logits[:n], v, frame_ids[r0: r0 + n], rows=n)
+            out_ids = torch.empty(r, dtype=torch.int32, device=self.device)
+            out_len = torch.empty(len(lens), dtype=torch.int32, device=self.device)
+            ops.ctc_collapse(frame_ids, cu_rows, 1 << self.blank_id, True, out_ids, out_len)
+            if taps is not None:
+                taps.update(feats=feats, enc=enc, frame_ids=frame_ids, cu_rows=cu_rows, rows=rows)
+            return out_ids, out_len, cu_rows, rows
+
+    def recognize(self, waves: Sequence[np.ndarray], language: str = "auto", textnorm: str = "woitn") -> List[List[int]]:
+        """CTC-greedy token ids per utterance (blank dropped).  Utterances shorter than one frame give []."""
+        results: List[List[int]] = [[] for _ in waves]
+        lens_all = [int(w.shape[0]) for w in waves]
+        _, rows = self.frontend.plan(lens_all)
+        order = sorted(range(len(waves)), key=lambda i: -rows[i])
+        batches, cur, cur_rows = [], [], 0
+        for i in order:
+            if rows[i] < 1:
+                continue
+            need = rows[i] + self.N_PROMPT
+            if cur and cur_rows + need > self.max_rows:
+                batches.append(cur)
+                cur, cur_rows = [], 0
+            cur.append(i)
+            cur_rows += need
+        if cur:
+            batches.append(cur)
+        with torch.cuda.device(self.device):
+            for batch in batches:
+                lens = [lens_all[i] for i in batch]
+                wave = torch.empty(sum(lens), dtype=torch.float32, device=self.device)
+                o = 0
+                for i, n in zip(batch, lens):
+                    src = torch.from_numpy(waves[i]) if isinstance(waves[i], np.ndarray) else waves[i]
+                    wave[o: o + n].copy_(src, non_blocking=True)
+                    o += n
+                ids, counts, cu_rows, _ = self.forward_packed(wave, lens, language, textnorm)
+                ids_h, cnt_h, cu_h = ids.cpu().numpy(), counts.cpu().numpy(), cu_rows.cpu().numpy()
+                for j, i in enumerate(batch):
+                    results[i] = ids_h[cu_h[j]: cu_h[j] + cnt_h[j]].tolist()
+        return results

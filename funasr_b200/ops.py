@@ -61,6 +61,14 @@ def lfr_cmvn(fb, cu_frames, cu_rows, total_rows, lfr_m=7, lfr_n=6, shift=None, s
     return out
 
 
+def fill_head_rows(head, cu_rows, out, pe_inv=None, scale=1.0):
+    """out[cu_rows[b] + j] = head[j] * scale + PE(j + 1) for the first head.shape[0] rows of every sequence."""
+    _chk(head, torch.float32, "fill_head_rows")
+    _lib.call("fb200_fill_head_rows", _p(head), head.shape[0], head.shape[1], _p(cu_rows), cu_rows.numel() - 1, _p(pe_inv),
+              scale, _p(out), out.stride(0), _stream())
+    return out
+
+
 def scale_add_pe(x, cu_rows, pe_inv, scale, out=None):
     _chk(x, torch.float32, "scale_add_pe")
     if out is None:

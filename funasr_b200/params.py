@@ -105,6 +105,16 @@ def paraformer_large_shapes(vocab_size: int = 8404, enc_blocks: int = 50, dec_bl
     return s
 
 
+def sense_voice_small_shapes(vocab_size: int = 25055, enc_blocks: int = 50, tp_blocks: int = 20) -> Shapes:
+    """SenseVoiceSmall (funasr/models/sense_voice/model.py:598-660): SenseVoiceEncoderSmall, the CTC
+    projection (funasr/models/ctc/ctc.py:28) and the 16 x 560 query embedding (:646-648)."""
+    s = sanm_encoder_shapes(num_blocks=enc_blocks, tp_blocks=tp_blocks)
+    s["ctc.ctc_lo.weight"] = (vocab_size, 512)
+    s["ctc.ctc_lo.bias"] = (vocab_size,)
+    s["embed.weight"] = (16, 560)
+    return s
+
+
 def count_params(shapes: Shapes) -> int:
     n = 0
     for shp in shapes.values():

@@ -89,6 +89,15 @@ int fb200_lfr_cmvn(const float* fbank, const int32_t* cu_frames, const int32_t* 
                    const float* cmvn_scale, const float* pe_inv_timescales, float pe_scale,
                    int row_skip, float* out, int ld_out, void* stream);
 
+/* Prompt rows of SenseVoiceSmall (funasr/models/sense_voice/model.py:852-876 prepends 4 embedding rows to
+ * the features of every utterance; SenseVoiceEncoderSmall.forward :561-563 then scales and adds the position
+ * code): out[cu_rows[b] + j, :] = head[j, :] * scale + PE(pos = j + 1), j < n_head, for every sequence b.
+ * Used with fb200_lfr_cmvn(row_skip = n_head), which writes the speech rows behind them.
+ *   head f32 [n_head, dim]; pe_inv_timescales f32 [dim/2] or NULL (no position code) */
+int fb200_fill_head_rows(const float* head, int n_head, int dim, const int32_t* cu_rows, int batch,
+                         const float* pe_inv_timescales, float scale, float* out, int ld_out,
+                         void* stream);
+
 /* Encoder prologue alone for callers that hand over features: out = x*scale + PE(pos = i+1). */
 int fb200_scale_add_pe(const float* x, int ld_x, const int32_t* cu_rows, int batch, int total_rows,
                        int dim, const float* pe_inv_timescales, float scale, float* out, int ld_out,

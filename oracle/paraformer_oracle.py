@@ -369,3 +369,43 @@ def recognize(wave: torch.Tensor, sd: SD, cmvn=None, window: str = "hamming", he
         if taps is not None:
             taps.update(logits=logits, score=score)
         return ids
+
+# --------------------------------------------------------------------------------------
+# SenseVoiceSmall (CTC) path -- BASELINE config 3, SURVEY.md 8a rows a22/a23
+# --------------------------------------------------------------------------------------
+SENSE_VOICE_LID = {"auto": 0, "zh": 3, "en": 4, "yue": 7, "ja": 11, "ko": 12, "nospeech": 13}  # sense_voice/model.py:642
+SENSE_VOICE_TEXTNORM = {"withitn": 14, "woitn": 15}                                             # :644
+
+
+def sense_voice_prompt(sd: SD, language: str = "auto", textnorm: str = "woitn") -> torch.Tensor:
+    """The 4 query rows prepended to the features (funasr/models/sense_voice/model.py:852-876):
+    [language, event (id 1), emotion (id 2), text-norm] rows of `embed.weight` [16, 560]."""
+    e = sd["embed.weight"]
+    ids = [SENSE_VOICE_LID.get(language, 0), 1, 2, SENSE_VOICE_TEXTNORM[textnorm]]
+    return e[torch.tensor(ids)]
+
+
+def sense_voice_encoder(x: torch.Tensor, sd: SD, prefix: str = "encoder.", heads: int = 4,
+                        eps: float = 1e-5) -> torch.Tensor:
+    """SenseVoiceEncoderSmall.forward (funasr/models/sense_voice/model.py:553-585) for one utterance:
+    x [T + 4, 560] (prompt rows included) -> [T + 4, 512].  Same SAN-M blocks as the Paraformer
+    encoder, LayerNorm eps 1e-5 (:275-287), then the 20 `tp_encoders` and `tp_norm`."""
+    x = sanm_encoder(x, sd, prefix=prefix, heads=heads, eps=eps)
+    for i in range(count_layers(sd, prefix + "tp_encoders.")):
+        x = encoder_layer(x, sd, prefix + "tp_encoders.%d." % i, heads, eps)
+    return layer_norm(x, sd, prefix + "tp_norm.", eps)
+
+
+def sense_voice_recognize(wave: torch.Tensor, sd: SD, cmvn=None, window: str = "hamming", heads: int = 4,
+                          language: str = "auto", textnorm: str = "woitn", taps: Optional[dict] = None) -> List[int]:
+    """SenseVoiceSmall.inference for one utterance (funasr/models/sense_voice/model.py:836-906):
+    frontend -> prompt rows -> encoder -> ctc_lo -> log_softmax -> argmax -> unique_consecutive ->
+    drop blank 0 (funasr/models/ctc/ctc.py:173-197)."""
+    with torch.no_grad():
+        feats = wav_frontend(wave, cmvn, window)
+        x = torch.cat([sense_voice_prompt(sd, language, textnorm), feats], dim=0)
+        enc = sense_voice_encoder(x, sd, heads=heads)
+        logits = torch.log_softmax(F.linear(enc, sd["ctc.ctc_lo.weight"], sd["ctc.ctc_lo.bias"]), dim=-1)
+        if taps is not None:
+            taps.update(feats=feats, enc=enc, logits=logits)
+        return ctc_greedy(logits, blank=0, drop=(0,))

@@ -38,3 +38,14 @@ def cmvn():
 
     shift, scale = synth.synth_cmvn(560, 3)
     return torch.from_numpy(shift), torch.from_numpy(scale)
+
+
+@pytest.fixture(scope="session")
+def sensevoice_sd():
+    """Seeded SenseVoiceSmall weights (234 M params: 50 + 20 SAN-M blocks, V = 25055)."""
+    import torch
+
+    from funasr_b200 import params, synth
+
+    sd = synth.synth_state_dict(params.sense_voice_small_shapes(), seed=0)
+    return {k: torch.from_numpy(v) for k, v in sd.items()}

@@ -139,3 +139,51 @@ def test_reference_call_sequence_through_dropin_modules_matches_oracle(paraforme
         assert float(encoder_out[i, ti:].abs().max()) == 0.0 if ti < t else True
         assert float((alphas[i, : ti + 1].cpu() - taps["alphas"]).abs().max()) < 1e-4
         assert float((peaks[i, : ti + 1].cpu() - taps["fires"]).abs().max()) < 1e-3
+
+
+# ------------------------------------------------------------------- SenseVoiceSmall (config 3)
+SV_ENC = dict(output_size=512, attention_heads=4, linear_units=2048, num_blocks=50, tp_blocks=20, dropout_rate=0.1,
+              positional_dropout_rate=0.1, attention_dropout_rate=0.1, input_layer="pe", normalize_before=True,
+              kernel_size=11, sanm_shfit=0, selfattention_layer_type="sanm")
+
+
+def test_sensevoice_encoder_state_dict_keys_are_the_reference_inventory():
+    enc = dropin.SenseVoiceEncoderSmall(560, **SV_ENC)
+    got = {"encoder." + k: tuple(v.shape) for k, v in enc.state_dict().items()}
+    want = {k: v for k, v in params.sense_voice_small_shapes().items() if k.startswith("encoder.")}
+    assert got == want
+    assert ("encoder_classes", "SenseVoiceEncoderSmall") in dropin.DROPIN_CLASSES
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        enc(torch.zeros(1, 8, 560), torch.tensor([8]))
+
+
+@pytest.mark.gpu
+def test_sensevoice_call_sequence_through_dropin_encoder_matches_golden(sensevoice_sd, cmvn, golden_dir, tmp_path):
+    """SenseVoiceSmall.inference's own steps (funasr/models/sense_voice/model.py:852-906) around the drop-in
+    frontend and encoder, on a PADDED batch of the two golden utterances."""
+    dev = torch.device("cuda:0")
+    g = np.load(os.path.join(golden_dir, "sensevoice.npz"))
+    shift, scale = synth.synth_cmvn()
+    cmvn_file = str(tmp_path / "am.mvn")
+    synth.write_cmvn_file(cmvn_file, shift, scale)
+    frontend = dropin.WavFrontend(cmvn_file=cmvn_file, fs=16000, window="hamming", n_mels=80, frame_length=25,
+                                  frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0)
+    enc = dropin.SenseVoiceEncoderSmall(560, **SV_ENC).to(dev)
+    enc.load_state_dict({k[len("encoder."):]: v for k, v in sensevoice_sd.items() if k.startswith("encoder.")}, strict=True)
+    embed = sensevoice_sd["embed.weight"].to(dev)
+    w_ctc, b_ctc = sensevoice_sd["ctc.ctc_lo.weight"].to(dev), sensevoice_sd["ctc.ctc_lo.bias"].to(dev)
+    for ci in (0, 1):  # one language / text-norm query per call, like the reference
+        ui, n, lang, itn = (int(v) for v in g["case_%d" % ci])
+        wave = torch.from_numpy(synth.synth_waveform(ui, n))
+        speech, speech_lengths = frontend(wave[None, :], torch.tensor([n], dtype=torch.int32))
+        speech_lengths = speech_lengths.to(dev)
+        q = embed[torch.tensor([lang, 1, 2, 14 if itn else 15], device=dev)][None]
+        speech = torch.cat([q, speech], dim=1)
+        speech_lengths = speech_lengths + 4
+        encoder_out, encoder_out_lens = enc(speech, speech_lengths)
+        ref = torch.from_numpy(g["enc_%d" % ci]).to(dev)
+        assert encoder_out.shape[1:] == ref.shape and int(encoder_out_lens[0]) == ref.shape[0]
+        assert float((encoder_out[0] - ref).abs().max() / ref.abs().max()) < 1e-3
+        logp = torch.log_softmax(torch.nn.functional.linear(encoder_out[0], w_ctc, b_ctc), dim=-1)
+        yseq = torch.unique_consecutive(logp.argmax(-1))
+        assert yseq[yseq != 0].tolist() == g["ids_%d" % ci].tolist()

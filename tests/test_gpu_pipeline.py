@@ -144,3 +144,45 @@ def test_fp32_mode_error_budget_is_reported(golden_dir, eng_fp32, eng_fp32x6):
         print("%s: encoder max-rel error %.3e, alpha max abs %.3e" % (
             name, err, float((taps["alphas"].cpu() - torch.from_numpy(g["alphas"][:-1])).abs().max())))
         assert err < 1e-3
+
+
+# ------------------------------------------------------------------- SenseVoiceSmall (config 3)
+@pytest.fixture(scope="module")
+def sv_eng(sensevoice_sd, cmvn):
+    from funasr_b200.engine import SenseVoiceEngine
+
+    return SenseVoiceEngine(sensevoice_sd, "cuda:0", precision="fp32", cmvn=cmvn)
+
+
+SV_LANG = {0: "auto", 4: "en"}
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ci", [0, 1])
+def test_sensevoice_stages_match_reference_golden(golden_dir, sv_eng, ci):
+    """Encoder output within 1e-3 max-rel, per-frame argmax and CTC-greedy ids identical to the reference's
+    SenseVoiceSmall.inference (tests/golden/sensevoice.npz)."""
+    g = np.load(os.path.join(golden_dir, "sensevoice.npz"))
+    ui, n, lang, itn = (int(v) for v in g["case_%d" % ci])
+    wave = torch.from_numpy(synth.synth_waveform(ui, n)).to("cuda:0")
+    taps = {}
+    ids, counts, cu_rows, rows = sv_eng.forward_packed(wave, [n], SV_LANG[lang], "withitn" if itn else "woitn", taps=taps)
+    assert rows == [g["enc_%d" % ci].shape[0]]
+    assert rel(taps["enc"], g["enc_%d" % ci]) < 1e-3
+    assert taps["frame_ids"].cpu().tolist() == g["argmax_%d" % ci].tolist()
+    assert ids[: int(counts[0])].cpu().tolist() == g["ids_%d" % ci].tolist()
+
+
+@pytest.mark.gpu
+def test_sensevoice_ragged_batch_matches_oracle(sv_eng, sensevoice_sd, cmvn):
+    """A ragged batch through recognize(): every utterance equals the oracle's batch-1 result."""
+    from oracle import paraformer_oracle as O
+
+    lens = [16000 * 2 + 11, 52000, 16000 * 4, 399]  # the last one is shorter than a frame -> []
+    waves = [synth.synth_waveform(300 + i, n) for i, n in enumerate(lens)]
+    got = sv_eng.recognize(waves, language="zh", textnorm="woitn")
+    for w, ids in zip(waves, got):
+        if len(w) < 400:
+            assert ids == []
+            continue
+        assert ids == O.sense_voice_recognize(torch.from_numpy(w), sensevoice_sd, cmvn, language="zh", textnorm="woitn")

@@ -102,3 +102,26 @@ def test_ctc_greedy_collapse():
         logits[t, k] = 1.0
     assert O.ctc_greedy(logits) == [3, 3, 2]
     assert O.ctc_greedy(logits, drop=(0, 1, 2)) == [3, 3]
+
+
+# ---------------------------------------------------------------- SenseVoiceSmall (config 3)
+SV_LANG = {0: "auto", 4: "en"}
+
+
+def test_sensevoice_param_inventory():
+    assert params.count_params(params.sense_voice_small_shapes()) == 233999167  # the reference build reports 233.999 M
+
+
+@pytest.mark.parametrize("ci", [0, 1])
+def test_sensevoice_oracle_matches_reference(golden_dir, sensevoice_sd, cmvn, ci):
+    """Encoder output, per-frame argmax and CTC-greedy ids of the reference SenseVoiceSmall.inference."""
+    g = np.load(os.path.join(golden_dir, "sensevoice.npz"))
+    ui, n, lang, itn = (int(v) for v in g["case_%d" % ci])
+    wave = torch.from_numpy(synth.synth_waveform(ui, n))
+    taps = {}
+    ids = O.sense_voice_recognize(wave, sensevoice_sd, cmvn, language=SV_LANG[lang],
+                                  textnorm="withitn" if itn else "woitn", taps=taps)
+    assert taps["enc"].shape == g["enc_%d" % ci].shape
+    assert _rel(taps["enc"], g["enc_%d" % ci]) < 2e-5
+    assert taps["logits"].argmax(-1).tolist() == g["argmax_%d" % ci].tolist()
+    assert ids == g["ids_%d" % ci].tolist()
