@@ -1,6 +1,7 @@
 // Row-wise HBM-bound kernels: LayerNorm (fp32 and/or bf16 split-operand output), operand
 // splitting, FSMN depthwise conv with per-sequence zero halos.
 #include "common.cuh"
+#include "sm100_ptx.cuh"
 
 namespace fb200 {
 
@@ -106,84 +107,151 @@ __global__ void split_rows_kernel(const float* __restrict__ x, int ld_x, int row
   }
 }
 
-constexpr int kFsmnRows = 64;   // output rows per CTA: 18944 rows = 296 CTAs = two per SM, one wave
+constexpr int kFsmnRows = 64;    // output rows per CTA: 18944 rows = 296 CTAs = two per SM, one wave
 constexpr int kFsmnMaxK = 32;
-constexpr int kFsmnGroup = 8;   // rows fetched per step (independent loads in flight)
+constexpr int kFsmnBlock = 8;    // rows per ring stage
+constexpr int kFsmnStages = 3;   // ring depth: 3 x (8 input rows + 8 residual rows) x 2 KB = 96 KB per CTA
+constexpr int kFsmnCols = 512;   // channels per CTA (128 consumer threads x 4)
+constexpr int kFsmnThreads = 160;  // 4 consumer warps + 1 copy warp
+constexpr int kFsmnStageBytes = 2 * kFsmnBlock * kFsmnCols * 4;
+constexpr int kFsmnSmemBytes = kFsmnStages * kFsmnStageBytes + 1024;
 
 // out[r, c] = sum_j w[c, j] * v[r + j - left, c] (inside the sequence of r) + v[r, c] (+ res[r, c]).
-// One CTA = kFsmnRows consecutive packed rows x all channels; a thread owns 4 channels and walks
-// down the rows with the last KS inputs in registers (sliding window), so every input element is
-// read once (+ a (KS-1)-row halo per CTA) instead of KS times.
+// One CTA = kFsmnRows consecutive packed rows x 512 channels, streamed once: a copy warp moves 8-row blocks of the
+// input (and of the residual) global -> shared memory with bulk copies behind mbarriers (up to 96 KB in flight per
+// CTA, no registers tied up), the 4 consumer warps walk down the rows with the last KS inputs of their 4 channels
+// in registers (sliding window).  Every input element is read once (+ a (KS-1)-row halo per CTA).
+// Stream position t: input row r0 - LEFT + t arrives, output row r0 + t - (KS - 1) leaves.
 template <int KS>
-__global__ void __launch_bounds__(128)
-fsmn_window_kernel(const float* __restrict__ v, int ld_v, const int32_t* __restrict__ cu_rows, int batch,
+__global__ void __launch_bounds__(kFsmnThreads)
+fsmn_stream_kernel(const float* __restrict__ v, int ld_v, const int32_t* __restrict__ cu_rows, int batch,
                    int total_rows, int dim, const float* __restrict__ weight, const float* __restrict__ res,
                    int ld_res, float* __restrict__ out, int ld_out) {
-  constexpr int LEFT = (KS - 1) / 2, RIGHT = KS - 1 - LEFT;
-  __shared__ int s_beg[kFsmnRows], s_end[kFsmnRows];
-  const int r0 = blockIdx.x * kFsmnRows;
+  constexpr int LEFT = (KS - 1) / 2;
+  constexpr uint32_t FULL = (1u << KS) - 1u;
+  extern __shared__ __align__(128) uint8_t fsmn_smem[];
+  __shared__ uint32_t s_mask[kFsmnRows];  // bit j: tap j of this output row lies inside its sequence
+  __shared__ __align__(8) uint64_t s_bar[2 * kFsmnStages];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r0 = blockIdx.x * kFsmnRows, c0 = blockIdx.y * kFsmnCols;
+  const int nrows = min(kFsmnRows, total_rows - r0);
+  const int ncols = min(kFsmnCols, dim - c0);
+  const uint32_t row_bytes = (uint32_t)ncols * 4u;
+  const int nblocks = (nrows + KS - 1 + kFsmnBlock - 1) / kFsmnBlock;
+  const uint32_t ring = (smem_u32(fsmn_smem) + 127u) & ~127u;
+  auto bar_full = [&](int s) { return smem_u32(&s_bar[s]); };
+  auto bar_empty = [&](int s) { return smem_u32(&s_bar[kFsmnStages + s]); };
   if (threadIdx.x < kFsmnRows) {
-    const int r = r0 + threadIdx.x;
-    int b0 = 0, e0 = 0;
-    if (r < total_rows) {
+    uint32_t m = 0;
+    if ((int)threadIdx.x < nrows) {
+      const int r = r0 + threadIdx.x;
       const int b = find_seq(cu_rows, batch, r);
-      b0 = cu_rows[b];
-      e0 = cu_rows[b + 1];
+      const int beg = cu_rows[b], end = cu_rows[b + 1];
+#pragma unroll
+      for (int j = 0; j < KS; ++j)
+        if (r - LEFT + j >= beg && r - LEFT + j < end) m |= 1u << j;
     }
-    s_beg[threadIdx.x] = b0;
-    s_end[threadIdx.x] = e0;
+    s_mask[threadIdx.x] = m;
+  }
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kFsmnStages; ++s) {
+      mbar_init(bar_full(s), 1);
+      mbar_init(bar_empty(s), 4);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
-  const int nrows = min(kFsmnRows, total_rows - r0);
-  for (int c = threadIdx.x * 4; c < dim; c += blockDim.x * 4) {
-    float4 w[KS];
-#pragma unroll
-    for (int j = 0; j < KS; ++j)
-      w[j] = make_float4(__ldg(weight + (size_t)(c + 0) * KS + j), __ldg(weight + (size_t)(c + 1) * KS + j),
-                         __ldg(weight + (size_t)(c + 2) * KS + j), __ldg(weight + (size_t)(c + 3) * KS + j));
-    // win[j] holds input row (r - LEFT + j) while output row r is produced
-    float4 win[KS];
-    auto load_row = [&](int rr) -> float4 {
-      return (rr >= 0 && rr < total_rows) ? *reinterpret_cast<const float4*>(v + (size_t)rr * ld_v + c)
-                                          : make_float4(0.f, 0.f, 0.f, 0.f);
-    };
-#pragma unroll
-    for (int j = 1; j < KS; ++j) win[j] = load_row(r0 - LEFT + j - 1);  // rows r0-LEFT .. r0+RIGHT-1, shifted in below
-    for (int i0 = 0; i0 < nrows; i0 += kFsmnGroup) {
-      float4 nxt[kFsmnGroup], rs[kFsmnGroup];
-#pragma unroll
-      for (int g = 0; g < kFsmnGroup; ++g) {
-        nxt[g] = load_row(r0 + i0 + g + RIGHT);
-        rs[g] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (res != nullptr && i0 + g < nrows) rs[g] = *reinterpret_cast<const float4*>(res + (size_t)(r0 + i0 + g) * ld_res + c);
+
+  if (warp == 4) {
+    // ---- copy warp: one lane per row of a block (lanes 0..7 input rows, 8..15 residual rows)
+    for (int b = 0; b < nblocks; ++b) {
+      const int s = b % kFsmnStages, use = b / kFsmnStages;
+      if (use > 0) mbar_wait(bar_empty(s), (uint32_t)(use - 1) & 1u);
+      const int t0 = b * kFsmnBlock;
+      const int g = lane & 7;
+      const bool is_res = lane >= 8;
+      bool ok = false;
+      const float* src = nullptr;
+      if (lane < 8) {
+        const int rr = r0 - LEFT + t0 + g;  // input row; rows outside the matrix are never inside a sequence
+        ok = rr >= 0 && rr < total_rows && t0 + g < nrows + KS - 1;
+        src = v + (size_t)rr * ld_v + c0;
+      } else if (lane < 16 && res != nullptr) {
+        const int i = t0 + g - (KS - 1);  // output row the residual belongs to
+        ok = i >= 0 && i < nrows;
+        src = res + (size_t)(r0 + i) * ld_res + c0;
       }
+      const uint32_t n_ok = __popc(__ballot_sync(0xffffffffu, ok));
+      if (lane == 0) mbar_expect_tx(bar_full(s), n_ok * row_bytes);
+      __syncwarp();
+      if (ok) {
+        const uint32_t dst = ring + (uint32_t)s * kFsmnStageBytes + (uint32_t)((is_res ? kFsmnBlock : 0) + g) * (kFsmnCols * 4);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                     "l"(src), "r"(row_bytes), "r"(bar_full(s))
+                     : "memory");
+      }
+    }
+    return;
+  }
+
+  // ---- consumer warps: thread = 4 channels
+  const int c = threadIdx.x * 4;
+  const bool active = c < ncols;
+  float4 w[KS];
 #pragma unroll
-      for (int g = 0; g < kFsmnGroup; ++g) {
+  for (int j = 0; j < KS; ++j)
+    w[j] = active ? make_float4(__ldg(weight + (size_t)(c0 + c + 0) * KS + j), __ldg(weight + (size_t)(c0 + c + 1) * KS + j),
+                                __ldg(weight + (size_t)(c0 + c + 2) * KS + j), __ldg(weight + (size_t)(c0 + c + 3) * KS + j))
+                  : make_float4(0.f, 0.f, 0.f, 0.f);
+  float4 win[KS];  // win[j] holds input row (r - LEFT + j) while output row r is produced
 #pragma unroll
-        for (int j = 0; j < KS - 1; ++j) win[j] = win[j + 1];
-        win[KS - 1] = nxt[g];
-        const int i = i0 + g;
-        if (i < nrows) {
-          const int r = r0 + i;
-          const int beg = s_beg[i], end = s_end[i];
-          float4 acc = win[LEFT];  // + v (the identity branch)
-          acc.x += rs[g].x; acc.y += rs[g].y; acc.z += rs[g].z; acc.w += rs[g].w;
-          float4 conv = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int j = 0; j < KS; ++j) win[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const bool has_res = res != nullptr;
+  for (int b = 0; b < nblocks; ++b) {
+    const int s = b % kFsmnStages, use = b / kFsmnStages;
+    mbar_wait(bar_full(s), (uint32_t)use & 1u);
+    const uint32_t base = ring + (uint32_t)s * kFsmnStageBytes + (uint32_t)c * 4u;
+#pragma unroll
+    for (int g = 0; g < kFsmnBlock; ++g) {
+      const int i = b * kFsmnBlock + g - (KS - 1);
+      uint4 xv, rv = make_uint4(0u, 0u, 0u, 0u);
+      ld_shared_v4(base + (uint32_t)g * (kFsmnCols * 4), xv);
+      if (has_res) ld_shared_v4(base + (uint32_t)(kFsmnBlock + g) * (kFsmnCols * 4), rv);
+#pragma unroll
+      for (int j = 0; j < KS - 1; ++j) win[j] = win[j + 1];
+      win[KS - 1] = make_float4(__uint_as_float(xv.x), __uint_as_float(xv.y), __uint_as_float(xv.z), __uint_as_float(xv.w));
+      if (i >= 0 && i < nrows && active) {
+        const uint32_t m = s_mask[i];
+        float4 conv = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (m == FULL) {
 #pragma unroll
           for (int j = 0; j < KS; ++j) {
-            const int rr = r - LEFT + j;
-            if (rr >= beg && rr < end) {
+            conv.x = fmaf(w[j].x, win[j].x, conv.x);
+            conv.y = fmaf(w[j].y, win[j].y, conv.y);
+            conv.z = fmaf(w[j].z, win[j].z, conv.z);
+            conv.w = fmaf(w[j].w, win[j].w, conv.w);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < KS; ++j)
+            if ((m >> j) & 1u) {
               conv.x = fmaf(w[j].x, win[j].x, conv.x);
               conv.y = fmaf(w[j].y, win[j].y, conv.y);
               conv.z = fmaf(w[j].z, win[j].z, conv.z);
               conv.w = fmaf(w[j].w, win[j].w, conv.w);
             }
-          }
-          acc.x += conv.x; acc.y += conv.y; acc.z += conv.z; acc.w += conv.w;
-          *reinterpret_cast<float4*>(out + (size_t)r * ld_out + c) = acc;
         }
+        float4 acc = win[LEFT];  // + v (the identity branch)
+        if (has_res) {
+          acc.x += __uint_as_float(rv.x); acc.y += __uint_as_float(rv.y);
+          acc.z += __uint_as_float(rv.z); acc.w += __uint_as_float(rv.w);
+        }
+        acc.x += conv.x; acc.y += conv.y; acc.z += conv.z; acc.w += conv.w;
+        *reinterpret_cast<float4*>(out + (size_t)(r0 + i) * ld_out + c0 + c) = acc;
       }
     }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_empty(s));
   }
 }
 
@@ -343,9 +411,20 @@ extern "C" __attribute__((visibility("default"))) int fb200_fsmn(const float* v,
   FB_CHECK_ARG(residual == nullptr || ld_res % 4 == 0, "fsmn: ld_res must be a multiple of 4");
   if (total_rows == 0) return FB200_OK;
   ProfScope prof(kProfFsmn, stream, (double)total_rows * dim * 4.0 * (residual ? 3.0 : 2.0));
-  if (ksize == 11)
-    fsmn_window_kernel<11><<<(total_rows + kFsmnRows - 1) / kFsmnRows, 128, 0, (cudaStream_t)stream>>>(
+  if (ksize == 11) {
+    static bool attr_set = false;  // per process; idempotent
+    if (!attr_set) {
+      cudaError_t e = cudaFuncSetAttribute(fsmn_stream_kernel<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFsmnSmemBytes);
+      if (e != cudaSuccess) {
+        set_error("fsmn: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+        return FB200_ECUDA;
+      }
+      attr_set = true;
+    }
+    const dim3 grid((total_rows + kFsmnRows - 1) / kFsmnRows, (dim + kFsmnCols - 1) / kFsmnCols);
+    fsmn_stream_kernel<11><<<grid, kFsmnThreads, kFsmnSmemBytes, (cudaStream_t)stream>>>(
         v, ld_v, cu_rows, batch, total_rows, dim, weight, residual, ld_res, out, ld_out);
+  }
   else
     fsmn_generic_kernel<<<total_rows, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight,
                                                                       ksize, residual, ld_res, out, ld_out);

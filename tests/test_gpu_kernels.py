@@ -135,6 +135,24 @@ def test_fsmn_matches_oracle(with_res):
         o += n
 
 
+@pytest.mark.parametrize("dim", [512, 320, 1024])
+def test_fsmn_streams_across_cta_and_sequence_boundaries(dim):
+    """64-row CTAs x 512-channel column blocks: sequences that start / end anywhere inside a CTA's rows, a
+    sequence spanning many CTAs, single-row sequences at CTA edges; channel counts below / above one column block."""
+    lens = [63, 1, 1, 70, 3, 64, 129, 1, 500, 5, 187]
+    g = torch.Generator().manual_seed(dim)
+    v = torch.randn(sum(lens), dim, generator=g)
+    w = torch.randn(dim, 1, 11, generator=g) * 0.3
+    res = torch.randn(sum(lens), dim, generator=g)
+    out = torch.full((sum(lens), dim), float("nan"), device=DEV)
+    ops.fsmn(v.to(DEV), cu(lens), w.reshape(dim, 11).to(DEV), out, residual=res.to(DEV))
+    o = 0
+    for n in lens:
+        ref = O.fsmn_memory(v[o: o + n], w) + res[o: o + n]
+        assert rel(out[o: o + n], ref) < 2e-6
+        o += n
+
+
 # ------------------------------------------------------------------ dense contractions
 GEMM_SHAPES = [(167, 1536, 560), (300, 512, 512), (129, 2048, 512), (64, 512, 2048), (71, 8404, 512), (1, 512, 512),
                (1000, 1024, 512), (18944, 512, 512), (9600, 2048, 512), (5000, 8404, 512), (10000, 512, 2048)]
