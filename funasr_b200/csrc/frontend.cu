@@ -114,6 +114,255 @@ fbank_kernel(const float* __restrict__ wave, const int64_t* __restrict__ cu_samp
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// nfft = 512: one warp turns TWO frames into log-mel energies with ONE complex 512-point FFT (frame A in the real
+// part, frame B in the imaginary part; the spectra are separated afterwards through X[k] and conj(X[N-k])).
+// The FFT is 8 x 8 x 8: three passes of in-register radix-8 butterflies (two per lane and pass) with two exchanges
+// through shared memory, instead of nine radix-2 passes through shared memory.
+//   n = p + 64 j,  k = q + 8 (r + 8 k''),  p = p0 + 8 p1:
+//   pass 1: y[p][q]      = W512^(p q)  * sum_j  x[p + 64 j]        W8^(j q)
+//   pass 2: z[q][p0][r]  = W64^(p0 r)  * sum_p1 y[p0 + 8 p1][q]    W8^(p1 r)
+//   pass 3: X[q+8r+64k''] =              sum_p0 z[q][p0][r]        W8^(p0 k'')
+constexpr int kF5Warps = 4;
+constexpr int kF5Ex = 576;     // exchange buffer entries: 8 rows of 72 (pass 1 -> 2), 8 of 65 (2 -> 3), 512 (spectrum)
+constexpr int kF5Pw = 264;     // power spectrum entries per frame (257 used)
+constexpr int kF5MelW = 1024;  // compacted non-zero mel weights (80 triangular filters over 257 bins: ~520)
+
+// In-place forward DFT of 8 complex values, natural order in and out (decimation in frequency).
+__device__ __forceinline__ void dft8(float (&re)[8], float (&im)[8]) {
+  constexpr float h = 0.70710678118654752440f;
+  float br[8], bi[8];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    br[j] = re[j] + re[j + 4];
+    bi[j] = im[j] + im[j + 4];
+    br[j + 4] = re[j] - re[j + 4];
+    bi[j + 4] = im[j] - im[j + 4];
+  }
+  {  // W8^1 = h (1 - i), W8^2 = -i, W8^3 = -h (1 + i)
+    const float a5 = br[5], b5 = bi[5], a6 = br[6], b6 = bi[6], a7 = br[7], b7 = bi[7];
+    br[5] = h * (a5 + b5);
+    bi[5] = h * (b5 - a5);
+    br[6] = b6;
+    bi[6] = -a6;
+    br[7] = h * (b7 - a7);
+    bi[7] = -h * (a7 + b7);
+  }
+#pragma unroll
+  for (int g = 0; g < 2; ++g) {  // 4-point DFT of the even-output half (g = 0) and the odd-output half (g = 1)
+    const int o = g * 4;
+    const float d0r = br[o] + br[o + 2], d0i = bi[o] + bi[o + 2];
+    const float d2r = br[o] - br[o + 2], d2i = bi[o] - bi[o + 2];
+    const float d1r = br[o + 1] + br[o + 3], d1i = bi[o + 1] + bi[o + 3];
+    const float d3r = bi[o + 1] - bi[o + 3], d3i = br[o + 3] - br[o + 1];  // (c1 - c3) * (-i)
+    re[g + 0] = d0r + d1r;
+    im[g + 0] = d0i + d1i;
+    re[g + 2] = d2r + d3r;
+    im[g + 2] = d2i + d3i;
+    re[g + 4] = d0r - d1r;
+    im[g + 4] = d0i - d1i;
+    re[g + 6] = d2r - d3r;
+    im[g + 6] = d2i - d3i;
+  }
+}
+
+__global__ void __launch_bounds__(kF5Warps * 32)
+fbank512_kernel(const float* __restrict__ wave, const int64_t* __restrict__ cu_samples,
+                const int32_t* __restrict__ cu_frames, int batch, int total_frames,
+                const float* __restrict__ window, int frame_len, int frame_shift,
+                const float* __restrict__ mel_bank, int n_mels, float upscale, float preemph,
+                float* __restrict__ out) {
+  constexpr int N = 512, NB = N / 2 + 1;
+  __shared__ float s_re[kF5Warps][kF5Ex];
+  __shared__ float s_im[kF5Warps][kF5Ex];
+  __shared__ float s_pw[kF5Warps][2][kF5Pw];
+  __shared__ float2 s_tw[N];  // W512^t = (cos, -sin)(2 pi t / 512)
+  __shared__ float s_win[N];
+  __shared__ float s_melw[kF5MelW];
+  __shared__ int s_lo[kMaxMel], s_hi[kMaxMel], s_off[kMaxMel];
+  __shared__ int s_compact;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int t = tid; t < N; t += blockDim.x) {
+    float sn, cs;
+    sincospif(-2.0f * (float)t / (float)N, &sn, &cs);
+    s_tw[t] = make_float2(cs, sn);
+    s_win[t] = t < frame_len ? __ldg(window + t) : 0.f;
+  }
+  // non-zero span of every mel filter: one warp per filter
+  for (int m = warp; m < n_mels; m += kF5Warps) {
+    const float* row = mel_bank + (size_t)m * NB;
+    int lo = NB, hi = 0;
+    for (int k = lane; k < NB; k += 32)
+      if (__ldg(row + k) != 0.0f) {
+        lo = min(lo, k);
+        hi = max(hi, k + 1);
+      }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+      hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if (lane == 0) {
+      s_lo[m] = hi > lo ? lo : 0;
+      s_hi[m] = hi > lo ? hi : 0;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int tot = 0;
+    for (int m = 0; m < n_mels; ++m) {
+      s_off[m] = tot;
+      tot += s_hi[m] - s_lo[m];
+    }
+    s_compact = tot <= kF5MelW;
+  }
+  __syncthreads();
+  const bool compact = s_compact != 0;
+  if (compact)
+    for (int m = warp; m < n_mels; m += kF5Warps)
+      for (int k = s_lo[m] + lane; k < s_hi[m]; k += 32) s_melw[s_off[m] + k - s_lo[m]] = __ldg(mel_bank + (size_t)m * NB + k);
+  __syncthreads();
+
+  float* ex_re = s_re[warp];
+  float* ex_im = s_im[warp];
+  const int npairs = (total_frames + 1) / 2;
+  for (int pr = blockIdx.x * kF5Warps + warp; pr < npairs; pr += gridDim.x * kF5Warps) {
+    // ---- load both frames: remove DC, pre-emphasis, window.  Element t of a lane is sample n = lane + 32 t.
+    float v[2][16];
+#pragma unroll
+    for (int f = 0; f < 2; ++f) {
+      const int frame = 2 * pr + f;
+      if (frame < total_frames) {
+        const int b = find_seq(cu_frames, batch, frame);
+        const float* x = wave + cu_samples[b] + (int64_t)(frame - cu_frames[b]) * frame_shift;
+        float acc = 0.f;
+#pragma unroll
+        for (int t = 0; t < 16; ++t) {
+          const int n = lane + 32 * t;
+          v[f][t] = n < frame_len ? __ldg(x + n) * upscale : 0.f;
+          acc += v[f][t];
+        }
+        const float mean = warp_sum(acc) / (float)frame_len;
+#pragma unroll
+        for (int t = 0; t < 16; ++t) {
+          const int n = lane + 32 * t;
+          float y = 0.f;
+          if (n < frame_len) {
+            const float prv = __ldg(x + (n > 0 ? n - 1 : 0)) * upscale - mean;
+            y = ((v[f][t] - mean) - preemph * prv) * s_win[n];
+          }
+          v[f][t] = y;
+        }
+      } else {
+#pragma unroll
+        for (int t = 0; t < 16; ++t) v[f][t] = 0.f;
+      }
+    }
+    // ---- pass 1: lane owns p = lane + 32 u, all j (sample p + 64 j is element t = u + 2 j)
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      float re[8], im[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        re[j] = v[0][u + 2 * j];
+        im[j] = v[1][u + 2 * j];
+      }
+      dft8(re, im);
+      const int pp = lane + 32 * u;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float2 w = s_tw[(pp * q) & (N - 1)];
+        ex_re[q * 72 + pp] = re[q] * w.x - im[q] * w.y;
+        ex_im[q * 72 + pp] = re[q] * w.y + im[q] * w.x;
+      }
+    }
+    __syncwarp();
+    // ---- pass 2: lane owns (q, p0) = (c >> 3, c & 7), c = lane + 32 u, all p1
+    {
+      float re[2][8], im[2][8];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int c = lane + 32 * u, q = c >> 3, p0 = c & 7;
+#pragma unroll
+        for (int p1 = 0; p1 < 8; ++p1) {
+          re[u][p1] = ex_re[q * 72 + p0 + 8 * p1];
+          im[u][p1] = ex_im[q * 72 + p0 + 8 * p1];
+        }
+      }
+      __syncwarp();
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int c = lane + 32 * u, q = c >> 3, p0 = c & 7;
+        dft8(re[u], im[u]);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          const float2 w = s_tw[(8 * p0 * r) & (N - 1)];
+          ex_re[p0 * 65 + 8 * q + r] = re[u][r] * w.x - im[u][r] * w.y;
+          ex_im[p0 * 65 + 8 * q + r] = re[u][r] * w.y + im[u][r] * w.x;
+        }
+      }
+    }
+    __syncwarp();
+    // ---- pass 3: lane owns (q, r) = (c >> 3, c & 7), all p0; the spectrum goes back in natural order
+    {
+      float re[2][8], im[2][8];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int c = lane + 32 * u;
+#pragma unroll
+        for (int p0 = 0; p0 < 8; ++p0) {
+          re[u][p0] = ex_re[p0 * 65 + c];
+          im[u][p0] = ex_im[p0 * 65 + c];
+        }
+      }
+      __syncwarp();
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int c = lane + 32 * u, q = c >> 3, r = c & 7;
+        dft8(re[u], im[u]);
+#pragma unroll
+        for (int k2 = 0; k2 < 8; ++k2) {
+          ex_re[q + 8 * r + 64 * k2] = re[u][k2];
+          ex_im[q + 8 * r + 64 * k2] = im[u][k2];
+        }
+      }
+    }
+    __syncwarp();
+    // ---- separate the two real spectra and square: A = (Z[k] + conj Z[N-k]) / 2, B = (Z[k] - conj Z[N-k]) / (2 i)
+#pragma unroll
+    for (int i = 0; i < 9; ++i) {
+      const int k = lane + 32 * i;
+      if (k < NB) {
+        const float a = ex_re[k], b = ex_im[k];
+        const float c = ex_re[(N - k) & (N - 1)], d = ex_im[(N - k) & (N - 1)];
+        const float ar = 0.5f * (a + c), ai = 0.5f * (b - d);
+        const float br = 0.5f * (b + d), bi = 0.5f * (c - a);
+        s_pw[warp][0][k] = ar * ar + ai * ai;
+        s_pw[warp][1][k] = br * br + bi * bi;
+      }
+    }
+    __syncwarp();
+    // ---- mel filters + log
+    for (int idx = lane; idx < 2 * n_mels; idx += 32) {
+      const int f = idx >= n_mels ? 1 : 0, m = idx - f * n_mels;
+      const int frame = 2 * pr + f;
+      const int lo = s_lo[m], hi = s_hi[m];
+      const float* pw = s_pw[warp][f];
+      float e = 0.f;
+      if (compact) {
+        const float* wm = s_melw + s_off[m] - lo;
+        for (int k = lo; k < hi; ++k) e = fmaf(pw[k], wm[k], e);
+      } else {
+        const float* row = mel_bank + (size_t)m * NB;
+        for (int k = lo; k < hi; ++k) e = fmaf(pw[k], __ldg(row + k), e);
+      }
+      if (frame < total_frames) out[(size_t)frame * n_mels + m] = logf(fmaxf(e, FLT_EPSILON));
+    }
+    __syncwarp();
+  }
+}
+
 // One CTA per output row; float4 per thread.
 __global__ void lfr_cmvn_kernel(const float* __restrict__ fbank, const int32_t* __restrict__ cu_frames,
                                 const int32_t* __restrict__ cu_rows, int batch, int n_mels, int lfr_m,
@@ -201,9 +450,18 @@ extern "C" __attribute__((visibility("default"))) int fb200_fbank(const float* w
   int grid = (total_frames + kFbankWarps - 1) / kFbankWarps;
   const int cap = 148 * 8;  // persistent: a multiple of the SM count
   if (grid > cap) grid = cap;
-  fbank_kernel<<<grid, kFbankWarps * 32, 0, (cudaStream_t)stream>>>(
-      wave, cu_samples, cu_frames, batch, total_frames, window, frame_len, frame_shift, nfft, log2n,
-      mel_bank, n_mels, upscale, preemph, out);
+  if (nfft == 512) {
+    const int npairs = (total_frames + 1) / 2;
+    int g5 = (npairs + kF5Warps - 1) / kF5Warps;
+    if (g5 > 148 * 5) g5 = 148 * 5;  // 38 KB of shared memory per CTA: five CTAs per SM, persistent
+    fbank512_kernel<<<g5, kF5Warps * 32, 0, (cudaStream_t)stream>>>(wave, cu_samples, cu_frames, batch, total_frames, window,
+                                                                    frame_len, frame_shift, mel_bank, n_mels, upscale, preemph,
+                                                                    out);
+  } else {
+    fbank_kernel<<<grid, kFbankWarps * 32, 0, (cudaStream_t)stream>>>(
+        wave, cu_samples, cu_frames, batch, total_frames, window, frame_len, frame_shift, nfft, log2n,
+        mel_bank, n_mels, upscale, preemph, out);
+  }
   FB_CHECK_LAUNCH("fbank");
   return FB200_OK;
 }

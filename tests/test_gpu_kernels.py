@@ -48,6 +48,22 @@ def test_fbank_matches_oracle(window):
         o += f
 
 
+def test_fbank_generic_fft_size_matches_oracle():
+    """8 kHz: 200-sample frames, 256-point FFT -- the generic radix-2 kernel (the 512-point one is specialised)."""
+    lens = [200, 4000, 9999]
+    waves = [synth.synth_waveform(40 + i, n) for i, n in enumerate(lens)]
+    packed = torch.from_numpy(np.concatenate(waves)).to(DEV)
+    frames = [tables.num_frames(n, 200, 80) for n in lens]
+    out = ops.fbank(packed, cu(lens, torch.int64), cu(frames), sum(frames), tables.feature_window("hamming", 200).to(DEV),
+                    tables.mel_filterbank(80, 256, 8000.0).to(DEV), frame_shift=80, nfft=256)
+    o = 0
+    for w, f in zip(waves, frames):
+        ref = O.kaldi_fbank(torch.from_numpy(w) * 32768.0, fs=8000)
+        assert ref.shape[0] == f
+        assert rel(out[o: o + f], ref) < 1e-4
+        o += f
+
+
 def test_lfr_cmvn_matches_oracle_bit_exact():
     frames = [1, 5, 6, 7, 201, 998]
     g = torch.Generator().manual_seed(0)
