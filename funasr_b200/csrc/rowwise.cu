@@ -107,7 +107,7 @@ __global__ void split_rows_kernel(const float* __restrict__ x, int ld_x, int row
   }
 }
 
-constexpr int kFsmnRows = 64;    // output rows per CTA: 18944 rows = 296 CTAs = two per SM, one wave
+constexpr int kFsmnRows = 64;    // output rows per CTA at most: 18944 rows = 296 CTAs = two per SM, one wave
 constexpr int kFsmnMaxK = 32;
 constexpr int kFsmnBlock = 8;    // rows per ring stage
 constexpr int kFsmnStages = 3;   // ring depth: 3 x (8 input rows + 8 residual rows) x 2 KB = 96 KB per CTA
@@ -126,15 +126,15 @@ template <int KS>
 __global__ void __launch_bounds__(kFsmnThreads)
 fsmn_stream_kernel(const float* __restrict__ v, int ld_v, const int32_t* __restrict__ cu_rows, int batch,
                    int total_rows, int dim, const float* __restrict__ weight, const float* __restrict__ res,
-                   int ld_res, float* __restrict__ out, int ld_out) {
+                   int ld_res, float* __restrict__ out, int ld_out, int cta_rows) {
   constexpr int LEFT = (KS - 1) / 2;
   constexpr uint32_t FULL = (1u << KS) - 1u;
   extern __shared__ __align__(128) uint8_t fsmn_smem[];
   __shared__ uint32_t s_mask[kFsmnRows];  // bit j: tap j of this output row lies inside its sequence
   __shared__ __align__(8) uint64_t s_bar[2 * kFsmnStages];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int r0 = blockIdx.x * kFsmnRows, c0 = blockIdx.y * kFsmnCols;
-  const int nrows = min(kFsmnRows, total_rows - r0);
+  const int r0 = blockIdx.x * cta_rows, c0 = blockIdx.y * kFsmnCols;
+  const int nrows = min(cta_rows, total_rows - r0);
   const int ncols = min(kFsmnCols, dim - c0);
   const uint32_t row_bytes = (uint32_t)ncols * 4u;
   const int nblocks = (nrows + KS - 1 + kFsmnBlock - 1) / kFsmnBlock;
@@ -421,9 +421,14 @@ extern "C" __attribute__((visibility("default"))) int fb200_fsmn(const float* v,
       }
       attr_set = true;
     }
-    const dim3 grid((total_rows + kFsmnRows - 1) / kFsmnRows, (dim + kFsmnCols - 1) / kFsmnCols);
+    // rows per CTA: 64 when that fills the GPU (two CTAs per SM), fewer for small batches (a CTA walks its rows
+    // serially, so short walks are what keeps a small launch short; the halo re-read grows to (rows + 10) / rows)
+    int cta_rows = (total_rows + 2 * 148 - 1) / (2 * 148);
+    cta_rows = (cta_rows + kFsmnBlock - 1) / kFsmnBlock * kFsmnBlock;
+    cta_rows = cta_rows < 16 ? 16 : (cta_rows > kFsmnRows ? kFsmnRows : cta_rows);
+    const dim3 grid((total_rows + cta_rows - 1) / cta_rows, (dim + kFsmnCols - 1) / kFsmnCols);
     fsmn_stream_kernel<11><<<grid, kFsmnThreads, kFsmnSmemBytes, (cudaStream_t)stream>>>(
-        v, ld_v, cu_rows, batch, total_rows, dim, weight, residual, ld_res, out, ld_out);
+        v, ld_v, cu_rows, batch, total_rows, dim, weight, residual, ld_res, out, ld_out, cta_rows);
   }
   else
     fsmn_generic_kernel<<<total_rows, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight,

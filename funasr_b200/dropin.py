@@ -5,6 +5,7 @@ Each class keeps the reference class's name, constructor keywords, `forward` sig
 tuple and state_dict keys, so `AutoModel(model="Paraformer", ...)` builds them
 by string key and `load_pretrained_model(strict=True)` loads a reference checkpoint unchanged:
 
+    Paraformer             funasr/models/paraformer/model.py:30-596 (`inference` only: one packed engine call)
     WavFrontend            funasr/frontends/wav_frontend.py:78-158
     SANMEncoder            funasr/models/sanm/encoder.py:188-430
     CifPredictorV2         funasr/models/paraformer/cif_predictor.py:172-253
@@ -351,6 +352,171 @@ class ParaformerSANMDecoder(_ParamTree):
         return out, torch.as_tensor(toks, dtype=torch.int64, device=dev)
 
 
+def _as_waveforms(data_in, data_lengths, fs: int, kwargs) -> List["np.ndarray"]:
+    """The waveforms of one `inference` call as 1-D float32 host arrays.  Arrays / tensors (what
+    `AutoModel.generate(input=ndarray)` and the VAD segment batching of
+    funasr/auto/auto_model.py:423-459 pass) are taken as they are; anything else (paths, urls, bytes,
+    kaldi ark) goes through the host application's own loader, funasr/utils/load_utils.py:32-111."""
+    import numpy as np
+
+    def one(x):
+        if isinstance(x, torch.Tensor):
+            x = x.detach().cpu().numpy()
+        if isinstance(x, np.ndarray):
+            return np.ascontiguousarray(x.reshape(-1), dtype=np.float32)
+        return None
+
+    if isinstance(data_in, torch.Tensor) and data_in.dim() == 2:
+        lens = _lengths_list(data_lengths) if data_lengths is not None else [data_in.shape[1]] * data_in.shape[0]
+        return [one(data_in[i, :n]) for i, n in enumerate(lens)]
+    items = list(data_in) if isinstance(data_in, (list, tuple)) else [data_in]
+    waves = [one(x) for x in items]
+    if all(w is not None for w in waves):
+        return waves
+    try:
+        from funasr.utils.load_utils import load_audio_text_image_video  # noqa: WPS433 (host application)
+    except ImportError as e:
+        raise TypeError("funasr_b200.Paraformer.inference: input is neither an array nor a tensor, and the "
+                        "reference's loader (funasr.utils.load_utils) is not importable") from e
+    loaded = load_audio_text_image_video(data_in, fs=fs, audio_fs=kwargs.get("fs", 16000),
+                                         data_type=kwargs.get("data_type", "sound"), tokenizer=kwargs.get("tokenizer"))
+    return [one(x) for x in (loaded if isinstance(loaded, (list, tuple)) else [loaded])]
+
+
+class ParaformerInference:
+    """`Paraformer.inference` (funasr/models/paraformer/model.py:443-596) as ONE call into the packed
+    engine: no padded tensors, no per-utterance device->host reads, no Python loop over frames.  Mixed
+    into the reference's own `Paraformer` by `install()` (so construction, checkpoints and training are
+    the reference's), or into the stand-alone `Paraformer` below.  Returns the reference's
+    `(results, meta_data)`; `[]` when no utterance has a token (model.py:514-515).  Beam search / LM /
+    CTC rescoring, fbank inputs and timestamps are not on this path: those calls go to the reference
+    method when there is one."""
+
+    _fb200_engine = None
+    _fb200_engine_key = None
+
+    def _engine_for(self, frontend) -> engine.ParaformerEngine:
+        dev = next(self.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("funasr_b200.Paraformer: the model lives on %s -- this path runs on a CUDA device only "
+                               "(no CPU fallback); build the model with device='cuda'" % dev)
+        key = (tuple((p.data_ptr(), p._version) for p in self.parameters()), str(dev), PRECISION,
+               getattr(frontend, "cmvn_file", None), getattr(frontend, "window", "hamming"))
+        if self._fb200_engine is None or self._fb200_engine_key != key:
+            sd = {k: v.detach() for k, v in self.state_dict().items()}
+            self._fb200_engine = engine.ParaformerEngine(sd, dev, precision=PRECISION, cmvn=getattr(frontend, "cmvn", None),
+                                                         window=getattr(frontend, "window", "hamming"))
+            self._fb200_engine_key = key
+        return self._fb200_engine
+
+    def inference(self, data_in, data_lengths=None, key: list = None, tokenizer=None, frontend=None, **kwargs):
+        import time
+
+        off_path = (kwargs.get("decoding_ctc_weight", 0.0) > 0.00001 and getattr(self, "ctc", None) is not None) or (
+            kwargs.get("lm_weight", 0.0) > 0.00001 and kwargs.get("lm_file") is not None) or kwargs.get(
+            "pred_timestamp", False) or kwargs.get("data_type", "sound") == "fbank" or getattr(self, "beam_search", None) is not None
+        if off_path:
+            ref = getattr(super(), "inference", None)
+            if ref is None:
+                raise NotImplementedError("funasr_b200.Paraformer.inference: beam search / LM / CTC rescoring, fbank input "
+                                          "and timestamps are outside the accelerated path")
+            return ref(data_in, data_lengths=data_lengths, key=key, tokenizer=tokenizer, frontend=frontend, **kwargs)
+        meta_data = {}
+        t1 = time.perf_counter()
+        waves = _as_waveforms(data_in, data_lengths, frontend.fs, dict(kwargs, tokenizer=tokenizer))
+        t2 = time.perf_counter()
+        meta_data["load_data"] = f"{t2 - t1:0.3f}"
+        eng = self._engine_for(frontend)
+        ids, scores = eng.recognize(waves, with_scores=True)
+        t3 = time.perf_counter()
+        meta_data["extract_feat"] = f"{t3 - t2:0.3f}"  # here: the whole device path (the reference times fbank alone)
+        _, rows = eng.frontend.plan([len(w) for w in waves])
+        meta_data["batch_data_time"] = sum(rows) * frontend.frame_shift * frontend.lfr_n / 1000
+        if not any(eng.last_token_num):
+            return []
+        b = len(waves)
+        key = list(key) if key is not None else ["utt%d" % i for i in range(b)]
+        if key and isinstance(key[0], (list, tuple)):
+            key = list(key[0])
+        if len(key) < b:
+            key = key * b
+        writer = None
+        if kwargs.get("output_dir") is not None:
+            if not hasattr(self, "writer"):
+                from funasr.utils.datadir_writer import DatadirWriter  # noqa: WPS433 (host application)
+
+                self.writer = DatadirWriter(kwargs.get("output_dir"))
+            writer = self.writer["1best_recog"]
+        results = []
+        for i in range(b):
+            token_int = ids[i]  # blank / sos / eos already dropped (model.py:561-565)
+            if tokenizer is None:
+                results.append({"key": key[i], "token_int": token_int})
+                continue
+            token = tokenizer.ids2tokens(token_int)
+            text = tokenizer.tokens2text(token)
+            if not hasattr(tokenizer, "bpemodel"):
+                try:
+                    from funasr.utils import postprocess_utils  # noqa: WPS433 (host application; text only)
+
+                    text, _ = postprocess_utils.sentence_postprocess(token)
+                except ImportError:
+                    pass
+            results.append({"key": key[i], "text": text})
+            if writer is not None:
+                writer["token"][key[i]] = " ".join(token)
+                writer["text"][key[i]] = text
+        return results, meta_data
+
+
+class _CTCHead(_ParamTree):
+    """`ctc.ctc_lo` of funasr/models/ctc/ctc.py:27-33: present in checkpoints trained with ctc_weight > 0."""
+
+    def __init__(self, odim: int, encoder_output_size: int, **kwargs):
+        super().__init__()
+        self._declare({"ctc_lo.weight": (odim, encoder_output_size), "ctc_lo.bias": (odim,)}, "")
+
+
+class Paraformer(ParaformerInference, nn.Module):
+    """Stand-alone `Paraformer` (funasr/models/paraformer/model.py:30-175) for hosts without the reference
+    package: same constructor keywords, sub-module names (`encoder`, `predictor`, `decoder`, `ctc`) and
+    therefore state_dict keys; inference only (`forward`, the training loss, is the reference's business)."""
+
+    def __init__(self, specaug=None, specaug_conf=None, normalize=None, normalize_conf=None, encoder: str = None,
+                 encoder_conf: Optional[Dict] = None, decoder: str = None, decoder_conf: Optional[Dict] = None,
+                 ctc: str = None, ctc_conf: Optional[Dict] = None, predictor: str = None,
+                 predictor_conf: Optional[Dict] = None, ctc_weight: float = 0.5, input_size: int = 80,
+                 vocab_size: int = -1, ignore_id: int = -1, blank_id: int = 0, sos: int = 1, eos: int = 2,
+                 lsm_weight: float = 0.0, length_normalized_loss: bool = False, predictor_weight: float = 0.0,
+                 predictor_bias: int = 0, sampling_ratio: float = 0.2, share_embedding: bool = False,
+                 use_1st_decoder_loss: bool = False, **kwargs):
+        super().__init__()
+        if share_embedding:
+            raise NotImplementedError("funasr_b200.Paraformer: share_embedding is a training-time option")
+
+        def lookup(table, name):
+            cls = DROPIN_CLASSES.get((table, name))
+            if cls is None:
+                raise NotImplementedError("funasr_b200.Paraformer: no drop-in for %s[%s]" % (table, name))
+            return cls
+
+        self.encoder = lookup("encoder_classes", encoder)(input_size=input_size, **(encoder_conf or {}))
+        self.decoder = None
+        if decoder is not None and ctc_weight != 1.0:
+            self.decoder = lookup("decoder_classes", decoder)(vocab_size=vocab_size, encoder_output_size=self.encoder.output_size(),
+                                                              **(decoder_conf or {}))
+        self.ctc = _CTCHead(vocab_size, self.encoder.output_size(), **(ctc_conf or {})) if ctc_weight > 0.0 else None
+        self.predictor = lookup("predictor_classes", predictor)(**(predictor_conf or {}))
+        self.blank_id, self.vocab_size, self.ignore_id, self.ctc_weight = blank_id, vocab_size, ignore_id, ctc_weight
+        self.sos = sos if sos is not None else vocab_size - 1
+        self.eos = eos if eos is not None else vocab_size - 1
+        self.predictor_weight, self.predictor_bias, self.sampling_ratio = predictor_weight, predictor_bias, sampling_ratio
+        self.beam_search = None
+
+    def forward(self, *args, **kwargs):
+        raise NotImplementedError("funasr_b200.Paraformer: the training forward is not part of the accelerated path")
+
+
 DROPIN_CLASSES = {
     ("frontend_classes", "WavFrontend"): WavFrontend,
     ("frontend_classes", "wav_frontend"): WavFrontend,
@@ -358,7 +524,22 @@ DROPIN_CLASSES = {
     ("encoder_classes", "SenseVoiceEncoderSmall"): SenseVoiceEncoderSmall,
     ("predictor_classes", "CifPredictorV2"): CifPredictorV2,
     ("decoder_classes", "ParaformerSANMDecoder"): ParaformerSANMDecoder,
+    ("model_classes", "Paraformer"): Paraformer,
 }
+
+
+def _model_class(key: str, cls):
+    """The class registered under model_classes[key]: the reference's own class with `inference` replaced
+    when the reference is importable (construction, checkpoints and training stay the reference's), else the
+    stand-alone class."""
+    if cls is Paraformer:
+        try:
+            from funasr.models.paraformer.model import Paraformer as ref_cls  # noqa: WPS433
+        except ImportError:
+            return cls
+        return type("Paraformer", (ParaformerInference, ref_cls), {"__doc__": ParaformerInference.__doc__,
+                                                                    "__module__": __name__})
+    return cls
 
 
 def install(tables_obj=None) -> List[str]:
@@ -368,6 +549,6 @@ def install(tables_obj=None) -> List[str]:
         from funasr.register import tables as tables_obj  # noqa: WPS433 (the host application's registry)
     done = []
     for (table, key), cls in DROPIN_CLASSES.items():
-        getattr(tables_obj, table)[key] = cls
+        getattr(tables_obj, table)[key] = _model_class(key, cls) if table == "model_classes" else cls
         done.append("%s[%s]" % (table, key))
     return done

@@ -377,6 +377,7 @@ class ParaformerEngine:
         self.nparts = self.PRECISIONS[precision]
         self.max_rows = max_rows
         self._copy_stream = None
+        self.last_token_num: List[int] = []
         self._drop_ids = np.array(sorted(self.DROP_IDS), dtype=np.int32)
         with torch.cuda.device(self.device):
             self.frontend = FrontendPack(self.device, cmvn=cmvn, window=window)
@@ -440,6 +441,7 @@ class ParaformerEngine:
         with no predicted token give [] (model.py:514-515)."""
         results: List[List[int]] = [[] for _ in waves]
         scores = [0.0 for _ in waves]
+        self.last_token_num = [0 for _ in waves]  # predicted token counts of the last call (before id filtering)
         lens_all = [int(w.shape[0]) for w in waves]
         batches = self.plan_batches(lens_all)
         if not batches:
@@ -470,6 +472,7 @@ class ParaformerEngine:
                 keep = ~np.isin(ids_h, self._drop_ids)
                 o = 0
                 for i, n in zip(batch, tok):
+                    self.last_token_num[i] = int(n)
                     results[i] = ids_h[o: o + n][keep[o: o + n]].tolist()
                     if with_scores:
                         scores[i] = float(logp_h[o: o + n].sum())

@@ -68,7 +68,8 @@ def test_registers_into_reference_tables_and_loads_reference_checkpoint(tmp_path
     cfg["decoder_conf"]["att_layer_num"] = 2
     ref = AutoModel(**cfg, device="cpu", disable_update=True, disable_pbar=True)
     ref_sd = ref.model.state_dict()
-    saved = {k: dict(getattr(tables, k)) for k in ("frontend_classes", "encoder_classes", "predictor_classes", "decoder_classes")}
+    saved = {k: dict(getattr(tables, k)) for k in ("frontend_classes", "encoder_classes", "predictor_classes", "decoder_classes",
+                                                   "model_classes")}
     try:
         done = dropin.install()
         assert "encoder_classes[SANMEncoder]" in done
@@ -78,6 +79,10 @@ def test_registers_into_reference_tables_and_loads_reference_checkpoint(tmp_path
         assert type(ours.model.predictor) is dropin.CifPredictorV2
         assert type(ours.kwargs["frontend"]) is dropin.WavFrontend
         assert ours.kwargs["frontend"].output_size() == 560
+        # model_classes["Paraformer"]: the reference's class with `inference` replaced by the packed engine call
+        from funasr.models.paraformer.model import Paraformer as RefParaformer
+        assert isinstance(ours.model, RefParaformer) and isinstance(ours.model, dropin.ParaformerInference)
+        assert type(ours.model).inference is dropin.ParaformerInference.inference
         mine = ours.model.state_dict()
         assert set(mine.keys()) == set(ref_sd.keys())
         assert all(mine[k].shape == ref_sd[k].shape for k in ref_sd)
@@ -90,7 +95,79 @@ def test_registers_into_reference_tables_and_loads_reference_checkpoint(tmp_path
             getattr(tables, k).update(v)
 
 
+MODEL = dict(encoder="SANMEncoder", encoder_conf=ENC, decoder="ParaformerSANMDecoder", decoder_conf=DEC,
+             predictor="CifPredictorV2", predictor_conf=PRED, ctc_weight=0.0, input_size=560, vocab_size=8404)
+
+
+class _Tokenizer:
+    """What `inference` needs of funasr/tokenizer/char_tokenizer.py: ids2tokens, tokens2text."""
+
+    def __init__(self):
+        self.token_list = synth.synth_token_list(8404)
+        self.bpemodel = None  # skips the reference's text post-processing (host side, not on the path)
+
+    def ids2tokens(self, ids):
+        return [self.token_list[i] for i in ids]
+
+    def tokens2text(self, tokens):
+        return " ".join(tokens)
+
+
+def test_standalone_model_has_the_reference_state_dict_and_fails_loudly_on_cpu():
+    model = dropin.Paraformer(**dict(MODEL, encoder_conf=dict(ENC, num_blocks=2), decoder_conf=dict(DEC, num_blocks=2, att_layer_num=2)))
+    want = params.paraformer_large_shapes(enc_blocks=2, dec_blocks=2)
+    assert {k: tuple(v.shape) for k, v in model.state_dict().items()} == dict(want)
+    with_ctc = dropin.Paraformer(**dict(MODEL, ctc_weight=0.3, encoder_conf=dict(ENC, num_blocks=1),
+                                        decoder_conf=dict(DEC, num_blocks=1, att_layer_num=1)))
+    assert tuple(with_ctc.state_dict()["ctc.ctc_lo.weight"].shape) == (8404, 512)
+    assert ("model_classes", "Paraformer") in dropin.DROPIN_CLASSES
+    frontend = dropin.WavFrontend(lfr_m=7, lfr_n=6, dither=0.0)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        model.inference([synth.synth_waveform(0, 16000)], key=["a"], tokenizer=None, frontend=frontend, device="cpu")
+    with pytest.raises(NotImplementedError):
+        model.inference([synth.synth_waveform(0, 16000)], key=["a"], frontend=frontend, pred_timestamp=True)
+
+
 # ---------------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+def test_model_inference_override_returns_the_reference_results(paraformer_sd, cmvn, tmp_path):
+    """`Paraformer.inference` (model.py:443-596) through the packed engine: results list + meta_data as the
+    reference returns them, token ids equal to the oracle's batch-1 recognition."""
+    from oracle import paraformer_oracle as O
+
+    dev = torch.device("cuda:0")
+    shift, scale = synth.synth_cmvn()
+    cmvn_file = str(tmp_path / "am.mvn")
+    synth.write_cmvn_file(cmvn_file, shift, scale)
+    frontend = dropin.WavFrontend(cmvn_file=cmvn_file, fs=16000, window="hamming", n_mels=80, frame_length=25,
+                                  frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0)
+    model = dropin.Paraformer(**MODEL).to(dev)
+    model.load_state_dict(paraformer_sd, strict=True)
+    lens = [48000, 16000 * 2 + 77, 300, 70000]  # the third is shorter than one frame
+    waves = [synth.synth_waveform(500 + i, n) for i, n in enumerate(lens)]
+    tok = _Tokenizer()
+    want = [O.recognize(torch.from_numpy(w), paraformer_sd, cmvn) if len(w) >= 400 else [] for w in waves]
+    # 1. a list of arrays with keys, no tokenizer -> token_int
+    results, meta = model.inference(waves, key=["a", "b", "c", "d"], tokenizer=None, frontend=frontend, device="cuda:0")
+    assert [r["key"] for r in results] == ["a", "b", "c", "d"]
+    assert [r["token_int"] for r in results] == want
+    rows = sum((1 + (n - 400) // 160 + 5) // 6 for n in lens if n >= 400)
+    assert meta["batch_data_time"] == pytest.approx(rows * 10 * 6 / 1000)
+    assert set(meta) == {"load_data", "extract_feat", "batch_data_time"}
+    # 2. a padded tensor + lengths (what extract_fbank's callers hold), tokenizer -> text
+    data = torch.nn.utils.rnn.pad_sequence([torch.from_numpy(w) for w in waves], batch_first=True)
+    results, _ = model.inference(data, data_lengths=torch.tensor(lens), key=[["a", "b", "c", "d"]], tokenizer=tok,
+                                 frontend=frontend, device="cuda:0")
+    assert [r["text"] for r in results] == [" ".join(tok.ids2tokens(w)) for w in want]
+    # 3. nothing recognisable -> [] (model.py:514-515)
+    assert model.inference([waves[2]], key=["c"], tokenizer=tok, frontend=frontend, device="cuda:0") == []
+    # 4. new weights are picked up (the engine's weight pack follows the parameters)
+    with torch.no_grad():
+        model.decoder.get_parameter("output_layer.bias").add_(torch.arange(8404, device=dev).float())
+    results, _ = model.inference([waves[0]], key=["a"], tokenizer=None, frontend=frontend, device="cuda:0")
+    assert results[0]["token_int"] and set(results[0]["token_int"]) == {8403}
+
+
 @pytest.mark.gpu
 def test_reference_call_sequence_through_dropin_modules_matches_oracle(paraformer_sd, cmvn, tmp_path):
     from oracle import paraformer_oracle as O
