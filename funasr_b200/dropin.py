@@ -6,6 +6,8 @@ tuple and state_dict keys, so `AutoModel(model="Paraformer", .
 by string key and `load_pretrained_model(strict=True)` loads a reference checkpoint unchanged:
 
     Paraformer             funasr/models/paraformer/model.py:30-596 (`inference` only: one packed engine call)
+    SenseVoiceSmall        funasr/models/sense_voice/model.py:588-906 (`inference` only)
+    SenseVoiceEncoderSmall funasr/models/sense_voice/model.py:444-585
     WavFrontend            funasr/frontends/wav_frontend.py:78-158
     SANMEncoder            funasr/models/sanm/encoder.py:188-430
     CifPredictorV2         funasr/models/paraformer/cif_predictor.py:172-253
@@ -517,6 +519,114 @@ class Paraformer(ParaformerInference, nn.Module):
         raise NotImplementedError("funasr_b200.Paraformer: the training forward is not part of the accelerated path")
 
 
+class SenseVoiceInference:
+    """`SenseVoiceSmall.inference` (funasr/models/sense_voice/model.py:809-906) as one call into the packed
+    engine: query rows, 50 + 20 SAN-M layers, CTC projection, per-frame argmax, unique_consecutive and blank
+    removal all stay on the device; the host gets token ids.  Returns the reference's `(results, meta_data)`.
+    `output_timestamp` (forced alignment) and fbank inputs go to the reference method when there is one."""
+
+    _fb200_engine = None
+    _fb200_engine_key = None
+    LID = engine.SenseVoiceEngine.LID
+    TEXTNORM = engine.SenseVoiceEngine.TEXTNORM
+    EMO_UNK = 25009  # emo_dict["unk"], model.py:649-655
+
+    def _engine_for(self, frontend) -> engine.SenseVoiceEngine:
+        dev = next(self.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("funasr_b200.SenseVoiceSmall: the model lives on %s -- this path runs on a CUDA device "
+                               "only (no CPU fallback); build the model with device='cuda'" % dev)
+        key = (tuple((p.data_ptr(), p._version) for p in self.parameters()), str(dev), PRECISION,
+               getattr(frontend, "cmvn_file", None), getattr(frontend, "window", "hamming"))
+        if self._fb200_engine is None or self._fb200_engine_key != key:
+            sd = {k: v.detach() for k, v in self.state_dict().items()}
+            self._fb200_engine = engine.SenseVoiceEngine(sd, dev, precision=PRECISION, cmvn=getattr(frontend, "cmvn", None),
+                                                         window=getattr(frontend, "window", "hamming"),
+                                                         blank_id=getattr(self, "blank_id", 0))
+            self._fb200_engine_key = key
+        return self._fb200_engine
+
+    def inference(self, data_in, data_lengths=None, key: list = ("wav_file_tmp_name",), tokenizer=None, frontend=None,
+                  **kwargs):
+        import time
+
+        if kwargs.get("output_timestamp", False) or kwargs.get("data_type", "sound") == "fbank":
+            ref = getattr(super(), "inference", None)
+            if ref is None:
+                raise NotImplementedError("funasr_b200.SenseVoiceSmall.inference: timestamps (forced alignment) and "
+                                          "fbank input are outside the accelerated path")
+            return ref(data_in, data_lengths=data_lengths, key=key, tokenizer=tokenizer, frontend=frontend, **kwargs)
+        meta_data = {}
+        t1 = time.perf_counter()
+        waves = _as_waveforms(data_in, data_lengths, frontend.fs, dict(kwargs, tokenizer=tokenizer))
+        t2 = time.perf_counter()
+        meta_data["load_data"] = f"{t2 - t1:0.3f}"
+        language = kwargs.get("language", "auto")
+        language = language if language in self.LID else "auto"  # unknown names fall back to id 0 (model.py:853-855)
+        textnorm = kwargs.get("text_norm", None)
+        if textnorm is None:
+            textnorm = "withitn" if kwargs.get("use_itn", False) else "woitn"
+        if textnorm not in self.TEXTNORM:
+            raise KeyError(textnorm)
+        eng = self._engine_for(frontend)
+        ban = (self.EMO_UNK,) if kwargs.get("ban_emo_unk", False) else ()
+        ids = eng.recognize(waves, language=language, textnorm=textnorm, ban_ids=ban)
+        t3 = time.perf_counter()
+        meta_data["extract_feat"] = f"{t3 - t2:0.3f}"  # here: the whole device path
+        _, rows = eng.frontend.plan([len(w) for w in waves])
+        meta_data["batch_data_time"] = sum(rows) * frontend.frame_shift * frontend.lfr_n / 1000
+        b = len(waves)
+        key = list(key)
+        if key and isinstance(key[0], (list, tuple)):
+            key = list(key[0])
+        if len(key) < b:
+            key = key * b
+        writer = None
+        if kwargs.get("output_dir") is not None:
+            if not hasattr(self, "writer"):
+                from funasr.utils.datadir_writer import DatadirWriter  # noqa: WPS433 (host application)
+
+                self.writer = DatadirWriter(kwargs.get("output_dir"))
+            writer = self.writer["1best_recog"]
+        results = []
+        for i in range(b):
+            if tokenizer is None:
+                results.append({"key": key[i], "token_int": ids[i]})
+                continue
+            text = tokenizer.decode(ids[i])
+            if writer is not None:
+                writer["text"][key[i]] = text
+            results.append({"key": key[i], "text": text})
+        return results, meta_data
+
+
+class SenseVoiceSmall(SenseVoiceInference, nn.Module):
+    """Stand-alone `SenseVoiceSmall` (funasr/models/sense_voice/model.py:588-660) for hosts without the
+    reference package: same constructor keywords and state_dict keys (`encoder.*`, `ctc.ctc_lo.*`,
+    `embed.weight`); inference only."""
+
+    def __init__(self, specaug=None, specaug_conf=None, normalize=None, normalize_conf=None, encoder: str = None,
+                 encoder_conf: Optional[Dict] = None, ctc_conf: Optional[Dict] = None, input_size: int = 80,
+                 vocab_size: int = -1, ignore_id: int = -1, blank_id: int = 0, sos: int = 1, eos: int = 2,
+                 length_normalized_loss: bool = False, **kwargs):
+        super().__init__()
+        cls = DROPIN_CLASSES.get(("encoder_classes", encoder))
+        if cls is None:
+            raise NotImplementedError("funasr_b200.SenseVoiceSmall: no drop-in for encoder_classes[%s]" % encoder)
+        self.encoder = cls(input_size=input_size, **(encoder_conf or {}))
+        self.encoder_output_size = self.encoder.output_size()
+        self.ctc = _CTCHead(vocab_size, self.encoder_output_size, **(ctc_conf or {}))
+        self.blank_id, self.vocab_size, self.ignore_id = blank_id, vocab_size, ignore_id
+        self.sos = sos if sos is not None else vocab_size - 1
+        self.eos = eos if eos is not None else vocab_size - 1
+        self.lid_dict, self.textnorm_dict = dict(self.LID), dict(self.TEXTNORM)
+        self.emo_dict = {"unk": 25009, "happy": 25001, "sad": 25002, "angry": 25003, "neutral": 25004}
+        self.embed = nn.Embedding(7 + len(self.lid_dict) + len(self.textnorm_dict), input_size)
+
+    def forward(self, *args, **kwargs):
+        raise NotImplementedError("funasr_b200.SenseVoiceSmall: the training forward is not part of the accelerated path")
+
+
 DROPIN_CLASSES = {
     ("frontend_classes", "WavFrontend"): WavFrontend,
     ("frontend_classes", "wav_frontend"): WavFrontend,
@@ -525,6 +635,7 @@ DROPIN_CLASSES = {
     ("predictor_classes", "CifPredictorV2"): CifPredictorV2,
     ("decoder_classes", "ParaformerSANMDecoder"): ParaformerSANMDecoder,
     ("model_classes", "Paraformer"): Paraformer,
+    ("model_classes", "SenseVoiceSmall"): SenseVoiceSmall,
 }
 
 
@@ -539,6 +650,13 @@ def _model_class(key: str, cls):
             return cls
         return type("Paraformer", (ParaformerInference, ref_cls), {"__doc__": ParaformerInference.__doc__,
                                                                     "__module__": __name__})
+    if cls is SenseVoiceSmall:
+        try:
+            from funasr.models.sense_voice.model import SenseVoiceSmall as ref_sv  # noqa: WPS433
+        except ImportError:
+            return cls
+        return type("SenseVoiceSmall", (SenseVoiceInference, ref_sv), {"__doc__": SenseVoiceInference.__doc__,
+                                                                        "__module__": __name__})
     return cls
 
 

@@ -513,6 +513,18 @@ class SenseVoiceEngine:
             self.ctc = _Linear(state_dict["ctc.ctc_lo.weight"], state_dict["ctc.ctc_lo.bias"], self.nparts, self.device)
             self.embed = _dev(state_dict["embed.weight"], self.device)
         self._prompts: Dict[Tuple[str, str], torch.Tensor] = {}
+        self._ban_bias: Dict[Tuple[int, ...], torch.Tensor] = {}
+
+    def _bias(self, ban_ids: Sequence[int]) -> torch.Tensor:
+        """CTC bias with -inf at the banned ids (`ban_emo_unk`, model.py:886-887: the id can never win the argmax)."""
+        key = tuple(sorted(int(i) for i in ban_ids))
+        if not key:
+            return self.ctc.bias
+        if key not in self._ban_bias:
+            b = self.ctc.bias.clone()
+            b[torch.tensor(key, device=self.device)] = float("-inf")
+            self._ban_bias[key] = b
+        return self._ban_bias[key]
 
     def prompt(self, language: str = "auto", textnorm: str = "woitn") -> torch.Tensor:
         """[language, event, emotion, text-norm] rows of the query embedding, [4, 560] on the device."""
@@ -523,7 +535,7 @@ class SenseVoiceEngine:
         return self._prompts[key]
 
     def forward_packed(self, wave: torch.Tensor, lens: Sequence[int], language: str = "auto", textnorm: str = "woitn",
-                       taps: Optional[dict] = None):
+                       taps: Optional[dict] = None, ban_ids: Sequence[int] = ()):
         """Device-resident packed waveforms -> (token ids i32 packed at cu_rows, counts i32 [B], cu_rows, rows)."""
         with torch.cuda.device(self.device):
             scale = float(self.encoder.d) ** 0.5
@@ -533,11 +545,12 @@ class SenseVoiceEngine:
             r, v = enc.shape[0], self.ctc.n
             enc_split = ops.split_rows(enc, self.nparts)
             frame_ids = torch.empty(r, dtype=torch.int32, device=self.device)
+            bias = self._bias(ban_ids)
             ld = (v + 3) // 4 * 4
             logits = torch.empty(min(r, self.LOGIT_ROWS), ld, dtype=torch.float32, device=self.device)
             for r0 in range(0, r, self.LOGIT_ROWS):
                 n = min(self.LOGIT_ROWS, r - r0)
-                ops.gemm(enc_split[r0: r0 + n], self.nparts, self.ctc.w, self.nparts, n, v, self.ctc.k, bias=self.ctc.bias,
+                ops.gemm(enc_split[r0: r0 + n], self.nparts, self.ctc.w, self.nparts, n, v, self.ctc.k, bias=bias,
                          out_f32=logits[:n])
                 ops.argmax_logprob(logits[:n], v, frame_ids[r0: r0 + n], rows=n)
             out_ids = torch.empty(r, dtype=torch.int32, device=self.device)
@@ -547,7 +560,8 @@ class SenseVoiceEngine:
                 taps.update(feats=feats, enc=enc, frame_ids=frame_ids, cu_rows=cu_rows, rows=rows)
             return out_ids, out_len, cu_rows, rows
 
-    def recognize(self, waves: Sequence[np.ndarray], language: str = "auto", textnorm: str = "woitn") -> List[List[int]]:
+    def recognize(self, waves: Sequence[np.ndarray], language: str = "auto", textnorm: str = "woitn",
+                  ban_ids: Sequence[int] = ()) -> List[List[int]]:
         """CTC-greedy token ids per utterance (blank dropped).  Utterances shorter than one frame give []."""
         results: List[List[int]] = [[] for _ in waves]
         lens_all = [int(w.shape[0]) for w in waves]
@@ -574,7 +588,7 @@ class SenseVoiceEngine:
                     src = torch.from_numpy(waves[i]) if isinstance(waves[i], np.ndarray) else waves[i]
                     wave[o: o + n].copy_(src, non_blocking=True)
                     o += n
-                ids, counts, cu_rows, _ = self.forward_packed(wave, lens, language, textnorm)
+                ids, counts, cu_rows, _ = self.forward_packed(wave, lens, language, textnorm, ban_ids=ban_ids)
                 ids_h, cnt_h, cu_h = ids.cpu().numpy(), counts.cpu().numpy(), cu_rows.cpu().numpy()
                 for j, i in enumerate(batch):
                     results[i] = ids_h[cu_h[j]: cu_h[j] + cnt_h[j]].tolist()

@@ -264,3 +264,81 @@ def test_sensevoice_call_sequence_through_dropin_encoder_matches_golden(sensevoi
         logp = torch.log_softmax(torch.nn.functional.linear(encoder_out[0], w_ctc, b_ctc), dim=-1)
         yseq = torch.unique_consecutive(logp.argmax(-1))
         assert yseq[yseq != 0].tolist() == g["ids_%d" % ci].tolist()
+
+
+SV_MODEL = dict(encoder="SenseVoiceEncoderSmall", encoder_conf=SV_ENC, input_size=560, vocab_size=25055)
+
+
+class _SvTokenizer:
+    """What SenseVoiceSmall.inference needs of the sentencepiece tokenizer: decode(list) -> str."""
+
+    def decode(self, ids):
+        return " ".join("t%d" % i for i in ids)
+
+
+def test_standalone_sensevoice_model_has_the_reference_state_dict():
+    model = dropin.SenseVoiceSmall(**dict(SV_MODEL, encoder_conf=dict(SV_ENC, num_blocks=2, tp_blocks=1)))
+    want = params.sense_voice_small_shapes(enc_blocks=2, tp_blocks=1)
+    assert {k: tuple(v.shape) for k, v in model.state_dict().items()} == dict(want)
+    assert ("model_classes", "SenseVoiceSmall") in dropin.DROPIN_CLASSES
+    frontend = dropin.WavFrontend(lfr_m=7, lfr_n=6, dither=0.0)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        model.inference([synth.synth_waveform(0, 16000)], key=["a"], tokenizer=_SvTokenizer(), frontend=frontend)
+    with pytest.raises(NotImplementedError):
+        model.inference([synth.synth_waveform(0, 16000)], key=["a"], frontend=frontend, output_timestamp=True)
+
+
+@pytest.mark.skipif(not reference_available(), reason="reference tree not present (GPU box)")
+def test_install_wraps_the_reference_model_classes():
+    from ref_loader import import_reference
+
+    import_reference()
+    from funasr.models.sense_voice.model import SenseVoiceSmall as RefSenseVoice
+    from funasr.register import tables
+
+    saved = {k: dict(getattr(tables, k)) for k in ("frontend_classes", "encoder_classes", "predictor_classes", "decoder_classes",
+                                                   "model_classes")}
+    try:
+        dropin.install()
+        cls = tables.model_classes["SenseVoiceSmall"]
+        assert issubclass(cls, RefSenseVoice) and issubclass(cls, dropin.SenseVoiceInference)
+        assert cls.inference is dropin.SenseVoiceInference.inference
+        model = cls(**dict(SV_MODEL, encoder_conf=dict(SV_ENC, num_blocks=2, tp_blocks=1)))
+        assert type(model.encoder) is dropin.SenseVoiceEncoderSmall  # built through the (re-registered) tables
+        want = params.sense_voice_small_shapes(enc_blocks=2, tp_blocks=1)
+        assert {k: tuple(v.shape) for k, v in model.state_dict().items()} == dict(want)
+    finally:
+        for k, v in saved.items():
+            getattr(tables, k).clear()
+            getattr(tables, k).update(v)
+
+
+@pytest.mark.gpu
+def test_sensevoice_model_inference_override_matches_golden(sensevoice_sd, golden_dir, tmp_path):
+    """`SenseVoiceSmall.inference` (sense_voice/model.py:809-906) through the packed engine: token ids of the
+    reference's own run (tests/golden/sensevoice.npz), decoded by the tokenizer it is handed."""
+    dev = torch.device("cuda:0")
+    g = np.load(os.path.join(golden_dir, "sensevoice.npz"))
+    shift, scale = synth.synth_cmvn()
+    cmvn_file = str(tmp_path / "am.mvn")
+    synth.write_cmvn_file(cmvn_file, shift, scale)
+    frontend = dropin.WavFrontend(cmvn_file=cmvn_file, fs=16000, window="hamming", n_mels=80, frame_length=25,
+                                  frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0)
+    model = dropin.SenseVoiceSmall(**SV_MODEL).to(dev)
+    model.load_state_dict(sensevoice_sd, strict=True)
+    tok = _SvTokenizer()
+    names = {0: "auto", 4: "en"}
+    for ci in (0, 1):
+        ui, n, lang, itn = (int(v) for v in g["case_%d" % ci])
+        wave = synth.synth_waveform(ui, n)
+        results, meta = model.inference([wave], key=["k%d" % ci], tokenizer=tok, frontend=frontend, device="cuda:0",
+                                        language=names[lang], use_itn=bool(itn))
+        assert results == [{"key": "k%d" % ci, "text": tok.decode(g["ids_%d" % ci].tolist())}]
+        assert meta["batch_data_time"] == pytest.approx(((1 + (n - 400) // 160 + 5) // 6) * 0.06)
+    # ban_emo_unk (model.py:886-887): the banned id never appears; banning the most frequent id changes the result
+    ui, n, lang, itn = (int(v) for v in g["case_0"])
+    wave = synth.synth_waveform(ui, n)
+    base = model._engine_for(frontend).recognize([wave])[0]
+    top = max(set(base), key=base.count)
+    banned = model._engine_for(frontend).recognize([wave], ban_ids=(top,))[0]
+    assert top not in banned and banned != base
