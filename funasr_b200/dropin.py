@@ -373,13 +373,15 @@ def _as_waveforms(data_in, data_lengths, fs: int, kwargs) -> List["np.ndarray"]:
         return [one(data_in[i, :n]) for i, n in enumerate(lens)]
     items = list(data_in) if isinstance(data_in, (list, tuple)) else [data_in]
     waves = [one(x) for x in items]
-    if all(w is not None for w in waves):
+    same_rate = int(kwargs.get("fs", 16000)) == int(fs)  # else the loader resamples (load_utils.py:91-96)
+    if all(w is not None for w in waves) and same_rate:
         return waves
     try:
         from funasr.utils.load_utils import load_audio_text_image_video  # noqa: WPS433 (host application)
     except ImportError as e:
-        raise TypeError("funasr_b200.Paraformer.inference: input is neither an array nor a tensor, and the "
-                        "reference's loader (funasr.utils.load_utils) is not importable") from e
+        raise TypeError("funasr_b200 inference: the input needs the reference's loader (file / url / bytes input, or "
+                        "resampling from fs=%s to %s), and funasr.utils.load_utils is not importable"
+                        % (kwargs.get("fs", 16000), fs)) from e
     loaded = load_audio_text_image_video(data_in, fs=fs, audio_fs=kwargs.get("fs", 16000),
                                          data_type=kwargs.get("data_type", "sound"), tokenizer=kwargs.get("tokenizer"))
     return [one(x) for x in (loaded if isinstance(loaded, (list, tuple)) else [loaded])]

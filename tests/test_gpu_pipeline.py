@@ -103,6 +103,31 @@ def test_multiple_batches_and_short_inputs(eng_fp32, paraformer_sd, cmvn):
         assert out[i] == ref, i
 
 
+def test_long_audio_config5(eng_fp32, paraformer_sd, cmvn):
+    """BASELINE configs[4]: long segments.  60 s and 120 s (T = 1000 / 2000 rows, 16 / 32 query tiles x 16 / 32 key tiles
+    per head) against the oracle; 600 s (T = 10 000 rows, more than half the row budget of a batch) through
+    batch-composition invariance: alone, and packed behind another utterance, it gives the same ids."""
+    w60, w120 = synth.synth_waveform(700, 16000 * 60), synth.synth_waveform(701, 16000 * 120)
+    taps = {}
+    wave, lens = eng_fp32.upload([w60, w120])
+    ids, _, tok = eng_fp32.forward_packed(wave, lens, taps=taps)
+    assert taps["rows"] == [1000, 2000]
+    o_enc, o_tok = 0, 0
+    for w, t, n in zip((w60, w120), taps["rows"], tok):
+        ref = {}
+        want = O.recognize(torch.from_numpy(w), paraformer_sd, cmvn, taps=ref)
+        assert rel(taps["enc"][o_enc: o_enc + t], ref["enc"]) < 1e-3
+        assert n == ref["token_num"]
+        got = ids[o_tok: o_tok + n].cpu().tolist()
+        assert [v for v in got if v not in (0, 1, 2)] == want
+        o_enc, o_tok = o_enc + t, o_tok + n
+    w600 = synth.synth_waveform(702, 16000 * 600)
+    alone = eng_fp32.recognize([w600])[0]
+    packed = eng_fp32.recognize([w60, w600])
+    assert len(alone) > 1000 and packed[1] == alone
+    assert packed[0] == eng_fp32.recognize([w60])[0]
+
+
 def test_bf16_mode_within_stated_tolerance(golden_dir, eng_bf16):
     g = np.load(os.path.join(golden_dir, "stages_10s.npz"))
     wave, lens = eng_bf16.upload([synth.synth_waveform(11, 160000)])
