@@ -115,6 +115,52 @@ def sense_voice_small_shapes(vocab_size: int = 25055, enc_blocks: int = 50, tp_b
     return s
 
 
+def conformer_encoder_shapes(input_size: int = 80, d: int = 256, linear_units: int = 2048, num_blocks: int = 12,
+                             cnn_kernel: int = 15, prefix: str = "encoder.") -> Shapes:
+    """ConformerEncoder (funasr/models/conformer/encoder.py:285-528) with the aishell recipe's options
+    (examples/aishell/conformer/conf/conformer_12e_6d_2048_256.yaml:16-31): conv2d input layer
+    (funasr/models/transformer/utils/subsampling.py:49-94), legacy rel-pos attention
+    (funasr/models/transformer/attention.py:221-312), macaron FFN pair, ConvolutionModule (encoder.py:53-120)."""
+    s: Shapes = OrderedDict()
+    f2 = ((input_size - 1) // 2 - 1) // 2
+    s[prefix + "embed.conv.0.weight"] = (d, 1, 3, 3)
+    s[prefix + "embed.conv.0.bias"] = (d,)
+    s[prefix + "embed.conv.2.weight"] = (d, d, 3, 3)
+    s[prefix + "embed.conv.2.bias"] = (d,)
+    _linear(s, prefix + "embed.out.0", d * f2, d)
+    for i in range(num_blocks):
+        p = prefix + "encoders.%d." % i
+        for name in ("linear_q", "linear_k", "linear_v", "linear_out"):
+            _linear(s, p + "self_attn." + name, d, d)
+        _linear(s, p + "self_attn.linear_pos", d, d, bias=False)
+        s[p + "self_attn.pos_bias_u"] = (4, d // 4)
+        s[p + "self_attn.pos_bias_v"] = (4, d // 4)
+        for ff in ("feed_forward", "feed_forward_macaron"):
+            _linear(s, p + ff + ".w_1", d, linear_units)
+            _linear(s, p + ff + ".w_2", linear_units, d)
+        s[p + "conv_module.pointwise_conv1.weight"] = (2 * d, d, 1)
+        s[p + "conv_module.pointwise_conv1.bias"] = (2 * d,)
+        s[p + "conv_module.depthwise_conv.weight"] = (d, 1, cnn_kernel)
+        s[p + "conv_module.depthwise_conv.bias"] = (d,)
+        _norm(s, p + "conv_module.norm", d)
+        s[p + "conv_module.norm.running_mean"] = (d,)
+        s[p + "conv_module.norm.running_var"] = (d,)
+        s[p + "conv_module.pointwise_conv2.weight"] = (d, d, 1)
+        s[p + "conv_module.pointwise_conv2.bias"] = (d,)
+        for name in ("norm_ff", "norm_mha", "norm_ff_macaron", "norm_conv", "norm_final"):
+            _norm(s, p + name, d)
+    _norm(s, prefix + "after_norm", d)
+    return s
+
+
+def conformer_ctc_shapes(vocab_size: int = 4234, num_blocks: int = 12, d: int = 256) -> Shapes:
+    """`model_classes["CTC"]` (funasr/models/ctc/model.py:17-72) over a ConformerEncoder -- BASELINE config 4."""
+    s = conformer_encoder_shapes(num_blocks=num_blocks, d=d)
+    s["ctc.ctc_lo.weight"] = (vocab_size, d)
+    s["ctc.ctc_lo.bias"] = (vocab_size,)
+    return s
+
+
 def count_params(shapes: Shapes) -> int:
     n = 0
     for shp in shapes.values():

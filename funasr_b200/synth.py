@@ -73,8 +73,10 @@ def synth_tensor(name: str, shape: Iterable[int], seed: int = 0) -> np.ndarray:
     is_norm = ".norm" in name or "after_norm" in name or "tp_norm" in name
     if is_norm and len(shape) == 1:
         u = rng.uniform(-1.0, 1.0, size=shape)
+        if leaf == "running_var":  # BatchNorm statistics of the Conformer conv module: positive
+            return (1.0 + 0.5 * u).astype(np.float32)
         return (1.0 + 0.1 * u if leaf == "weight" else 0.1 * u).astype(np.float32)
-    if "embed" in name and len(shape) == 2:
+    if "embed" in name and "embed.out" not in name and len(shape) == 2:
         return rng.standard_normal(size=shape).astype(np.float32)
     if leaf == "weight":
         fan_in = int(np.prod(shape[1:])) if len(shape) > 1 else shape[0]

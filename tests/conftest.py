@@ -49,3 +49,14 @@ def sensevoice_sd():
 
     sd = synth.synth_state_dict(params.sense_voice_small_shapes(), seed=0)
     return {k: torch.from_numpy(v) for k, v in sd.items()}
+
+
+@pytest.fixture(scope="session")
+def conformer_sd():
+    """Seeded Conformer-CTC weights (34.6 M params: conv2d input layer, 12 blocks, V = 4234)."""
+    import torch
+
+    from funasr_b200 import params, synth
+
+    sd = synth.synth_state_dict(params.conformer_ctc_shapes(), seed=0)
+    return {k: torch.from_numpy(v) for k, v in sd.items()}
