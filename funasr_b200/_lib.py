@@ -27,6 +27,12 @@ SIGNATURES = {
     "fb200_unpack_rows": [_P, _I, _P, _I, _I, _I, _F, _P, _P],
     "fb200_fsmn": [_P, _I, _P, _I, _I, _I, _P, _I, _P, _I, _P, _I, _P],
     "fb200_gemm": [_P, _I, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
+    "fb200_gemm_ex": [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
+    "fb200_conv2d_sub1": [_P, _I, _P, _P, _I, _I, _I, _P, _P, _I, _P, _I, _P],
+    "fb200_gather_rows": [_P, _I, _P, _P, _I, _P, _I, _I, _I, _P],
+    "fb200_glu_dwconv": [_P, _I, _P, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _I, _P],
+    "fb200_attention_relpos": [_P, _I, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _P, _I, ctypes.c_longlong, _P, _I, _I, _I,
+                               _I, _I, _F, _P, _I, _P, _I, _P],
     "fb200_split_weight": [_P, _I, _I, _P, _I, _P],
     "fb200_fill_head_rows": [_P, _I, _I, _P, _I, _P, _F, _P, _I, _P],
     "fb200_attention_plan": [_P, _P, _I, _P, _I, _P],
@@ -41,7 +47,8 @@ SIGNATURES = {
 EXPORTS = sorted(list(SIGNATURES) + ["fb200_version", "fb200_last_error", "fb200_launch_count",
                   "fb200_profile_enable", "fb200_profile_read"])
 PROFILE_KINDS = ["fbank", "lfr_cmvn", "scale_add_pe", "layernorm", "split_rows", "fsmn", "gemm", "attention",
-                 "cif_alpha", "cif_scan", "cif_integrate", "argmax_logprob", "ctc_collapse"]
+                 "cif_alpha", "cif_scan", "cif_integrate", "argmax_logprob", "ctc_collapse", "conv2d_sub1", "glu_dwconv",
+                 "attention_relpos"]
 
 _lib = None
 

@@ -16,7 +16,8 @@ void count_launch(int n = 1);
 // was called by this thread; `work` is the algorithmic bytes or FLOPs of the call.
 enum ProfKind {
   kProfFbank = 0, kProfLfr, kProfPe, kProfLayerNorm, kProfSplit, kProfFsmn, kProfGemm, kProfAttention,
-  kProfCifAlpha, kProfCifScan, kProfCifIntegrate, kProfArgmax, kProfCtc, kProfKinds
+  kProfCifAlpha, kProfCifScan, kProfCifIntegrate, kProfArgmax, kProfCtc, kProfConvSub, kProfGluDw, kProfRelAttention,
+  kProfKinds
 };
 class ProfScope {
  public:

@@ -26,14 +26,17 @@ constexpr int BK = 64;  // bf16 elements = 128 bytes = one swizzle row
 constexpr int kGemmThreads = 192;
 constexpr int kEpiWarpBytes = 8192;  // per epilogue warp: fp32 box 32x32 (4 KB, SW128) + 2 bf16 part boxes 32x32 (2 KB each, SW64)
 constexpr int kMaxTerms = 6;
+constexpr int kMaxTaps = 24;
 
 struct GemmParams {
   int m, n, k_blocks, kp_a, kp_w;
   int taps, nterms;
   int term_a[kMaxTerms], term_b[kMaxTerms];
+  int a_col0;                                // first A column; tap j reads A row m + tap_row[j], columns + tap_col[j]
+  int tap_row[kMaxTaps], tap_col[kMaxTaps];
   int tiles_m, tiles_n;
   const float* bias;
-  int relu;
+  int act;  // 0 none, 1 ReLU, 2 swish y * sigmoid(y)
   const float* res1;
   int ld_res1;
   float* out_f32;
@@ -46,7 +49,8 @@ struct GemmParams {
 __device__ __forceinline__ float epilogue_value(const GemmParams& p, int row, int col, float acc) {
   float y = acc;
   if (p.bias) y += __ldg(p.bias + col);
-  if (p.relu) y = fmaxf(y, 0.f);
+  if (p.act == 1) y = fmaxf(y, 0.f);
+  if (p.act == 2) y = y / (1.f + expf(-y));
   if (p.res1) y += p.res1[(size_t)row * p.ld_res1 + col];
   return y;
 }
@@ -158,7 +162,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       int it = 0;
       for (int tile = unit0; tile < total_tiles; tile += unit_step) {
         const int m0 = ((tile / p.tiles_n) * CL + cta_rank) * BM, n0 = (tile % p.tiles_n) * BN;
-        for (int tap = 0; tap < p.taps; ++tap)
+        for (int tap = 0; tap < p.taps; ++tap) {
+          const int a_r = m0 + p.tap_row[tap], a_c = p.a_col0 + p.tap_col[tap];
           for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
             const int s = it % STAGES;
             const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
@@ -169,7 +174,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               mbar_expect_tx(full_bar(s), kStageBytes);
 #pragma unroll
               for (int pa = 0; pa < NP; ++pa)
-                tma_load_2d(sa + pa * kAPart, &map_a, pa * p.kp_a + kb * BK, m0 + tap, full_bar(s));
+                tma_load_2d(sa + pa * kAPart, &map_a, a_c + pa * p.kp_a + kb * BK, a_r, full_bar(s));
 #pragma unroll
               for (int pb = 0; pb < NP; ++pb)
                 tma_load_2d(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK, tap * p.n + n0, full_bar(s));
@@ -180,13 +185,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               if (leader) mbar_expect_tx(full_bar(s), CL * kStageBytes);
 #pragma unroll
               for (int pa = 0; pa < NP; ++pa)
-                tma_load_2d_pair(sa + pa * kAPart, &map_a, pa * p.kp_a + kb * BK, m0 + tap, lbar);
+                tma_load_2d_pair(sa + pa * kAPart, &map_a, a_c + pa * p.kp_a + kb * BK, a_r, lbar);
 #pragma unroll
               for (int pb = 0; pb < NP; ++pb)
                 tma_load_2d_pair(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK,
                                  tap * p.n + n0 + cta_rank * (BN / CL), lbar);
             }
           }
+        }
       }
     }
   } else if (warp == 1) {
@@ -243,7 +249,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     const float* __restrict__ bias = p.bias;
     const float* __restrict__ res1 = p.res1;
     const bool has_f32 = p.out_f32 != nullptr, has_split = p.out_split != nullptr;
-    const float lo = p.relu ? 0.f : -INFINITY;
+    const float lo = p.act == 1 ? 0.f : -INFINITY;
+    const bool swish = p.act == 2;
     const int ncols = has_split ? out_kp : n;
     const uint32_t sw128 = (uint32_t)(lane & 7), sw64 = (uint32_t)((lane >> 1) & 3);
     // Residual, coalesced: the warp reads the NEXT chunk's [32 rows x 32 columns] one row per instruction
@@ -307,6 +314,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
 #pragma unroll
         for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], lo);
+        if (swish) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) y[j] = y[j] / (1.f + expf(-y[j]));
+        }
         if (res_coal) {
           // rv -> box (128-byte swizzle, like the fp32 output box) -> this lane's row
 #pragma unroll

@@ -201,3 +201,65 @@ def argmax_logprob(logits, vocab, ids, score=None, rows=None):
 def ctc_collapse(ids, cu_rows, drop_mask, collapse, out_ids, out_len):
     _lib.call("fb200_ctc_collapse", _p(ids), _p(cu_rows), cu_rows.numel() - 1, drop_mask, 1 if collapse else 0,
               _p(out_ids), _p(out_len), _stream())
+
+
+# ---- Conformer path (BASELINE config 4) -------------------------------------------------------------------
+
+_ACT = {None: 0, "none": 0, "relu": 1, "swish": 2}
+
+
+def _host_i32(values):
+    import ctypes
+
+    arr = (ctypes.c_int32 * len(values))(*[int(v) for v in values])
+    return arr, ctypes.cast(arr, ctypes.c_void_p)
+
+
+def gemm_ex(a, a_parts, w_split, w_parts, m, n, k, lda=0, a_part_stride=0, a_col0=0, tap_row=None, tap_col=None,
+            taps=1, bias=None, act=None, res1=None, out_f32=None, out_split=None, out_parts=1, impl=0, a_rows=None,
+            f32_col0=0):
+    """fb200_gemm with a general A operand: row pitch, part stride, first column, per-tap row / column offsets
+    (host lists), activation "relu" / "swish"."""
+    _chk(a, torch.bfloat16, "gemm_ex")
+    _chk(w_split, torch.bfloat16, "gemm_ex")
+    a_rows = a.shape[0] if a_rows is None else a_rows
+    keep_r, p_r = _host_i32(tap_row) if tap_row is not None else (None, None)
+    keep_c, p_c = _host_i32(tap_col) if tap_col is not None else (None, None)
+    _lib.call("fb200_gemm_ex", _p(a), a_rows, lda, a_part_stride, a_col0, a_parts, _p(w_split), w_parts, m, n, k, taps,
+              p_r, p_c, _p(bias), _ACT[act], _p(res1), 0 if res1 is None else res1.stride(0), _p(out_f32),
+              0 if out_f32 is None else out_f32.stride(0), f32_col0, _p(out_split), out_parts, impl, _stream())
+    del keep_r, keep_c
+
+
+def conv2d_sub1(feats, cu_frames, cu_seg, total_seg, weight, bias, planes, nparts):
+    """feats fp32 [frames, n_mels]; planes bf16 [4 * total_seg * FP, nparts * C] (every slot written)."""
+    _chk(feats, torch.float32, "conv2d_sub1")
+    _lib.call("fb200_conv2d_sub1", _p(feats), feats.stride(0), _p(cu_frames), _p(cu_seg), cu_frames.numel() - 1,
+              total_seg, feats.shape[1], _p(weight), _p(bias), weight.shape[0], _p(planes), nparts, _stream())
+
+
+def gather_rows(src, cu_src, dst, cu_dst, dim=None):
+    _chk(src, torch.float32, "gather_rows")
+    dim = dst.shape[1] if dim is None else dim
+    _lib.call("fb200_gather_rows", _p(src), src.stride(0), _p(cu_src), _p(dst), dst.stride(0), _p(cu_dst),
+              cu_dst.numel() - 1, dst.shape[0], dim, _stream())
+    return dst
+
+
+def glu_dwconv(g, cu_rows, max_len, channels, weight, bias, bn_scale, bn_shift, out_split, nparts, rows=None):
+    _chk(g, torch.float32, "glu_dwconv")
+    rows = g.shape[0] if rows is None else rows
+    _lib.call("fb200_glu_dwconv", _p(g), g.stride(0), _p(cu_rows), cu_rows.numel() - 1, rows, max_len, channels,
+              _p(weight), weight.shape[-1], _p(bias), _p(bn_scale), _p(bn_shift), _p(out_split), nparts, _stream())
+
+
+def attention_relpos(q, q_col0, q_ps, k, k_col0, v, v_col0, kv_ps, nparts, bd, cu_rows, max_len, heads, scale,
+                     out_f32=None, out_split=None, out_parts=None, rows=None, head_dim=64):
+    """bd fp32 [heads, rows, ld_bd] (contiguous heads)."""
+    _chk(q, torch.bfloat16, "attention_relpos")
+    _chk(bd, torch.float32, "attention_relpos")
+    rows = q.shape[0] if rows is None else rows
+    _lib.call("fb200_attention_relpos", _p(q), q.stride(0), q_col0, q_ps, _p(k), k.stride(0), k_col0, _p(v), v.stride(0),
+              v_col0, kv_ps, nparts, _p(bd), bd.stride(1), bd.stride(0), _p(cu_rows), cu_rows.numel() - 1, rows, max_len,
+              heads, head_dim, scale, _p(out_f32), 0 if out_f32 is None else out_f32.stride(0), _p(out_split),
+              nparts if out_parts is None else out_parts, _stream())

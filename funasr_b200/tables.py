@@ -92,3 +92,18 @@ def cu_from_lengths(lengths, dtype=torch.int32, device: Optional[torch.device] =
     cu = np.zeros(len(lengths) + 1, dtype=np.int64)
     np.cumsum(np.asarray(lengths, dtype=np.int64), out=cu[1:])
     return torch.from_numpy(cu).to(dtype).to(device) if device is not None else torch.from_numpy(cu).to(dtype)
+
+
+def legacy_rel_position_table(rows: int, d: int, max_len: int = 5000) -> torch.Tensor:
+    """[rows, d] fp32: the first `rows` rows of LegacyRelPositionalEncoding's table
+    (funasr/models/transformer/embedding.py:59-78 with reverse=True, :215-252): row i encodes position
+    max_len - 1 - i, sin in even columns, cos in odd ones.  The reference builds the table once for
+    max_len = 5000 and hands its first T rows to every layer, so row i does not depend on T (T <= max_len)."""
+    if rows > max_len:
+        raise ValueError("funasr_b200: %d rows exceed the reference's %d-row position table" % (rows, max_len))
+    position = torch.arange(max_len - 1, -1, -1.0, dtype=torch.float32).unsqueeze(1)[:rows]
+    div_term = torch.exp(torch.arange(0, d, 2, dtype=torch.float32) * -(math.log(10000.0) / d))
+    pe = torch.zeros(rows, d)
+    pe[:, 0::2] = torch.sin(position * div_term)
+    pe[:, 1::2] = torch.cos(position * div_term)
+    return pe

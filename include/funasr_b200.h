@@ -49,10 +49,11 @@ long long fb200_launch_count(int reset);
 /* Optional per-entry-point device timing for the calling thread: while enabled every call below
  * is bracketed by CUDA events on its stream.  `kind` indexes the entry points in header order:
  * 0 fbank, 1 lfr_cmvn, 2 scale_add_pe, 3 layernorm, 4 split_rows/split_weight, 5 fsmn, 6 gemm,
- * 7 attention, 8 cif_alpha, 9 cif_scan, 10 cif_integrate, 11 argmax_logprob, 12 ctc_collapse.
+ * 7 attention, 8 cif_alpha, 9 cif_scan, 10 cif_integrate, 11 argmax_logprob, 12 ctc_collapse, 13 conv2d_sub1,
+ * 14 glu_dwconv, 15 attention_relpos (gemm_ex counts as gemm, gather_rows as split_rows).
  * fb200_profile_read synchronises on the recorded events and returns the summed milliseconds,
  * call count and algorithmic work (bytes for HBM-bound kinds, FLOPs for gemm/attention). */
-#define FB200_PROFILE_KINDS 13
+#define FB200_PROFILE_KINDS 16
 int fb200_profile_enable(int on);
 int fb200_profile_read(int kind, double* ms, long long* calls, double* work, int reset);
 
@@ -168,6 +169,27 @@ int fb200_gemm(const void* a, int a_rows, int a_parts, const void* w, int w_part
                float* out_f32, int ld_out, int f32_col0, void* out_split, int out_parts, int impl,
                void* stream);
 
+/* fb200_gemm with a general A operand, for contractions whose rows are gathered by fixed offsets:
+ *   a            bf16, row pitch `lda` elements (0: a_parts*Kp), part p of the K columns at
+ *                a_col0 + tap_col[j] + p * a_part_stride (0: Kp)
+ *   h_tap_row    HOST int32 [taps]: tap j of output row m reads A row m + h_tap_row[j]; rows outside [0, a_rows)
+ *                read as zeros.  NULL: tap j reads row m + j.   h_tap_col: HOST int32 [taps] or NULL (zeros).
+ *   w            [taps][n, w_parts*Kp] as for fb200_gemm; taps <= 24
+ *   act          0 none, 1 ReLU, 2 swish y*sigmoid(y) (funasr/models/transformer/utils/nets_utils.py:496-528)
+ * Uses on the Conformer path (BASELINE config 4):
+ *   - second 3x3 stride-2 convolution of Conv2dSubsampling (funasr/models/transformer/utils/subsampling.py:66) as a
+ *     9-tap contraction over the parity planes written by fb200_conv2d_sub1 (tap (dt,df): row offset
+ *     ((dt&1)*2 + (df&1)) * plane_rows + (dt>>1)*FP + (df>>1));
+ *   - its Linear over (channel, frequency) pairs (:70,91) as a 19-tap contraction with COLUMN offsets over the
+ *     conv output viewed as [segment rows, FP * nparts * C];
+ *   - (q + pos_bias_v) . p^T per head (funasr/models/transformer/attention.py:303-305): A = one head's 64 columns of
+ *     the fused q_u | q_v | k | v projection (a_col0, a_part_stride);
+ *   - FFN w_1 with swish (funasr/models/transformer/positionwise_feed_forward.py:14-34). */
+int fb200_gemm_ex(const void* a, int a_rows, int lda, int a_part_stride, int a_col0, int a_parts, const void* w,
+                  int w_parts, int m, int n, int k, int taps, const int32_t* h_tap_row, const int32_t* h_tap_col,
+                  const float* bias, int act, const float* res1, int ld_res1, float* out_f32, int ld_out, int f32_col0,
+                  void* out_split, int out_parts, int impl, void* stream);
+
 /* fp32 weight [n, k] -> bf16 split [n, nparts*Kp] (done once at load). */
 int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts, void* stream);
 
@@ -200,6 +222,47 @@ int fb200_attention(const void* q, int ld_q, int q_col0, int q_part_stride, cons
                     int q_rows, int kv_rows, int max_q, int heads, int head_dim, float scale,
                     float* out_f32, int ld_out, void* out_split, int out_parts, int impl,
                     void* stream);
+
+/* ------------------------------------------------------------------ Conformer ---------- */
+
+/* First convolution of Conv2dSubsampling (funasr/models/transformer/utils/subsampling.py:64-65: Conv2d(1, C, 3, 2)
+ * + ReLU) over packed fbank frames, written as a bf16 split operand in four parity planes so that the second
+ * convolution is a 9-tap fb200_gemm_ex.  Per utterance b: F_b = cu_frames[b+1]-cu_frames[b] frames,
+ * T1 = (F_b-3)/2+1, T2 = (T1-3)/2+1, a segment of T2+1 rows (cu_seg = prefix sums of T2_b + 1);
+ * F1 = (n_mels-3)/2+1, FP = (F1+1)/2 slots per segment row, plane_rows = total_seg * FP.
+ *   planes  bf16 [4 * plane_rows, nparts*C]; plane (pt,pf) row (seg_b + t')*FP + f' = relu(conv)(t1=2t'+pt, f1=2f'+pf),
+ *           zeros where t1 >= T1 or f1 >= F1 (every slot is written)
+ *   weight  f32 [C, 9] (= Conv2d weight [C,1,3,3]), bias f32 [C]; C even, <= 256 */
+int fb200_conv2d_sub1(const float* feats, int ld_f, const int32_t* cu_frames, const int32_t* cu_seg, int batch,
+                      int total_seg, int n_mels, const float* weight, const float* bias, int channels, void* planes,
+                      int nparts, void* stream);
+
+/* dst[cu_dst[b] + t, :] = src[cu_src[b] + t, :] for t < cu_dst[b+1] - cu_dst[b]: drops the scratch row each
+ * utterance's segment carries after the subsampling contractions. */
+int fb200_gather_rows(const float* src, int ld_src, const int32_t* cu_src, float* dst, int ld_dst,
+                      const int32_t* cu_dst, int batch, int rows, int dim, void* stream);
+
+/* ConvolutionModule between its pointwise convolutions (funasr/models/conformer/encoder.py:110-116):
+ * GLU over g = [a | gate] -> depthwise Conv1d(C, C, ksize, padding (ksize-1)/2, groups=C) with bias, zero halo PER
+ * UTTERANCE -> BatchNorm1d in eval mode folded by the caller into bn_scale = gamma/sqrt(var+eps),
+ * bn_shift = beta - mean*bn_scale -> swish.  g f32 [rows, ld_g >= 2C]; weight f32 [C, ksize]; ksize 7, 15 or 31;
+ * out_split bf16 split [rows, nparts*Kp(C)] (the A operand of pointwise_conv2). */
+int fb200_glu_dwconv(const float* g, int ld_g, const int32_t* cu_rows, int batch, int total_rows, int max_len,
+                     int channels, const float* weight, int ksize, const float* bias, const float* bn_scale,
+                     const float* bn_shift, void* out_split, int nparts, void* stream);
+
+/* LegacyRelPositionMultiHeadedAttention core (funasr/models/transformer/attention.py:271-312 with rel_shift
+ * :249-269 and forward_attention :69-102), var-len, per utterance and head, streaming softmax:
+ *   s[i,j] = ((q_i+u).k_j + shift(bd)[i,j]) * scale;  shift(bd)[i,j] = bd[i, T-1-i+j] (j<=i), 0 (j=i+1),
+ *   bd[i+1, j-i-2] (j>=i+2)  -- the reference's pad/view/slice in closed form (T = utterance length)
+ *   q (already q+u), k, v  bf16 split matrices, head h of part p at col0 + p*part_stride + h*head_dim
+ *   bd  f32 [heads][rows, ld_bd] (head stride bd_head_stride elements): bd[r, c] = (q_r+v) . p_c, c < T of r's utterance
+ *   out f32 [rows, ld_out] and/or bf16 split [rows, out_parts*Kp(heads*head_dim)];  head_dim 64. */
+int fb200_attention_relpos(const void* q, int ld_q, int q_col0, int q_part_stride, const void* k, int ld_k, int k_col0,
+                           const void* v, int ld_v, int v_col0, int kv_part_stride, int nparts, const float* bd,
+                           int ld_bd, long long bd_head_stride, const int32_t* cu_rows, int batch, int rows,
+                           int max_len, int heads, int head_dim, float scale, float* out_f32, int ld_out,
+                           void* out_split, int out_parts, void* stream);
 
 /* ------------------------------------------------------------------ CIF predictor ------ */
 
