@@ -31,8 +31,8 @@ SIGNATURES = {
     "fb200_conv2d_sub1": [_P, _I, _P, _P, _I, _I, _I, _P, _P, _I, _P, _I, _P],
     "fb200_gather_rows": [_P, _I, _P, _P, _I, _P, _I, _I, _I, _P],
     "fb200_glu_dwconv": [_P, _I, _P, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _I, _P],
-    "fb200_attention_relpos": [_P, _I, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _P, _I, ctypes.c_longlong, _P, _I, _I, _I,
-                               _I, _I, _F, _P, _I, _P, _I, _P],
+    "fb200_attention_relpos": [_P, _I, _I, _I, _P, _I, _I, _P, _I, _I, _I, _I, _P, _I, ctypes.c_longlong, _P, _P, _I, _I,
+                               _I, _I, _I, _F, _P, _I, _P, _I, _I, _P],
     "fb200_split_weight": [_P, _I, _I, _P, _I, _P],
     "fb200_fill_head_rows": [_P, _I, _I, _P, _I, _P, _F, _P, _I, _P],
     "fb200_attention_plan": [_P, _P, _I, _P, _I, _P],

@@ -193,7 +193,7 @@ class ConformerEncoderPack:
             ops.gemm_ex(qkv, np_, ly.pos[h], np_, r, max_t, dk, lda=np_ * 4 * d, a_part_stride=4 * d, a_col0=d + h * dk,
                         out_f32=bd[h])
         ops.attention_relpos(qkv, 0, 4 * d, qkv, 2 * d, qkv, 3 * d, 4 * d, np_, bd, cu_rows, max_t, heads,
-                             float(dk) ** -0.5, out_split=ws["xs"])
+                             float(dk) ** -0.5, out_split=ws["xs"], plan=ws["plan"])
         ops.gemm(ws["xs"], np_, ly.out.w, np_, r, d, d, bias=ly.out.bias, res1=x1, out_f32=xb)
         # convolution module
         ops.layernorm(xb, ly.norm_conv.g, ly.norm_conv.b, self.eps, out_split=ws["xs"], nparts=np_)
@@ -212,6 +212,7 @@ class ConformerEncoderPack:
         self.ensure_positions(max_t)
         r = x.shape[0]
         ws = self.workspace(r, max_t)
+        ws["plan"] = ops.attention_plan(cu_rows, cu_rows, r)  # 128-row query blocks, shared by every layer
         bufs = [torch.empty_like(x), torch.empty_like(x)]
         for i, ly in enumerate(self.layers):
             x = self._layer(ly, x, cu_rows, max_t, ws, bufs[i & 1])

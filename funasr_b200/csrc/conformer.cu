@@ -388,7 +388,9 @@ extern "C" __attribute__((visibility("default"))) int fb200_glu_dwconv(
   return FB200_OK;
 }
 
-extern "C" __attribute__((visibility("default"))) int fb200_attention_relpos(
+namespace fb200 {
+// SIMT check kernel of fb200_attention_relpos (impl = 1, and the 3-part mode); entry in relpos_attention_sm100.cu
+int relpos_attention_simt(
     const void* q, int ld_q, int q_col0, int q_part_stride, const void* k, int ld_k, int k_col0, const void* v, int ld_v,
     int v_col0, int kv_part_stride, int nparts, const float* bd, int ld_bd, long long bd_head_stride, const int32_t* cu_rows,
     int batch, int rows, int max_len, int heads, int head_dim, float scale, float* out_f32, int ld_out, void* out_split,
@@ -421,6 +423,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_attention_relpos(
       (const __nv_bfloat16*)q + q_col0, ld_q, q_part_stride, (const __nv_bfloat16*)k + k_col0, ld_k,
       (const __nv_bfloat16*)v + v_col0, ld_v, kv_part_stride, nparts, bd, ld_bd, bd_head_stride, cu_rows, scale, out_f32, ld_out,
       (__nv_bfloat16*)out_split, out_parts, out_kp);
-  FB_CHECK_LAUNCH("attention_relpos");
+  FB_CHECK_LAUNCH("attention_relpos_simt");
   return FB200_OK;
 }
+}  // namespace fb200

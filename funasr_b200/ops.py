@@ -254,12 +254,14 @@ def glu_dwconv(g, cu_rows, max_len, channels, weight, bias, bn_scale, bn_shift, 
 
 
 def attention_relpos(q, q_col0, q_ps, k, k_col0, v, v_col0, kv_ps, nparts, bd, cu_rows, max_len, heads, scale,
-                     out_f32=None, out_split=None, out_parts=None, rows=None, head_dim=64):
-    """bd fp32 [heads, rows, ld_bd] (contiguous heads)."""
+                     out_f32=None, out_split=None, out_parts=None, rows=None, head_dim=64, plan=None, impl=0):
+    """bd fp32 [heads, rows, ld_bd] (contiguous heads); plan = attention_plan(cu_rows, cu_rows, rows) (impl 0)."""
     _chk(q, torch.bfloat16, "attention_relpos")
     _chk(bd, torch.float32, "attention_relpos")
     rows = q.shape[0] if rows is None else rows
+    if plan is None and impl == 0 and nparts < 3:
+        plan = attention_plan(cu_rows, cu_rows, rows)
     _lib.call("fb200_attention_relpos", _p(q), q.stride(0), q_col0, q_ps, _p(k), k.stride(0), k_col0, _p(v), v.stride(0),
-              v_col0, kv_ps, nparts, _p(bd), bd.stride(1), bd.stride(0), _p(cu_rows), cu_rows.numel() - 1, rows, max_len,
-              heads, head_dim, scale, _p(out_f32), 0 if out_f32 is None else out_f32.stride(0), _p(out_split),
-              nparts if out_parts is None else out_parts, _stream())
+              v_col0, kv_ps, nparts, _p(bd), bd.stride(1), bd.stride(0), _p(cu_rows), _p(plan), cu_rows.numel() - 1, rows,
+              max_len, heads, head_dim, scale, _p(out_f32), 0 if out_f32 is None else out_f32.stride(0), _p(out_split),
+              nparts if out_parts is None else out_parts, impl, _stream())

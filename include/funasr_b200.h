@@ -257,12 +257,15 @@ int fb200_glu_dwconv(const float* g, int ld_g, const int32_t* cu_rows, int batch
  *   bd[i+1, j-i-2] (j>=i+2)  -- the reference's pad/view/slice in closed form (T = utterance length)
  *   q (already q+u), k, v  bf16 split matrices, head h of part p at col0 + p*part_stride + h*head_dim
  *   bd  f32 [heads][rows, ld_bd] (head stride bd_head_stride elements): bd[r, c] = (q_r+v) . p_c, c < T of r's utterance
- *   out f32 [rows, ld_out] and/or bf16 split [rows, out_parts*Kp(heads*head_dim)];  head_dim 64. */
+ *   out f32 [rows, ld_out] and/or bf16 split [rows, out_parts*Kp(heads*head_dim)];  head_dim 64.
+ *   plan from fb200_attention_plan(cu_rows, cu_rows, ...) (128-row query blocks); required by impl 0.
+ * impl: 0 = tcgen05 (S = Q K^T and P V as UMMAs, P in tensor memory, the shifted bias band staged through shared
+ * memory; product path), 1 = SIMT fp32 check kernel over the same operands (also the 3-part mode). */
 int fb200_attention_relpos(const void* q, int ld_q, int q_col0, int q_part_stride, const void* k, int ld_k, int k_col0,
                            const void* v, int ld_v, int v_col0, int kv_part_stride, int nparts, const float* bd,
-                           int ld_bd, long long bd_head_stride, const int32_t* cu_rows, int batch, int rows,
-                           int max_len, int heads, int head_dim, float scale, float* out_f32, int ld_out,
-                           void* out_split, int out_parts, void* stream);
+                           int ld_bd, long long bd_head_stride, const int32_t* cu_rows, const int32_t* plan, int batch,
+                           int rows, int max_len, int heads, int head_dim, float scale, float* out_f32, int ld_out,
+                           void* out_split, int out_parts, int impl, void* stream);
 
 /* ------------------------------------------------------------------ CIF predictor ------ */
 

@@ -109,12 +109,13 @@ def test_glu_dwconv_matches_torch(conformer_sd):
         o += x.shape[0]
 
 
-def test_relpos_attention_matches_oracle():
+@pytest.mark.parametrize("impl", [0, 1])
+def test_relpos_attention_matches_oracle(impl):
     """Streaming softmax with the closed-form rel_shift vs the pad/view/slice transcription, ragged batch
     (lengths around the 64-row tile edges, T = 1 and 2 where the shift degenerates)."""
     heads, dk, np_ = 4, 64, 2
     d = heads * dk
-    lens = [1, 2, 63, 64, 65, 130]
+    lens = [1, 2, 63, 64, 65, 130, 300]
     g = torch.Generator().manual_seed(9)
     r, max_t = sum(lens), max(lens)
     qu, qv, k, v = (torch.randn(r, d, generator=g) for _ in range(4))
@@ -127,7 +128,11 @@ def test_relpos_attention_matches_oracle():
         ops.gemm_ex(qkv, np_, ph, np_, r, max_t, dk, lda=np_ * 4 * d, a_part_stride=4 * d, a_col0=d + h * dk, out_f32=bd[h])
     out = torch.zeros(r, d, device=DEV)
     ops.attention_relpos(qkv, 0, 4 * d, qkv, 2 * d, qkv, 3 * d, 4 * d, np_, bd, tables.cu_from_lengths(lens, torch.int32, DEV),
-                         max_t, heads, dk ** -0.5, out_f32=out)
+                         max_t, heads, dk ** -0.5, out_f32=out, impl=impl)
+    osp = torch.zeros(r, 2 * d, dtype=torch.bfloat16, device=DEV)
+    ops.attention_relpos(qkv, 0, 4 * d, qkv, 2 * d, qkv, 3 * d, 4 * d, np_, bd, tables.cu_from_lengths(lens, torch.int32, DEV),
+                         max_t, heads, dk ** -0.5, out_split=osp, impl=impl)
+    assert rel(osp[:, :d].float() + osp[:, d:].float(), out) < 2e-5
     out = out.cpu()
     o = 0
     for t in lens:
