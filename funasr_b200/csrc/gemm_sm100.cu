@@ -45,12 +45,16 @@ struct GemmParams {
   int out_parts, out_kp;
 };
 
+// swish y * sigmoid(y) on the SFU (ex2.approx + rcp.approx: ~2 ulp, far inside the 16-bit-mantissa operand rounding that
+// follows); the IEEE expf + division made the epilogue of the K = 256 FFN contractions longer than their mainloop
+__device__ __forceinline__ float swish_fast(float y) { return __fdividef(y, 1.f + __expf(-y)); }
+
 // y = acc (+bias)(relu)(+res1) for one output element (scalar path shared with the SIMT kernel)
 __device__ __forceinline__ float epilogue_value(const GemmParams& p, int row, int col, float acc) {
   float y = acc;
   if (p.bias) y += __ldg(p.bias + col);
   if (p.act == 1) y = fmaxf(y, 0.f);
-  if (p.act == 2) y = y / (1.f + expf(-y));
+  if (p.act == 2) y = swish_fast(y);
   if (p.res1) y += p.res1[(size_t)row * p.ld_res1 + col];
   return y;
 }
@@ -316,7 +320,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], lo);
         if (swish) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) y[j] = y[j] / (1.f + expf(-y[j]));
+          for (int j = 0; j < 32; ++j) y[j] = swish_fast(y[j]);
         }
         if (res_coal) {
           // rv -> box (128-byte swizzle, like the fp32 output box) -> this lane's row

@@ -7,7 +7,8 @@
 // One CTA = one item of the plan (fb200_attention_plan): 128 query rows of one (utterance, head); key / value tiles of
 // 64 rows stream through a 3-stage shared-memory ring.
 //   warps 0..3  softmax      thread r owns query row r = TMEM lane r: stages the shifted bias tile of its warp's 32 rows
-//                            through shared memory (coalesced global reads along the band, conflict-free row reads),
+//                            through shared memory one tile ahead (4-byte cp.async along the band: coalesced global
+//                            reads, conflict-free row reads),
 //                            online softmax, P packed to bf16 hi (+ mid) pairs INTO TENSOR MEMORY, O kept in registers
 //   warp 4      TMA producer Q tile once, then K_j / V_j tiles (one elected thread)
 //   warp 5      MMA issuer   S_j = Q K_j^T (A, B from shared memory) two tiles ahead; PV_j = P_j V_j (A = P in tensor
@@ -54,7 +55,7 @@ struct Params {
 };
 
 __host__ __device__ constexpr size_t smem_bytes(int np) {
-  return (size_t)np * kQTile + (size_t)NS * np * 2 * kTile + 4 * 32 * kBiasPitch * 4 + 256 + 1024;
+  return (size_t)np * kQTile + (size_t)NS * np * 2 * kTile + 2 * 4 * 32 * kBiasPitch * 4 + 256 + 1024;
 }
 
 template <int NP>
@@ -72,7 +73,7 @@ relpos_attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t q_sm = base, kv_sm = q_sm + NP * kQTile, bias_sm = kv_sm + NS * kStage;
-  const uint32_t bar_base = bias_sm + 4 * 32 * kBiasPitch * 4;
+  const uint32_t bar_base = bias_sm + 2 * 4 * 32 * kBiasPitch * 4;
   const uint32_t tmem_slot = bar_base;
   const uint32_t bar_q = bar_base + 8;
   auto bar_full = [&](int i) { return bar_base + 16u + 8u * i; };
@@ -177,7 +178,7 @@ relpos_attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
     const float c = p.scale_log2e;
     const float* bdh = p.bd + (size_t)head * p.bd_head_stride;
     const int qi0 = q_row - beg + warp * 32;  // utterance-local index of this warp's first query row
-    float* bias_w = reinterpret_cast<float*>(smem_raw + (bias_sm - smem_u32(smem_raw))) + warp * 32 * kBiasPitch;
+    const float* bias_all = reinterpret_cast<const float*>(smem_raw + (bias_sm - smem_u32(smem_raw)));
     float o[HD];
 #pragma unroll
     for (int u = 0; u < HD; ++u) o[u] = 0.f;
@@ -195,23 +196,39 @@ relpos_attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __gr
       }
     };
 
-    for (int j = 0; j < ntiles; ++j) {
+    // Shifted bias tile of this warp's 32 rows, tile j -> buffer j & 1: lanes run along the band (coalesced), one row
+    // at a time, as 4-byte cp.async copies (zero-filled outside the band) -- issued one tile ahead, no registers held.
+    auto stage_bias = [&](int j) {
       const int kj0 = j * TK;
-      // shifted bias tile of this warp's 32 rows: lanes run along the band (coalesced), one row at a time
-      __syncwarp();
+      const uint32_t dst0 = bias_sm + (uint32_t)(((j & 1) * 4 + warp) * 32 * kBiasPitch + lane) * 4u;
 #pragma unroll 8
       for (int rr = 0; rr < 32; ++rr) {
         const int qi = qi0 + rr;
-        float b0 = 0.f, b1 = 0.f;
-        if (qi < T) {
-          const float* row0 = bdh + (size_t)(beg + qi) * p.ld_bd + (T - 1 - qi);  // [kj] for kj <= qi
-          const float* row1 = bdh + (size_t)(beg + qi + 1) * p.ld_bd;             // [kj - qi - 2] for kj >= qi + 2
-          const int ka = kj0 + lane, kb = ka + 32;
-          if (ka < T) b0 = ka <= qi ? __ldg(row0 + ka) : (ka == qi + 1 ? 0.f : __ldg(row1 + (ka - qi - 2)));
-          if (kb < T) b1 = kb <= qi ? __ldg(row0 + kb) : (kb == qi + 1 ? 0.f : __ldg(row1 + (kb - qi - 2)));
+        const float* row0 = bdh + (size_t)(beg + qi) * p.ld_bd + (T - 1 - qi);  // [kj] for kj <= qi
+        const float* row1 = bdh + (size_t)(beg + qi + 1) * p.ld_bd - (qi + 2);   // [kj] for kj >= qi + 2
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int kj = kj0 + h * 32 + lane;
+          const bool in = qi < T && kj < T && kj != qi + 1;
+          const float* src = in ? (kj <= qi ? row0 + kj : row1 + kj) : bdh;
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst0 + (uint32_t)(rr * kBiasPitch + h * 32) * 4u),
+                       "l"(src), "r"(in ? 4 : 0)
+                       : "memory");
         }
-        bias_w[rr * kBiasPitch + lane] = b0;
-        bias_w[rr * kBiasPitch + 32 + lane] = b1;
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    stage_bias(0);
+
+    for (int j = 0; j < ntiles; ++j) {
+      const int kj0 = j * TK;
+      const float* bias_w = bias_all + ((j & 1) * 4 + warp) * 32 * kBiasPitch;
+      __syncwarp();  // every lane has read buffer (j + 1) & 1 (tile j - 1)
+      if (j + 1 < ntiles) {
+        stage_bias(j + 1);
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+      } else {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
       }
       __syncwarp();
       uint32_t s[TK], pm[TK / 2];
