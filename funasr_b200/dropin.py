@@ -10,6 +10,8 @@ by string key and `load_pretrained_model(strict=True)` loads a reference checkpo
     SenseVoiceEncoderSmall funasr/models/sense_voice/model.py:444-585
     WavFrontend            funasr/frontends/wav_frontend.py:78-158
     SANMEncoder            funasr/models/sanm/encoder.py:188-430
+    ConformerEncoder       funasr/models/conformer/encoder.py:285-607 (aishell recipe options: conv2d input layer,
+                           legacy rel-pos attention, macaron FFN, convolution module; BASELINE config 4)
     CifPredictorV2         funasr/models/paraformer/cif_predictor.py:172-253
     ParaformerSANMDecoder  funasr/models/paraformer/decoder.py:224-411
 
@@ -24,7 +26,7 @@ from typing import Dict, List, Optional, Tuple
 import torch
 from torch import nn
 
-from . import engine, ops, params, tables
+from . import conformer, engine, ops, params, tables
 
 PRECISION = "fp32"  # module-level default; override per module with `precision=` or set_precision()
 
@@ -254,6 +256,82 @@ class SenseVoiceEncoderSmall(_ParamTree):
             out = ops.unpack_rows(y, cu_rows, xs_pad.shape[1])
         olens = torch.as_tensor(lens, dtype=torch.int32, device=dev)  # masks.squeeze(1).sum(1).int()
         return out, olens
+
+
+class ConformerEncoder(_ParamTree):
+    """funasr/models/conformer/encoder.py:285-607 with the options of the aishell recipe
+    (examples/aishell/conformer/conf/conformer_12e_6d_2048_256.yaml:16-31): `input_layer="conv2d"`, `rel_pos_type`
+    left at its default "legacy" (so rel_pos / rel_selfattn resolve to the legacy classes, encoder.py:352-356),
+    swish, macaron FFN pair, convolution module, pre-norm.  `forward(xs_pad, ilens) -> (xs_pad, olens, None)`.
+
+    Every utterance is computed with batch-1 semantics: olens[b] = ((ilens[b] - 1) // 2 - 1) // 2 and its rows do not
+    see the padding frames of the batch (the reference's padded run lets the two stride-2 convolutions read them and
+    counts ceil-rounded mask lengths for the shorter utterances, subsampling.py:94)."""
+
+    def __init__(self, input_size: int, output_size: int = 256, attention_heads: int = 4, linear_units: int = 2048,
+                 num_blocks: int = 6, dropout_rate: float = 0.1, positional_dropout_rate: float = 0.1,
+                 attention_dropout_rate: float = 0.0, input_layer: str = "conv2d", normalize_before: bool = True,
+                 concat_after: bool = False, positionwise_layer_type: str = "linear",
+                 positionwise_conv_kernel_size: int = 3, macaron_style: bool = False, rel_pos_type: str = "legacy",
+                 pos_enc_layer_type: str = "rel_pos", selfattention_layer_type: str = "rel_selfattn",
+                 activation_type: str = "swish", use_cnn_module: bool = True, zero_triu: bool = False,
+                 cnn_module_kernel: int = 31, padding_idx: int = -1, interctc_layer_idx: List[int] = [],
+                 interctc_use_conditioning: bool = False, stochastic_depth_rate=0.0, precision: Optional[str] = None,
+                 **kwargs):
+        super().__init__()
+        unsupported = []
+        if input_layer != "conv2d":
+            unsupported.append("input_layer=%r (only 'conv2d')" % (input_layer,))
+        if rel_pos_type != "legacy" or pos_enc_layer_type not in ("rel_pos", "legacy_rel_pos") or \
+                selfattention_layer_type not in ("rel_selfattn", "legacy_rel_selfattn"):
+            unsupported.append("position / attention types other than the legacy relative ones")
+        if not (macaron_style and use_cnn_module and normalize_before) or concat_after or zero_triu:
+            unsupported.append("non-macaron / no cnn module / post-norm / concat_after / zero_triu")
+        if activation_type != "swish" or positionwise_layer_type != "linear" or interctc_layer_idx:
+            unsupported.append("activation other than swish / non-linear positionwise layer / interctc")
+        if attention_heads != 4 or output_size // attention_heads != 64:
+            unsupported.append("%d heads of dim %d (4 x 64 only)" % (attention_heads, output_size // attention_heads))
+        if cnn_module_kernel not in (7, 15, 31):
+            unsupported.append("cnn_module_kernel %d (7, 15, 31)" % cnn_module_kernel)
+        if unsupported:
+            raise NotImplementedError("funasr_b200.ConformerEncoder does not support: " + "; ".join(unsupported))
+        self._output_size, self.precision = output_size, precision
+        self.interctc_layer_idx, self.interctc_use_conditioning, self.conditioning_layer = [], False, None
+        self.normalize_before = True
+        self._declare(params.conformer_encoder_shapes(input_size, output_size, linear_units, num_blocks, cnn_module_kernel, ""), "")
+        # BatchNorm1d running statistics are buffers in the reference (and in its checkpoints)
+        for blk in self._modules["encoders"]._modules.values():
+            bn = blk._modules["conv_module"]._modules["norm"]
+            for name, fill in (("running_mean", 0.0), ("running_var", 1.0)):
+                shape = bn._parameters.pop(name).shape
+                bn.register_buffer(name, torch.full(shape, fill))
+            bn.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long))
+
+    def output_size(self) -> int:
+        return self._output_size
+
+    def _state_key(self):
+        return tuple((t.data_ptr(), t._version, str(t.device)) for t in list(self.parameters()) + list(self.buffers()))
+
+    def _enc(self, dev) -> "conformer.ConformerEncoderPack":
+        return self._packed(lambda: conformer.ConformerEncoderPack(self._sd("encoder."), dev, nparts=self._nparts))
+
+    def forward(self, xs_pad: torch.Tensor, ilens: torch.Tensor, prev_states: torch.Tensor = None, ctc=None):
+        _require_cuda(xs_pad, "ConformerEncoder")
+        lens = _lengths_list(ilens)
+        dev = xs_pad.device
+        if xs_pad.shape[1] < 7 or min(lens) < 7:  # check_short_utt / TooShortUttError (encoder.py:555-563)
+            raise RuntimeError("has %d frames and is too short for subsampling (it needs more than 7 frames), return empty "
+                               "results" % min(min(lens), xs_pad.shape[1]))
+        with torch.cuda.device(dev):
+            cu_frames = tables.cu_from_lengths(lens, torch.int32, dev)
+            enc = self._enc(dev)
+            feats = ops.pack_rows(xs_pad.float(), cu_frames, sum(lens))
+            x, cu_rows, rows = enc.embed(feats, cu_frames, lens)
+            y = enc.run(x, cu_rows, max(rows))
+            out = ops.unpack_rows(y, cu_rows, conformer.subsampled_lengths(xs_pad.shape[1])[1])
+        olens = torch.as_tensor(rows, dtype=torch.int64, device=dev)
+        return out, olens, None
 
 
 class CifPredictorV2(_ParamTree):
@@ -638,6 +716,7 @@ DROPIN_CLASSES = {
     ("decoder_classes", "ParaformerSANMDecoder"): ParaformerSANMDecoder,
     ("model_classes", "Paraformer"): Paraformer,
     ("model_classes", "SenseVoiceSmall"): SenseVoiceSmall,
+    ("encoder_classes", "ConformerEncoder"): ConformerEncoder,
 }
 
 

@@ -342,3 +342,69 @@ def test_sensevoice_model_inference_override_matches_golden(sensevoice_sd, golde
     top = max(set(base), key=base.count)
     banned = model._engine_for(frontend).recognize([wave], ban_ids=(top,))[0]
     assert top not in banned and banned != base
+
+
+# ---- ConformerEncoder (BASELINE config 4) -------------------------------------------------------------------
+
+CONF_ENC = dict(output_size=256, attention_heads=4, linear_units=2048, num_blocks=12, dropout_rate=0.1,
+                positional_dropout_rate=0.1, attention_dropout_rate=0.0, input_layer="conv2d", normalize_before=True,
+                pos_enc_layer_type="rel_pos", selfattention_layer_type="rel_selfattn", activation_type="swish",
+                macaron_style=True, use_cnn_module=True, cnn_module_kernel=15)
+
+
+def test_conformer_encoder_state_dict_keys_are_the_reference_inventory():
+    enc = dropin.ConformerEncoder(80, **CONF_ENC)
+    got = {"encoder." + k: tuple(v.shape) for k, v in enc.state_dict().items() if not k.endswith("num_batches_tracked")}
+    assert got == dict(params.conformer_encoder_shapes())
+    assert enc.output_size() == 256
+    with pytest.raises(NotImplementedError):
+        dropin.ConformerEncoder(80, **dict(CONF_ENC, rel_pos_type="latest"))
+    with pytest.raises(NotImplementedError):
+        dropin.ConformerEncoder(80, **dict(CONF_ENC, input_layer="linear"))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        enc(torch.zeros(1, 40, 80), torch.tensor([40]))
+
+
+@pytest.mark.skipif(not reference_available(), reason="reference tree not present (GPU box)")
+def test_conformer_encoder_loads_the_reference_state_dict_strictly():
+    from ref_loader import import_reference
+
+    import_reference()
+    from funasr.register import tables
+
+    ref_cls = tables.encoder_classes["ConformerEncoder"]
+    ref = ref_cls(input_size=80, **dict(CONF_ENC, num_blocks=2))
+    mine = dropin.ConformerEncoder(80, **dict(CONF_ENC, num_blocks=2))
+    assert {k: tuple(v.shape) for k, v in ref.state_dict().items()} == {k: tuple(v.shape) for k, v in mine.state_dict().items()}
+    mine.load_state_dict(ref.state_dict(), strict=True)
+    try:
+        assert "encoder_classes[ConformerEncoder]" in dropin.install(tables)
+        assert tables.encoder_classes["ConformerEncoder"] is dropin.ConformerEncoder
+    finally:
+        tables.encoder_classes["ConformerEncoder"] = ref_cls
+
+
+@pytest.mark.gpu
+def test_conformer_dropin_padded_forward_matches_oracle(conformer_sd):
+    """The reference's encoder call `self.encoder(speech, speech_lengths)` (funasr/models/ctc/model.py:139) with a
+    PADDED batch through the drop-in module == the oracle's batch-1 runs."""
+    from oracle import conformer_oracle as C
+    from oracle import paraformer_oracle as P
+
+    enc = dropin.ConformerEncoder(80, **CONF_ENC)
+    enc.load_state_dict({k[len("encoder."):]: v for k, v in conformer_sd.items() if k.startswith("encoder.")}, strict=False)
+    enc = enc.cuda().eval()
+    waves = [synth.synth_waveform(60, 24000), synth.synth_waveform(61, 50000), synth.synth_waveform(62, 9000)]
+    feats = [P.wav_frontend(torch.from_numpy(w), None, window="hamming", lfr_m=1, lfr_n=1) for w in waves]
+    lens = [f.shape[0] for f in feats]
+    pad = torch.nn.utils.rnn.pad_sequence(feats, batch_first=True).cuda()
+    with torch.no_grad():
+        out, olens, _ = enc(pad, torch.tensor(lens).cuda())
+    assert out.shape[:2] == (3, ((max(lens) - 1) // 2 - 1) // 2)
+    for b, f in enumerate(feats):
+        with torch.no_grad():
+            want = C.conformer_encoder(f, conformer_sd)
+        assert int(olens[b]) == want.shape[0]
+        got = out[b, : want.shape[0]].cpu()
+        assert float((got - want).abs().max() / want.abs().max()) < 1e-3
+        assert float(out[b, want.shape[0]:].abs().max()) == 0.0 if want.shape[0] < out.shape[1] else True
