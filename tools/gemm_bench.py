@@ -24,9 +24,24 @@ SHAPES = [
 ]
 
 
+# Conformer (d = 256) shapes and epilogue variants: `python tools/gemm_bench.py 2 18944 conformer`
+CONFORMER = [
+    ("c_w1 swish split", 2048, 256, False, True, False, "swish", 0),
+    ("c_w1 none  split", 2048, 256, False, True, False, False, 0),
+    ("c_w1 none  f32  ", 2048, 256, True, False, False, False, 0),
+    ("c_w2 res   f32  ", 256, 2048, True, False, True, False, 0),
+    ("c_qkv      split", 1024, 256, False, True, False, False, 0),
+    ("c_out res  f32  ", 256, 256, True, False, True, False, 0),
+    ("c_pw1      f32  ", 512, 256, True, False, False, False, 0),
+    ("c_bd  k64  f32  ", 752, 64, True, False, False, False, 0),
+    ("c_ctc      f32  ", 4236, 256, True, False, False, False, 0),
+]
+
+
 def main():
     g = torch.Generator().manual_seed(0)
-    for name, n, k, f32, split, res, relu, c0 in SHAPES:
+    shapes = CONFORMER if len(sys.argv) > 3 and sys.argv[3] == "conformer" else SHAPES
+    for name, n, k, f32, split, res, relu, c0 in shapes:
         m = M if name != "vocab " else 5000
         a = ops.split_rows(torch.randn(m, k, generator=g).to(DEV), NP)
         w = ops.split_rows((torch.randn(n, k, generator=g) / k ** 0.5).to(DEV), NP)
@@ -36,8 +51,11 @@ def main():
         r = torch.randn(m, n, generator=g).to(DEV) if res else None
 
         def run():
-            ops.gemm(a, NP, w, NP, m, n, k, bias=bias, relu=relu, res1=r, out_f32=out, out_split=sp, out_parts=NP,
-                     f32_col0=c0)
+            if relu == "swish":
+                ops.gemm_ex(a, NP, w, NP, m, n, k, bias=bias, act="swish", res1=r, out_f32=out, out_split=sp, out_parts=NP)
+            else:
+                ops.gemm(a, NP, w, NP, m, n, k, bias=bias, relu=relu, res1=r, out_f32=out, out_split=sp, out_parts=NP,
+                         f32_col0=c0)
 
         for _ in range(3):
             run()
