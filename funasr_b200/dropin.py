@@ -6,6 +6,7 @@ tuple and state_dict keys, so `AutoModel(model="Paraformer", .
 by string key and `load_pretrained_model(strict=True)` loads a reference checkpoint unchanged:
 
     Paraformer             funasr/models/paraformer/model.py:30-596 (`inference` only: one packed engine call)
+    CTC                    funasr/models/ctc/model.py:17-247 (`inference` only, over a ConformerEncoder)
     SenseVoiceSmall        funasr/models/sense_voice/model.py:588-906 (`inference` only)
     SenseVoiceEncoderSmall funasr/models/sense_voice/model.py:444-585
     WavFrontend            funasr/frontends/wav_frontend.py:78-158
@@ -720,6 +721,103 @@ DROPIN_CLASSES = {
 }
 
 
+class CTCInference:
+    """`inference` of `model_classes["CTC"]` (funasr/models/ctc/model.py:162-247) over a ConformerEncoder as ONE
+    call into the packed engine (BASELINE config 4): waveforms -> fbank -> conv2d subsampling -> Conformer blocks ->
+    ctc_lo -> per-frame argmax -> unique_consecutive -> blank / sos / eos removed.  Returns the reference's
+    `(results, meta_data)` with `{"key", "token", "text"}` entries.  Unlike the reference method (which raises for
+    batch_size > 1, :172-173) a list of inputs is decoded as one packed batch.  Other encoders and fbank inputs go
+    to the reference method when there is one."""
+
+    _fb200_engine = None
+    _fb200_engine_key = None
+
+    def _engine_for(self, frontend) -> "conformer.ConformerCTCEngine":
+        dev = next(self.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("funasr_b200.CTC: the model lives on %s -- this path runs on a CUDA device only "
+                               "(no CPU fallback); build the model with device='cuda'" % dev)
+        key = (tuple((t.data_ptr(), t._version) for t in list(self.parameters()) + list(self.buffers())), str(dev), PRECISION,
+               getattr(frontend, "window", "hamming"))
+        if self._fb200_engine is None or self._fb200_engine_key != key:
+            sd = {k: v.detach() for k, v in self.state_dict().items()}
+            prec = "fp32" if PRECISION == "fp32x6" else PRECISION
+            self._fb200_engine = conformer.ConformerCTCEngine(sd, dev, precision=prec, window=getattr(frontend, "window", "hamming"))
+            self._fb200_engine_key = key
+        return self._fb200_engine
+
+    def inference(self, data_in, data_lengths=None, key: list = None, tokenizer=None, frontend=None, **kwargs):
+        import time
+
+        enc = getattr(self, "encoder", None)
+        on_path = "encoder.embed.conv.0.weight" in self.state_dict() and "encoder.encoders.0.conv_module.norm.running_var" in \
+            self.state_dict() and kwargs.get("data_type", "sound") != "fbank" and getattr(frontend, "lfr_m", 1) == 1 and \
+            getattr(frontend, "lfr_n", 1) == 1 and getattr(frontend, "cmvn_file", None) is None
+        if not on_path:
+            ref = getattr(super(), "inference", None)
+            if ref is None:
+                raise NotImplementedError("funasr_b200.CTC.inference: only a ConformerEncoder (conv2d input layer) fed by "
+                                          "WavFrontend(lfr_m=1, lfr_n=1, no CMVN) is on the accelerated path (encoder: %s)"
+                                          % type(enc).__name__)
+            return ref(data_in, data_lengths=data_lengths, key=key, tokenizer=tokenizer, frontend=frontend, **kwargs)
+        meta_data = {}
+        t1 = time.perf_counter()
+        waves = _as_waveforms(data_in, data_lengths, frontend.fs, dict(kwargs, tokenizer=tokenizer))
+        t2 = time.perf_counter()
+        meta_data["load_data"] = f"{t2 - t1:0.3f}"
+        eng = self._engine_for(frontend)
+        ids = eng.recognize(waves)
+        t3 = time.perf_counter()
+        meta_data["extract_feat"] = f"{t3 - t2:0.3f}"  # here: the whole device path
+        frames = [tables.num_frames(len(w), eng.frontend.frame_len, eng.frontend.frame_shift) for w in waves]
+        meta_data["batch_data_time"] = sum(frames) * frontend.frame_shift * frontend.lfr_n / 1000
+        b = len(waves)
+        key = list(key) if key is not None else ["utt%d" % i for i in range(b)]
+        if key and isinstance(key[0], (list, tuple)):
+            key = list(key[0])
+        if len(key) < b:
+            key = key * b
+        results = []
+        for i in range(b):
+            token_int = ids[i]
+            if tokenizer is None:
+                results.append({"key": key[i], "token_int": token_int})
+                continue
+            token = tokenizer.ids2tokens(token_int)
+            text = tokenizer.tokens2text(token)
+            try:
+                from funasr.utils import postprocess_utils  # noqa: WPS433 (host application; text only)
+
+                text, _ = postprocess_utils.sentence_postprocess(token)
+            except ImportError:
+                pass
+            results.append({"key": key[i], "token": token, "text": text})
+        return results, meta_data
+
+
+class CTC(CTCInference, nn.Module):
+    """Stand-alone `model_classes["CTC"]` (funasr/models/ctc/model.py:17-72) for hosts without the reference package:
+    encoder by registry key + `ctc.ctc_lo`, the reference's state_dict keys."""
+
+    def __init__(self, specaug=None, specaug_conf=None, normalize=None, normalize_conf=None, encoder: str = None,
+                 encoder_conf: dict = None, ctc_conf: dict = None, input_size: int = 80, vocab_size: int = -1,
+                 ignore_id: int = -1, blank_id: int = 0, sos: int = 1, eos: int = 2, length_normalized_loss: bool = False,
+                 **kwargs):
+        super().__init__()
+        cls = DROPIN_CLASSES.get(("encoder_classes", encoder))
+        if cls is None:
+            raise NotImplementedError("funasr_b200.CTC: encoder %r has no B200 implementation" % (encoder,))
+        self.encoder = cls(input_size=input_size, **(encoder_conf or {}))
+        self.ctc = _CTCHead(vocab_size, self.encoder.output_size())
+        self.blank_id, self.sos, self.eos, self.vocab_size, self.ignore_id = blank_id, sos, eos, vocab_size, ignore_id
+
+    def forward(self, *args, **kwargs):
+        raise NotImplementedError("funasr_b200.CTC: training / loss computation is outside the accelerated path")
+
+
+DROPIN_CLASSES[("model_classes", "CTC")] = CTC
+
+
 def _model_class(key: str, cls):
     """The class registered under model_classes[key]: the reference's own class with `inference` replaced
     when the reference is importable (construction, checkpoints and training stay the reference's), else the
@@ -738,6 +836,12 @@ def _model_class(key: str, cls):
             return cls
         return type("SenseVoiceSmall", (SenseVoiceInference, ref_sv), {"__doc__": SenseVoiceInference.__doc__,
                                                                         "__module__": __name__})
+    if cls is CTC:
+        try:
+            from funasr.models.ctc.model import Transformer as ref_ctc  # noqa: WPS433 (registered as "CTC", model.py:17)
+        except ImportError:
+            return cls
+        return type("CTC", (CTCInference, ref_ctc), {"__doc__": CTCInference.__doc__, "__module__": __name__})
     return cls
 
 

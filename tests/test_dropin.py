@@ -408,3 +408,60 @@ def test_conformer_dropin_padded_forward_matches_oracle(conformer_sd):
         got = out[b, : want.shape[0]].cpu()
         assert float((got - want).abs().max() / want.abs().max()) < 1e-3
         assert float(out[b, want.shape[0]:].abs().max()) == 0.0 if want.shape[0] < out.shape[1] else True
+
+
+class _CtcTokenizer:
+    def ids2tokens(self, ids):
+        return ["t%d" % i for i in ids]
+
+    def tokens2text(self, tokens):
+        return " ".join(tokens)
+
+
+def test_standalone_ctc_model_has_the_reference_state_dict_and_fails_loudly_on_cpu():
+    m = dropin.CTC(encoder="ConformerEncoder", encoder_conf=dict(CONF_ENC, num_blocks=1), input_size=80, vocab_size=50)
+    keys = {k for k in m.state_dict() if not k.endswith("num_batches_tracked")}
+    assert keys == set(params.conformer_ctc_shapes(50, num_blocks=1))
+    fe = dropin.WavFrontend(cmvn_file=None, window="hamming", lfr_m=1, lfr_n=1, dither=0.0)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m.inference([synth.synth_waveform(0, 16000)], key=["a"], tokenizer=None, frontend=fe, device="cpu")
+
+
+@pytest.mark.skipif(not reference_available(), reason="reference tree not present (GPU box)")
+def test_install_wraps_the_reference_ctc_model_class():
+    from ref_loader import import_reference
+
+    import_reference()
+    from funasr.register import tables
+
+    saved = (dict(tables.model_classes), dict(tables.encoder_classes), dict(tables.frontend_classes),
+             dict(tables.predictor_classes), dict(tables.decoder_classes))
+    try:
+        dropin.install(tables)
+        cls = tables.model_classes["CTC"]
+        from funasr.models.ctc.model import Transformer as ref_ctc
+
+        assert issubclass(cls, ref_ctc) and issubclass(cls, dropin.CTCInference)
+        m = cls(encoder="ConformerEncoder", encoder_conf=dict(CONF_ENC, num_blocks=1), input_size=80, vocab_size=50)
+        assert isinstance(m.encoder, dropin.ConformerEncoder)
+    finally:
+        for table, old in zip((tables.model_classes, tables.encoder_classes, tables.frontend_classes,
+                               tables.predictor_classes, tables.decoder_classes), saved):
+            table.clear()
+            table.update(old)
+
+
+@pytest.mark.gpu
+def test_ctc_model_inference_override_matches_golden(conformer_sd, golden_dir):
+    g = np.load(os.path.join(golden_dir, "conformer.npz"))
+    m = dropin.CTC(encoder="ConformerEncoder", encoder_conf=CONF_ENC, input_size=80, vocab_size=4234)
+    missing = m.load_state_dict(conformer_sd, strict=False)
+    assert not missing.unexpected_keys and all(k.endswith("num_batches_tracked") for k in missing.missing_keys)
+    m = m.cuda().eval()
+    fe = dropin.WavFrontend(cmvn_file=None, window="hamming", lfr_m=1, lfr_n=1, dither=0.0)
+    waves = [synth.synth_waveform(*(int(v) for v in g["case_%d" % ci])) for ci in (0, 1)]
+    results, meta = m.inference(waves, key=["a", "b"], tokenizer=_CtcTokenizer(), frontend=fe, device="cuda")
+    assert [r["key"] for r in results] == ["a", "b"]
+    for ci, r in enumerate(results):
+        assert r["token"] == ["t%d" % i for i in g["ids_%d" % ci].tolist()]
+    assert meta["batch_data_time"] > 0
