@@ -89,3 +89,26 @@ def recognize_sharded(engine, waves, rank: int, world_size: int, group=None):
     if merged is None:
         return None
     return [merged[i] for i in range(len(waves))]
+
+
+def slice_segments(speech, segments_ms):
+    """Waveforms of VAD segments `[[beg_ms, end_ms], ...]` of one long recording, cut like the reference's
+    `slice_padding_audio_samples` (funasr/utils/vad_utils.py:21-33: 16 samples per millisecond, end clipped to the
+    recording)."""
+    n = int(speech.shape[0])
+    out = []
+    for beg_ms, end_ms in segments_ms:
+        b = int(beg_ms * 16)
+        e = min(int(end_ms * 16), n)
+        out.append(speech[b:e])
+    return out
+
+
+def recognize_segments(engine, speech, segments_ms):
+    """Second stage of the reference's long-audio pipeline (`AutoModel.inference_with_vad`,
+    funasr/auto/auto_model.py:400-470: VAD segments sorted by duration, batched under `batch_size_s`, one
+    `inference` call per batch, results put back in time order) as ONE call into the packed engine: every segment
+    of the recording goes through `engine.recognize`, which length-sorts and packs them under its row budget, and
+    the token ids come back in segment order.  Because each segment is computed with batch-1 semantics the result
+    does not depend on how the segments were grouped."""
+    return engine.recognize(slice_segments(speech, segments_ms))

@@ -211,3 +211,16 @@ def test_sensevoice_ragged_batch_matches_oracle(sv_eng, sensevoice_sd, cmvn):
             assert ids == []
             continue
         assert ids == O.sense_voice_recognize(torch.from_numpy(w), sensevoice_sd, cmvn, language="zh", textnorm="woitn")
+
+
+def test_vad_segments_second_stage_matches_oracle(eng_fp32, paraformer_sd, cmvn):
+    """The long-audio pipeline's second stage (AutoModel.inference_with_vad, funasr/auto/auto_model.py:400-470):
+    segments of one recording, out of duration order, as one packed call == the oracle on each slice."""
+    from funasr_b200 import schedule
+
+    speech = synth.synth_waveform(70, 16000 * 9)
+    segs = [[300, 2400], [2500, 7000], [7100, 8100], [8200, 8999]]
+    got = schedule.recognize_segments(eng_fp32, speech, segs)
+    for ids, w in zip(got, schedule.slice_segments(speech, segs)):
+        with torch.no_grad():
+            assert ids == O.recognize(torch.from_numpy(w.copy()), paraformer_sd, cmvn)

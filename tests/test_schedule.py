@@ -70,3 +70,29 @@ def test_recognize_sharded_two_ranks_gloo(tmp_path):
     got = torch.load(out_path)
     waves = [synth.synth_waveform(i, n) for i, n in enumerate(lens)]
     assert got == _FakeEngine().recognize(waves)
+
+
+def test_slice_segments_matches_reference_slicing():
+    speech = np.arange(16000 * 3, dtype=np.float32)
+    segs = [[0, 500], [480, 1999], [2500, 3500], [100, 100]]
+    got = schedule.slice_segments(speech, segs)
+    assert [len(x) for x in got] == [8000, 24304, 8000, 0]
+    assert got[1][0] == 480 * 16 and got[2][-1] == len(speech) - 1
+    ref_root = os.environ.get("FUNASR_REFERENCE_ROOT", "/root/reference")
+    path = os.path.join(ref_root, "funasr", "utils", "vad_utils.py")
+    if os.path.exists(path):  # the reference's own slicer (imports torch only)
+        import importlib.util
+
+        spec = importlib.util.spec_from_file_location("ref_vad_utils", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        want, want_len = mod.slice_padding_audio_samples(speech, len(speech), [(s, i) for i, s in enumerate(segs)])
+        assert [len(x) for x in want] == [len(x) for x in got]
+        assert all(np.array_equal(a, b) for a, b in zip(want, got))
+
+
+def test_recognize_segments_keeps_segment_order():
+    speech = synth.synth_waveform(3, 16000 * 4)
+    segs = [[0, 900], [1000, 3900], [3000, 3200]]
+    got = schedule.recognize_segments(_FakeEngine(), speech, segs)
+    assert got == _FakeEngine().recognize(schedule.slice_segments(speech, segs))
