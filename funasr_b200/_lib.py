@@ -44,7 +44,18 @@ SIGNATURES = {
     "fb200_argmax_logprob": [_P, _I, _I, _I, _P, _P, _P],
     "fb200_ctc_collapse": [_P, _P, _I, c_uint32, _I, _P, _P, _P],
 }
-EXPORTS = sorted(list(SIGNATURES) + ["fb200_version", "fb200_last_error", "fb200_launch_count",
+# native offline runtime (csrc/runtime.cu): name -> (argument types, return type)
+RUNTIME_SIGNATURES = {
+    "fb200_offline_init": ([ctypes.c_char_p, _I, _I, _I], _P),
+    "fb200_offline_infer": ([_P, ctypes.POINTER(_P), ctypes.POINTER(ctypes.c_int32), _I], _P),
+    "fb200_offline_infer_buffer": ([_P, ctypes.c_char_p, _I, _I], _P),
+    "fb200_result_count": ([_P], _I),
+    "fb200_result_text": ([_P, _I], ctypes.c_char_p),
+    "fb200_result_ids": ([_P, _I, ctypes.POINTER(_I)], ctypes.POINTER(ctypes.c_int32)),
+    "fb200_free_result": ([_P], None),
+    "fb200_offline_uninit": ([_P], None),
+}
+EXPORTS = sorted(list(SIGNATURES) + list(RUNTIME_SIGNATURES) + ["fb200_version", "fb200_last_error", "fb200_launch_count",
                   "fb200_profile_enable", "fb200_profile_read"])
 PROFILE_KINDS = ["fbank", "lfr_cmvn", "scale_add_pe", "layernorm", "split_rows", "fsmn", "gemm", "attention",
                  "cif_alpha", "cif_scan", "cif_integrate", "argmax_logprob", "ctc_collapse", "conv2d_sub1", "glu_dwconv",
@@ -67,6 +78,10 @@ def load():
         fn = getattr(lib, name)
         fn.argtypes = args
         fn.restype = c_int
+    for name, (args, ret) in RUNTIME_SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.argtypes = args
+        fn.restype = ret
     lib.fb200_version.restype = c_int
     lib.fb200_last_error.restype = ctypes.c_char_p
     lib.fb200_launch_count.argtypes = [c_int]

@@ -1,0 +1,663 @@
+// Native offline recogniser: the packed Paraformer path (frontend -> SAN-M encoder -> CIF predictor -> SAN-M decoder
+// -> greedy pick) orchestrated in C++ over the kernels of this library -- no Python, no torch.  It is the B200
+// counterpart of the reference's C++ offline runtime (runtime/onnxruntime/include/funasrruntime.h:99-114:
+// FunOfflineInit / FunOfflineInferBuffer / FunASRGetResult / FunASRGetRetNumber / FunASRFreeResult / FunOfflineUninit,
+// implemented over ONNX Runtime / libtorch in runtime/onnxruntime/src/paraformer.cpp and paraformer-torch.cpp).
+//
+// Model directory (data formats either side of the path):
+//   model.fb200   weights under the reference's state_dict names, fp32, written by tools/export_model.py from a
+//                 model.pt / state_dict (the reference's C++ runtime reads model.pt through libtorch, which this
+//                 library does not link); also carries the frontend tables (window, mel bank) the exporter computed
+//   am.mvn        Kaldi-nnet CMVN text, parsed here like runtime/onnxruntime/src/paraformer.cpp:314-349
+//   tokens.json   optional JSON array of token strings (runtime/onnxruntime/src/vocab.cpp); without it the result
+//                 text is the space-separated token ids
+//
+// The op sequence is the one of funasr_b200/engine.py (ParaformerEngine.forward_packed), which cites the reference
+// model code line by line; tests/test_gpu_runtime.py checks that both produce identical token ids.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <fstream>
+#include <map>
+#include <numeric>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace fb200 {
+namespace rt {
+
+typedef __nv_bfloat16 bf16;
+
+#define RT_CUDA(call)                                                                   \
+  do {                                                                                  \
+    cudaError_t e_ = (call);                                                            \
+    if (e_ != cudaSuccess) {                                                            \
+      set_error("runtime: %s failed: %s", #call, cudaGetErrorString(e_));               \
+      return FB200_ECUDA;                                                               \
+    }                                                                                   \
+  } while (0)
+#define RT_OK(call)            \
+  do {                         \
+    int rc_ = (call);          \
+    if (rc_ != FB200_OK) return rc_; \
+  } while (0)
+
+static inline int kp64(int k) { return (k + 63) / 64 * 64; }
+
+// Bump allocator over one device slab: per-batch activations (reset before every batch).
+struct Arena {
+  char* base = nullptr;
+  size_t cap = 0, off = 0;
+  template <typename T>
+  T* get(size_t n) {  // never fails; the caller checks ok() before touching what it was given
+    size_t bytes = (n * sizeof(T) + 255) / 256 * 256;
+    T* p = reinterpret_cast<T*>(base + off);
+    off += bytes;
+    return p;
+  }
+  bool ok() const { return off <= cap; }
+};
+
+struct HostTensor {
+  std::vector<int64_t> shape;
+  std::vector<float> data;
+  int64_t numel() const { return std::accumulate(shape.begin(), shape.end(), (int64_t)1, std::multiplies<int64_t>()); }
+};
+
+struct Linear {  // bf16 split weight [taps * n, nparts * Kp] + fp32 bias
+  bf16* w = nullptr;
+  float* bias = nullptr;
+  int n = 0, k = 0, taps = 1;
+};
+struct Norm {
+  float *g = nullptr, *b = nullptr;
+};
+struct EncLayer {
+  Norm norm1, norm2;
+  Linear qkv, out, w1, w2;
+  float* fsmn = nullptr;
+  int fsmn_k = 0, din = 0;
+};
+struct DecLayer {
+  Norm norm1, ffn_norm, norm2, norm3;
+  Linear w1, w2, q, out;
+  float* fsmn = nullptr;
+  int fsmn_k = 0;
+  bool has_fsmn = false, has_src = false;
+  int src_index = -1;
+};
+
+struct Result {
+  std::vector<std::vector<int32_t>> ids;
+  std::vector<std::string> text;
+};
+
+class Recognizer {
+ public:
+  ~Recognizer() {
+    for (void* p : owned_) cudaFree(p);
+    if (arena_.base) cudaFree(arena_.base);
+    if (stream_) cudaStreamDestroy(stream_);
+  }
+  int init(const std::string& dir, int device, int nparts, int max_rows);
+  int recognize(const float* const* waves, const int* lens, int n, Result* res);
+
+ private:
+  int load_file(const std::string& path);
+  int load_cmvn(const std::string& path);
+  void load_tokens(const std::string& path);
+  const HostTensor* find(const std::string& name) const {
+    auto it = host_.find(name);
+    return it == host_.end() ? nullptr : &it->second;
+  }
+  bool has(const std::string& name) const { return host_.count(name) != 0; }
+  int upload(const std::vector<float>& v, float** out);
+  int make_norm(const std::string& prefix, Norm* n);
+  int make_linear(const std::string& wname, const std::string& bname, Linear* l);
+  int make_linear_from(const std::vector<float>& w, int rows, int k, int taps, const std::vector<float>* bias, Linear* l);
+  int forward(const std::vector<int>& batch, const float* const* waves, const int* lens, Result* res);
+
+  int device_ = 0, np_ = 2, max_rows_ = 18944, heads_ = 4;
+  int d_ = 512, din_ = 560, ff_ = 2048, vocab_ = 0, n_mels_ = 80, lfr_m_ = 7, lfr_n_ = 6;
+  int frame_len_ = 400, frame_shift_ = 160, nfft_ = 512;
+  float eps_ = 1e-12f, tail_ = 0.45f;
+  cudaStream_t stream_ = nullptr;
+  std::map<std::string, HostTensor> host_;
+  std::vector<void*> owned_;
+  Arena arena_;
+  float *window_ = nullptr, *mel_ = nullptr, *pe_inv_ = nullptr, *shift_ = nullptr, *scale_ = nullptr;
+  std::vector<EncLayer> enc_;
+  Norm enc_after_;
+  Linear cif_conv_;
+  float *cif_w_ = nullptr, *cif_b_ = nullptr;
+  std::vector<DecLayer> dec_;
+  Norm dec_after_;
+  Linear dec_out_, dec_kv_;
+  std::vector<std::string> tokens_;
+};
+
+// ---------------------------------------------------------------- loading -----------------
+int Recognizer::load_file(const std::string& path) {
+  std::ifstream f(path, std::ios::binary);
+  if (!f) {
+    set_error("runtime: cannot open %s", path.c_str());
+    return FB200_EINVAL;
+  }
+  char magic[8];
+  uint32_t count = 0;
+  f.read(magic, 8);
+  f.read(reinterpret_cast<char*>(&count), 4);
+  if (!f || memcmp(magic, "FB200W1\0", 8) != 0) {
+    set_error("runtime: %s is not a model.fb200 file", path.c_str());
+    return FB200_EINVAL;
+  }
+  for (uint32_t i = 0; i < count; ++i) {
+    uint16_t nlen = 0;
+    uint8_t ndim = 0;
+    f.read(reinterpret_cast<char*>(&nlen), 2);
+    std::string name(nlen, '\0');
+    f.read(&name[0], nlen);
+    f.read(reinterpret_cast<char*>(&ndim), 1);
+    HostTensor t;
+    t.shape.resize(ndim);
+    f.read(reinterpret_cast<char*>(t.shape.data()), 8 * ndim);
+    t.data.resize((size_t)t.numel());
+    f.read(reinterpret_cast<char*>(t.data.data()), 4 * (std::streamsize)t.data.size());
+    if (!f) {
+      set_error("runtime: %s is truncated at tensor %u (%s)", path.c_str(), i, name.c_str());
+      return FB200_EINVAL;
+    }
+    host_[name] = std::move(t);
+  }
+  return FB200_OK;
+}
+
+// Kaldi-nnet am.mvn: the <LearnRateCoef> line after <AddShift> is the shift, after <Rescale> the scale; values are
+// fields [3 : -1] of that line (funasr/frontends/wav_frontend.py:15-38, runtime/onnxruntime/src/paraformer.cpp:314-349).
+int Recognizer::load_cmvn(const std::string& path) {
+  std::ifstream f(path);
+  if (!f) return FB200_EINVAL;  // optional
+  std::vector<std::string> lines;
+  for (std::string ln; std::getline(f, ln);) lines.push_back(ln);
+  std::vector<float> shift, scale;
+  for (size_t i = 0; i + 1 < lines.size(); ++i) {
+    std::istringstream a(lines[i]);
+    std::string tag;
+    a >> tag;
+    if (tag != "<AddShift>" && tag != "<Rescale>") continue;
+    std::istringstream b(lines[i + 1]);
+    std::vector<std::string> fld;
+    for (std::string s; b >> s;) fld.push_back(s);
+    if (fld.empty() || fld[0] != "<LearnRateCoef>" || fld.size() < 5) continue;
+    std::vector<float>& dst = tag == "<AddShift>" ? shift : scale;
+    for (size_t j = 3; j + 1 < fld.size(); ++j) dst.push_back((float)atof(fld[j].c_str()));
+  }
+  if (shift.empty() || shift.size() != scale.size()) {
+    set_error("runtime: %s holds no <AddShift>/<Rescale> statistics", path.c_str());
+    return FB200_EINVAL;
+  }
+  shift.resize(din_);
+  scale.resize(din_);
+  RT_OK(upload(shift, &shift_));
+  RT_OK(upload(scale, &scale_));
+  return FB200_OK;
+}
+
+// tokens.json: a JSON array of strings (\" \\ \uXXXX escapes of the BMP handled).
+void Recognizer::load_tokens(const std::string& path) {
+  std::ifstream f(path);
+  if (!f) return;
+  std::stringstream ss;
+  ss << f.rdbuf();
+  const std::string s = ss.str();
+  size_t i = 0;
+  while (i < s.size()) {
+    if (s[i] != '"') {
+      ++i;
+      continue;
+    }
+    std::string tok;
+    for (++i; i < s.size() && s[i] != '"'; ++i) {
+      if (s[i] != '\\' || i + 1 >= s.size()) {
+        tok.push_back(s[i]);
+        continue;
+      }
+      const char c = s[++i];
+      if (c == 'u' && i + 4 < s.size()) {
+        const unsigned cp = (unsigned)strtoul(s.substr(i + 1, 4).c_str(), nullptr, 16);
+        i += 4;
+        if (cp < 0x80) tok.push_back((char)cp);
+        else if (cp < 0x800) tok.push_back((char)(0xC0 | (cp >> 6))), tok.push_back((char)(0x80 | (cp & 0x3F)));
+        else tok.push_back((char)(0xE0 | (cp >> 12))), tok.push_back((char)(0x80 | ((cp >> 6) & 0x3F))), tok.push_back((char)(0x80 | (cp & 0x3F)));
+      } else {
+        tok.push_back(c == 'n' ? '\n' : c == 't' ? '\t' : c);
+      }
+    }
+    ++i;
+    tokens_.push_back(tok);
+  }
+}
+
+int Recognizer::upload(const std::vector<float>& v, float** out) {
+  float* p = nullptr;
+  RT_CUDA(cudaMalloc(&p, std::max<size_t>(v.size(), 1) * sizeof(float)));
+  owned_.push_back(p);
+  RT_CUDA(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(float), cudaMemcpyHostToDevice, stream_));
+  RT_CUDA(cudaStreamSynchronize(stream_));
+  *out = p;
+  return FB200_OK;
+}
+
+int Recognizer::make_norm(const std::string& prefix, Norm* n) {
+  const HostTensor *g = find(prefix + "weight"), *b = find(prefix + "bias");
+  if (!g || !b) {
+    set_error("runtime: missing %sweight / bias", prefix.c_str());
+    return FB200_EINVAL;
+  }
+  RT_OK(upload(g->data, &n->g));
+  return upload(b->data, &n->b);
+}
+
+int Recognizer::make_linear_from(const std::vector<float>& w, int rows, int k, int taps, const std::vector<float>* bias, Linear* l) {
+  float* tmp = nullptr;
+  RT_CUDA(cudaMalloc(&tmp, w.size() * sizeof(float)));
+  RT_CUDA(cudaMemcpyAsync(tmp, w.data(), w.size() * sizeof(float), cudaMemcpyHostToDevice, stream_));
+  bf16* sp = nullptr;
+  RT_CUDA(cudaMalloc(&sp, (size_t)rows * np_ * kp64(k) * sizeof(bf16)));
+  owned_.push_back(sp);
+  int rc = fb200_split_weight(tmp, rows, k, sp, np_, stream_);
+  cudaStreamSynchronize(stream_);
+  cudaFree(tmp);
+  RT_OK(rc);
+  l->w = sp;
+  l->n = rows / taps;
+  l->k = k;
+  l->taps = taps;
+  l->bias = nullptr;
+  if (bias) RT_OK(upload(*bias, &l->bias));
+  return FB200_OK;
+}
+
+int Recognizer::make_linear(const std::string& wname, const std::string& bname, Linear* l) {
+  const HostTensor* w = find(wname);
+  if (!w) {
+    set_error("runtime: missing %s", wname.c_str());
+    return FB200_EINVAL;
+  }
+  const HostTensor* b = bname.empty() ? nullptr : find(bname);
+  if (w->shape.size() == 3) {  // Conv1d [out, in, taps] -> [taps][out, in]
+    const int out = (int)w->shape[0], in = (int)w->shape[1], taps = (int)w->shape[2];
+    std::vector<float> r((size_t)taps * out * in);
+    for (int o = 0; o < out; ++o)
+      for (int c = 0; c < in; ++c)
+        for (int t = 0; t < taps; ++t) r[((size_t)t * out + o) * in + c] = w->data[((size_t)o * in + c) * taps + t];
+    return make_linear_from(r, taps * out, in, taps, b ? &b->data : nullptr, l);
+  }
+  return make_linear_from(w->data, (int)w->shape[0], (int)w->shape[1], 1, b ? &b->data : nullptr, l);
+}
+
+int Recognizer::init(const std::string& dir, int device, int nparts, int max_rows) {
+  device_ = device;
+  np_ = nparts;
+  max_rows_ = max_rows;
+  RT_CUDA(cudaSetDevice(device_));
+  RT_CUDA(cudaStreamCreate(&stream_));
+  RT_OK(load_file(dir + "/model.fb200"));
+  load_tokens(dir + "/tokens.json");
+  const HostTensor *win = find("frontend.window"), *mel = find("frontend.mel"), *pe = find("frontend.pe_inv");
+  const HostTensor* meta = find("frontend.meta");  // [lfr_m, lfr_n, frame_shift, nfft, heads, tail_threshold]
+  if (!win || !mel || !pe || !meta || meta->data.size() < 6) {
+    set_error("runtime: model.fb200 lacks the frontend tables (frontend.window / mel / pe_inv / meta)");
+    return FB200_EINVAL;
+  }
+  frame_len_ = (int)win->data.size();
+  n_mels_ = (int)mel->shape[0];
+  lfr_m_ = (int)meta->data[0];
+  lfr_n_ = (int)meta->data[1];
+  frame_shift_ = (int)meta->data[2];
+  nfft_ = (int)meta->data[3];
+  heads_ = (int)meta->data[4];
+  tail_ = meta->data[5];
+  din_ = n_mels_ * lfr_m_;
+  RT_OK(upload(win->data, &window_));
+  RT_OK(upload(mel->data, &mel_));
+  RT_OK(upload(pe->data, &pe_inv_));
+  if (load_cmvn(dir + "/am.mvn") != FB200_OK) {
+    const HostTensor *sh = find("frontend.cmvn_shift"), *sc = find("frontend.cmvn_scale");
+    if (sh && sc) {
+      RT_OK(upload(sh->data, &shift_));
+      RT_OK(upload(sc->data, &scale_));
+    }
+  }
+  // encoder
+  for (const char* group : {"encoder.encoders0.", "encoder.encoders."}) {
+    for (int i = 0;; ++i) {
+      const std::string p = std::string(group) + std::to_string(i) + ".";
+      if (!has(p + "norm1.weight")) break;
+      EncLayer ly;
+      RT_OK(make_norm(p + "norm1.", &ly.norm1));
+      RT_OK(make_norm(p + "norm2.", &ly.norm2));
+      RT_OK(make_linear(p + "self_attn.linear_q_k_v.weight", p + "self_attn.linear_q_k_v.bias", &ly.qkv));
+      RT_OK(make_linear(p + "self_attn.linear_out.weight", p + "self_attn.linear_out.bias", &ly.out));
+      RT_OK(make_linear(p + "feed_forward.w_1.weight", p + "feed_forward.w_1.bias", &ly.w1));
+      RT_OK(make_linear(p + "feed_forward.w_2.weight", p + "feed_forward.w_2.bias", &ly.w2));
+      const HostTensor* fw = find(p + "self_attn.fsmn_block.weight");
+      if (!fw) {
+        set_error("runtime: missing %sself_attn.fsmn_block.weight", p.c_str());
+        return FB200_EINVAL;
+      }
+      ly.fsmn_k = (int)fw->shape.back();
+      RT_OK(upload(fw->data, &ly.fsmn));
+      ly.din = ly.qkv.k;
+      enc_.push_back(ly);
+    }
+  }
+  if (enc_.empty()) {
+    set_error("runtime: model.fb200 holds no encoder layers");
+    return FB200_EINVAL;
+  }
+  d_ = enc_[0].out.n;
+  ff_ = enc_[0].w1.n;
+  RT_OK(make_norm("encoder.after_norm.", &enc_after_));
+  // predictor
+  RT_OK(make_linear("predictor.cif_conv1d.weight", "predictor.cif_conv1d.bias", &cif_conv_));
+  RT_OK(upload(find("predictor.cif_output.weight")->data, &cif_w_));
+  RT_OK(upload(find("predictor.cif_output.bias")->data, &cif_b_));
+  // decoder
+  std::vector<float> kvw, kvb;
+  int n_src = 0;
+  for (const char* group : {"decoder.decoders.", "decoder.decoders2.", "decoder.decoders3."}) {
+    for (int i = 0;; ++i) {
+      const std::string p = std::string(group) + std::to_string(i) + ".";
+      if (!has(p + "norm1.weight")) break;
+      DecLayer ly;
+      RT_OK(make_norm(p + "norm1.", &ly.norm1));
+      RT_OK(make_linear(p + "feed_forward.w_1.weight", p + "feed_forward.w_1.bias", &ly.w1));
+      RT_OK(make_norm(p + "feed_forward.norm.", &ly.ffn_norm));
+      RT_OK(make_linear(p + "feed_forward.w_2.weight", has(p + "feed_forward.w_2.bias") ? p + "feed_forward.w_2.bias" : "", &ly.w2));
+      ly.has_fsmn = has(p + "self_attn.fsmn_block.weight");
+      ly.has_src = has(p + "src_attn.linear_q.weight");
+      if (ly.has_fsmn) {
+        RT_OK(make_norm(p + "norm2.", &ly.norm2));
+        const HostTensor* fw = find(p + "self_attn.fsmn_block.weight");
+        ly.fsmn_k = (int)fw->shape.back();
+        RT_OK(upload(fw->data, &ly.fsmn));
+      }
+      if (ly.has_src) {
+        RT_OK(make_norm(p + "norm3.", &ly.norm3));
+        RT_OK(make_linear(p + "src_attn.linear_q.weight", p + "src_attn.linear_q.bias", &ly.q));
+        RT_OK(make_linear(p + "src_attn.linear_out.weight", p + "src_attn.linear_out.bias", &ly.out));
+        const HostTensor *w = find(p + "src_attn.linear_k_v.weight"), *b = find(p + "src_attn.linear_k_v.bias");
+        kvw.insert(kvw.end(), w->data.begin(), w->data.end());
+        kvb.insert(kvb.end(), b->data.begin(), b->data.end());
+        ly.src_index = n_src++;
+      }
+      dec_.push_back(ly);
+    }
+  }
+  // K / V projections of the memory for every cross-attention layer as ONE contraction
+  RT_OK(make_linear_from(kvw, n_src * 2 * d_, d_, 1, &kvb, &dec_kv_));
+  RT_OK(make_norm("decoder.after_norm.", &dec_after_));
+  RT_OK(make_linear("decoder.output_layer.weight", "decoder.output_layer.bias", &dec_out_));
+  vocab_ = dec_out_.n;
+  host_.clear();  // the fp32 host copies are no longer needed
+  // activation slab: sized for one batch of max_rows encoder rows (decoder rows <= encoder rows)
+  const size_t r = (size_t)max_rows_ + 64, wave_bytes = (size_t)r * lfr_n_ * frame_shift_ * 4 + (size_t)frame_len_ * 4 * 4096;
+  size_t cap = wave_bytes + r * lfr_n_ * n_mels_ * 4 + r * din_ * 4  // wave, fbank, feats
+               + r * (size_t)np_ * (kp64(din_) + 7 * kp64(d_) + 2 * kp64(ff_) + kp64(3 * d_) + kp64(dec_kv_.n)) * 2  // splits
+               + r * (size_t)d_ * 4 * 16 + r * (size_t)ff_ * 4 + r * (size_t)((vocab_ + 3) / 4 * 4) * 4 + (64u << 20);
+  RT_CUDA(cudaMalloc(&arena_.base, cap));
+  arena_.cap = cap;
+  RT_CUDA(cudaStreamSynchronize(stream_));
+  return FB200_OK;
+}
+
+// ---------------------------------------------------------------- one packed batch --------
+int Recognizer::forward(const std::vector<int>& batch, const float* const* waves, const int* lens, Result* res) {
+  const int B = (int)batch.size(), np = np_, d = d_;
+  void* st = stream_;
+  arena_.off = 0;
+  std::vector<int64_t> cu_samples(B + 1, 0);
+  std::vector<int32_t> cu_frames(B + 1, 0), cu_rows(B + 1, 0);
+  int max_t = 0;
+  for (int i = 0; i < B; ++i) {
+    const int n = lens[batch[i]];
+    const int frames = n < frame_len_ ? 0 : 1 + (n - frame_len_) / frame_shift_;
+    const int rows = (frames + lfr_n_ - 1) / lfr_n_;
+    cu_samples[i + 1] = cu_samples[i] + n;
+    cu_frames[i + 1] = cu_frames[i] + frames;
+    cu_rows[i + 1] = cu_rows[i] + rows;
+    max_t = std::max(max_t, rows);
+  }
+  const int F = cu_frames[B], R = cu_rows[B];
+  float* wave = arena_.get<float>((size_t)cu_samples[B]);
+  int64_t* d_cus = arena_.get<int64_t>(B + 1);
+  int32_t *d_cuf = arena_.get<int32_t>(B + 1), *d_cur = arena_.get<int32_t>(B + 1), *d_cut = arena_.get<int32_t>(B + 1);
+  float* fb = arena_.get<float>((size_t)F * n_mels_);
+  float* feats = arena_.get<float>((size_t)R * din_);
+  const int wd = np * kp64(d), wdin = np * kp64(din_), wff = np * kp64(ff_), wqkv = np * kp64(3 * d);
+  bf16 *xs0 = arena_.get<bf16>((size_t)R * wdin), *xs = arena_.get<bf16>((size_t)R * wd), *h = arena_.get<bf16>((size_t)R * wff);
+  bf16* qkv = arena_.get<bf16>((size_t)R * wqkv);
+  float *v = arena_.get<float>((size_t)R * d), *mem = arena_.get<float>((size_t)R * d), *x0 = arena_.get<float>((size_t)R * d),
+        *x1 = arena_.get<float>((size_t)R * d), *enc = arena_.get<float>((size_t)R * d);
+  bf16* halo = arena_.get<bf16>((size_t)(R + B + 1) * wd);
+  const int plan_cap = R / 128 + B;
+  int32_t* plan = arena_.get<int32_t>(4 + 4 * (size_t)plan_cap);
+  float *conv = arena_.get<float>((size_t)(R + B) * d), *alphas = arena_.get<float>(R), *fire_rem = arena_.get<float>(R + B);
+  int32_t *token_num = arena_.get<int32_t>(B), *fire_pos = arena_.get<int32_t>(R + B);
+  if (!arena_.ok()) {
+    set_error("runtime: activation slab too small for a batch of %d rows", R);
+    return FB200_EINVAL;
+  }
+  // host -> device
+  for (int i = 0; i < B; ++i)
+    RT_CUDA(cudaMemcpyAsync(wave + cu_samples[i], waves[batch[i]], (size_t)lens[batch[i]] * 4, cudaMemcpyHostToDevice, stream_));
+  RT_CUDA(cudaMemcpyAsync(d_cus, cu_samples.data(), (B + 1) * 8, cudaMemcpyHostToDevice, stream_));
+  RT_CUDA(cudaMemcpyAsync(d_cuf, cu_frames.data(), (B + 1) * 4, cudaMemcpyHostToDevice, stream_));
+  RT_CUDA(cudaMemcpyAsync(d_cur, cu_rows.data(), (B + 1) * 4, cudaMemcpyHostToDevice, stream_));
+  // frontend + encoder prologue (x * sqrt(d) + PE)
+  RT_OK(fb200_fbank(wave, d_cus, d_cuf, B, F, window_, frame_len_, frame_shift_, nfft_, mel_, n_mels_, 32768.f, 0.97f, fb, st));
+  RT_OK(fb200_lfr_cmvn(fb, d_cuf, d_cur, B, R, n_mels_, lfr_m_, lfr_n_, shift_, scale_, pe_inv_, sqrtf((float)d), 0, feats, din_, st));
+  // encoder
+  RT_OK(fb200_attention_plan(d_cur, d_cur, B, plan, plan_cap, st));
+  const float scale = 1.f / sqrtf((float)(d / heads_));
+  const float* x = feats;
+  int ldx = din_;
+  for (const EncLayer& ly : enc_) {
+    bf16* a = ly.din == d ? xs : xs0;
+    RT_OK(fb200_layernorm(x, ldx, R, ly.din, ly.norm1.g, ly.norm1.b, eps_, nullptr, 0, a, np, 0, nullptr, 0, st));
+    RT_OK(fb200_gemm(a, R, np, ly.qkv.w, np, R, 3 * d, ly.din, 1, ly.qkv.bias, 0, nullptr, 0, v, d, 2 * d, qkv, np, 0, st));
+    RT_OK(fb200_fsmn(v, d, d_cur, B, R, d, ly.fsmn, ly.fsmn_k, ly.din == d ? x : nullptr, ldx, mem, d, st));
+    RT_OK(fb200_attention(qkv, wqkv, 0, wqkv / np, qkv, wqkv, d, qkv, wqkv, 2 * d, wqkv / np, np, d_cur, d_cur, plan, B, R, R, max_t,
+                          heads_, d / heads_, scale, nullptr, 0, xs, np, 0, st));
+    RT_OK(fb200_gemm(xs, R, np, ly.out.w, np, R, d, d, 1, ly.out.bias, 0, mem, d, x1, d, 0, nullptr, np, 0, st));
+    RT_OK(fb200_layernorm(x1, d, R, d, ly.norm2.g, ly.norm2.b, eps_, nullptr, 0, xs, np, 0, nullptr, 0, st));
+    RT_OK(fb200_gemm(xs, R, np, ly.w1.w, np, R, ff_, d, 1, ly.w1.bias, 1, nullptr, 0, nullptr, 0, 0, h, np, 0, st));
+    RT_OK(fb200_gemm(h, R, np, ly.w2.w, np, R, d, ff_, 1, ly.w2.bias, 0, x1, d, x0, d, 0, nullptr, np, 0, st));
+    x = x0;
+    ldx = d;
+  }
+  RT_OK(fb200_layernorm(x, d, R, d, enc_after_.g, enc_after_.b, eps_, enc, d, halo, np, 1, d_cur, B, st));
+  // predictor: k = 3 conv over the halo layout, alpha head, integrate-and-fire scan
+  RT_OK(fb200_gemm(halo, R + B + 1, np, cif_conv_.w, np, R + B - 1, d, d, 3, cif_conv_.bias, 1, nullptr, 0, conv, d, 0, nullptr, np, 0, st));
+  RT_OK(fb200_cif_alpha(conv, d, d_cur, B, R, d, cif_w_, cif_b_, 1.f, 0.f, alphas, st));
+  RT_OK(fb200_cif_scan(alphas, d_cur, B, tail_, token_num, fire_pos, fire_rem, nullptr, st));
+  std::vector<int32_t> tok(B), cu_tok(B + 1, 0);
+  RT_CUDA(cudaMemcpyAsync(tok.data(), token_num, B * 4, cudaMemcpyDeviceToHost, stream_));
+  RT_CUDA(cudaStreamSynchronize(stream_));  // the one device -> host read before the decoder: [B] token counts
+  int max_l = 0;
+  for (int i = 0; i < B; ++i) cu_tok[i + 1] = cu_tok[i] + tok[i], max_l = std::max(max_l, tok[i]);
+  const int L = cu_tok[B];
+  if (L == 0 || max_l < 1) return FB200_OK;  // no utterance has a token (paraformer/model.py:514-515)
+  RT_CUDA(cudaMemcpyAsync(d_cut, cu_tok.data(), (B + 1) * 4, cudaMemcpyHostToDevice, stream_));
+  float* embeds = arena_.get<float>((size_t)L * d);
+  RT_OK(fb200_cif_integrate(enc, d, alphas, d_cur, d_cut, B, L, d, tail_, fire_pos, fire_rem, embeds, d, st));
+  // decoder
+  const int wkv = np * kp64(dec_kv_.n);
+  bf16 *encs = arena_.get<bf16>((size_t)R * wd), *kv = arena_.get<bf16>((size_t)R * wkv), *qs = arena_.get<bf16>((size_t)L * wd),
+       *ys = arena_.get<bf16>((size_t)L * wd), *hs = arena_.get<bf16>((size_t)L * wff);
+  float *hf = arena_.get<float>((size_t)L * ff_), *t = arena_.get<float>((size_t)L * d), *t2 = arena_.get<float>((size_t)L * d),
+        *n2 = arena_.get<float>((size_t)L * d), *b0 = arena_.get<float>((size_t)L * d), *b1 = arena_.get<float>((size_t)L * d);
+  const int dplan_cap = L / 128 + B;
+  int32_t* dplan = arena_.get<int32_t>(4 + 4 * (size_t)dplan_cap);
+  const int ldv = (vocab_ + 3) / 4 * 4;
+  float* logits = arena_.get<float>((size_t)L * ldv);
+  int32_t* ids = arena_.get<int32_t>(L);
+  float* logp = arena_.get<float>(L);
+  if (!arena_.ok()) {
+    set_error("runtime: activation slab too small for %d tokens", L);
+    return FB200_EINVAL;
+  }
+  RT_OK(fb200_split_rows(enc, d, R, d, encs, np, st));
+  RT_OK(fb200_gemm(encs, R, np, dec_kv_.w, np, R, dec_kv_.n, d, 1, dec_kv_.bias, 0, nullptr, 0, nullptr, 0, 0, kv, np, 0, st));
+  RT_OK(fb200_attention_plan(d_cut, d_cur, B, dplan, dplan_cap, st));
+  const float* y = embeds;
+  for (const DecLayer& ly : dec_) {
+    RT_OK(fb200_layernorm(y, d, L, d, ly.norm1.g, ly.norm1.b, eps_, nullptr, 0, ys, np, 0, nullptr, 0, st));
+    RT_OK(fb200_gemm(ys, L, np, ly.w1.w, np, L, ff_, d, 1, ly.w1.bias, 1, nullptr, 0, hf, ff_, 0, nullptr, np, 0, st));
+    RT_OK(fb200_layernorm(hf, ff_, L, ff_, ly.ffn_norm.g, ly.ffn_norm.b, eps_, nullptr, 0, hs, np, 0, nullptr, 0, st));
+    float* tt = (y == t) ? t2 : t;
+    RT_OK(fb200_gemm(hs, L, np, ly.w2.w, np, L, d, ff_, 1, ly.w2.bias, 0, nullptr, 0, tt, d, 0, nullptr, np, 0, st));
+    if (!ly.has_fsmn) {  // decoders3: FFN only, no residual (paraformer/decoder.py:102-108)
+      y = tt;
+      continue;
+    }
+    RT_OK(fb200_layernorm(tt, d, L, d, ly.norm2.g, ly.norm2.b, eps_, n2, d, nullptr, np, 0, nullptr, 0, st));
+    float* yo = (y == b0) ? b1 : b0;
+    RT_OK(fb200_fsmn(n2, d, d_cut, B, L, d, ly.fsmn, ly.fsmn_k, y, d, yo, d, st));  // x + conv(n2) + n2
+    if (ly.has_src) {
+      RT_OK(fb200_layernorm(yo, d, L, d, ly.norm3.g, ly.norm3.b, eps_, nullptr, 0, ys, np, 0, nullptr, 0, st));
+      RT_OK(fb200_gemm(ys, L, np, ly.q.w, np, L, d, d, 1, ly.q.bias, 0, nullptr, 0, nullptr, 0, 0, qs, np, 0, st));
+      const int j = ly.src_index;
+      RT_OK(fb200_attention(qs, wd, 0, wd / np, kv, wkv, j * 2 * d, kv, wkv, j * 2 * d + d, wkv / np, np, d_cut, d_cur, dplan, B, L, R,
+                            max_l, heads_, d / heads_, scale, nullptr, 0, ys, np, 0, st));
+      float* xo = (yo == b0) ? b1 : b0;
+      RT_OK(fb200_gemm(ys, L, np, ly.out.w, np, L, d, d, 1, ly.out.bias, 0, yo, d, xo, d, 0, nullptr, np, 0, st));
+      y = xo;
+    } else {
+      y = yo;
+    }
+  }
+  RT_OK(fb200_layernorm(y, d, L, d, dec_after_.g, dec_after_.b, eps_, nullptr, 0, ys, np, 0, nullptr, 0, st));
+  RT_OK(fb200_gemm(ys, L, np, dec_out_.w, np, L, vocab_, d, 1, dec_out_.bias, 0, nullptr, 0, logits, ldv, 0, nullptr, np, 0, st));
+  RT_OK(fb200_argmax_logprob(logits, ldv, L, vocab_, ids, logp, st));
+  std::vector<int32_t> h_ids(L);
+  RT_CUDA(cudaMemcpyAsync(h_ids.data(), ids, (size_t)L * 4, cudaMemcpyDeviceToHost, stream_));
+  RT_CUDA(cudaStreamSynchronize(stream_));
+  for (int i = 0; i < B; ++i) {
+    std::vector<int32_t>& out = res->ids[batch[i]];
+    for (int k = cu_tok[i]; k < cu_tok[i + 1]; ++k)
+      if (h_ids[k] > 2) out.push_back(h_ids[k]);  // blank, sos, eos dropped (paraformer/model.py:561-565)
+  }
+  return FB200_OK;
+}
+
+int Recognizer::recognize(const float* const* waves, const int* lens, int n, Result* res) {
+  RT_CUDA(cudaSetDevice(device_));
+  res->ids.assign(n, std::vector<int32_t>());
+  res->text.assign(n, std::string());
+  // length-sorted batches under the packed-row budget (ref. analogue: funasr/auto/auto_model.py:423-459)
+  std::vector<int> rows(n), order;
+  for (int i = 0; i < n; ++i) {
+    const int frames = lens[i] < frame_len_ ? 0 : 1 + (lens[i] - frame_len_) / frame_shift_;
+    rows[i] = (frames + lfr_n_ - 1) / lfr_n_;
+    if (rows[i] >= 1) order.push_back(i);
+  }
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return rows[a] > rows[b]; });
+  std::vector<int> cur;
+  int cur_rows = 0;
+  for (size_t k = 0; k <= order.size(); ++k) {
+    const bool flush = k == order.size() || (!cur.empty() && cur_rows + rows[order[k]] > max_rows_);
+    if (flush && !cur.empty()) {
+      RT_OK(forward(cur, waves, lens, res));
+      cur.clear();
+      cur_rows = 0;
+    }
+    if (k < order.size()) {
+      if (rows[order[k]] > max_rows_) {
+        set_error("runtime: an utterance of %d encoder rows exceeds max_rows %d", rows[order[k]], max_rows_);
+        return FB200_EINVAL;
+      }
+      cur.push_back(order[k]);
+      cur_rows += rows[order[k]];
+    }
+  }
+  for (int i = 0; i < n; ++i) {
+    std::string& s = res->text[i];
+    for (int32_t id : res->ids[i]) {
+      if (!s.empty() && tokens_.empty()) s.push_back(' ');
+      if (tokens_.empty()) s += std::to_string(id);
+      else if ((size_t)id < tokens_.size()) s += tokens_[id];
+    }
+  }
+  return FB200_OK;
+}
+
+}  // namespace rt
+}  // namespace fb200
+
+using fb200::rt::Recognizer;
+using fb200::rt::Result;
+#define RT_API extern "C" __attribute__((visibility("default")))
+
+RT_API void* fb200_offline_init(const char* model_dir, int device, int precision, int max_rows) {
+  if (model_dir == nullptr || (precision != 0 && precision != 1)) {
+    fb200::set_error("offline_init: model_dir / precision (0 = fp32 parity, 1 = bf16)");
+    return nullptr;
+  }
+  Recognizer* r = new Recognizer();
+  if (r->init(model_dir, device, precision == 0 ? 2 : 1, max_rows > 0 ? max_rows : 18944) != FB200_OK) {
+    delete r;
+    return nullptr;
+  }
+  return r;
+}
+
+RT_API void* fb200_offline_infer(void* handle, const float* const* waves, const int32_t* lens, int count) {
+  if (handle == nullptr || count < 0 || (count > 0 && (waves == nullptr || lens == nullptr))) {
+    fb200::set_error("offline_infer: bad arguments");
+    return nullptr;
+  }
+  Result* res = new Result();
+  if (static_cast<Recognizer*>(handle)->recognize(waves, lens, count, res) != FB200_OK) {
+    delete res;
+    return nullptr;
+  }
+  return res;
+}
+
+RT_API void* fb200_offline_infer_buffer(void* handle, const char* pcm16, int n_bytes, int sampling_rate) {
+  if (sampling_rate != 16000 || pcm16 == nullptr || n_bytes < 0) {
+    fb200::set_error("offline_infer_buffer: 16 kHz mono PCM16 only (got %d Hz)", sampling_rate);
+    return nullptr;
+  }
+  const int n = n_bytes / 2;
+  std::vector<float> wave(n);
+  const int16_t* s = reinterpret_cast<const int16_t*>(pcm16);
+  for (int i = 0; i < n; ++i) wave[i] = (float)s[i] / 32768.f;  // the frontend scales by 1 << 15 again (wav_frontend.py:130)
+  const float* w = wave.data();
+  const int32_t len = n;
+  return fb200_offline_infer(handle, &w, &len, 1);
+}
+
+RT_API int fb200_result_count(void* result) { return result ? (int)static_cast<Result*>(result)->ids.size() : 0; }
+RT_API const char* fb200_result_text(void* result, int index) {
+  Result* r = static_cast<Result*>(result);
+  return (r && index >= 0 && index < (int)r->text.size()) ? r->text[index].c_str() : nullptr;
+}
+RT_API const int32_t* fb200_result_ids(void* result, int index, int* count) {
+  Result* r = static_cast<Result*>(result);
+  if (!r || index < 0 || index >= (int)r->ids.size()) {
+    if (count) *count = 0;
+    return nullptr;
+  }
+  if (count) *count = (int)r->ids[index].size();
+  return r->ids[index].data();
+}
+RT_API void fb200_free_result(void* result) { delete static_cast<Result*>(result); }
+RT_API void fb200_offline_uninit(void* handle) { delete static_cast<Recognizer*>(handle); }

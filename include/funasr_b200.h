@@ -310,6 +310,30 @@ int fb200_argmax_logprob(const float* logits, int ld, int rows, int vocab, int32
 int fb200_ctc_collapse(const int32_t* ids, const int32_t* cu_rows, int batch, uint32_t drop_mask,
                        int collapse_repeats, int32_t* out_ids, int32_t* out_len, void* stream);
 
+/* ------------------------------------------------------------------ native offline runtime ---- */
+
+/* The packed Paraformer path orchestrated in C++ inside this library (csrc/runtime.cu) -- no Python, no torch: the
+ * B200 counterpart of the reference's C++ offline runtime API (runtime/onnxruntime/include/funasrruntime.h:99-114).
+ *   reference                                   here
+ *   FunOfflineInit(model_path, threads, gpu)     fb200_offline_init(model_dir, device, precision, max_rows)
+ *   FunOfflineInferBuffer(h, pcm, n_bytes, ...)  fb200_offline_infer_buffer(h, pcm16, n_bytes, 16000)   one recording
+ *   (batched: paraformer-torch.cpp:301-470)      fb200_offline_infer(h, waves, lens, count)             a packed batch
+ *   FunASRGetRetNumber / FunASRGetResult         fb200_result_count / fb200_result_text (+ fb200_result_ids)
+ *   FunASRFreeResult / FunOfflineUninit          fb200_free_result / fb200_offline_uninit
+ * model_dir holds model.fb200 (tools/export_model.py, reference state_dict names), optionally am.mvn (Kaldi-nnet CMVN,
+ * parsed as paraformer.cpp:314-349) and tokens.json (JSON array of token strings).  precision: 0 = fp32 parity
+ * (hi + mid bf16 operands), 1 = bf16.  waves are HOST float32 in [-1, 1] (16 kHz); every utterance is computed with
+ * batch-1 semantics.  NULL is returned on failure (text in fb200_last_error()).  Handles are not thread-safe: one
+ * handle per thread / GPU. */
+void* fb200_offline_init(const char* model_dir, int device, int precision, int max_rows);
+void* fb200_offline_infer(void* handle, const float* const* h_waves, const int32_t* h_lens, int count);
+void* fb200_offline_infer_buffer(void* handle, const char* h_pcm16, int n_bytes, int sampling_rate);
+int fb200_result_count(void* result);
+const char* fb200_result_text(void* result, int index);
+const int32_t* fb200_result_ids(void* result, int index, int* count);
+void fb200_free_result(void* result);
+void fb200_offline_uninit(void* handle);
+
 #ifdef __cplusplus
 }
 #endif

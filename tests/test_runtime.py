@@ -1,0 +1,70 @@
+"""Native offline runtime (csrc/runtime.cu): model directory writer and failure behaviour on CPU; on the GPU the
+C++ orchestration must give the token ids of the Python engine (and so of the oracle / reference goldens)."""
+import os
+import struct
+
+import numpy as np
+import pytest
+import torch
+
+from funasr_b200 import _lib, params, runtime, synth
+
+
+def _small_sd():
+    shapes = params.paraformer_large_shapes(enc_blocks=3, dec_blocks=2)
+    return synth.synth_state_dict(shapes, seed=0)
+
+
+def test_model_file_layout(tmp_path):
+    sd = _small_sd()
+    path = runtime.export_model(sd, str(tmp_path), cmvn=synth.synth_cmvn(), token_list=synth.synth_token_list())
+    raw = open(path, "rb").read()
+    assert raw[:8] == runtime.MAGIC
+    (count,) = struct.unpack("<I", raw[8:12])
+    assert count == len(sd) + 4  # + frontend.window / mel / pe_inv / meta
+    (nlen,) = struct.unpack("<H", raw[12:14])
+    name = raw[14:14 + nlen].decode()
+    assert name in sd
+    assert os.path.exists(tmp_path / "am.mvn") and os.path.exists(tmp_path / "tokens.json")
+
+
+def test_init_fails_loudly_without_model_or_gpu(tmp_path):
+    lib = _lib.load()
+    h = lib.fb200_offline_init(str(tmp_path / "missing").encode(), 0, 0, 0)
+    assert not h
+    assert lib.fb200_last_error().decode() != ""
+    assert lib.fb200_result_count(None) == 0
+    with pytest.raises(RuntimeError):
+        runtime.OfflineRecognizer(str(tmp_path / "missing"))
+
+
+@pytest.mark.gpu
+def test_native_runtime_matches_python_engine(tmp_path, cmvn):
+    from funasr_b200 import engine
+
+    sd = _small_sd()
+    runtime.export_model(sd, str(tmp_path), cmvn=synth.synth_cmvn(), token_list=synth.synth_token_list())
+    waves = [synth.synth_waveform(80 + i, n) for i, n in enumerate([32000, 300, 57001, 16000, 96000])]
+    rec = runtime.OfflineRecognizer(str(tmp_path), precision="fp32", max_rows=600)  # several packed batches
+    ids, text = rec.recognize(waves, with_text=True)
+    eng = engine.ParaformerEngine({k: torch.from_numpy(v) for k, v in sd.items()}, "cuda:0", "fp32", cmvn=cmvn)
+    want = eng.recognize(waves)
+    assert ids == want
+    assert ids[1] == [] and text[1] == ""
+    toks = synth.synth_token_list()
+    assert text[0] == "".join(toks[i] for i in ids[0])
+    pcm = (np.clip(waves[3], -1, 1) * 32768.0).astype(np.int16)
+    ids_pcm, _ = rec.recognize_pcm16(pcm.tobytes())
+    assert ids_pcm == eng.recognize([pcm.astype(np.float32) / 32768.0])[0]
+    rec.close()
+
+
+@pytest.mark.gpu
+def test_native_runtime_full_depth_matches_reference_golden(tmp_path, paraformer_sd, golden_dir):
+    """Paraformer-large at full depth through the C++ runtime == the unmodified reference's transcripts."""
+    g = np.load(os.path.join(golden_dir, "stages_2s.npz"))
+    runtime.export_model(paraformer_sd, str(tmp_path), cmvn=synth.synth_cmvn())
+    rec = runtime.OfflineRecognizer(str(tmp_path))
+    ids = rec.recognize([synth.synth_waveform(10, 32000)])
+    assert ids[0] == g["token_int"].tolist()
+    rec.close()
