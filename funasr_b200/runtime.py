@@ -73,7 +73,7 @@ class OfflineRecognizer:
             for i in range(self._lib.fb200_result_count(res)):
                 n = ctypes.c_int(0)
                 p = self._lib.fb200_result_ids(res, i, ctypes.byref(n))
-                ids.append([int(p[j]) for j in range(n.value)])
+                ids.append(np.ctypeslib.as_array(p, shape=(n.value,)).tolist() if n.value else [])
                 text.append(self._lib.fb200_result_text(res, i).decode("utf-8"))
             return ids, text
         finally:

@@ -68,3 +68,49 @@ def test_native_runtime_full_depth_matches_reference_golden(tmp_path, paraformer
     ids = rec.recognize([synth.synth_waveform(10, 32000)])
     assert ids[0] == g["token_int"].tolist()
     rec.close()
+
+
+def _example_binary():
+    """examples/offline_recognize, built with g++ against the in-tree library when missing or stale."""
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src, exe = os.path.join(root, "examples", "offline_recognize.cpp"), os.path.join(root, "examples", "offline_recognize")
+    libdir = os.path.join(root, "funasr_b200")
+    if not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(src):
+        subprocess.run(["g++", "-O2", "-std=c++17", "-I" + os.path.join(root, "include"), src, "-L" + libdir, "-lfunasr_b200",
+                        "-Wl,-rpath," + libdir, "-o", exe], check=True)
+    return exe, libdir
+
+
+def test_example_program_builds_and_fails_loudly_without_a_model(tmp_path):
+    import subprocess
+
+    exe, libdir = _example_binary()
+    r = subprocess.run([exe, str(tmp_path / "missing"), str(tmp_path / "a.pcm")], capture_output=True, text=True,
+                       env=dict(os.environ, LD_LIBRARY_PATH=libdir))
+    assert r.returncode == 1 and "fb200_offline_init" in r.stderr
+
+
+@pytest.mark.gpu
+def test_example_program_without_python_matches_engine(tmp_path, cmvn):
+    """PCM16 files -> stand-alone C++ program (no Python in the process) -> ids == the Python engine on the same samples."""
+    import subprocess
+
+    from funasr_b200 import engine
+
+    sd = _small_sd()
+    runtime.export_model(sd, str(tmp_path), cmvn=synth.synth_cmvn(), token_list=synth.synth_token_list())
+    exe, libdir = _example_binary()
+    paths, quant = [], []
+    for i, n in enumerate([24000, 40000]):
+        pcm = (np.clip(synth.synth_waveform(90 + i, n), -1, 1) * 32767.0).astype(np.int16)
+        path = str(tmp_path / ("u%d.pcm" % i))
+        pcm.tofile(path)
+        paths.append(path)
+        quant.append(pcm.astype(np.float32) / 32768.0)
+    r = subprocess.run([exe, str(tmp_path)] + paths, capture_output=True, text=True, env=dict(os.environ, LD_LIBRARY_PATH=libdir))
+    assert r.returncode == 0, r.stderr
+    got = [[int(t) for t in line.split("\t")[1].split()] for line in r.stdout.strip().splitlines()]
+    eng = engine.ParaformerEngine({k: torch.from_numpy(v) for k, v in sd.items()}, "cuda:0", "fp32", cmvn=cmvn)
+    assert got == eng.recognize(quant)
