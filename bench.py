@@ -53,7 +53,7 @@ def parse():
     ap.add_argument("--precision", default="fp32", choices=["fp32", "fp32x6", "bf16"])
     ap.add_argument("--utts", type=int, default=1024)
     ap.add_argument("--max-rows", type=int, default=18944, help="packed rows per batch (148 SMs x 128-row tiles)")
-    ap.add_argument("--cpu-utts", type=int, default=12, help="utterances of the workload timed on the host cores")
+    ap.add_argument("--cpu-utts", type=int, default=96, help="utterances of the workload timed on the host cores (~12 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
