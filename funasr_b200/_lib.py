@@ -28,6 +28,7 @@ SIGNATURES = {
     "fb200_fsmn": [_P, _I, _P, _I, _I, _I, _P, _I, _P, _I, _P, _I, _P],
     "fb200_gemm": [_P, _I, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
     "fb200_gemm_ex": [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
+    "fb200_gemm_heads": [_P, _I, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P, _I, _I, _P],
     "fb200_conv2d_sub1": [_P, _I, _P, _P, _I, _I, _I, _P, _P, _I, _P, _I, _P],
     "fb200_gather_rows": [_P, _I, _P, _P, _I, _P, _I, _I, _I, _P],
     "fb200_glu_dwconv": [_P, _I, _P, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _I, _P],

@@ -57,7 +57,7 @@ class _ConformerLayer:
         self.quqvkv = _Linear(w, b, nparts, device)
         self.out = lin("self_attn.linear_out")
         self.pos_w = _Linear(sd[a + "linear_pos.weight"], None, nparts, device)
-        self.pos: List[torch.Tensor] = []  # per head: linear_pos(pe)[:, head] as a split operand, filled by the encoder
+        self.pos: Optional[torch.Tensor] = None  # linear_pos(pe)[:, head] as split operands, heads stacked along the rows
         c = p + "conv_module."
         w1 = sd[c + "pointwise_conv1.weight"]
         self.pw1 = _Linear(w1.reshape(w1.shape[0], w1.shape[1]), sd[c + "pointwise_conv1.bias"], nparts, device)
@@ -121,7 +121,8 @@ class ConformerEncoderPack:
         p = torch.empty(rows, d, dtype=torch.float32, device=self.device)
         for ly in self.layers:
             ops.gemm(pe, np_, ly.pos_w.w, np_, rows, d, d, out_f32=p)
-            ly.pos = [ops.split_rows(p[:, h * dk:(h + 1) * dk], np_) for h in range(self.heads)]
+            # heads stacked along the rows: ONE grouped launch computes every head's (q+v).p^T (ops.gemm_heads)
+            ly.pos = torch.cat([ops.split_rows(p[:, h * dk:(h + 1) * dk], np_) for h in range(self.heads)], dim=0)
         self._pos_rows = rows
 
     def plan(self, frames: Sequence[int]):
@@ -162,12 +163,12 @@ class ConformerEncoderPack:
     def workspace(self, r: int, max_t: int):
         dev, np_, d = self.device, self.nparts, self.d
         bf, f32 = torch.bfloat16, torch.float32
-        ld_bd = (max_t + 3) // 4 * 4
+        bd_pitch = (max_t + 255) // 256 * 256  # columns per head of the grouped (q+v).p^T product
         return {
             "xs": torch.empty(r, ops.split_width(d, np_), dtype=bf, device=dev),
             "h": torch.empty(r, ops.split_width(self.ff, np_), dtype=bf, device=dev),
             "qkv": torch.empty(r, ops.split_width(4 * d, np_), dtype=bf, device=dev),
-            "bd": torch.empty(self.heads, r, ld_bd, dtype=f32, device=dev),
+            "bd": torch.empty(r, self.heads, bd_pitch, dtype=f32, device=dev),
             "g": torch.empty(r, 2 * d, dtype=f32, device=dev),
             "xa": torch.empty(r, d, dtype=f32, device=dev),
             "xb": torch.empty(r, d, dtype=f32, device=dev),
@@ -188,11 +189,10 @@ class ConformerEncoderPack:
         ops.layernorm(x1, ly.norm_mha.g, ly.norm_mha.b, self.eps, out_split=ws["xs"], nparts=np_)
         qkv = ws["qkv"]
         ops.gemm(ws["xs"], np_, ly.quqvkv.w, np_, r, 4 * d, d, bias=ly.quqvkv.bias, out_split=qkv, out_parts=np_)
-        bd = ws["bd"]
-        for h in range(heads):  # bd[h][r, c] = (q_r + v) . p_c for c < max_t
-            ops.gemm_ex(qkv, np_, ly.pos[h], np_, r, max_t, dk, lda=np_ * 4 * d, a_part_stride=4 * d, a_col0=d + h * dk,
-                        out_f32=bd[h])
-        ops.attention_relpos(qkv, 0, 4 * d, qkv, 2 * d, qkv, 3 * d, 4 * d, np_, bd, cu_rows, max_t, heads,
+        bd = ws["bd"]  # bd[r, h, c] = (q_r + v)_h . p_c for c < max_t, every head in one launch
+        ops.gemm_heads(qkv, np_, ly.pos, self._pos_rows, r, max_t, heads, dk, bd.view(r, -1), lda=np_ * 4 * d,
+                       a_part_stride=4 * d, a_col0=d, a_col_step=dk)
+        ops.attention_relpos(qkv, 0, 4 * d, qkv, 2 * d, qkv, 3 * d, 4 * d, np_, bd.permute(1, 0, 2), cu_rows, max_t, heads,
                              float(dk) ** -0.5, out_split=ws["xs"], plan=ws["plan"])
         ops.gemm(ws["xs"], np_, ly.out.w, np_, r, d, d, bias=ly.out.bias, res1=x1, out_f32=xb)
         # convolution module

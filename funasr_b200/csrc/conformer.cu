@@ -95,67 +95,109 @@ __global__ void gather_rows_kernel(const float* __restrict__ src, int ld_src, co
 }
 
 // ---------------------------------------------------------------- GLU + depthwise + BN + swish
-constexpr int kDwRows = 32;  // output rows per CTA
+// One CTA = kDwRows consecutive PACKED rows x all channels (the grid is rows / kDwRows whatever the utterance
+// lengths: 18 944 rows = one full wave of 2 CTAs per SM).  Phase 1: GLU of the kDwRows + K - 1 input rows into shared
+// memory, every thread busy; phase 2: thread = (kDwRpt rows, channel pair), weights and input window in registers,
+// taps that fall outside the row's own utterance masked (= the zero padding of the reference's Conv1d), BatchNorm
+// (folded), swish, bf16 split store.  (A first version walked the rows serially from global memory with a register
+// window per thread: 41 us per 18 944-row call at 9 % of the warp slots -- latency-bound; a second read the strided
+// weights through __ldg per tap: 85 us, L1-bound; tiling per utterance left a nearly empty second wave: 47 us.)
+constexpr int kDwRows = 64;
+constexpr int kDwRpt = 16;
+constexpr int kDwThreads = 512;
 
 template <int K>
-__global__ void __launch_bounds__(512)
-glu_dwconv_kernel(const float* __restrict__ g, int ld_g, const int32_t* __restrict__ cu_rows, int C,
+__global__ void __launch_bounds__(kDwThreads)
+glu_dwconv_kernel(const float* __restrict__ g, int ld_g, const int32_t* __restrict__ cu_rows, int batch, int total_rows, int C,
                   const float* __restrict__ weight, const float* __restrict__ bias, const float* __restrict__ bn_scale,
                   const float* __restrict__ bn_shift, __nv_bfloat16* __restrict__ out_split, int nparts, int out_kp) {
   constexpr int PAD = (K - 1) / 2;
-  const int b = blockIdx.y;
-  const int beg = __ldg(cu_rows + b), len = __ldg(cu_rows + b + 1) - beg;
-  const int t0 = blockIdx.x * kDwRows;
-  if (t0 >= len) return;
-  const int c0 = 2 * threadIdx.x;
-  if (c0 >= C) return;
-  float w0[K], w1[K];
-#pragma unroll
-  for (int j = 0; j < K; ++j) {
-    w0[j] = __ldg(weight + (size_t)c0 * K + j);
-    w1[j] = __ldg(weight + (size_t)(c0 + 1) * K + j);
-  }
-  const float2 bi = *reinterpret_cast<const float2*>(bias + c0);
-  const float2 sc = *reinterpret_cast<const float2*>(bn_scale + c0);
-  const float2 sh = *reinterpret_cast<const float2*>(bn_shift + c0);
-  float2 win[K];
-#pragma unroll
-  for (int j = 0; j < K; ++j) win[j] = make_float2(0.f, 0.f);
-  const int t_end = min(t0 + kDwRows, len);
-  // input row t enters the window's last slot; output row t - PAD is complete once it has
-  for (int t = t0 - PAD; t < t_end + PAD; ++t) {
-#pragma unroll
-    for (int j = 0; j < K - 1; ++j) win[j] = win[j + 1];
-    float2 v = make_float2(0.f, 0.f);
-    if (t >= 0 && t < len) {
-      const float* gp = g + (size_t)(beg + t) * ld_g + c0;
-      const float2 a = *reinterpret_cast<const float2*>(gp);
-      const float2 gate = *reinterpret_cast<const float2*>(gp + C);
-      v.x = a.x / (1.f + expf(-gate.x));
-      v.y = a.y / (1.f + expf(-gate.y));
+  extern __shared__ float glu[];  // [kDwRows + K - 1][C]
+  __shared__ int tap_lo[kDwRows], tap_hi[kDwRows];  // taps [lo, hi) of a row stay inside its utterance
+  const int g0 = blockIdx.x * kDwRows;
+  const int rows = min(kDwRows, total_rows - g0);
+  if (threadIdx.x < rows) {
+    const int gr = g0 + threadIdx.x;
+    int lo = 0, hi = batch;  // largest b with cu_rows[b] <= gr
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (__ldg(cu_rows + mid) <= gr) lo = mid; else hi = mid;
     }
-    win[K - 1] = v;
-    const int to = t - PAD;
-    if (to < t0) continue;
-    float y0 = 0.f, y1 = 0.f;
+    const int beg = __ldg(cu_rows + lo), end = __ldg(cu_rows + lo + 1);
+    tap_lo[threadIdx.x] = max(0, PAD - (gr - beg));
+    tap_hi[threadIdx.x] = min(K, PAD + (end - gr));
+  }
+  const int half = C >> 1;
+  const int items = (kDwRows + K - 1) * half;
+#pragma unroll 4
+  for (int i = threadIdx.x; i < items; i += kDwThreads) {
+    const int rr = i / half, c0 = (i - rr * half) * 2;
+    const int t = g0 - PAD + rr;
+    const bool ok = t >= 0 && t < total_rows;
+    const float* gp = g + (size_t)(ok ? t : 0) * ld_g + c0;
+    const float2 a = __ldg(reinterpret_cast<const float2*>(gp));
+    const float2 gate = __ldg(reinterpret_cast<const float2*>(gp + C));
+    float2 v;
+    v.x = ok ? __fdividef(a.x, 1.f + __expf(-gate.x)) : 0.f;
+    v.y = ok ? __fdividef(a.y, 1.f + __expf(-gate.y)) : 0.f;
+    *reinterpret_cast<float2*>(glu + rr * C + c0) = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < (kDwRows / kDwRpt) * half; i += kDwThreads) {
+    const int grp = i / half, c0 = (i - grp * half) * 2;
+    const int r0 = grp * kDwRpt;
+    if (r0 >= rows) continue;
+    float w0[K], w1[K];
 #pragma unroll
     for (int j = 0; j < K; ++j) {
-      y0 = fmaf(w0[j], win[j].x, y0);
-      y1 = fmaf(w1[j], win[j].y, y1);
+      w0[j] = __ldg(weight + (size_t)c0 * K + j);
+      w1[j] = __ldg(weight + (size_t)(c0 + 1) * K + j);
     }
-    y0 = (y0 + bi.x) * sc.x + sh.x;
-    y1 = (y1 + bi.y) * sc.y + sh.y;
-    y0 = y0 / (1.f + expf(-y0));
-    y1 = y1 / (1.f + expf(-y1));
-    __nv_bfloat16* orow = out_split + (size_t)(beg + to) * (nparts * out_kp) + c0;
-    const __nv_bfloat162 h = __floats2bfloat162_rn(y0, y1);
-    *reinterpret_cast<__nv_bfloat162*>(orow) = h;
-    if (nparts > 1) {
-      const float r0 = y0 - __low2float(h), r1 = y1 - __high2float(h);
-      const __nv_bfloat162 m = __floats2bfloat162_rn(r0, r1);
-      *reinterpret_cast<__nv_bfloat162*>(orow + out_kp) = m;
-      if (nparts > 2)
-        *reinterpret_cast<__nv_bfloat162*>(orow + 2 * out_kp) = __floats2bfloat162_rn(r0 - __low2float(m), r1 - __high2float(m));
+    const float2 bi = *reinterpret_cast<const float2*>(bias + c0);
+    const float2 sc = *reinterpret_cast<const float2*>(bn_scale + c0);
+    const float2 sh = *reinterpret_cast<const float2*>(bn_shift + c0);
+    constexpr bool kWindow = K <= 15;
+    float2 win[kWindow ? kDwRpt + K - 1 : 1];
+    if constexpr (kWindow) {
+#pragma unroll
+      for (int j = 0; j < kDwRpt + K - 1; ++j) win[j] = *reinterpret_cast<const float2*>(glu + (r0 + j) * C + c0);
+    }
+#pragma unroll
+    for (int rr = 0; rr < kDwRpt; ++rr) {
+      const int r = r0 + rr;
+      if (r >= rows) break;
+      const int lo = tap_lo[r], hi = tap_hi[r];
+      float y0 = 0.f, y1 = 0.f;
+      if (lo == 0 && hi == K) {  // interior row (the whole warp shares r): no masking
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          const float2 x = kWindow ? win[kWindow ? rr + j : 0] : *reinterpret_cast<const float2*>(glu + (r + j) * C + c0);
+          y0 = fmaf(w0[j], x.x, y0);
+          y1 = fmaf(w1[j], x.y, y1);
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < K; ++j) {
+          float2 x = kWindow ? win[kWindow ? rr + j : 0] : *reinterpret_cast<const float2*>(glu + (r + j) * C + c0);
+          if (j < lo || j >= hi) x = make_float2(0.f, 0.f);
+          y0 = fmaf(w0[j], x.x, y0);
+          y1 = fmaf(w1[j], x.y, y1);
+        }
+      }
+      y0 = (y0 + bi.x) * sc.x + sh.x;
+      y1 = (y1 + bi.y) * sc.y + sh.y;
+      y0 = __fdividef(y0, 1.f + __expf(-y0));
+      y1 = __fdividef(y1, 1.f + __expf(-y1));
+      __nv_bfloat16* orow = out_split + (size_t)(g0 + r) * (nparts * out_kp) + c0;
+      const __nv_bfloat162 h = __floats2bfloat162_rn(y0, y1);
+      *reinterpret_cast<__nv_bfloat162*>(orow) = h;
+      if (nparts > 1) {
+        const float e0 = y0 - __low2float(h), e1 = y1 - __high2float(h);
+        const __nv_bfloat162 m = __floats2bfloat162_rn(e0, e1);
+        *reinterpret_cast<__nv_bfloat162*>(orow + out_kp) = m;
+        if (nparts > 2)
+          *reinterpret_cast<__nv_bfloat162*>(orow + 2 * out_kp) = __floats2bfloat162_rn(e0 - __low2float(m), e1 - __high2float(m));
+      }
     }
   }
 }
@@ -369,13 +411,25 @@ extern "C" __attribute__((visibility("default"))) int fb200_glu_dwconv(
   FB_CHECK_ARG(nparts >= 1 && nparts <= 3, "glu_dwconv: nparts must be 1, 2 or 3");
   if (total_rows == 0 || max_len == 0) return FB200_OK;
   ProfScope prof(kProfGluDw, stream, (double)total_rows * channels * (8.0 + 2.0 * nparts));
-  dim3 grid((max_len + kDwRows - 1) / kDwRows, batch);
-  const int threads = (channels / 2 + 31) / 32 * 32;
+  const int grid = (total_rows + kDwRows - 1) / kDwRows;
   const int kp = round_up(channels, 64);
   cudaStream_t st = (cudaStream_t)stream;
+  const size_t smem = (size_t)(kDwRows + ksize - 1) * channels * sizeof(float);
+  FB_CHECK_ARG(smem <= 200 * 1024, "glu_dwconv: %d channels x kernel %d needs %zu B of shared memory", channels, ksize, smem);
 #define DW_LAUNCH(K)                                                                                                   \
-  glu_dwconv_kernel<K><<<grid, threads, 0, st>>>(g, ld_g, cu_rows, channels, weight, bias, bn_scale, bn_shift,        \
-                                                (__nv_bfloat16*)out_split, nparts, kp)
+  do {                                                                                                                 \
+    static bool attr_set = false;                                                                                      \
+    if (!attr_set && smem > 48 * 1024) {                                                                               \
+      cudaError_t e = cudaFuncSetAttribute(glu_dwconv_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); \
+      if (e != cudaSuccess) {                                                                                          \
+        set_error("glu_dwconv: cudaFuncSetAttribute: %s", cudaGetErrorString(e));                                      \
+        return FB200_ECUDA;                                                                                            \
+      }                                                                                                                \
+      attr_set = true;                                                                                                 \
+    }                                                                                                                  \
+    glu_dwconv_kernel<K><<<grid, kDwThreads, smem, st>>>(g, ld_g, cu_rows, batch, total_rows, channels, weight, bias,   \
+                                                         bn_scale, bn_shift, (__nv_bfloat16*)out_split, nparts, kp);   \
+  } while (0)
   if (ksize == 15) DW_LAUNCH(15);
   else if (ksize == 31) DW_LAUNCH(31);
   else if (ksize == 7) DW_LAUNCH(7);

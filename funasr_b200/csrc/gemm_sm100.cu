@@ -34,6 +34,10 @@ struct GemmParams {
   int term_a[kMaxTerms], term_b[kMaxTerms];
   int a_col0;                                // first A column; tap j reads A row m + tap_row[j], columns + tap_col[j]
   int tap_row[kMaxTaps], tap_col[kMaxTaps];
+  // Column groups (0 = none): output columns [g * group_n, (g + 1) * group_n) are an independent product of the A
+  // columns shifted by g * a_col_step with the weight rows starting at g * w_group_rows -- the per-head (q+v).p^T
+  // products of the rel-pos attention as ONE launch.
+  int group_n, a_col_step, w_group_rows;
   int tiles_m, tiles_n;
   const float* bias;
   int act;  // 0 none, 1 ReLU, 2 swish y * sigmoid(y)
@@ -166,8 +170,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       int it = 0;
       for (int tile = unit0; tile < total_tiles; tile += unit_step) {
         const int m0 = ((tile / p.tiles_n) * CL + cta_rank) * BM, n0 = (tile % p.tiles_n) * BN;
+        int a_cg = 0, w_r0 = n0;
+        if (p.group_n > 0) {
+          const int g = n0 / p.group_n;
+          a_cg = g * p.a_col_step;
+          w_r0 = g * p.w_group_rows + (n0 - g * p.group_n);
+        }
         for (int tap = 0; tap < p.taps; ++tap) {
-          const int a_r = m0 + p.tap_row[tap], a_c = p.a_col0 + p.tap_col[tap];
+          const int a_r = m0 + p.tap_row[tap], a_c = p.a_col0 + p.tap_col[tap] + a_cg;
           for (int kb = 0; kb < p.k_blocks; ++kb, ++it) {
             const int s = it % STAGES;
             const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
@@ -181,7 +191,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
                 tma_load_2d(sa + pa * kAPart, &map_a, a_c + pa * p.kp_a + kb * BK, a_r, full_bar(s));
 #pragma unroll
               for (int pb = 0; pb < NP; ++pb)
-                tma_load_2d(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK, tap * p.n + n0, full_bar(s));
+                tma_load_2d(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK, tap * p.n + w_r0, full_bar(s));
             } else {  // own A rows and own half of the weight rows; the bytes are counted on the leader's barrier
               // Only the leader arms the barrier (for both CTAs' bytes): the peer's bytes may land first, the phase
               // still cannot complete before the leader's arrival, and the peer is spared a remote arrive per stage.
@@ -193,7 +203,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 #pragma unroll
               for (int pb = 0; pb < NP; ++pb)
                 tma_load_2d_pair(sa + NP * kAPart + pb * kBPart, &map_w, pb * p.kp_w + kb * BK,
-                                 tap * p.n + n0 + cta_rank * (BN / CL), lbar);
+                                 tap * p.n + w_r0 + cta_rank * (BN / CL), lbar);
             }
           }
         }

@@ -231,6 +231,17 @@ def gemm_ex(a, a_parts, w_split, w_parts, m, n, k, lda=0, a_part_stride=0, a_col
     del keep_r, keep_c
 
 
+def gemm_heads(a, a_parts, w_all, w_group_rows, m, n_group, groups, k, out_f32, lda=0, a_part_stride=0, a_col0=0,
+               a_col_step=0, impl=0, a_rows=None):
+    """out[r, g * P + c] = A[r, a_col0 + g * a_col_step : +k] . W[g * w_group_rows + c, :k], P = n_group rounded up to
+    256, for every group g in ONE launch; out fp32 [m, >= groups * P]."""
+    _chk(a, torch.bfloat16, "gemm_heads")
+    _chk(w_all, torch.bfloat16, "gemm_heads")
+    a_rows = a.shape[0] if a_rows is None else a_rows
+    _lib.call("fb200_gemm_heads", _p(a), a_rows, lda, a_part_stride, a_col0, a_col_step, a_parts, _p(w_all), w_group_rows,
+              a_parts, m, n_group, groups, k, _p(out_f32), out_f32.stride(0), impl, _stream())
+
+
 def conv2d_sub1(feats, cu_frames, cu_seg, total_seg, weight, bias, planes, nparts):
     """feats fp32 [frames, n_mels]; planes bf16 [4 * total_seg * FP, nparts * C] (every slot written)."""
     _chk(feats, torch.float32, "conv2d_sub1")

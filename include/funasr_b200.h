@@ -190,6 +190,14 @@ int fb200_gemm_ex(const void* a, int a_rows, int lda, int a_part_stride, int a_c
                   const float* bias, int act, const float* res1, int ld_res1, float* out_f32, int ld_out, int f32_col0,
                   void* out_split, int out_parts, int impl, void* stream);
 
+/* `groups` independent products over the SAME rows in one launch (the per-head (q+v).p^T of the rel-pos attention):
+ *   out[r, g*P + c] = sum_k A[r, a_col0 + g*a_col_step + k] * W[g*w_group_rows + c, k],  c < P = n_group rounded up to 256
+ * (columns n_group <= c < P of a group hold products with the weight rows that follow -- callers ignore them).
+ * a as for fb200_gemm_ex; w bf16 split [groups * w_group_rows, w_parts*Kp]; out f32 [m, ld_out >= groups*P]. */
+int fb200_gemm_heads(const void* a, int a_rows, int lda, int a_part_stride, int a_col0, int a_col_step, int a_parts,
+                     const void* w, int w_group_rows, int w_parts, int m, int n_group, int groups, int k, float* out_f32,
+                     int ld_out, int impl, void* stream);
+
 /* fp32 weight [n, k] -> bf16 split [n, nparts*Kp] (done once at load). */
 int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts, void* stream);
 

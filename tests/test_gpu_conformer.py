@@ -60,6 +60,27 @@ def test_gemm_ex_taps_offsets_and_swish_match_simt():
     assert rel(outs[0], want) < 1e-4
 
 
+@pytest.mark.parametrize("m,n_group", [(640, 300), (130, 61), (1500, 770)])
+def test_gemm_heads_matches_per_head_products(m, n_group):
+    """One grouped launch = the per-head (q+v).p^T products: tcgen05 vs the SIMT check kernel vs torch."""
+    g = torch.Generator().manual_seed(9)
+    heads, dk, np_, wrows = 4, 64, 2, 1024
+    a = torch.randn(m, 4 * heads * dk, generator=g)            # the fused q+u | q+v | k | v layout
+    pos = torch.randn(heads, wrows, dk, generator=g) * 0.3
+    a_s = ops.split_rows(a.to(DEV), np_)
+    w_s = torch.cat([ops.split_rows(pos[h].to(DEV), np_) for h in range(heads)], dim=0)
+    pitch = (n_group + 255) // 256 * 256
+    outs = []
+    for impl in (0, 1):
+        o = torch.zeros(m, heads * pitch, device=DEV)
+        ops.gemm_heads(a_s, np_, w_s, wrows, m, n_group, heads, dk, o, lda=np_ * a.shape[1], a_part_stride=a.shape[1],
+                       a_col0=heads * dk, a_col_step=dk, impl=impl)
+        outs.append(o.view(m, heads, pitch)[:, :, :n_group].cpu())
+    want = torch.stack([a[:, heads * dk + h * dk: heads * dk + (h + 1) * dk] @ pos[h, :n_group].T for h in range(heads)], dim=1)
+    assert rel(outs[0], outs[1]) < 1e-5
+    assert rel(outs[0], want) < 1e-4
+
+
 @pytest.mark.parametrize("frames", [[7, 8, 11, 250], [401, 30]])
 def test_conv2d_subsampling_matches_oracle(eng, conformer_sd, frames):
     """conv 1 (parity planes) -> conv 2 (9-tap contraction) -> Linear (19-tap contraction) -> gather, ragged batch
