@@ -60,6 +60,22 @@ def cif_predictor_shapes(idim: int = 512, l_order: int = 1, r_order: int = 1, pr
     return s
 
 
+def bicif_predictor_shapes(idim: int = 512, upsample_times: int = 3, prefix: str = "predictor.") -> Shapes:
+    """CifPredictorV3 with `upsample_type: cnn_blstm` (funasr/models/bicif_paraformer/cif_predictor.py:96-169;
+    funasr/models/bicif_paraformer/template.yaml:47-58): the V2 tensors plus the upsampling ConvTranspose1d, the
+    one-layer bidirectional LSTM and the second alpha head."""
+    s = cif_predictor_shapes(idim, prefix=prefix)
+    s[prefix + "upsample_cnn.weight"] = (idim, idim, upsample_times)
+    s[prefix + "upsample_cnn.bias"] = (idim,)
+    for suffix in ("", "_reverse"):
+        s[prefix + "blstm.weight_ih_l0" + suffix] = (4 * idim, idim)
+        s[prefix + "blstm.weight_hh_l0" + suffix] = (4 * idim, idim)
+        s[prefix + "blstm.bias_ih_l0" + suffix] = (4 * idim,)
+        s[prefix + "blstm.bias_hh_l0" + suffix] = (4 * idim,)
+    _linear(s, prefix + "cif_output2", 2 * idim, 1)
+    return s
+
+
 def paraformer_decoder_shapes(vocab_size: int = 8404, d: int = 512, linear_units: int = 2048,
                               att_layer_num: int = 16, num_blocks: int = 16, kernel_size: int = 11,
                               prefix: str = "decoder.") -> Shapes:
@@ -102,6 +118,15 @@ def paraformer_large_shapes(vocab_size: int = 8404, enc_blocks: int = 50, dec_bl
     s.update(sanm_encoder_shapes(num_blocks=enc_blocks))
     s.update(paraformer_decoder_shapes(vocab_size, att_layer_num=dec_blocks, num_blocks=dec_blocks))
     s.update(cif_predictor_shapes())
+    return s
+
+
+def bicif_paraformer_shapes(vocab_size: int = 8404, enc_blocks: int = 50, dec_blocks: int = 16) -> Shapes:
+    """BiCifParaformer (funasr/models/bicif_paraformer/template.yaml): Paraformer-large with CifPredictorV3."""
+    s: Shapes = OrderedDict()
+    s.update(sanm_encoder_shapes(num_blocks=enc_blocks))
+    s.update(paraformer_decoder_shapes(vocab_size, att_layer_num=dec_blocks, num_blocks=dec_blocks))
+    s.update(bicif_predictor_shapes())
     return s
 
 

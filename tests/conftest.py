@@ -60,3 +60,14 @@ def conformer_sd():
 
     sd = synth.synth_state_dict(params.conformer_ctc_shapes(), seed=0)
     return {k: torch.from_numpy(v) for k, v in sd.items()}
+
+
+@pytest.fixture(scope="session")
+def bicif_sd():
+    """Seeded BiCifParaformer weights: Paraformer-large + CifPredictorV3 (upsampling conv, BLSTM, second alpha head)."""
+    import torch
+
+    from funasr_b200 import params, synth
+
+    sd = synth.synth_state_dict(params.bicif_paraformer_shapes(), seed=0)
+    return {k: torch.from_numpy(v) for k, v in sd.items()}
