@@ -29,6 +29,10 @@ SIGNATURES = {
     "fb200_gemm": [_P, _I, _I, _P, _I, _I, _I, _I, _I, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
     "fb200_gemm_ex": [_P, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, _I, _P, _I, _P, _I, _I, _P, _I, _I, _P],
     "fb200_gemm_heads": [_P, _I, _I, _I, _I, _I, _I, _P, _I, _I, _I, _I, _I, _I, _P, _I, _I, _P],
+    "fb200_lstm_workspace_bytes": [_I, _I, _P],
+    "fb200_lstm_parts": [_I, _P],
+    "fb200_lstm_bidir": [_P, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, ctypes.c_longlong, _P, _P, _P],
+    "fb200_us_fires": [_P, _I, _I, _F, _F, _F, _F, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "fb200_conv2d_sub1": [_P, _I, _P, _P, _I, _I, _I, _P, _P, _I, _P, _I, _P],
     "fb200_gather_rows": [_P, _I, _P, _P, _I, _P, _I, _I, _I, _P],
     "fb200_glu_dwconv": [_P, _I, _P, _I, _I, _I, _I, _P, _I, _P, _P, _P, _P, _I, _P],
@@ -60,7 +64,7 @@ EXPORTS = sorted(list(SIGNATURES) + list(RUNTIME_SIGNATURES) + ["fb200_version",
                   "fb200_profile_enable", "fb200_profile_read"])
 PROFILE_KINDS = ["fbank", "lfr_cmvn", "scale_add_pe", "layernorm", "split_rows", "fsmn", "gemm", "attention",
                  "cif_alpha", "cif_scan", "cif_integrate", "argmax_logprob", "ctc_collapse", "conv2d_sub1", "glu_dwconv",
-                 "attention_relpos"]
+                 "attention_relpos", "lstm_bidir", "us_fires"]
 
 _lib = None
 

@@ -8,7 +8,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfunasr_b200.so")
-SOURCES = ["api.cu", "frontend.cu", "rowwise.cu", "gemm_sm100.cu", "attention_sm100.cu", "cif_decode.cu", "conformer.cu", "relpos_attention_sm100.cu", "runtime.cu"]
+SOURCES = ["api.cu", "frontend.cu", "rowwise.cu", "gemm_sm100.cu", "attention_sm100.cu", "cif_decode.cu", "conformer.cu", "relpos_attention_sm100.cu", "bicif.cu", "runtime.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 

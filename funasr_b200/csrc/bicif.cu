@@ -1,0 +1,396 @@
+// BiCifParaformer's time-stamp head on the device:
+//   * fb200_lstm_bidir  -- the one-layer bidirectional LSTM of CifPredictorV3 (`self.blstm`,
+//     funasr/models/bicif_paraformer/cif_predictor.py:142-145, :262-265) over a packed var-len batch, fused with the
+//     dot product of `cif_output2` (:145, :270): a cooperative, persistent kernel, recurrent weights resident in shared
+//     memory, one grid barrier per time step and direction;
+//   * fb200_us_fires    -- sigmoid / smooth / noise / length scaling of the upsampled alphas (:270-283), the sequential
+//     fp32 integrate-and-fire of `cif_wo_hidden` (:71-93) and the re-normalised second scan of
+//     `ts_prediction_lfr6_standard` (funasr/utils/timestamp_tools.py:46-53), one warp per utterance.
+#include "common.cuh"
+
+namespace fb200 {
+namespace lstm {
+
+constexpr int H = 512;        // hidden units per direction
+constexpr int UPC = 8;        // hidden units owned by one CTA (all four gates of each)
+constexpr int CTAS = H / UPC; // CTAs per direction
+constexpr int BC = 64;        // utterances staged per chunk
+constexpr int HP = H + 4;     // shared-memory row pitch in floats (16-byte aligned, bank-shifted)
+constexpr int THREADS = 256;
+constexpr int MAX_CHUNKS = 16;
+constexpr size_t kSmem = (size_t)(4 * UPC * HP + BC * HP + 128 * 16 + BC * UPC) * sizeof(float);
+
+struct Params {
+  const float* xg;      // [rows3, ld_xg]: W_ih x + b_ih + b_hh, columns [dir][gate i,f,g,o][H]
+  int ld_xg;
+  const int32_t* cu_rows;  // [batch + 1] prefix of the encoder rows; utterance b owns upsampled rows [up*cu[b], up*cu[b+1])
+  int up, batch, rows3, max_len3;
+  const float* w_hh;    // [2][4H][H]
+  const float* w_out;   // [2][H]  cif_output2.weight split by direction
+  float* hbuf;          // [2 dir][2 phase][batch][H]   zero on entry
+  float* cbuf;          // [2 dir][batch][H]            zero on entry
+  unsigned int* counters;  // [2]                        zero on entry
+  float* part;          // [2 * CTAS][rows3] partial logits of every CTA
+  float* out_h;         // optional [rows3][2H]
+};
+
+__device__ __forceinline__ unsigned int ld_acquire(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release(unsigned int* p) {
+  asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ float sigmoidf(float x) { return 1.f / (1.f + expf(-x)); }
+
+__global__ void __launch_bounds__(THREADS, 1) lstm_bidir_kernel(const Params p) {
+  extern __shared__ __align__(16) float smem[];
+  float* Ws = smem;                    // [4 * UPC][HP]   row = gate * UPC + unit
+  float* hs = Ws + 4 * UPC * HP;       // [BC][HP]
+  float* red = hs + BC * HP;           // [16][128]
+  float* lg = red + 128 * 16;          // [BC][UPC]
+  __shared__ int chunk_max[MAX_CHUNKS];
+
+  const int tid = threadIdx.x;
+  const int dir = blockIdx.x / CTAS, cta = blockIdx.x % CTAS, u0 = cta * UPC;
+  const int B = p.batch;
+  const int nchunks = (B + BC - 1) / BC;
+  for (int i = tid; i < 4 * UPC * (H / 4); i += THREADS) {
+    const int row = i / (H / 4), k4 = i % (H / 4);
+    const int gate = row / UPC, unit = row % UPC;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(p.w_hh + ((size_t)dir * 4 * H + gate * H + u0 + unit) * H) + k4);
+    *reinterpret_cast<float4*>(Ws + row * HP + k4 * 4) = v;
+  }
+  if (tid < MAX_CHUNKS) {
+    int m = 0;
+    for (int b = tid * BC; b < min(B, (tid + 1) * BC); ++b) m = max(m, p.up * (p.cu_rows[b + 1] - p.cu_rows[b]));
+    chunk_max[tid] = m;
+  }
+  __syncthreads();
+
+  const int ks = tid >> 7, rem = tid & 127, u = rem >> 4, bg = rem & 15;
+  const float wout = __ldg(p.w_out + dir * H + u0 + u);
+  unsigned int* counter = p.counters + dir;
+
+  for (int t = 0; t < p.max_len3; ++t) {
+    const float* rd = p.hbuf + ((size_t)(dir * 2 + (t & 1)) * B) * H;
+    float* wr = p.hbuf + ((size_t)(dir * 2 + ((t + 1) & 1)) * B) * H;
+    if (t > 0) {
+      if (tid == 0) {
+        const unsigned int target = (unsigned int)t * CTAS;
+        unsigned int spins = 0;
+        while (ld_acquire(counter) < target) {
+          if (++spins > (1u << 27)) {
+            printf("funasr_b200 lstm: barrier timeout dir %d cta %d step %d\n", dir, cta, t);
+            __trap();
+          }
+        }
+      }
+      __syncthreads();
+    }
+    for (int c = 0; c < nchunks; ++c) {
+      if (t >= chunk_max[c]) continue;
+      const int b0 = c * BC, nb = min(BC, B - b0);
+      for (int i = tid; i < nb * (H / 4); i += THREADS) {
+        const int row = i >> 7, k4 = i & 127;
+        cp_async16(hs + row * HP + k4 * 4, rd + (size_t)(b0 + row) * H + k4 * 4);
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      // this thread's (utterance, unit) pairs: the input projections are fetched while the copy is in flight
+      float xv[4][4];
+      bool act[4];
+      int rowi[4];
+      if (ks == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int b = b0 + i * 16 + bg;
+          act[i] = false;
+          rowi[i] = 0;
+          if (b < B) {
+            const int beg = p.cu_rows[b], len3 = p.up * (p.cu_rows[b + 1] - beg);
+            if (t < len3) {
+              act[i] = true;
+              rowi[i] = p.up * beg + (dir ? len3 - 1 - t : t);
+            }
+          }
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+            xv[i][g] = act[i] ? __ldg(p.xg + (size_t)rowi[i] * p.ld_xg + dir * 4 * H + g * H + u0 + u) : 0.f;
+        }
+      }
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();
+      float acc[4][4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int g = 0; g < 4; ++g) acc[i][g] = 0.f;
+      const int kbeg = ks * (H / 2);
+#pragma unroll 2
+      for (int k = kbeg; k < kbeg + H / 2; k += 4) {
+        float4 w[4];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) w[g] = *reinterpret_cast<const float4*>(Ws + (g * UPC + u) * HP + k);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float4 hv = *reinterpret_cast<const float4*>(hs + (i * 16 + bg) * HP + k);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            acc[i][g] = fmaf(hv.x, w[g].x, acc[i][g]);
+            acc[i][g] = fmaf(hv.y, w[g].y, acc[i][g]);
+            acc[i][g] = fmaf(hv.z, w[g].z, acc[i][g]);
+            acc[i][g] = fmaf(hv.w, w[g].w, acc[i][g]);
+          }
+        }
+      }
+      if (ks == 1) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int g = 0; g < 4; ++g) red[(i * 4 + g) * 128 + rem] = acc[i][g];
+      }
+      __syncthreads();
+      if (ks == 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float logit = 0.f;
+          if (act[i]) {
+            const int b = b0 + i * 16 + bg;
+            float gate[4];
+#pragma unroll
+            for (int g = 0; g < 4; ++g) gate[g] = acc[i][g] + red[(i * 4 + g) * 128 + rem] + xv[i][g];
+            float* cp = p.cbuf + ((size_t)dir * B + b) * H + u0 + u;
+            const float cn = sigmoidf(gate[1]) * *cp + sigmoidf(gate[0]) * tanhf(gate[2]);
+            const float hn = sigmoidf(gate[3]) * tanhf(cn);
+            *cp = cn;
+            wr[(size_t)b * H + u0 + u] = hn;
+            if (p.out_h) p.out_h[(size_t)rowi[i] * 2 * H + dir * H + u0 + u] = hn;
+            logit = hn * wout;
+          }
+          lg[(i * 16 + bg) * UPC + u] = logit;
+        }
+      }
+      __syncthreads();
+      if (tid < nb) {
+        const int b = b0 + tid;
+        const int beg = p.cu_rows[b], len3 = p.up * (p.cu_rows[b + 1] - beg);
+        if (t < len3) {
+          float s = 0.f;
+#pragma unroll
+          for (int j = 0; j < UPC; ++j) s += lg[tid * UPC + j];
+          p.part[(size_t)(dir * CTAS + cta) * p.rows3 + p.up * beg + (dir ? len3 - 1 - t : t)] = s;
+        }
+      }
+      __syncthreads();
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) red_release(counter);
+  }
+}
+
+// ---------------------------------------------------------------- upsampled alphas -> fires
+struct FireParams {
+  const float* part;   // [nparts][rows3]
+  int nparts;
+  float bias, smooth, noise, threshold;
+  const int32_t* cu_rows;
+  int up, batch, rows3;
+  const int32_t* token_num;  // [batch] predicted token counts (the length the alphas are scaled to)
+  const int32_t* ids;        // packed token ids, utterance b owns [cu_tok[b], cu_tok[b+1])
+  const int32_t* cu_tok;
+  int drop0, drop1, drop2;   // ids not counted as characters (blank, sos, eos)
+  float* us_alphas;          // [rows3]
+  float* us_peaks;           // optional [rows3]: integrate value after each frame (first scan)
+  int32_t* fire_idx;         // [rows3] fired frames of utterance b from up*cu[b], in order
+  int32_t* fire_count;       // [batch]
+  int32_t* num_chars;        // [batch]
+};
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Sequential fp32 integrate-and-fire over alphas[0 .. n) * mul (or / div when div != 0): every lane carries the same
+// scalar, lane i of a 32-frame chunk records the fire of frame i.  Returns the number of fires.
+__device__ int fire_scan(const float* alphas, int n, float div, float thr, float* peaks, int32_t* fire_idx, int lane) {
+  float integrate = 0.f;
+  int count = 0;
+  for (int base = 0; base < n; base += 32) {
+    float mine = base + lane < n ? alphas[base + lane] : 0.f;
+    if (div != 0.f) mine = mine / div;
+    const int m = min(32, n - base);
+    float my_peak = 0.f;
+    bool my_fire = false;
+    for (int i = 0; i < m; ++i) {
+      const float a = __shfl_sync(0xffffffffu, mine, i);
+      integrate = integrate + a;
+      const bool fire = integrate >= thr;
+      if (lane == i) {
+        my_peak = integrate;
+        my_fire = fire;
+      }
+      if (fire) integrate = integrate - thr;
+    }
+    if (peaks != nullptr && base + lane < n) peaks[base + lane] = my_peak;
+    const unsigned int mask = __ballot_sync(0xffffffffu, my_fire);
+    if (my_fire) fire_idx[count + __popc(mask & ((1u << lane) - 1u))] = base + lane;
+    count += __popc(mask);
+  }
+  return count;
+}
+
+__global__ void __launch_bounds__(128) us_fires_kernel(const FireParams p) {
+  const int lane = threadIdx.x & 31;
+  const int b = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (b >= p.batch) return;
+  const int beg3 = p.up * p.cu_rows[b], n = p.up * p.cu_rows[b + 1] - beg3;
+  float* alphas = p.us_alphas + beg3;
+  int32_t* fire_idx = p.fire_idx + beg3;
+  float sum = 0.f;
+  for (int r = lane; r < n; r += 32) {
+    float logit = p.bias;
+    for (int j = 0; j < p.nparts; ++j) logit += p.part[(size_t)j * p.rows3 + beg3 + r];
+    float a = 1.f / (1.f + expf(-logit));
+    a = fmaxf(a * p.smooth - p.noise, 0.f);
+    alphas[r] = a;
+    sum += a;
+  }
+  sum = warp_sum(sum);
+  const float scale = (float)p.token_num[b] / sum;
+  float sum2 = 0.f;
+  for (int r = lane; r < n; r += 32) {
+    const float a = alphas[r] * scale;
+    alphas[r] = a;
+    sum2 += a;
+  }
+  sum2 = warp_sum(sum2);
+  int chars = 0;
+  for (int j = p.cu_tok[b] + lane; j < p.cu_tok[b + 1]; j += 32) {
+    const int id = p.ids[j];
+    chars += (id != p.drop0 && id != p.drop1 && id != p.drop2) ? 1 : 0;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) chars += __shfl_xor_sync(0xffffffffu, chars, o);
+  __syncwarp();
+  int count = fire_scan(alphas, n, 0.f, p.threshold, p.us_peaks ? p.us_peaks + beg3 : nullptr, fire_idx, lane);
+  if (chars > 0 && count != chars + 1) {  // timestamp_tools.py:46-53: rescale so the alphas sum to chars + 1, fire again
+    __syncwarp();
+    count = fire_scan(alphas, n, sum2 / (float)(chars + 1), p.threshold, nullptr, fire_idx, lane);
+  }
+  if (lane == 0) {
+    p.fire_count[b] = count;
+    p.num_chars[b] = chars;
+  }
+}
+
+}  // namespace lstm
+}  // namespace fb200
+
+using namespace fb200;
+
+extern "C" __attribute__((visibility("default"))) int fb200_lstm_bidir(
+    const float* xg, int ld_xg, const int32_t* cu_rows, int upsample, int batch, int rows3, int max_len3, int hidden,
+    const float* w_hh, const float* w_out, float* workspace, long long workspace_bytes, float* part, float* out_h, void* stream) {
+  using namespace fb200::lstm;
+  FB_CHECK_ARG(hidden == H, "lstm_bidir: hidden size %d unsupported (512 only)", hidden);
+  FB_CHECK_ARG(batch > 0 && batch <= BC * MAX_CHUNKS, "lstm_bidir: batch %d outside 1..%d", batch, BC * MAX_CHUNKS);
+  FB_CHECK_ARG(upsample >= 1 && ld_xg >= 8 * H, "lstm_bidir: upsample %d / ld_xg %d", upsample, ld_xg);
+  if (rows3 == 0 || max_len3 == 0) return FB200_OK;
+  const size_t h_bytes = (size_t)2 * 2 * batch * H * sizeof(float), c_bytes = (size_t)2 * batch * H * sizeof(float);
+  const size_t need = h_bytes + c_bytes + 256;
+  FB_CHECK_ARG(workspace != nullptr && (size_t)workspace_bytes >= need, "lstm_bidir: workspace %lld B < %zu B", workspace_bytes, need);
+  cudaStream_t st = (cudaStream_t)stream;
+  ProfScope prof(kProfLstm, stream, 2.0 * rows3 * 2.0 * 4.0 * H * H);
+  cudaError_t e = cudaMemsetAsync(workspace, 0, need, st);
+  if (e != cudaSuccess) {
+    set_error("lstm_bidir: cudaMemsetAsync: %s", cudaGetErrorString(e));
+    return FB200_ECUDA;
+  }
+  Params p;
+  p.xg = xg;
+  p.ld_xg = ld_xg;
+  p.cu_rows = cu_rows;
+  p.up = upsample;
+  p.batch = batch;
+  p.rows3 = rows3;
+  p.max_len3 = max_len3;
+  p.w_hh = w_hh;
+  p.w_out = w_out;
+  p.hbuf = workspace;
+  p.cbuf = workspace + (size_t)2 * 2 * batch * H;
+  p.counters = reinterpret_cast<unsigned int*>(workspace + (size_t)2 * 2 * batch * H + (size_t)2 * batch * H);
+  p.part = part;
+  p.out_h = out_h;
+  static bool attr_set = false;
+  if (!attr_set) {
+    e = cudaFuncSetAttribute(lstm_bidir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
+    if (e != cudaSuccess) {
+      set_error("lstm_bidir: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+      return FB200_ECUDA;
+    }
+    attr_set = true;
+  }
+  // every CTA waits for all the others of its direction at every step: they must be co-resident
+  void* args[] = {(void*)&p};
+  e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_kernel, dim3(2 * CTAS), dim3(THREADS), args, kSmem, st);
+  if (e != cudaSuccess) {
+    set_error("lstm_bidir: cooperative launch: %s", cudaGetErrorString(e));
+    return FB200_ECUDA;
+  }
+  count_launch();
+  return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_lstm_workspace_bytes(int batch, int hidden, long long* bytes) {
+  FB_CHECK_ARG(bytes != nullptr && batch > 0 && hidden > 0, "lstm_workspace_bytes: bad arguments");
+  *bytes = (long long)((size_t)6 * batch * hidden * sizeof(float) + 256);
+  return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_lstm_parts(int hidden, int* parts) {
+  FB_CHECK_ARG(parts != nullptr && hidden == fb200::lstm::H, "lstm_parts: hidden size %d unsupported (512 only)", hidden);
+  *parts = 2 * fb200::lstm::CTAS;
+  return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_us_fires(
+    const float* part, int nparts, int rows3, float bias, float smooth, float noise, float threshold, const int32_t* cu_rows,
+    int upsample, int batch, const int32_t* token_num, const int32_t* ids, const int32_t* cu_tok, const int32_t* drop_ids,
+    float* us_alphas, float* us_peaks, int32_t* fire_idx, int32_t* fire_count, int32_t* num_chars, void* stream) {
+  FB_CHECK_ARG(batch > 0 && nparts >= 1 && upsample >= 1, "us_fires: batch %d / parts %d / upsample %d", batch, nparts, upsample);
+  FB_CHECK_ARG(drop_ids != nullptr, "us_fires: drop_ids (3 host ints) missing");
+  if (rows3 == 0) return FB200_OK;
+  ProfScope prof(kProfUsFires, stream, (double)rows3 * (nparts + 4.0) * 4.0);
+  fb200::lstm::FireParams p;
+  p.part = part;
+  p.nparts = nparts;
+  p.bias = bias;
+  p.smooth = smooth;
+  p.noise = noise;
+  p.threshold = threshold;
+  p.cu_rows = cu_rows;
+  p.up = upsample;
+  p.batch = batch;
+  p.rows3 = rows3;
+  p.token_num = token_num;
+  p.ids = ids;
+  p.cu_tok = cu_tok;
+  p.drop0 = drop_ids[0];
+  p.drop1 = drop_ids[1];
+  p.drop2 = drop_ids[2];
+  p.us_alphas = us_alphas;
+  p.us_peaks = us_peaks;
+  p.fire_idx = fire_idx;
+  p.fire_count = fire_count;
+  p.num_chars = num_chars;
+  fb200::lstm::us_fires_kernel<<<(batch + 3) / 4, 128, 0, (cudaStream_t)stream>>>(p);
+  FB_CHECK_LAUNCH("us_fires");
+  return FB200_OK;
+}

@@ -17,7 +17,7 @@ void count_launch(int n = 1);
 enum ProfKind {
   kProfFbank = 0, kProfLfr, kProfPe, kProfLayerNorm, kProfSplit, kProfFsmn, kProfGemm, kProfAttention,
   kProfCifAlpha, kProfCifScan, kProfCifIntegrate, kProfArgmax, kProfCtc, kProfConvSub, kProfGluDw, kProfRelAttention,
-  kProfKinds
+  kProfLstm, kProfUsFires, kProfKinds
 };
 class ProfScope {
  public:

@@ -277,7 +277,7 @@ class PredictorPack:
         total = int(sum(tok))
         embeds = torch.empty(total, d, dtype=torch.float32, device=dev)
         ops.cif_integrate(enc, alphas, cu_rows, cu_tok, total, self.tail, fire_pos, fire_rem, embeds)
-        return dict(alphas=alphas, token_num=tok, cu_tok=cu_tok, embeds=embeds, fires=fires)
+        return dict(alphas=alphas, token_num=tok, token_num_dev=token_num, cu_tok=cu_tok, embeds=embeds, fires=fires)
 
 
 class DecoderPack:

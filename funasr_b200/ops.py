@@ -193,6 +193,42 @@ def cif_integrate(hidden, alphas, cu_rows, cu_tok, total_tok, tail, fire_pos, fi
               embeds.stride(0), _stream())
 
 
+def lstm_parts(hidden: int = 512) -> int:
+    import ctypes
+
+    n = ctypes.c_int()
+    _lib.call("fb200_lstm_parts", hidden, ctypes.byref(n))
+    return int(n.value)
+
+
+def lstm_bidir(xg, cu_rows, upsample, max_len3, w_hh, w_out, part, out_h=None, hidden=512):
+    """Bidirectional LSTM over packed rows fused with the Linear(2H -> 1) dot product: xg fp32 [rows3, >= 8H], w_hh fp32
+    [2, 4H, H], w_out fp32 [2, H], part fp32 [lstm_parts(H), rows3] (out), out_h fp32 [rows3, 2H] or None."""
+    import ctypes
+
+    _chk(xg, torch.float32, "lstm_bidir")
+    _chk(part, torch.float32, "lstm_bidir")
+    batch, rows3 = cu_rows.numel() - 1, xg.shape[0]
+    nbytes = ctypes.c_longlong()
+    _lib.call("fb200_lstm_workspace_bytes", batch, hidden, ctypes.byref(nbytes))
+    ws = torch.empty((int(nbytes.value) + 3) // 4, dtype=torch.float32, device=xg.device)
+    _lib.call("fb200_lstm_bidir", _p(xg), xg.stride(0), _p(cu_rows), upsample, batch, rows3, max_len3, hidden, _p(w_hh),
+              _p(w_out), _p(ws), int(nbytes.value), _p(part), _p(out_h), _stream())
+
+
+def us_fires(part, bias, smooth, noise, threshold, cu_rows, upsample, token_num, ids, cu_tok, drop_ids, us_alphas, fire_idx,
+             fire_count, num_chars, us_peaks=None):
+    """Upsampled alphas, their fires and the per-utterance character counts (see include/funasr_b200.h)."""
+    import ctypes
+
+    _chk(part, torch.float32, "us_fires")
+    drop = (ctypes.c_int32 * 3)(*[int(d) for d in drop_ids])
+    _lib.call("fb200_us_fires", _p(part), part.shape[0], part.shape[1], float(bias), float(smooth), float(noise),
+              float(threshold), _p(cu_rows), upsample, cu_rows.numel() - 1, _p(token_num), _p(ids), _p(cu_tok),
+              ctypes.cast(drop, ctypes.c_void_p), _p(us_alphas), _p(us_peaks), _p(fire_idx), _p(fire_count), _p(num_chars),
+              _stream())
+
+
 def argmax_logprob(logits, vocab, ids, score=None, rows=None):
     rows = logits.shape[0] if rows is None else rows
     _lib.call("fb200_argmax_logprob", _p(logits), logits.stride(0), rows, vocab, _p(ids), _p(score), _stream())

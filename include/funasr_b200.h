@@ -50,10 +50,11 @@ long long fb200_launch_count(int reset);
  * is bracketed by CUDA events on its stream.  `kind` indexes the entry points in header order:
  * 0 fbank, 1 lfr_cmvn, 2 scale_add_pe, 3 layernorm, 4 split_rows/split_weight, 5 fsmn, 6 gemm,
  * 7 attention, 8 cif_alpha, 9 cif_scan, 10 cif_integrate, 11 argmax_logprob, 12 ctc_collapse, 13 conv2d_sub1,
- * 14 glu_dwconv, 15 attention_relpos (gemm_ex counts as gemm, gather_rows as split_rows).
+ * 14 glu_dwconv, 15 attention_relpos, 16 lstm_bidir, 17 us_fires (gemm_ex / gemm_heads count as gemm, gather_rows as
+ * split_rows).
  * fb200_profile_read synchronises on the recorded events and returns the summed milliseconds,
  * call count and algorithmic work (bytes for HBM-bound kinds, FLOPs for gemm/attention). */
-#define FB200_PROFILE_KINDS 16
+#define FB200_PROFILE_KINDS 18
 int fb200_profile_enable(int on);
 int fb200_profile_read(int kind, double* ms, long long* calls, double* work, int reset);
 
@@ -302,6 +303,38 @@ int fb200_cif_integrate(const float* hidden, int ld_h, const float* alphas, cons
                         const int32_t* cu_tok, int batch, int total_tok, int dim, float tail_threshold,
                         const int32_t* fire_pos, const float* fire_rem, float* embeds, int ld_e,
                         void* stream);
+
+/* ------------------------------------------------------------------ time-stamp head ---- */
+/* BiCifParaformer (funasr/models/bicif_paraformer/model.py:135-142, :307-309): CifPredictorV3.get_upsample_timestamp
+ * (funasr/models/bicif_paraformer/cif_predictor.py:248-293) and the fire search of ts_prediction_lfr6_standard
+ * (funasr/utils/timestamp_tools.py:31-53).  The upsampling ConvTranspose1d and the LSTM input projections are
+ * fb200_gemm / fb200_gemm_ex launches; these two entries are the recurrent part and the fires. */
+
+/* Bidirectional one-layer LSTM (torch.nn.LSTM gate order i, f, g, o; zero initial state) over a packed batch, both
+ * directions in one cooperative launch, fused with the Linear(2H -> 1) that follows it:
+ *   xg    f32 [rows3, ld_xg]   W_ih x + b_ih + b_hh, columns [direction][gate][H] (direction 1 = reverse)
+ *   utterance b owns rows [upsample*cu_rows[b], upsample*cu_rows[b+1]); each direction starts at its own end
+ *   w_hh  f32 [2][4H][H], w_out f32 [2][H] (the Linear's weight split by direction)
+ *   part  f32 [fb200_lstm_parts][rows3]  partial dot products: the Linear's output is bias + the sum over parts
+ *   out_h f32 [rows3, 2H] or NULL        the LSTM output itself (tests)
+ *   workspace: fb200_lstm_workspace_bytes(batch, H) bytes of device memory (state double buffer, cell state, barrier).
+ * H = 512 only; batch <= 1024. */
+int fb200_lstm_workspace_bytes(int batch, int hidden, long long* bytes);
+int fb200_lstm_parts(int hidden, int* parts);
+int fb200_lstm_bidir(const float* xg, int ld_xg, const int32_t* cu_rows, int upsample, int batch, int rows3, int max_len3,
+                     int hidden, const float* w_hh, const float* w_out, float* workspace, long long workspace_bytes,
+                     float* part, float* out_h, void* stream);
+
+/* alphas2 = relu(sigmoid(bias + sum(part)) * smooth - noise), scaled so each utterance sums to token_num[b]
+ * (cif_predictor.py:270-283) -> us_alphas [rows3]; then the sequential fp32 integrate-and-fire of cif_wo_hidden with
+ * `threshold` (:71-93) -> us_peaks (optional) and the fired frame indices, relative to the utterance, in fire_idx from
+ * upsample*cu_rows[b]; fire_count[b] of them.  num_chars[b] = ids of the utterance not in drop_ids (3 HOST ints);
+ * when fire_count != num_chars + 1 the alphas are divided by sum / (num_chars + 1) and fired again
+ * (timestamp_tools.py:46-53). */
+int fb200_us_fires(const float* part, int nparts, int rows3, float bias, float smooth, float noise, float threshold,
+                   const int32_t* cu_rows, int upsample, int batch, const int32_t* token_num, const int32_t* ids,
+                   const int32_t* cu_tok, const int32_t* drop_ids, float* us_alphas, float* us_peaks, int32_t* fire_idx,
+                   int32_t* fire_count, int32_t* num_chars, void* stream);
 
 /* ------------------------------------------------------------------ decoding ----------- */
 
