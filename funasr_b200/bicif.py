@@ -109,27 +109,24 @@ class BiCifParaformerEngine(ParaformerEngine):
         stamps: List[List[List[int]]] = [[] for _ in waves]
         scores = [0.0 for _ in waves]
         self.last_token_num = [0 for _ in waves]
-        batches = self.plan_batches([int(w.shape[0]) for w in waves])
-        with torch.cuda.device(self.device):
-            for batch in batches:
-                wave, lens = self.upload([waves[i] for i in batch])
-                ids, logp, tok, rows, ts = self.forward_packed_ts(wave, lens)
-                ids_h = ids.cpu().numpy()
-                logp_h = logp.cpu().numpy() if with_scores else None
-                keep = ~np.isin(ids_h, self._drop_ids)
-                if ts is not None:
-                    fire_idx, fire_count = ts["fire_idx"].cpu().numpy(), ts["fire_count"].cpu().numpy()
-                    num_chars = ts["num_chars"].cpu().numpy()
-                o = r0 = 0
-                for j, (i, n) in enumerate(zip(batch, tok)):
-                    self.last_token_num[i] = int(n)
-                    results[i] = ids_h[o: o + n][keep[o: o + n]].tolist()
-                    if with_scores:
-                        scores[i] = float(logp_h[o: o + n].sum())
-                    if ts is not None and n > 0:
-                        f0 = 3 * r0
-                        stamps[i] = timestamp.stamps_from_fires(fire_idx[f0: f0 + int(fire_count[j])], 3 * rows[j],
-                                                                int(num_chars[j]), vad_offset=begin_time)
-                    o += n
-                    r0 += rows[j]
+        for batch, wave, lens in self.uploaded_batches(waves):
+            ids, logp, tok, rows, ts = self.forward_packed_ts(wave, lens)
+            ids_h = ids.cpu().numpy()
+            logp_h = logp.cpu().numpy() if with_scores else None
+            keep = ~np.isin(ids_h, self._drop_ids)
+            if ts is not None:
+                fire_idx, fire_count = ts["fire_idx"].cpu().numpy(), ts["fire_count"].cpu().numpy()
+                num_chars = ts["num_chars"].cpu().numpy()
+            o = r0 = 0
+            for j, (i, n) in enumerate(zip(batch, tok)):
+                self.last_token_num[i] = int(n)
+                results[i] = ids_h[o: o + n][keep[o: o + n]].tolist()
+                if with_scores:
+                    scores[i] = float(logp_h[o: o + n].sum())
+                if ts is not None and n > 0:
+                    f0 = 3 * r0
+                    stamps[i] = timestamp.stamps_from_fires(fire_idx[f0: f0 + int(fire_count[j])], 3 * rows[j],
+                                                            int(num_chars[j]), vad_offset=begin_time)
+                o += n
+                r0 += rows[j]
         return (results, stamps, scores) if with_scores else (results, stamps)

@@ -246,6 +246,16 @@ __device__ int fire_scan(const float* alphas, int n, float div, float thr, float
   return count;
 }
 
+// alphas2 = relu(sigmoid(bias + sum of the LSTM kernel's partial dot products) * smooth - noise), one thread per frame
+__global__ void __launch_bounds__(256) us_alpha_kernel(const FireParams p) {
+  const int r = blockIdx.x * 256 + threadIdx.x;
+  if (r >= p.rows3) return;
+  float logit = p.bias;
+  for (int j = 0; j < p.nparts; ++j) logit += __ldg(p.part + (size_t)j * p.rows3 + r);
+  const float a = 1.f / (1.f + expf(-logit));
+  p.us_alphas[r] = fmaxf(a * p.smooth - p.noise, 0.f);
+}
+
 __global__ void __launch_bounds__(128) us_fires_kernel(const FireParams p) {
   const int lane = threadIdx.x & 31;
   const int b = blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -254,14 +264,7 @@ __global__ void __launch_bounds__(128) us_fires_kernel(const FireParams p) {
   float* alphas = p.us_alphas + beg3;
   int32_t* fire_idx = p.fire_idx + beg3;
   float sum = 0.f;
-  for (int r = lane; r < n; r += 32) {
-    float logit = p.bias;
-    for (int j = 0; j < p.nparts; ++j) logit += p.part[(size_t)j * p.rows3 + beg3 + r];
-    float a = 1.f / (1.f + expf(-logit));
-    a = fmaxf(a * p.smooth - p.noise, 0.f);
-    alphas[r] = a;
-    sum += a;
-  }
+  for (int r = lane; r < n; r += 32) sum += alphas[r];  // alphas2 from us_alpha_kernel
   sum = warp_sum(sum);
   const float scale = (float)p.token_num[b] / sum;
   float sum2 = 0.f;
@@ -390,6 +393,8 @@ extern "C" __attribute__((visibility("default"))) int fb200_us_fires(
   p.fire_idx = fire_idx;
   p.fire_count = fire_count;
   p.num_chars = num_chars;
+  fb200::lstm::us_alpha_kernel<<<(rows3 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(p);
+  FB_CHECK_LAUNCH("us_alpha");
   fb200::lstm::us_fires_kernel<<<(batch + 3) / 4, 128, 0, (cudaStream_t)stream>>>(p);
   FB_CHECK_LAUNCH("us_fires");
   return FB200_OK;

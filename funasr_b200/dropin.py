@@ -387,6 +387,30 @@ class CifPredictorV2(_ParamTree):
         return embeds, token_num, alphas, peaks
 
 
+class CifPredictorV3(CifPredictorV2):
+    """funasr/models/bicif_paraformer/cif_predictor.py:96-246 at inference: the V2 head (same tensors; `cif` is the same
+    recurrence as `cif_v1`) plus the parameters of the time-stamp head (`upsample_cnn`, `blstm`, `cif_output2`), which
+    `BiCifParaformer.inference` runs through `bicif.TimestampPack`.  `forward` returns the reference's 5-tuple; the
+    fifth value (`token_num2`, a training loss input) is None."""
+
+    def __init__(self, idim, l_order, r_order, threshold=1.0, dropout=0.1, smooth_factor=1.0, noise_threshold=0,
+                 tail_threshold=0.0, tf2torch_tensor_name_prefix_torch="predictor",
+                 tf2torch_tensor_name_prefix_tf="seq2seq/cif", smooth_factor2=1.0, noise_threshold2=0, upsample_times=5,
+                 upsample_type="cnn", use_cif1_cnn=True, tail_mask=True, precision: Optional[str] = None, **kwargs):
+        super().__init__(idim, l_order, r_order, threshold=threshold, dropout=dropout, smooth_factor=smooth_factor,
+                         noise_threshold=noise_threshold, tail_threshold=tail_threshold, tail_mask=tail_mask, precision=precision)
+        if upsample_type != "cnn_blstm" or use_cif1_cnn or upsample_times != 3:
+            raise NotImplementedError("funasr_b200.CifPredictorV3: only upsample_type = cnn_blstm, use_cif1_cnn = false, "
+                                      "upsample_times = 3 (funasr/models/bicif_paraformer/template.yaml:47-58)")
+        self.smooth_factor2, self.noise_threshold2, self.upsample_times = smooth_factor2, noise_threshold2, upsample_times
+        extra = {k: v for k, v in params.bicif_predictor_shapes(idim, upsample_times, "").items() if k not in dict(self.named_parameters())}
+        self._declare(extra, "")
+
+    def forward(self, hidden, target_label=None, mask=None, ignore_id=-1, mask_chunk_predictor=None,
+                target_label_length=None):
+        return super().forward(hidden, target_label, mask, ignore_id, mask_chunk_predictor, target_label_length) + (None,)
+
+
 class ParaformerSANMDecoder(_ParamTree):
     """funasr/models/paraformer/decoder.py:224-411: `forward(hs_pad, hlens, ys_in_pad, ys_in_lens)`
     -> (logits [B, Lmax, V], olens)."""
@@ -477,6 +501,8 @@ class ParaformerInference:
 
     _fb200_engine = None
     _fb200_engine_key = None
+    _fb200_engine_cls = engine.ParaformerEngine
+    _fb200_timestamps = False  # BiCifParaformer: time stamps are part of the path
 
     def _engine_for(self, frontend) -> engine.ParaformerEngine:
         dev = next(self.parameters()).device
@@ -487,8 +513,8 @@ class ParaformerInference:
                getattr(frontend, "cmvn_file", None), getattr(frontend, "window", "hamming"))
         if self._fb200_engine is None or self._fb200_engine_key != key:
             sd = {k: v.detach() for k, v in self.state_dict().items()}
-            self._fb200_engine = engine.ParaformerEngine(sd, dev, precision=PRECISION, cmvn=getattr(frontend, "cmvn", None),
-                                                         window=getattr(frontend, "window", "hamming"))
+            self._fb200_engine = self._fb200_engine_cls(sd, dev, precision=PRECISION, cmvn=getattr(frontend, "cmvn", None),
+                                                        window=getattr(frontend, "window", "hamming"))
             self._fb200_engine_key = key
         return self._fb200_engine
 
@@ -496,8 +522,9 @@ class ParaformerInference:
         import time
 
         off_path = (kwargs.get("decoding_ctc_weight", 0.0) > 0.00001 and getattr(self, "ctc", None) is not None) or (
-            kwargs.get("lm_weight", 0.0) > 0.00001 and kwargs.get("lm_file") is not None) or kwargs.get(
-            "pred_timestamp", False) or kwargs.get("data_type", "sound") == "fbank" or getattr(self, "beam_search", None) is not None
+            kwargs.get("lm_weight", 0.0) > 0.00001 and kwargs.get("lm_file") is not None) or (
+            kwargs.get("pred_timestamp", False) and not self._fb200_timestamps) or kwargs.get(
+            "data_type", "sound") == "fbank" or getattr(self, "beam_search", None) is not None
         if off_path:
             ref = getattr(super(), "inference", None)
             if ref is None:
@@ -510,7 +537,11 @@ class ParaformerInference:
         t2 = time.perf_counter()
         meta_data["load_data"] = f"{t2 - t1:0.3f}"
         eng = self._engine_for(frontend)
-        ids, scores = eng.recognize(waves, with_scores=True)
+        stamps = None
+        if self._fb200_timestamps:
+            ids, stamps, scores = eng.recognize(waves, with_scores=True, begin_time=kwargs.get("begin_time", 0))
+        else:
+            ids, scores = eng.recognize(waves, with_scores=True)
         t3 = time.perf_counter()
         meta_data["extract_feat"] = f"{t3 - t2:0.3f}"  # here: the whole device path (the reference times fbank alone)
         _, rows = eng.frontend.plan([len(w) for w in waves])
@@ -538,6 +569,20 @@ class ParaformerInference:
                 continue
             token = tokenizer.ids2tokens(token_int)
             text = tokenizer.tokens2text(token)
+            if stamps is not None:  # bicif_paraformer/model.py:343-361: text and stamps post-processed together
+                stamp = stamps[i]
+                try:
+                    from funasr.utils import postprocess_utils  # noqa: WPS433 (host application; text only)
+
+                    text, stamp, _ = postprocess_utils.sentence_postprocess(token, stamp)
+                except ImportError:
+                    pass
+                results.append({"key": key[i], "text": text, "timestamp": stamp})
+                if writer is not None:
+                    writer["token"][key[i]] = " ".join(token)
+                    writer["timestamp"][key[i]] = stamp
+                    writer["text"][key[i]] = text
+                continue
             if not hasattr(tokenizer, "bpemodel"):
                 try:
                     from funasr.utils import postprocess_utils  # noqa: WPS433 (host application; text only)
@@ -818,6 +863,30 @@ class CTC(CTCInference, nn.Module):
 DROPIN_CLASSES[("model_classes", "CTC")] = CTC
 
 
+class BiCifParaformerInference(ParaformerInference):
+    """`BiCifParaformer.inference` (funasr/models/bicif_paraformer/model.py:222-369) as one call into
+    `bicif.BiCifParaformerEngine`: token ids as for Paraformer plus `"timestamp"`: [[begin ms, end ms], ...] per token
+    from the CifPredictorV3 time-stamp head (`begin_time` kwarg = the VAD offset, :349).  Returns the reference's
+    `(results, meta_data)`."""
+
+    _fb200_timestamps = True
+
+    @property
+    def _fb200_engine_cls(self):
+        from . import bicif
+
+        return bicif.BiCifParaformerEngine
+
+
+class BiCifParaformer(BiCifParaformerInference, Paraformer):
+    """Stand-alone `BiCifParaformer` (funasr/models/bicif_paraformer/model.py:37-52): Paraformer's constructor with a
+    CifPredictorV3 predictor; inference only."""
+
+
+DROPIN_CLASSES[("predictor_classes", "CifPredictorV3")] = CifPredictorV3
+DROPIN_CLASSES[("model_classes", "BiCifParaformer")] = BiCifParaformer
+
+
 def _model_class(key: str, cls):
     """The class registered under model_classes[key]: the reference's own class with `inference` replaced
     when the reference is importable (construction, checkpoints and training stay the reference's), else the
@@ -836,6 +905,13 @@ def _model_class(key: str, cls):
             return cls
         return type("SenseVoiceSmall", (SenseVoiceInference, ref_sv), {"__doc__": SenseVoiceInference.__doc__,
                                                                         "__module__": __name__})
+    if cls is BiCifParaformer:
+        try:
+            from funasr.models.bicif_paraformer.model import BiCifParaformer as ref_bicif  # noqa: WPS433
+        except ImportError:
+            return cls
+        return type("BiCifParaformer", (BiCifParaformerInference, ref_bicif), {"__doc__": BiCifParaformerInference.__doc__,
+                                                                                "__module__": __name__})
     if cls is CTC:
         try:
             from funasr.models.ctc.model import Transformer as ref_ctc  # noqa: WPS433 (registered as "CTC", model.py:17)

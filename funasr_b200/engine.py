@@ -436,18 +436,13 @@ class ParaformerEngine:
             batches.append(cur)
         return batches
 
-    def recognize(self, waves: Sequence[np.ndarray], with_scores: bool = False):
-        """Token ids per utterance (sos/eos/blank dropped).  Utterances shorter than one frame or
-        with no predicted token give [] (model.py:514-515)."""
-        results: List[List[int]] = [[] for _ in waves]
-        scores = [0.0 for _ in waves]
-        self.last_token_num = [0 for _ in waves]  # predicted token counts of the last call (before id filtering)
-        lens_all = [int(w.shape[0]) for w in waves]
-        batches = self.plan_batches(lens_all)
+    def uploaded_batches(self, waves: Sequence[np.ndarray]):
+        """Yields (utterance indices, packed device waveforms, sample counts) per planned batch, inside this engine's
+        device context; the host -> device copies of batch k + 1 run on their own stream under the kernels of batch k."""
+        batches = self.plan_batches([int(w.shape[0]) for w in waves])
         if not batches:
-            return (results, scores) if with_scores else results
+            return
         with torch.cuda.device(self.device):
-            # host -> device copies of batch k + 1 run on their own stream under the kernels of batch k
             compute = torch.cuda.current_stream()
             if self._copy_stream is None:
                 self._copy_stream = torch.cuda.Stream(device=self.device)
@@ -466,17 +461,26 @@ class ParaformerEngine:
                 wave.record_stream(compute)  # allocated under the copy stream, consumed on the compute stream
                 if bi + 1 < len(batches):
                     nxt = start_upload(batches[bi + 1])
-                ids, logp, tok = self.forward_packed(wave, lens)
-                ids_h = ids.cpu().numpy()
-                logp_h = logp.cpu().numpy() if with_scores else None
-                keep = ~np.isin(ids_h, self._drop_ids)
-                o = 0
-                for i, n in zip(batch, tok):
-                    self.last_token_num[i] = int(n)
-                    results[i] = ids_h[o: o + n][keep[o: o + n]].tolist()
-                    if with_scores:
-                        scores[i] = float(logp_h[o: o + n].sum())
-                    o += n
+                yield batch, wave, lens
+
+    def recognize(self, waves: Sequence[np.ndarray], with_scores: bool = False):
+        """Token ids per utterance (sos/eos/blank dropped).  Utterances shorter than one frame or
+        with no predicted token give [] (model.py:514-515)."""
+        results: List[List[int]] = [[] for _ in waves]
+        scores = [0.0 for _ in waves]
+        self.last_token_num = [0 for _ in waves]  # predicted token counts of the last call (before id filtering)
+        for batch, wave, lens in self.uploaded_batches(waves):
+            ids, logp, tok = self.forward_packed(wave, lens)
+            ids_h = ids.cpu().numpy()
+            logp_h = logp.cpu().numpy() if with_scores else None
+            keep = ~np.isin(ids_h, self._drop_ids)
+            o = 0
+            for i, n in zip(batch, tok):
+                self.last_token_num[i] = int(n)
+                results[i] = ids_h[o: o + n][keep[o: o + n]].tolist()
+                if with_scores:
+                    scores[i] = float(logp_h[o: o + n].sum())
+                o += n
         return (results, scores) if with_scores else results
 
 

@@ -465,3 +465,71 @@ def test_ctc_model_inference_override_matches_golden(conformer_sd, golden_dir):
     for ci, r in enumerate(results):
         assert r["token"] == ["t%d" % i for i in g["ids_%d" % ci].tolist()]
     assert meta["batch_data_time"] > 0
+
+
+# ---------------------------------------------------------------------------------------- BiCifParaformer (8f rank 3)
+PRED_V3 = dict(idim=512, threshold=1.0, l_order=1, r_order=1, tail_threshold=0.45, smooth_factor2=0.25, noise_threshold2=0.01,
+               upsample_times=3, use_cif1_cnn=False, upsample_type="cnn_blstm")
+
+
+def test_standalone_bicif_model_has_the_reference_state_dict():
+    conf = dict(MODEL, predictor="CifPredictorV3", predictor_conf=PRED_V3, encoder_conf=dict(ENC, num_blocks=2),
+                decoder_conf=dict(DEC, num_blocks=2, att_layer_num=2))
+    model = dropin.BiCifParaformer(**conf)
+    want = params.bicif_paraformer_shapes(enc_blocks=2, dec_blocks=2)
+    assert {k: tuple(v.shape) for k, v in model.state_dict().items()} == dict(want)
+    assert dropin.DROPIN_CLASSES[("model_classes", "BiCifParaformer")] is dropin.BiCifParaformer
+    with pytest.raises(NotImplementedError):
+        dropin.CifPredictorV3(**dict(PRED_V3, upsample_type="cnn"))
+    frontend = dropin.WavFrontend(lfr_m=7, lfr_n=6, dither=0.0)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        model.inference([synth.synth_waveform(0, 16000)], key=["a"], tokenizer=None, frontend=frontend, device="cpu")
+
+
+@pytest.mark.skipif(not reference_available(), reason="reference tree not present (GPU box)")
+def test_install_wraps_the_reference_bicif_model_class():
+    from ref_loader import import_reference
+
+    import_reference()
+    from funasr.models.bicif_paraformer.model import BiCifParaformer as ref_cls
+    from funasr.register import tables
+
+    saved = {t: dict(getattr(tables, t)) for t in ("model_classes", "predictor_classes", "encoder_classes", "decoder_classes",
+                                                    "frontend_classes")}
+    try:
+        dropin.install(tables)
+        cls = tables.model_classes["BiCifParaformer"]
+        assert issubclass(cls, ref_cls) and issubclass(cls, dropin.BiCifParaformerInference)
+        assert cls.inference is dropin.ParaformerInference.inference and cls._fb200_timestamps
+        assert tables.predictor_classes["CifPredictorV3"] is dropin.CifPredictorV3
+    finally:
+        for t, d in saved.items():
+            getattr(tables, t).clear()
+            getattr(tables, t).update(d)
+
+
+@pytest.mark.gpu
+def test_bicif_model_inference_override_matches_golden(bicif_sd, golden_dir, tmp_path):
+    """`BiCifParaformer.inference` (bicif_paraformer/model.py:222-369) through the packed engine: token ids and the
+    time stamps of the reference's batch-1 runs, for a ragged batch in one call."""
+    g = np.load(os.path.join(golden_dir, "bicif.npz"))
+    dev = torch.device("cuda:0")
+    shift, scale = synth.synth_cmvn()
+    cmvn_file = str(tmp_path / "am.mvn")
+    synth.write_cmvn_file(cmvn_file, shift, scale)
+    frontend = dropin.WavFrontend(cmvn_file=cmvn_file, fs=16000, window="hamming", n_mels=80, frame_length=25,
+                                  frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0)
+    model = dropin.BiCifParaformer(**dict(MODEL, predictor="CifPredictorV3", predictor_conf=PRED_V3)).to(dev)
+    model.load_state_dict(bicif_sd, strict=True)
+    waves = [synth.synth_waveform(int(g["seeds"][ci]), int(g["num_samples"][ci])) for ci in range(3)]
+    results, meta = model.inference(waves, key=["a", "b", "c"], tokenizer=None, frontend=frontend, device="cuda:0")
+    assert [r["token_int"] for r in results] == [g["ids_%d" % ci].tolist() for ci in range(3)]
+    tok = _Tokenizer()
+    results, _ = model.inference(waves, key=["a", "b", "c"], tokenizer=tok, frontend=frontend, device="cuda:0")
+    for ci, r in enumerate(results):
+        assert set(r) == {"key", "text", "timestamp"}
+        if not reference_available():  # without the reference's text post-processing the raw stamps come back
+            assert r["timestamp"] == g["timestamp_%d" % ci].tolist()
+    shifted, _ = model.inference([waves[0]], key=["a"], tokenizer=tok, frontend=frontend, device="cuda:0", begin_time=1000)
+    if not reference_available():
+        assert shifted[0]["timestamp"][0] == [g["timestamp_0"][0][0] + 1000, g["timestamp_0"][0][1] + 1000]

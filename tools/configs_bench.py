@@ -2,6 +2,7 @@
 
     python tools/configs_bench.py --config 3     # SenseVoiceSmall (50 + 20 SAN-M blocks, V = 25055), CTC greedy
     python tools/configs_bench.py --config 5     # Paraformer-large long-audio sweep: 60 / 120 / 300 / 600 s x 8 each
+    python tools/configs_bench.py --config 6     # BiCifParaformer (what `paraformer-zh` resolves to): ids + time stamps
 
 Prints ONE JSON line: throughput with waveforms resident in HBM, end to end from pinned host memory, per-kernel-kind
 device times of one step (fb200_profile_*), and the oracle timed on the host cores over a bounded sample.
@@ -22,7 +23,7 @@ from funasr_b200 import _lib, engine, params, synth  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, required=True, choices=[3, 5])
+    ap.add_argument("--config", type=int, required=True, choices=[3, 5, 6])
     ap.add_argument("--utts", type=int, default=256)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
@@ -40,6 +41,16 @@ def main():
         name = "configs[2]: SenseVoiceSmall (50 + 20 SAN-M blocks, V = 25055) CTC greedy, %d synthetic utterances U(2,30) s" % args.utts
         metric = "SenseVoiceSmall RTFx (audio s / wall s)"
         cpu_fn, cpu_n = (lambda w: O.sense_voice_recognize(torch.from_numpy(w), sd, cmvn)), 4
+    elif args.config == 6:
+        from funasr_b200 import bicif
+        from oracle import bicif_oracle as BO
+
+        sd = {k: torch.from_numpy(v) for k, v in synth.synth_state_dict(params.bicif_paraformer_shapes(), seed=0).items()}
+        eng = bicif.BiCifParaformerEngine(sd, dev, "fp32", cmvn=cmvn, max_rows=args.max_rows)
+        durs = synth.synth_durations(args.utts)
+        name = "BiCifParaformer (SURVEY 8f rank 3): Paraformer-large + CifPredictorV3 time-stamp head, %d synthetic utterances U(2,30) s" % args.utts
+        metric = "BiCifParaformer RTFx (audio s / wall s), token ids + time stamps"
+        cpu_fn, cpu_n = (lambda w: BO.recognize(torch.from_numpy(w), sd, cmvn)), 2
     else:
         sd = {k: torch.from_numpy(v) for k, v in synth.synth_state_dict(params.paraformer_large_shapes(), seed=0).items()}
         eng = engine.ParaformerEngine(sd, dev, "fp32", cmvn=cmvn, max_rows=args.max_rows)
