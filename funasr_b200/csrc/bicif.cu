@@ -193,6 +193,182 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_kernel(const Params p) 
   }
 }
 
+// ---------------------------------------------------------------- tensor-core recurrence
+// Same schedule as lstm_bidir_kernel with the h . W_hh^T product of a step on the tensor cores (warp-level
+// mma.sync m16n8k16, bf16 operands split hi + mid, 3 terms, fp32 accumulate -- the operand scheme of the GEMMs): the SIMT
+// kernel re-reads every staged h row once per hidden unit and is bound by shared-memory bandwidth (12.6 us per 64-utterance
+// chunk and step); here the CTA's W_hh slice lives in REGISTERS as B fragments (warp = one gate x 8 units, 32 k-steps x
+// 2 parts) and the staged h is read once per gate through ldmatrix.  h travels between CTAs as bf16 hi + mid.
+constexpr int HPB = H + 8;  // bf16 row pitch: 1040 B, ldmatrix rows land in distinct banks
+constexpr size_t kSmemMma = (size_t)2 * BC * HPB * sizeof(__nv_bfloat16) + (size_t)(4 * BC * UPC + BC * UPC) * sizeof(float);
+
+__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void split_pair(float x, float y, uint32_t& hi, uint32_t& mid) {
+  const __nv_bfloat162 h = __floats2bfloat162_rn(x, y);
+  const __nv_bfloat162 m = __floats2bfloat162_rn(x - __low2float(h), y - __high2float(h));
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  mid = *reinterpret_cast<const uint32_t*>(&m);
+}
+
+__global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __nv_bfloat16* hs_hi = reinterpret_cast<__nv_bfloat16*>(smem_raw);  // [BC][HPB]
+  __nv_bfloat16* hs_mid = hs_hi + BC * HPB;                           // [BC][HPB]
+  float* gates_s = reinterpret_cast<float*>(hs_mid + BC * HPB);       // [4 gates][BC][UPC]
+  float* lg = gates_s + 4 * BC * UPC;                                 // [BC][UPC]
+  __shared__ int chunk_max[MAX_CHUNKS];
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int dir = blockIdx.x / CTAS, cta = blockIdx.x % CTAS, u0 = cta * UPC;
+  const int B = p.batch;
+  const int nchunks = (B + BC - 1) / BC;
+  const int nt = warp & 3, mh = warp >> 2;  // this warp: gate nt (8 units), staged rows [32 mh, 32 mh + 32)
+  const int g = lane >> 2, t4 = lane & 3;
+  // B fragments of W_hh[dir][gate nt][unit u0 + g][:] for all 32 k-steps, hi and mid
+  uint32_t whi[32][2], wmid[32][2];
+  {
+    const float* wrow = p.w_hh + ((size_t)dir * 4 * H + nt * H + u0 + g) * H;
+#pragma unroll
+    for (int s = 0; s < 32; ++s) {
+      const float2 a = __ldg(reinterpret_cast<const float2*>(wrow + 16 * s + 2 * t4));
+      const float2 b = __ldg(reinterpret_cast<const float2*>(wrow + 16 * s + 2 * t4 + 8));
+      split_pair(a.x, a.y, whi[s][0], wmid[s][0]);
+      split_pair(b.x, b.y, whi[s][1], wmid[s][1]);
+    }
+  }
+  if (tid < MAX_CHUNKS) {
+    int m = 0;
+    for (int b = tid * BC; b < min(B, (tid + 1) * BC); ++b) m = max(m, p.up * (p.cu_rows[b + 1] - p.cu_rows[b]));
+    chunk_max[tid] = m;
+  }
+  __syncthreads();
+
+  __nv_bfloat16* hb = reinterpret_cast<__nv_bfloat16*>(p.hbuf);  // [dir][phase][B][hi 512 | mid 512]
+  unsigned int* counter = p.counters + dir;
+  const int eb = tid >> 2, eu = (tid & 3) * 2;  // epilogue: utterance eb of the chunk, units eu, eu + 1
+  const float2 wout = __ldg(reinterpret_cast<const float2*>(p.w_out + dir * H + u0 + eu));
+  // ldmatrix row address of this lane inside a 16 x 16 tile: matrices (rows 0-7 | 8-15) x (k 0-7 | 8-15)
+  const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8, lcol = (lane >> 4) * 8;
+  const uint32_t hi_base = (uint32_t)__cvta_generic_to_shared(hs_hi) + (uint32_t)((mh * 32 + lrow) * HPB + lcol) * 2u;
+  const uint32_t mid_base = (uint32_t)__cvta_generic_to_shared(hs_mid) + (uint32_t)((mh * 32 + lrow) * HPB + lcol) * 2u;
+
+  for (int t = 0; t < p.max_len3; ++t) {
+    const __nv_bfloat16* rd = hb + ((size_t)(dir * 2 + (t & 1)) * B) * (2 * H);
+    __nv_bfloat16* wr = hb + ((size_t)(dir * 2 + ((t + 1) & 1)) * B) * (2 * H);
+    if (t > 0) {
+      if (tid == 0) {
+        const unsigned int target = (unsigned int)t * CTAS;
+        unsigned int spins = 0;
+        while (ld_acquire(counter) < target) {
+          if (++spins > (1u << 27)) {
+            printf("funasr_b200 lstm: barrier timeout dir %d cta %d step %d\n", dir, cta, t);
+            __trap();
+          }
+        }
+      }
+      __syncthreads();
+    }
+    for (int c = 0; c < nchunks; ++c) {
+      if (t >= chunk_max[c]) continue;
+      const int b0 = c * BC, nb = min(BC, B - b0);
+      for (int i = tid; i < nb * 128; i += THREADS) {
+        const int row = i >> 7, c16 = i & 127, part = c16 >> 6, off = (c16 & 63) * 8;
+        cp_async16((part ? hs_mid : hs_hi) + row * HPB + off, rd + (size_t)(b0 + row) * (2 * H) + part * H + off);
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      const int b = b0 + eb;
+      bool act = false;
+      int rowi = 0;
+      if (b < B) {
+        const int beg = p.cu_rows[b], len3 = p.up * (p.cu_rows[b + 1] - beg);
+        if (t < len3) {
+          act = true;
+          rowi = p.up * beg + (dir ? len3 - 1 - t : t);
+        }
+      }
+      float2 xv[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q)
+        xv[q] = act ? __ldg(reinterpret_cast<const float2*>(p.xg + (size_t)rowi * p.ld_xg + dir * 4 * H + q * H + u0 + eu))
+                    : make_float2(0.f, 0.f);
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();
+      float acc[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[mt][q] = 0.f;
+#pragma unroll
+      for (int s = 0; s < 32; ++s) {
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt) {
+          uint32_t ah[4], am[4];
+          const uint32_t off = (uint32_t)(mt * 16 * HPB + s * 16) * 2u;
+          ldmatrix_x4(ah, hi_base + off);
+          ldmatrix_x4(am, mid_base + off);
+          mma_bf16(acc[mt], ah, whi[s][0], whi[s][1]);
+          mma_bf16(acc[mt], am, whi[s][0], whi[s][1]);
+          mma_bf16(acc[mt], ah, wmid[s][0], wmid[s][1]);
+        }
+      }
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        const int row = mh * 32 + mt * 16 + g;
+        *reinterpret_cast<float2*>(gates_s + (nt * BC + row) * UPC + 2 * t4) = make_float2(acc[mt][0], acc[mt][1]);
+        *reinterpret_cast<float2*>(gates_s + (nt * BC + row + 8) * UPC + 2 * t4) = make_float2(acc[mt][2], acc[mt][3]);
+      }
+      __syncthreads();
+      {
+        float2 logit = make_float2(0.f, 0.f);
+        if (act) {
+          float2 gate[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float2 a = *reinterpret_cast<const float2*>(gates_s + (q * BC + eb) * UPC + eu);
+            gate[q] = make_float2(a.x + xv[q].x, a.y + xv[q].y);
+          }
+          float2* cp = reinterpret_cast<float2*>(p.cbuf + ((size_t)dir * B + b) * H + u0 + eu);
+          float2 cn = *cp;
+          cn.x = sigmoidf(gate[1].x) * cn.x + sigmoidf(gate[0].x) * tanhf(gate[2].x);
+          cn.y = sigmoidf(gate[1].y) * cn.y + sigmoidf(gate[0].y) * tanhf(gate[2].y);
+          const float hx = sigmoidf(gate[3].x) * tanhf(cn.x), hy = sigmoidf(gate[3].y) * tanhf(cn.y);
+          *cp = cn;
+          uint32_t hi, mid;
+          split_pair(hx, hy, hi, mid);
+          *reinterpret_cast<uint32_t*>(wr + (size_t)b * (2 * H) + u0 + eu) = hi;
+          *reinterpret_cast<uint32_t*>(wr + (size_t)b * (2 * H) + H + u0 + eu) = mid;
+          if (p.out_h) *reinterpret_cast<float2*>(p.out_h + (size_t)rowi * 2 * H + dir * H + u0 + eu) = make_float2(hx, hy);
+          logit = make_float2(hx * wout.x, hy * wout.y);
+        }
+        *reinterpret_cast<float2*>(lg + eb * UPC + eu) = logit;
+      }
+      __syncthreads();
+      if (tid < nb) {
+        const int bb = b0 + tid;
+        const int beg = p.cu_rows[bb], len3 = p.up * (p.cu_rows[bb + 1] - beg);
+        if (t < len3) {
+          float sacc = 0.f;
+#pragma unroll
+          for (int j = 0; j < UPC; ++j) sacc += lg[tid * UPC + j];
+          p.part[(size_t)(dir * CTAS + cta) * p.rows3 + p.up * beg + (dir ? len3 - 1 - t : t)] = sacc;
+        }
+      }
+      __syncthreads();
+    }
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) red_release(counter);
+  }
+}
+
 // ---------------------------------------------------------------- upsampled alphas -> fires
 struct FireParams {
   const float* part;   // [nparts][rows3]
@@ -300,8 +476,10 @@ using namespace fb200;
 
 extern "C" __attribute__((visibility("default"))) int fb200_lstm_bidir(
     const float* xg, int ld_xg, const int32_t* cu_rows, int upsample, int batch, int rows3, int max_len3, int hidden,
-    const float* w_hh, const float* w_out, float* workspace, long long workspace_bytes, float* part, float* out_h, void* stream) {
+    const float* w_hh, const float* w_out, float* workspace, long long workspace_bytes, float* part, float* out_h, int impl,
+    void* stream) {
   using namespace fb200::lstm;
+  FB_CHECK_ARG(impl == 0 || impl == 1, "lstm_bidir: impl must be 0 (tensor cores) or 1 (fp32 SIMT check kernel)");
   FB_CHECK_ARG(hidden == H, "lstm_bidir: hidden size %d unsupported (512 only)", hidden);
   FB_CHECK_ARG(batch > 0 && batch <= BC * MAX_CHUNKS, "lstm_bidir: batch %d outside 1..%d", batch, BC * MAX_CHUNKS);
   FB_CHECK_ARG(upsample >= 1 && ld_xg >= 8 * H, "lstm_bidir: upsample %d / ld_xg %d", upsample, ld_xg);
@@ -334,6 +512,8 @@ extern "C" __attribute__((visibility("default"))) int fb200_lstm_bidir(
   static bool attr_set = false;
   if (!attr_set) {
     e = cudaFuncSetAttribute(lstm_bidir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(lstm_bidir_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMma);
     if (e != cudaSuccess) {
       set_error("lstm_bidir: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
       return FB200_ECUDA;
@@ -342,7 +522,10 @@ extern "C" __attribute__((visibility("default"))) int fb200_lstm_bidir(
   }
   // every CTA waits for all the others of its direction at every step: they must be co-resident
   void* args[] = {(void*)&p};
-  e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_kernel, dim3(2 * CTAS), dim3(THREADS), args, kSmem, st);
+  if (impl == 0)
+    e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_mma_kernel, dim3(2 * CTAS), dim3(THREADS), args, kSmemMma, st);
+  else
+    e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_kernel, dim3(2 * CTAS), dim3(THREADS), args, kSmem, st);
   if (e != cudaSuccess) {
     set_error("lstm_bidir: cooperative launch: %s", cudaGetErrorString(e));
     return FB200_ECUDA;

@@ -201,7 +201,7 @@ def lstm_parts(hidden: int = 512) -> int:
     return int(n.value)
 
 
-def lstm_bidir(xg, cu_rows, upsample, max_len3, w_hh, w_out, part, out_h=None, hidden=512):
+def lstm_bidir(xg, cu_rows, upsample, max_len3, w_hh, w_out, part, out_h=None, hidden=512, impl=0):
     """Bidirectional LSTM over packed rows fused with the Linear(2H -> 1) dot product: xg fp32 [rows3, >= 8H], w_hh fp32
     [2, 4H, H], w_out fp32 [2, H], part fp32 [lstm_parts(H), rows3] (out), out_h fp32 [rows3, 2H] or None."""
     import ctypes
@@ -213,7 +213,7 @@ def lstm_bidir(xg, cu_rows, upsample, max_len3, w_hh, w_out, part, out_h=None, h
     _lib.call("fb200_lstm_workspace_bytes", batch, hidden, ctypes.byref(nbytes))
     ws = torch.empty((int(nbytes.value) + 3) // 4, dtype=torch.float32, device=xg.device)
     _lib.call("fb200_lstm_bidir", _p(xg), xg.stride(0), _p(cu_rows), upsample, batch, rows3, max_len3, hidden, _p(w_hh),
-              _p(w_out), _p(ws), int(nbytes.value), _p(part), _p(out_h), _stream())
+              _p(w_out), _p(ws), int(nbytes.value), _p(part), _p(out_h), impl, _stream())
 
 
 def us_fires(part, bias, smooth, noise, threshold, cu_rows, upsample, token_num, ids, cu_tok, drop_ids, us_alphas, fire_idx,

@@ -318,12 +318,13 @@ int fb200_cif_integrate(const float* hidden, int ld_h, const float* alphas, cons
  *   part  f32 [fb200_lstm_parts][rows3]  partial dot products: the Linear's output is bias + the sum over parts
  *   out_h f32 [rows3, 2H] or NULL        the LSTM output itself (tests)
  *   workspace: fb200_lstm_workspace_bytes(batch, H) bytes of device memory (state double buffer, cell state, barrier).
- * H = 512 only; batch <= 1024. */
+ * impl 0: the recurrent product on the tensor cores (mma.sync, bf16 hi + mid operands, 3 terms, fp32 accumulate; the state
+ * travels between CTAs as bf16 hi + mid); impl 1: fp32 on the CUDA cores (check kernel).  H = 512 only; batch <= 1024. */
 int fb200_lstm_workspace_bytes(int batch, int hidden, long long* bytes);
 int fb200_lstm_parts(int hidden, int* parts);
 int fb200_lstm_bidir(const float* xg, int ld_xg, const int32_t* cu_rows, int upsample, int batch, int rows3, int max_len3,
                      int hidden, const float* w_hh, const float* w_out, float* workspace, long long workspace_bytes,
-                     float* part, float* out_h, void* stream);
+                     float* part, float* out_h, int impl, void* stream);
 
 /* alphas2 = relu(sigmoid(bias + sum(part)) * smooth - noise), scaled so each utterance sums to token_num[b]
  * (cif_predictor.py:270-283) -> us_alphas [rows3]; then the sequential fp32 integrate-and-fire of cif_wo_hidden with
