@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_kernel(const Params p) 
 // chunk and step); here the CTA's W_hh slice lives in REGISTERS as B fragments (warp = one gate x 8 units, 32 k-steps x
 // 2 parts) and the staged h is read once per gate through ldmatrix.  h travels between CTAs as bf16 hi + mid.
 constexpr int HPB = H + 8;  // bf16 row pitch: 1040 B, ldmatrix rows land in distinct banks
-constexpr size_t kSmemMma = (size_t)2 * BC * HPB * sizeof(__nv_bfloat16) + (size_t)(4 * BC * UPC + BC * UPC) * sizeof(float);
+constexpr size_t kSmemMma = (size_t)2 * BC * HPB * sizeof(__nv_bfloat16) + (size_t)(4 * BC * UPC) * sizeof(float);
 
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
@@ -223,7 +223,6 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
   __nv_bfloat16* hs_hi = reinterpret_cast<__nv_bfloat16*>(smem_raw);  // [BC][HPB]
   __nv_bfloat16* hs_mid = hs_hi + BC * HPB;                           // [BC][HPB]
   float* gates_s = reinterpret_cast<float*>(hs_mid + BC * HPB);       // [4 gates][BC][UPC]
-  float* lg = gates_s + 4 * BC * UPC;                                 // [BC][UPC]
   __shared__ int chunk_max[MAX_CHUNKS];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -279,11 +278,16 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
     for (int c = 0; c < nchunks; ++c) {
       if (t >= chunk_max[c]) continue;
       const int b0 = c * BC, nb = min(BC, B - b0);
-      for (int i = tid; i < nb * 128; i += THREADS) {
-        const int row = i >> 7, c16 = i & 127, part = c16 >> 6, off = (c16 & 63) * 8;
-        cp_async16((part ? hs_mid : hs_hi) + row * HPB + off, rd + (size_t)(b0 + row) * (2 * H) + part * H + off);
+      // four k-slices of 128 columns (hi and mid), one cp.async group each: the products of slice j start while the
+      // later slices are still in flight
+#pragma unroll
+      for (int ksl = 0; ksl < 4; ++ksl) {
+        for (int i = tid; i < nb * 32; i += THREADS) {
+          const int row = i >> 5, c16 = i & 31, part = c16 >> 4, off = ksl * 128 + (c16 & 15) * 8;
+          cp_async16((part ? hs_mid : hs_hi) + row * HPB + off, rd + (size_t)(b0 + row) * (2 * H) + part * H + off);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
       }
-      asm volatile("cp.async.commit_group;" ::: "memory");
       const int b = b0 + eb;
       bool act = false;
       int rowi = 0;
@@ -299,8 +303,6 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
       for (int q = 0; q < 4; ++q)
         xv[q] = act ? __ldg(reinterpret_cast<const float2*>(p.xg + (size_t)rowi * p.ld_xg + dir * 4 * H + q * H + u0 + eu))
                     : make_float2(0.f, 0.f);
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
-      __syncthreads();
       float acc[2][4];
 #pragma unroll
       for (int mt = 0; mt < 2; ++mt)
@@ -308,6 +310,13 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
         for (int q = 0; q < 4; ++q) acc[mt][q] = 0.f;
 #pragma unroll
       for (int s = 0; s < 32; ++s) {
+        if (s % 8 == 0) {
+          if (s == 0) asm volatile("cp.async.wait_group 3;" ::: "memory");
+          else if (s == 8) asm volatile("cp.async.wait_group 2;" ::: "memory");
+          else if (s == 16) asm volatile("cp.async.wait_group 1;" ::: "memory");
+          else asm volatile("cp.async.wait_group 0;" ::: "memory");
+          __syncthreads();
+        }
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt) {
           uint32_t ah[4], am[4];
@@ -348,20 +357,12 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
           if (p.out_h) *reinterpret_cast<float2*>(p.out_h + (size_t)rowi * 2 * H + dir * H + u0 + eu) = make_float2(hx, hy);
           logit = make_float2(hx * wout.x, hy * wout.y);
         }
-        *reinterpret_cast<float2*>(lg + eb * UPC + eu) = logit;
+        // the CTA's share of the Linear(2H -> 1): the four threads of an utterance hold its 8 units (fixed order)
+        float sacc = logit.x + logit.y;
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
+        sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
+        if (act && (tid & 3) == 0) p.part[(size_t)(dir * CTAS + cta) * p.rows3 + rowi] = sacc;
       }
-      __syncthreads();
-      if (tid < nb) {
-        const int bb = b0 + tid;
-        const int beg = p.cu_rows[bb], len3 = p.up * (p.cu_rows[bb + 1] - beg);
-        if (t < len3) {
-          float sacc = 0.f;
-#pragma unroll
-          for (int j = 0; j < UPC; ++j) sacc += lg[tid * UPC + j];
-          p.part[(size_t)(dir * CTAS + cta) * p.rows3 + p.up * beg + (dir ? len3 - 1 - t : t)] = sacc;
-        }
-      }
-      __syncthreads();
     }
     __threadfence();
     __syncthreads();
