@@ -58,7 +58,11 @@ int main(int argc, char** argv) {
     const int32_t* ids = fb200_result_ids(res, i, &n);
     printf("%s\t", argv[i + 2]);
     for (int k = 0; k < n; ++k) printf(k ? " %d" : "%d", ids[k]);
-    printf("\t%s\n", fb200_result_text(res, i));
+    printf("\t%s", fb200_result_text(res, i));
+    int ns = 0;
+    const int32_t* st = fb200_result_stamps(res, i, &ns);  // [begin ms, end ms] per token (BiCifParaformer models)
+    for (int k = 0; k < ns; ++k) printf(k ? " %d-%d" : "\t%d-%d", st[2 * k], st[2 * k + 1]);
+    printf("\n");
   }
   fb200_free_result(res);
   fb200_offline_uninit(h);

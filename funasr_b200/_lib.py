@@ -57,6 +57,7 @@ RUNTIME_SIGNATURES = {
     "fb200_result_count": ([_P], _I),
     "fb200_result_text": ([_P, _I], ctypes.c_char_p),
     "fb200_result_ids": ([_P, _I, ctypes.POINTER(_I)], ctypes.POINTER(ctypes.c_int32)),
+    "fb200_result_stamps": ([_P, _I, ctypes.POINTER(_I)], ctypes.POINTER(ctypes.c_int32)),
     "fb200_free_result": ([_P], None),
     "fb200_offline_uninit": ([_P], None),
 }

@@ -97,7 +97,30 @@ struct DecLayer {
 struct Result {
   std::vector<std::vector<int32_t>> ids;
   std::vector<std::string> text;
+  std::vector<std::vector<int32_t>> stamps;  // [begin ms, end ms] per kept token (models with the CifPredictorV3 head)
 };
+
+// fired upsampled frames -> [begin ms, end ms] per token: the arithmetic of ts_prediction_lfr6_standard
+// (funasr/utils/timestamp_tools.py:31-106) in double, as the reference (numpy int64 + Python floats) computes it
+static void stamps_from_fires(const int32_t* fire_idx, int n, int num_frames, int num_chars, std::vector<int32_t>* out) {
+  out->clear();
+  if (num_chars <= 0 || n < 2) return;
+  const double kShift = -1.5, kRate = 10.0 * 6 / 1000 / 3;
+  const int kStartEnd = 5, kMaxDur = 12;
+  const int m = std::min(n - 1, num_chars);
+  for (int i = 0; i < m; ++i) {
+    const double f0 = (double)fire_idx[i] + kShift, f1 = (double)fire_idx[i + 1] + kShift;
+    const bool split = f1 - f0 > kMaxDur;
+    const double begin = f0 * kRate;
+    double end = split ? (f0 + kMaxDur) * kRate : f1 * kRate;
+    if (i == n - 2 && !split) {  // the last list entry is the last token (otherwise the silence after it)
+      if (num_frames - f1 > kStartEnd) end = ((num_frames + f1) * 0.5) * kRate;
+      else end = num_frames * kRate;
+    }
+    out->push_back((int32_t)(begin * 1000));
+    out->push_back((int32_t)(end * 1000));
+  }
+}
 
 class Recognizer {
  public:
@@ -157,6 +180,11 @@ class Recognizer {
   Norm dec_after_;
   Linear dec_out_, dec_kv_;
   std::vector<std::string> tokens_;
+  // CifPredictorV3 time-stamp head (BiCifParaformer), present when the checkpoint holds predictor.blstm.*
+  bool has_stamps_ = false;
+  Linear ts_up_, ts_proj_;
+  float *ts_whh_ = nullptr, *ts_wout_ = nullptr, ts_bout_ = 0.f;
+  int ts_parts_ = 0;
 };
 
 // ---------------------------------------------------------------- loading -----------------
@@ -388,6 +416,42 @@ int Recognizer::init(const std::string& dir, int device, int nparts, int max_row
   RT_OK(make_linear("predictor.cif_conv1d.weight", "predictor.cif_conv1d.bias", &cif_conv_));
   RT_OK(upload(find("predictor.cif_output.weight")->data, &cif_w_));
   RT_OK(upload(find("predictor.cif_output.bias")->data, &cif_b_));
+  if (has("predictor.blstm.weight_hh_l0") && has("predictor.upsample_cnn.weight") && has("predictor.cif_output2.weight")) {
+    // bicif_paraformer/cif_predictor.py:139-145: ConvTranspose1d [in, out, k] (stride k) as a GEMM with weight rows (j, o),
+    // both directions' input projections stacked, recurrent weights and the Linear(2H -> 1) kept in fp32
+    const HostTensor* uw = find("predictor.upsample_cnn.weight");
+    const HostTensor* ub = find("predictor.upsample_cnn.bias");
+    const int cin = (int)uw->shape[0], cout = (int)uw->shape[1], k = (int)uw->shape[2];
+    if (k != 3 || cout != 512 || cin != d_) {
+      set_error("runtime: time-stamp head with upsample %d / hidden %d unsupported (3 / 512)", k, cout);
+      return FB200_EUNSUPPORTED;
+    }
+    std::vector<float> w((size_t)k * cout * cin), b((size_t)k * cout);
+    for (int j = 0; j < k; ++j)
+      for (int o = 0; o < cout; ++o) {
+        b[(size_t)j * cout + o] = ub->data[o];
+        for (int c = 0; c < cin; ++c) w[((size_t)j * cout + o) * cin + c] = uw->data[((size_t)c * cout + o) * k + j];
+      }
+    RT_OK(make_linear_from(w, k * cout, cin, 1, &b, &ts_up_));
+    std::vector<float> wih, bih, whh;
+    for (const char* sfx : {"", "_reverse"}) {
+      const HostTensor *wi = find(std::string("predictor.blstm.weight_ih_l0") + sfx), *wh = find(std::string("predictor.blstm.weight_hh_l0") + sfx);
+      const HostTensor *bi = find(std::string("predictor.blstm.bias_ih_l0") + sfx), *bh = find(std::string("predictor.blstm.bias_hh_l0") + sfx);
+      if (!wi || !wh || !bi || !bh) {
+        set_error("runtime: incomplete predictor.blstm.* tensors");
+        return FB200_EINVAL;
+      }
+      wih.insert(wih.end(), wi->data.begin(), wi->data.end());
+      whh.insert(whh.end(), wh->data.begin(), wh->data.end());
+      for (size_t i = 0; i < bi->data.size(); ++i) bih.push_back(bi->data[i] + bh->data[i]);
+    }
+    RT_OK(make_linear_from(wih, 8 * cout, cout, 1, &bih, &ts_proj_));
+    RT_OK(upload(whh, &ts_whh_));
+    RT_OK(upload(find("predictor.cif_output2.weight")->data, &ts_wout_));
+    ts_bout_ = find("predictor.cif_output2.bias")->data[0];
+    RT_OK(fb200_lstm_parts(cout, &ts_parts_));
+    has_stamps_ = true;
+  }
   // decoder
   std::vector<float> kvw, kvb;
   int n_src = 0;
@@ -431,6 +495,8 @@ int Recognizer::init(const std::string& dir, int device, int nparts, int max_row
   size_t cap = r * lfr_n_ * n_mels_ * 4 + r * din_ * 4  // fbank, feats
                + r * (size_t)np_ * (kp64(din_) + 7 * kp64(d_) + 2 * kp64(ff_) + kp64(3 * d_) + kp64(dec_kv_.n)) * 2  // splits
                + r * (size_t)d_ * 4 * 16 + r * (size_t)ff_ * 4 + r * (size_t)((vocab_ + 3) / 4 * 4) * 4 + (64u << 20);
+  if (has_stamps_)  // upsampled rows: split of the conv output, xg [3r, 8H], the LSTM kernel's partial sums, alphas and fires
+    cap += r * (size_t)np_ * 3 * 512 * 2 + 3 * r * (size_t)(8 * 512 + ts_parts_ + 4) * 4 + (8u << 20);
   RT_CUDA(cudaMalloc(&arena_.base, cap));
   arena_.cap = cap;
   RT_CUDA(cudaStreamSynchronize(stream_));
@@ -619,8 +685,45 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   RT_OK(fb200_argmax_logprob(logits, ldv, L, vocab_, ids, logp, st));
   std::vector<int32_t> h_ids(L);
   RT_CUDA(cudaMemcpyAsync(h_ids.data(), ids, (size_t)L * 4, cudaMemcpyDeviceToHost, stream_));
+  std::vector<int32_t> h_fire, h_fire_count, h_chars;
+  if (has_stamps_) {
+    // CifPredictorV3.get_upsample_timestamp + the fire search of ts_prediction_lfr6_standard (see funasr_b200/bicif.py)
+    const int H = 512, up = 3, R3 = up * R;
+    bf16* ups = arena_.get<bf16>((size_t)R * np * up * H);
+    float* xg = arena_.get<float>((size_t)R3 * 8 * H);
+    float* part = arena_.get<float>((size_t)ts_parts_ * R3);
+    long long ws_bytes = 0;
+    RT_OK(fb200_lstm_workspace_bytes(B, H, &ws_bytes));
+    float* ws = arena_.get<float>((size_t)(ws_bytes + 3) / 4);
+    float* us_alphas = arena_.get<float>(R3);
+    int32_t *fire_idx = arena_.get<int32_t>(R3), *fire_count = arena_.get<int32_t>(B), *num_chars = arena_.get<int32_t>(B);
+    if (!arena_.ok()) {
+      set_error("runtime: activation slab too small for the time-stamp head of %d rows", R);
+      return FB200_EINVAL;
+    }
+    RT_OK(fb200_gemm(encs, R, np, ts_up_.w, np, R, up * H, d, 1, ts_up_.bias, 0, nullptr, 0, nullptr, 0, 0, ups, np, 0, st));
+    const int zero_tap = 0;
+    for (int j = 0; j < up; ++j)  // sub-frame j of every encoder frame -> rows 3t + j of xg
+      RT_OK(fb200_gemm_ex(ups, R, np * up * H, up * H, j * H, np, ts_proj_.w, np, R, 8 * H, H, 1, &zero_tap, &zero_tap, ts_proj_.bias, 0,
+                          nullptr, 0, xg + (size_t)j * 8 * H, up * 8 * H, 0, nullptr, 1, 0, st));
+    RT_OK(fb200_lstm_bidir(xg, 8 * H, d_cur, up, B, R3, up * max_t, H, ts_whh_, ts_wout_, ws, ws_bytes, part, nullptr, 0, st));
+    const int32_t drop[3] = {0, 1, 2};
+    RT_OK(fb200_us_fires(part, ts_parts_, R3, ts_bout_, 0.25f, 0.01f, (float)(1.0 - 1e-4), d_cur, up, B, token_num, ids, d_cut, drop,
+                         us_alphas, nullptr, fire_idx, fire_count, num_chars, st));
+    h_fire.resize(R3);
+    h_fire_count.resize(B);
+    h_chars.resize(B);
+    RT_CUDA(cudaMemcpyAsync(h_fire.data(), fire_idx, (size_t)R3 * 4, cudaMemcpyDeviceToHost, stream_));
+    RT_CUDA(cudaMemcpyAsync(h_fire_count.data(), fire_count, (size_t)B * 4, cudaMemcpyDeviceToHost, stream_));
+    RT_CUDA(cudaMemcpyAsync(h_chars.data(), num_chars, (size_t)B * 4, cudaMemcpyDeviceToHost, stream_));
+  }
   t_dec = now_ms();
   RT_CUDA(cudaStreamSynchronize(stream_));
+  if (has_stamps_)
+    for (int i = 0; i < B; ++i)
+      if (tok[i] > 0)
+        stamps_from_fires(h_fire.data() + 3 * (size_t)cu_rows[i], h_fire_count[i], 3 * (cu_rows[i + 1] - cu_rows[i]), h_chars[i],
+                          &res->stamps[batch[i]]);
   if (trace)
     fprintf(stderr, "fb200 rt: batch %3d utts %6d rows %6d tok | launch enc %.2f  join upload %.2f  wait tokens %.2f  launch dec %.2f  wait ids %.2f ms\n",
             B, R, L, t_launched - t_begin, t_staged - t_launched, t_tokens - t_staged, t_dec - t_tokens, now_ms() - t_dec);
@@ -636,6 +739,7 @@ int Recognizer::recognize(const float* const* waves, const int* lens, int n, Res
   RT_CUDA(cudaSetDevice(device_));
   res->ids.assign(n, std::vector<int32_t>());
   res->text.assign(n, std::string());
+  res->stamps.assign(n, std::vector<int32_t>());
   // length-sorted batches under the packed-row budget (ref. analogue: funasr/auto/auto_model.py:423-459)
   std::vector<int> rows(n), order;
   for (int i = 0; i < n; ++i) {
@@ -743,6 +847,15 @@ RT_API const int32_t* fb200_result_ids(void* result, int index, int* count) {
   }
   if (count) *count = (int)r->ids[index].size();
   return r->ids[index].data();
+}
+RT_API const int32_t* fb200_result_stamps(void* result, int index, int* count) {
+  Result* r = static_cast<Result*>(result);
+  if (!r || index < 0 || index >= (int)r->stamps.size()) {
+    if (count) *count = 0;
+    return nullptr;
+  }
+  if (count) *count = (int)r->stamps[index].size() / 2;
+  return r->stamps[index].data();
 }
 RT_API void fb200_free_result(void* result) { delete static_cast<Result*>(result); }
 RT_API void fb200_offline_uninit(void* handle) { delete static_cast<Recognizer*>(handle); }

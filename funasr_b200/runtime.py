@@ -69,21 +69,27 @@ class OfflineRecognizer:
         if not res:
             raise RuntimeError("fb200_offline_infer failed: %s" % self._lib.fb200_last_error().decode())
         try:
-            ids, text = [], []
+            ids, text, stamps = [], [], []
             for i in range(self._lib.fb200_result_count(res)):
                 n = ctypes.c_int(0)
                 p = self._lib.fb200_result_ids(res, i, ctypes.byref(n))
                 ids.append(np.ctypeslib.as_array(p, shape=(n.value,)).tolist() if n.value else [])
                 text.append(self._lib.fb200_result_text(res, i).decode("utf-8"))
+                p = self._lib.fb200_result_stamps(res, i, ctypes.byref(n))
+                stamps.append(np.ctypeslib.as_array(p, shape=(n.value, 2)).tolist() if n.value else [])
+            self.last_stamps = stamps  # [[begin ms, end ms], ...] per utterance; empty lists without a time-stamp head
             return ids, text
         finally:
             self._lib.fb200_free_result(res)
 
-    def recognize(self, waves: Sequence[np.ndarray], with_text: bool = False):
+    def recognize(self, waves: Sequence[np.ndarray], with_text: bool = False, with_stamps: bool = False):
+        """Token ids per utterance; `with_stamps` adds the [begin ms, end ms] lists of a BiCifParaformer model directory."""
         arrs = [np.ascontiguousarray(w, dtype=np.float32) for w in waves]
         ptrs = (ctypes.c_void_p * len(arrs))(*[a.ctypes.data for a in arrs])
         lens = (ctypes.c_int32 * len(arrs))(*[a.shape[0] for a in arrs])
         ids, text = self._collect(self._lib.fb200_offline_infer(self._h, ptrs, lens, len(arrs)))
+        if with_stamps:
+            return (ids, text, self.last_stamps) if with_text else (ids, self.last_stamps)
         return (ids, text) if with_text else ids
 
     def recognize_pcm16(self, pcm: bytes, sampling_rate: int = 16000):

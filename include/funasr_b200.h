@@ -361,6 +361,7 @@ int fb200_ctc_collapse(const int32_t* ids, const int32_t* cu_rows, int batch, ui
  *   FunOfflineInferBuffer(h, pcm, n_bytes, ...)  fb200_offline_infer_buffer(h, pcm16, n_bytes, 16000)   one recording
  *   (batched: paraformer-torch.cpp:301-470)      fb200_offline_infer(h, waves, lens, count)             a packed batch
  *   FunASRGetRetNumber / FunASRGetResult         fb200_result_count / fb200_result_text (+ fb200_result_ids)
+ *   FunASRGetStamp                               fb200_result_stamps
  *   FunASRFreeResult / FunOfflineUninit          fb200_free_result / fb200_offline_uninit
  * model_dir holds model.fb200 (tools/export_model.py, reference state_dict names), optionally am.mvn (Kaldi-nnet CMVN,
  * parsed as paraformer.cpp:314-349) and tokens.json (JSON array of token strings).  precision: 0 = fp32 parity
@@ -373,6 +374,10 @@ void* fb200_offline_infer_buffer(void* handle, const char* h_pcm16, int n_bytes,
 int fb200_result_count(void* result);
 const char* fb200_result_text(void* result, int index);
 const int32_t* fb200_result_ids(void* result, int index, int* count);
+/* Time stamps of utterance `index` (FunASRGetStamp's content, funasrruntime.h): `*count` pairs [begin ms, end ms], one per
+ * id of fb200_result_ids, when the model directory holds a CifPredictorV3 head (predictor.blstm.* -- BiCifParaformer /
+ * paraformer-zh); count 0 otherwise. */
+const int32_t* fb200_result_stamps(void* result, int index, int* count);
 void fb200_free_result(void* result);
 void fb200_offline_uninit(void* handle);
 

@@ -70,6 +70,22 @@ def test_native_runtime_full_depth_matches_reference_golden(tmp_path, paraformer
     rec.close()
 
 
+@pytest.mark.gpu
+def test_native_runtime_time_stamps_match_reference_golden(tmp_path, bicif_sd, golden_dir):
+    """A BiCifParaformer model directory (predictor.blstm.* present) through the C++ runtime: ids and
+    [begin ms, end ms] per token of a ragged batch == the unmodified reference's batch-1 results; a Paraformer
+    directory gives no stamps."""
+    g = np.load(os.path.join(golden_dir, "bicif.npz"))
+    runtime.export_model(bicif_sd, str(tmp_path), cmvn=synth.synth_cmvn())
+    rec = runtime.OfflineRecognizer(str(tmp_path), max_rows=2048)
+    waves = [synth.synth_waveform(int(g["seeds"][ci]), int(g["num_samples"][ci])) for ci in range(3)]
+    ids, stamps = rec.recognize(waves, with_stamps=True)
+    for ci in range(3):
+        assert ids[ci] == g["ids_%d" % ci].tolist()
+        assert stamps[ci] == g["timestamp_%d" % ci].tolist()
+    rec.close()
+
+
 def _example_binary():
     """examples/offline_recognize, built with g++ against the in-tree library when missing or stale."""
     import subprocess
