@@ -197,10 +197,11 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_kernel(const Params p) 
 // Same schedule as lstm_bidir_kernel with the h . W_hh^T product of a step on the tensor cores (warp-level
 // mma.sync m16n8k16, bf16 operands split hi + mid, 3 terms, fp32 accumulate -- the operand scheme of the GEMMs): the SIMT
 // kernel re-reads every staged h row once per hidden unit and is bound by shared-memory bandwidth (12.6 us per 64-utterance
-// chunk and step); here the CTA's W_hh slice lives in REGISTERS as B fragments (warp = one gate x 8 units, 32 k-steps x
-// 2 parts) and the staged h is read once per gate through ldmatrix.  h travels between CTAs as bf16 hi + mid.
+// chunk and step); here the CTA's W_hh slice lives in REGISTERS as B fragments (warp = one gate x 8 units x one quarter
+// of K, 8 k-steps x 2 parts; the quarters' partial sums meet in shared memory) and the staged h is read once per gate
+// through ldmatrix.  h travels between CTAs as bf16 hi + mid.
 constexpr int HPB = H + 8;  // bf16 row pitch: 1040 B, ldmatrix rows land in distinct banks
-constexpr size_t kSmemMma = (size_t)2 * BC * HPB * sizeof(__nv_bfloat16) + (size_t)(4 * BC * UPC) * sizeof(float);
+constexpr size_t kSmemMma = (size_t)2 * BC * HPB * sizeof(__nv_bfloat16) + (size_t)(4 * 4 * BC * UPC) * sizeof(float);
 
 __device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];"
@@ -218,25 +219,28 @@ __device__ __forceinline__ void split_pair(float x, float y, uint32_t& hi, uint3
   mid = *reinterpret_cast<const uint32_t*>(&m);
 }
 
-__global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params p) {
+constexpr int MMA_THREADS = 512;  // 16 warps = 4 gates x 4 k-quarters
+
+__global__ void __launch_bounds__(MMA_THREADS, 1) lstm_bidir_mma_kernel(const Params p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __nv_bfloat16* hs_hi = reinterpret_cast<__nv_bfloat16*>(smem_raw);  // [BC][HPB]
   __nv_bfloat16* hs_mid = hs_hi + BC * HPB;                           // [BC][HPB]
-  float* gates_s = reinterpret_cast<float*>(hs_mid + BC * HPB);       // [4 gates][BC][UPC]
+  float* gates_s = reinterpret_cast<float*>(hs_mid + BC * HPB);       // [4 k-quarters][4 gates][BC][UPC] partial sums
   __shared__ int chunk_max[MAX_CHUNKS];
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int dir = blockIdx.x / CTAS, cta = blockIdx.x % CTAS, u0 = cta * UPC;
   const int B = p.batch;
   const int nchunks = (B + BC - 1) / BC;
-  const int nt = warp & 3, mh = warp >> 2;  // this warp: gate nt (8 units), staged rows [32 mh, 32 mh + 32)
+  // this warp: gate nt (8 units) over k-steps [8 kq, 8 kq + 8) for all 64 staged rows -- four warps per scheduler, so the
+  // ldmatrix latency of one warp hides under the products of the others
+  const int nt = warp & 3, kq = warp >> 2;
   const int g = lane >> 2, t4 = lane & 3;
-  // B fragments of W_hh[dir][gate nt][unit u0 + g][:] for all 32 k-steps, hi and mid
-  uint32_t whi[32][2], wmid[32][2];
+  uint32_t whi[8][2], wmid[8][2];  // B fragments of W_hh[dir][gate nt][unit u0 + g][128 kq ...], hi and mid
   {
-    const float* wrow = p.w_hh + ((size_t)dir * 4 * H + nt * H + u0 + g) * H;
+    const float* wrow = p.w_hh + ((size_t)dir * 4 * H + nt * H + u0 + g) * H + 128 * kq;
 #pragma unroll
-    for (int s = 0; s < 32; ++s) {
+    for (int s = 0; s < 8; ++s) {
       const float2 a = __ldg(reinterpret_cast<const float2*>(wrow + 16 * s + 2 * t4));
       const float2 b = __ldg(reinterpret_cast<const float2*>(wrow + 16 * s + 2 * t4 + 8));
       split_pair(a.x, a.y, whi[s][0], wmid[s][0]);
@@ -252,12 +256,12 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
 
   __nv_bfloat16* hb = reinterpret_cast<__nv_bfloat16*>(p.hbuf);  // [dir][phase][B][hi 512 | mid 512]
   unsigned int* counter = p.counters + dir;
-  const int eb = tid >> 2, eu = (tid & 3) * 2;  // epilogue: utterance eb of the chunk, units eu, eu + 1
-  const float2 wout = __ldg(reinterpret_cast<const float2*>(p.w_out + dir * H + u0 + eu));
+  const int eb = tid >> 3, eu = tid & 7;  // epilogue: utterance eb of the chunk, unit eu
+  const float wout = __ldg(p.w_out + dir * H + u0 + eu);
   // ldmatrix row address of this lane inside a 16 x 16 tile: matrices (rows 0-7 | 8-15) x (k 0-7 | 8-15)
-  const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8, lcol = (lane >> 4) * 8;
-  const uint32_t hi_base = (uint32_t)__cvta_generic_to_shared(hs_hi) + (uint32_t)((mh * 32 + lrow) * HPB + lcol) * 2u;
-  const uint32_t mid_base = (uint32_t)__cvta_generic_to_shared(hs_mid) + (uint32_t)((mh * 32 + lrow) * HPB + lcol) * 2u;
+  const int lrow = (lane & 7) + ((lane >> 3) & 1) * 8, lcol = (lane >> 4) * 8 + 128 * kq;
+  const uint32_t hi_base = (uint32_t)__cvta_generic_to_shared(hs_hi) + (uint32_t)(lrow * HPB + lcol) * 2u;
+  const uint32_t mid_base = (uint32_t)__cvta_generic_to_shared(hs_mid) + (uint32_t)(lrow * HPB + lcol) * 2u;
 
   for (int t = 0; t < p.max_len3; ++t) {
     const __nv_bfloat16* rd = hb + ((size_t)(dir * 2 + (t & 1)) * B) * (2 * H);
@@ -278,16 +282,12 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
     for (int c = 0; c < nchunks; ++c) {
       if (t >= chunk_max[c]) continue;
       const int b0 = c * BC, nb = min(BC, B - b0);
-      // four k-slices of 128 columns (hi and mid), one cp.async group each: the products of slice j start while the
-      // later slices are still in flight
-#pragma unroll
-      for (int ksl = 0; ksl < 4; ++ksl) {
-        for (int i = tid; i < nb * 32; i += THREADS) {
-          const int row = i >> 5, c16 = i & 31, part = c16 >> 4, off = ksl * 128 + (c16 & 15) * 8;
-          cp_async16((part ? hs_mid : hs_hi) + row * HPB + off, rd + (size_t)(b0 + row) * (2 * H) + part * H + off);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
+      for (int i = tid; i < nb * 128; i += MMA_THREADS) {
+        const int row = i >> 7, c16 = i & 127, part = c16 >> 6, off = (c16 & 63) * 8;
+        cp_async16((part ? hs_mid : hs_hi) + row * HPB + off, rd + (size_t)(b0 + row) * (2 * H) + part * H + off);
       }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      // the input projections of this thread's (utterance, unit) are fetched while the copy is in flight
       const int b = b0 + eb;
       bool act = false;
       int rowi = 0;
@@ -298,27 +298,20 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
           rowi = p.up * beg + (dir ? len3 - 1 - t : t);
         }
       }
-      float2 xv[4];
+      float xv[4];
 #pragma unroll
-      for (int q = 0; q < 4; ++q)
-        xv[q] = act ? __ldg(reinterpret_cast<const float2*>(p.xg + (size_t)rowi * p.ld_xg + dir * 4 * H + q * H + u0 + eu))
-                    : make_float2(0.f, 0.f);
-      float acc[2][4];
+      for (int q = 0; q < 4; ++q) xv[q] = act ? __ldg(p.xg + (size_t)rowi * p.ld_xg + dir * 4 * H + q * H + u0 + eu) : 0.f;
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncthreads();
+      float acc[4][4];
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt)
+      for (int mt = 0; mt < 4; ++mt)
 #pragma unroll
         for (int q = 0; q < 4; ++q) acc[mt][q] = 0.f;
 #pragma unroll
-      for (int s = 0; s < 32; ++s) {
-        if (s % 8 == 0) {
-          if (s == 0) asm volatile("cp.async.wait_group 3;" ::: "memory");
-          else if (s == 8) asm volatile("cp.async.wait_group 2;" ::: "memory");
-          else if (s == 16) asm volatile("cp.async.wait_group 1;" ::: "memory");
-          else asm volatile("cp.async.wait_group 0;" ::: "memory");
-          __syncthreads();
-        }
+      for (int s = 0; s < 8; ++s) {
 #pragma unroll
-        for (int mt = 0; mt < 2; ++mt) {
+        for (int mt = 0; mt < 4; ++mt) {
           uint32_t ah[4], am[4];
           const uint32_t off = (uint32_t)(mt * 16 * HPB + s * 16) * 2u;
           ldmatrix_x4(ah, hi_base + off);
@@ -328,40 +321,40 @@ __global__ void __launch_bounds__(THREADS, 1) lstm_bidir_mma_kernel(const Params
           mma_bf16(acc[mt], ah, wmid[s][0], wmid[s][1]);
         }
       }
+      float* gq = gates_s + (size_t)(kq * 4 + nt) * BC * UPC;
 #pragma unroll
-      for (int mt = 0; mt < 2; ++mt) {
-        const int row = mh * 32 + mt * 16 + g;
-        *reinterpret_cast<float2*>(gates_s + (nt * BC + row) * UPC + 2 * t4) = make_float2(acc[mt][0], acc[mt][1]);
-        *reinterpret_cast<float2*>(gates_s + (nt * BC + row + 8) * UPC + 2 * t4) = make_float2(acc[mt][2], acc[mt][3]);
+      for (int mt = 0; mt < 4; ++mt) {
+        const int row = mt * 16 + g;
+        *reinterpret_cast<float2*>(gq + row * UPC + 2 * t4) = make_float2(acc[mt][0], acc[mt][1]);
+        *reinterpret_cast<float2*>(gq + (row + 8) * UPC + 2 * t4) = make_float2(acc[mt][2], acc[mt][3]);
       }
       __syncthreads();
       {
-        float2 logit = make_float2(0.f, 0.f);
+        float logit = 0.f;
         if (act) {
-          float2 gate[4];
+          float gate[4];
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
-            const float2 a = *reinterpret_cast<const float2*>(gates_s + (q * BC + eb) * UPC + eu);
-            gate[q] = make_float2(a.x + xv[q].x, a.y + xv[q].y);
+            float a = xv[q];
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) a += gates_s[((kk * 4 + q) * BC + eb) * UPC + eu];
+            gate[q] = a;
           }
-          float2* cp = reinterpret_cast<float2*>(p.cbuf + ((size_t)dir * B + b) * H + u0 + eu);
-          float2 cn = *cp;
-          cn.x = sigmoidf(gate[1].x) * cn.x + sigmoidf(gate[0].x) * tanhf(gate[2].x);
-          cn.y = sigmoidf(gate[1].y) * cn.y + sigmoidf(gate[0].y) * tanhf(gate[2].y);
-          const float hx = sigmoidf(gate[3].x) * tanhf(cn.x), hy = sigmoidf(gate[3].y) * tanhf(cn.y);
+          float* cp = p.cbuf + ((size_t)dir * B + b) * H + u0 + eu;
+          const float cn = sigmoidf(gate[1]) * *cp + sigmoidf(gate[0]) * tanhf(gate[2]);
+          const float hn = sigmoidf(gate[3]) * tanhf(cn);
           *cp = cn;
-          uint32_t hi, mid;
-          split_pair(hx, hy, hi, mid);
-          *reinterpret_cast<uint32_t*>(wr + (size_t)b * (2 * H) + u0 + eu) = hi;
-          *reinterpret_cast<uint32_t*>(wr + (size_t)b * (2 * H) + H + u0 + eu) = mid;
-          if (p.out_h) *reinterpret_cast<float2*>(p.out_h + (size_t)rowi * 2 * H + dir * H + u0 + eu) = make_float2(hx, hy);
-          logit = make_float2(hx * wout.x, hy * wout.y);
+          const __nv_bfloat16 hi = __float2bfloat16_rn(hn);
+          wr[(size_t)b * (2 * H) + u0 + eu] = hi;
+          wr[(size_t)b * (2 * H) + H + u0 + eu] = __float2bfloat16_rn(hn - __bfloat162float(hi));
+          if (p.out_h) p.out_h[(size_t)rowi * 2 * H + dir * H + u0 + eu] = hn;
+          logit = hn * wout;
         }
-        // the CTA's share of the Linear(2H -> 1): the four threads of an utterance hold its 8 units (fixed order)
-        float sacc = logit.x + logit.y;
-        sacc += __shfl_xor_sync(0xffffffffu, sacc, 1);
-        sacc += __shfl_xor_sync(0xffffffffu, sacc, 2);
-        if (act && (tid & 3) == 0) p.part[(size_t)(dir * CTAS + cta) * p.rows3 + rowi] = sacc;
+        // the CTA's share of the Linear(2H -> 1): the eight threads of an utterance hold its 8 units (fixed order)
+        logit += __shfl_xor_sync(0xffffffffu, logit, 1);
+        logit += __shfl_xor_sync(0xffffffffu, logit, 2);
+        logit += __shfl_xor_sync(0xffffffffu, logit, 4);
+        if (act && eu == 0) p.part[(size_t)(dir * CTAS + cta) * p.rows3 + rowi] = logit;
       }
     }
     __threadfence();
@@ -524,7 +517,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_lstm_bidir(
   // every CTA waits for all the others of its direction at every step: they must be co-resident
   void* args[] = {(void*)&p};
   if (impl == 0)
-    e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_mma_kernel, dim3(2 * CTAS), dim3(THREADS), args, kSmemMma, st);
+    e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_mma_kernel, dim3(2 * CTAS), dim3(MMA_THREADS), args, kSmemMma, st);
   else
     e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_kernel, dim3(2 * CTAS), dim3(THREADS), args, kSmem, st);
   if (e != cudaSuccess) {
