@@ -156,3 +156,14 @@ def test_matches_oracle_on_other_utterances(eng, bicif_sd):
         want_ids, want_stamps = B.recognize(torch.from_numpy(w), bicif_sd, cmvn)
         assert i == want_ids
         assert s == want_stamps
+
+
+def test_too_short_and_ragged_inputs(eng, bicif_sd):
+    """Utterances shorter than one frame give ([], []) and do not disturb their neighbours (same ids / stamps as alone)."""
+    w = synth.synth_waveform(310, 16000 * 2 + 11)
+    alone_ids, alone_stamps = eng.recognize([w])
+    ids, stamps = eng.recognize([np.zeros(100, dtype=np.float32), w, synth.synth_waveform(311, 399)])
+    assert ids[0] == [] and stamps[0] == [] and ids[2] == [] and stamps[2] == []
+    assert ids[1] == alone_ids[0] and stamps[1] == alone_stamps[0]
+    assert len(stamps[1]) == len(ids[1]) and all(b <= e for b, e in stamps[1])
+    assert eng.recognize([]) == ([], [])

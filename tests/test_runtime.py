@@ -65,8 +65,9 @@ def test_native_runtime_full_depth_matches_reference_golden(tmp_path, paraformer
     g = np.load(os.path.join(golden_dir, "stages_2s.npz"))
     runtime.export_model(paraformer_sd, str(tmp_path), cmvn=synth.synth_cmvn())
     rec = runtime.OfflineRecognizer(str(tmp_path))
-    ids = rec.recognize([synth.synth_waveform(10, 32000)])
+    ids, stamps = rec.recognize([synth.synth_waveform(10, 32000)], with_stamps=True)
     assert ids[0] == g["token_int"].tolist()
+    assert stamps == [[]]  # no CifPredictorV3 head in this model directory
     rec.close()
 
 
