@@ -503,6 +503,8 @@ class ParaformerInference:
     _fb200_engine_key = None
     _fb200_engine_cls = engine.ParaformerEngine
     _fb200_timestamps = False  # BiCifParaformer: time stamps are part of the path
+    _fb200_hotwords = False    # SeacoParaformer: a `hotword` argument leaves the accelerated path
+    _fb200_empty = []          # what the reference returns when no utterance has a token
 
     def _engine_for(self, frontend) -> engine.ParaformerEngine:
         dev = next(self.parameters()).device
@@ -524,7 +526,8 @@ class ParaformerInference:
         off_path = (kwargs.get("decoding_ctc_weight", 0.0) > 0.00001 and getattr(self, "ctc", None) is not None) or (
             kwargs.get("lm_weight", 0.0) > 0.00001 and kwargs.get("lm_file") is not None) or (
             kwargs.get("pred_timestamp", False) and not self._fb200_timestamps) or kwargs.get(
-            "data_type", "sound") == "fbank" or getattr(self, "beam_search", None) is not None
+            "data_type", "sound") == "fbank" or getattr(self, "beam_search", None) is not None or (
+            self._fb200_hotwords and kwargs.get("hotword") is not None)
         if off_path:
             ref = getattr(super(), "inference", None)
             if ref is None:
@@ -547,7 +550,7 @@ class ParaformerInference:
         _, rows = eng.frontend.plan([len(w) for w in waves])
         meta_data["batch_data_time"] = sum(rows) * frontend.frame_shift * frontend.lfr_n / 1000
         if not any(eng.last_token_num):
-            return []
+            return self._fb200_empty
         b = len(waves)
         key = list(key) if key is not None else ["utt%d" % i for i in range(b)]
         if key and isinstance(key[0], (list, tuple)):
@@ -883,6 +886,30 @@ class BiCifParaformer(BiCifParaformerInference, Paraformer):
     CifPredictorV3 predictor; inference only."""
 
 
+class SeacoParaformerInference(BiCifParaformerInference):
+    """`SeacoParaformer.inference` (funasr/models/seaco_paraformer/model.py:361-510; the class the hub alias
+    `paraformer-zh` resolves to) WITHOUT hot words: `_seaco_decode_with_ASF` then returns the plain decoder's log-softmax
+    (:252-254, :325-327) and the rest is BiCifParaformer's inference -- pinned by tests/golden/seaco.npz (the unmodified
+    reference's SeACo results equal its BiCif results on the same weights).  A call WITH `hotword=` goes to the
+    reference's own method (bias encoder, SeACo decoder and ASF are not on the accelerated path); without the reference
+    package it raises NotImplementedError."""
+
+    _fb200_hotwords = True
+    _fb200_empty = ([],)  # model.py:417-418
+
+
+class SeacoParaformer(SeacoParaformerInference, Paraformer):
+    """Stand-alone `SeacoParaformer` for hosts without the reference package: BiCifParaformer's tensors only -- load a
+    SeACo checkpoint with `strict=False` (its `bias_encoder.*`, `seaco_decoder.*`, `hotword_output_layer.*` tensors serve
+    hot-word calls, which this class does not take)."""
+
+    def __init__(self, *args, inner_dim=None, bias_encoder_type=None, bias_encoder_bid=None, bias_encoder_dropout_rate=None,
+                 seaco_lsm_weight=None, seaco_length_normal=None, seaco_length_normalized_loss=None, train_decoder=None,
+                 NO_BIAS=None, seaco_decoder=None, seaco_decoder_conf=None, seaco_weight=None, **kwargs):
+        super().__init__(*args, **kwargs)
+
+
+DROPIN_CLASSES[("model_classes", "SeacoParaformer")] = SeacoParaformer
 DROPIN_CLASSES[("predictor_classes", "CifPredictorV3")] = CifPredictorV3
 DROPIN_CLASSES[("model_classes", "BiCifParaformer")] = BiCifParaformer
 
@@ -905,6 +932,13 @@ def _model_class(key: str, cls):
             return cls
         return type("SenseVoiceSmall", (SenseVoiceInference, ref_sv), {"__doc__": SenseVoiceInference.__doc__,
                                                                         "__module__": __name__})
+    if cls is SeacoParaformer:
+        try:
+            from funasr.models.seaco_paraformer.model import SeacoParaformer as ref_seaco  # noqa: WPS433
+        except ImportError:
+            return cls
+        return type("SeacoParaformer", (SeacoParaformerInference, ref_seaco), {"__doc__": SeacoParaformerInference.__doc__,
+                                                                                "__module__": __name__})
     if cls is BiCifParaformer:
         try:
             from funasr.models.bicif_paraformer.model import BiCifParaformer as ref_bicif  # noqa: WPS433

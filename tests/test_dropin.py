@@ -533,3 +533,71 @@ def test_bicif_model_inference_override_matches_golden(bicif_sd, golden_dir, tmp
     shifted, _ = model.inference([waves[0]], key=["a"], tokenizer=tok, frontend=frontend, device="cuda:0", begin_time=1000)
     if not reference_available():
         assert shifted[0]["timestamp"][0] == [g["timestamp_0"][0][0] + 1000, g["timestamp_0"][0][1] + 1000]
+
+
+# ---------------------------------------------------------------------------------------- SeacoParaformer without hot words
+def test_seaco_golden_equals_bicif_golden(golden_dir):
+    """The pin behind the SeACo drop-in: the unmodified reference's SeacoParaformer without hot words gives BiCifParaformer's
+    ids and time stamps on the same seeded weights (tests/golden/make_golden_seaco.py)."""
+    s, b = np.load(os.path.join(golden_dir, "seaco.npz")), np.load(os.path.join(golden_dir, "bicif.npz"))
+    for ci in range(3):
+        assert np.array_equal(s["ids_%d" % ci], b["ids_%d" % ci])
+        assert np.array_equal(s["timestamp_%d" % ci], b["timestamp_%d" % ci])
+    assert all(k.startswith(("bias_encoder.", "seaco_decoder.", "hotword_output_layer.")) for k in s["extra_keys"].tolist())
+
+
+def test_standalone_seaco_model_takes_the_reference_keywords():
+    conf = dict(MODEL, predictor="CifPredictorV3", predictor_conf=PRED_V3, encoder_conf=dict(ENC, num_blocks=1),
+                decoder_conf=dict(DEC, num_blocks=1, att_layer_num=1), inner_dim=512, bias_encoder_type="lstm",
+                bias_encoder_bid=False, seaco_lsm_weight=0.1, seaco_length_normal=True, train_decoder=False, NO_BIAS=8377,
+                seaco_decoder="ParaformerSANMDecoder", seaco_decoder_conf=dict(num_blocks=4))
+    model = dropin.SeacoParaformer(**conf)
+    assert set(model.state_dict()) == set(params.bicif_paraformer_shapes(enc_blocks=1, dec_blocks=1))
+    frontend = dropin.WavFrontend(lfr_m=7, lfr_n=6, dither=0.0)
+    with pytest.raises(NotImplementedError):  # hot words leave the accelerated path; no reference method to fall back to
+        model.inference([synth.synth_waveform(0, 16000)], key=["a"], frontend=frontend, hotword="some words")
+
+
+@pytest.mark.skipif(not reference_available(), reason="reference tree not present (GPU box)")
+def test_install_wraps_the_reference_seaco_model_class():
+    from ref_loader import import_reference
+
+    import_reference()
+    from funasr.models.seaco_paraformer.model import SeacoParaformer as ref_cls
+    from funasr.register import tables
+
+    saved = {t: dict(getattr(tables, t)) for t in ("model_classes", "predictor_classes", "encoder_classes", "decoder_classes",
+                                                    "frontend_classes")}
+    try:
+        dropin.install(tables)
+        cls = tables.model_classes["SeacoParaformer"]
+        assert issubclass(cls, ref_cls) and issubclass(cls, dropin.SeacoParaformerInference)
+        assert cls.inference is dropin.ParaformerInference.inference and cls._fb200_hotwords and cls._fb200_empty == ([],)
+    finally:
+        for t, d in saved.items():
+            getattr(tables, t).clear()
+            getattr(tables, t).update(d)
+
+
+@pytest.mark.gpu
+def test_seaco_model_inference_without_hotwords_matches_golden(bicif_sd, golden_dir, tmp_path):
+    g = np.load(os.path.join(golden_dir, "seaco.npz"))
+    dev = torch.device("cuda:0")
+    shift, scale = synth.synth_cmvn()
+    cmvn_file = str(tmp_path / "am.mvn")
+    synth.write_cmvn_file(cmvn_file, shift, scale)
+    frontend = dropin.WavFrontend(cmvn_file=cmvn_file, fs=16000, window="hamming", n_mels=80, frame_length=25,
+                                  frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0)
+    model = dropin.SeacoParaformer(**dict(MODEL, predictor="CifPredictorV3", predictor_conf=PRED_V3, inner_dim=512,
+                                          seaco_decoder="ParaformerSANMDecoder")).to(dev)
+    sd = dict(bicif_sd)
+    sd["hotword_output_layer.weight"] = torch.zeros(8404, 512)  # a SeACo checkpoint's extra tensors are ignored
+    missing = model.load_state_dict(sd, strict=False)
+    assert not missing.missing_keys and missing.unexpected_keys == ["hotword_output_layer.weight"]
+    waves = [synth.synth_waveform(int(g["seeds"][ci]), int(g["num_samples"][ci])) for ci in range(3)]
+    results, _ = model.inference(waves, key=["a", "b", "c"], tokenizer=None, frontend=frontend, device="cuda:0")
+    assert [r["token_int"] for r in results] == [g["ids_%d" % ci].tolist() for ci in range(3)]
+    results, _ = model.inference(waves, key=["a", "b", "c"], tokenizer=_Tokenizer(), frontend=frontend, device="cuda:0")
+    if not reference_available():
+        assert [r["timestamp"] for r in results] == [g["timestamp_%d" % ci].tolist() for ci in range(3)]
+    assert model.inference([np.zeros(200, dtype=np.float32)], key=["z"], frontend=frontend, device="cuda:0") == ([],)
