@@ -112,3 +112,16 @@ def recognize_segments(engine, speech, segments_ms):
     the token ids come back in segment order.  Because each segment is computed with batch-1 semantics the result
     does not depend on how the segments were grouped."""
     return engine.recognize(slice_segments(speech, segments_ms))
+
+
+def recognize_segments_with_stamps(engine, speech, segments_ms):
+    """The same for an engine with a time-stamp head (`bicif.BiCifParaformerEngine`): returns (ids, stamps) of the WHOLE
+    recording in time order, every segment's `[begin ms, end ms]` pairs shifted by the segment's start as the reference's
+    result combination does (funasr/auto/auto_model.py:510-518: `t[0] += vadsegments[j][0]`, integers, after the
+    per-segment inference)."""
+    ids, stamps = engine.recognize(slice_segments(speech, segments_ms))
+    all_ids, all_stamps = [], []
+    for (beg_ms, _), seg_ids, seg_stamps in zip(segments_ms, ids, stamps):
+        all_ids.extend(seg_ids)
+        all_stamps.extend([[b + int(beg_ms), e + int(beg_ms)] for b, e in seg_stamps])
+    return all_ids, all_stamps

@@ -96,3 +96,22 @@ def test_recognize_segments_keeps_segment_order():
     segs = [[0, 900], [1000, 3900], [3000, 3200]]
     got = schedule.recognize_segments(_FakeEngine(), speech, segs)
     assert got == _FakeEngine().recognize(schedule.slice_segments(speech, segs))
+
+
+def test_recognize_segments_with_stamps_shifts_by_segment_start():
+    """Result combination of the long-audio pipeline for a time-stamp engine (auto_model.py:510-518), host logic only."""
+    import numpy as np
+
+    from funasr_b200 import schedule
+
+    class FakeEngine:
+        def recognize(self, waves):
+            self.lens = [len(w) for w in waves]
+            return [[10 + i, 20 + i] for i in range(len(waves))], [[[5, 50], [50, 90 + i]] for i in range(len(waves))]
+
+    eng = FakeEngine()
+    speech = np.zeros(16000 * 3, dtype=np.float32)
+    ids, stamps = schedule.recognize_segments_with_stamps(eng, speech, [[100, 900], [1500, 4000]])
+    assert eng.lens == [800 * 16, 16000 * 3 - 1500 * 16]  # the second segment is clipped to the recording
+    assert ids == [10, 20, 11, 21]
+    assert stamps == [[105, 150], [150, 190], [1505, 1550], [1550, 1591]]
