@@ -109,24 +109,44 @@ class BiCifParaformerEngine(ParaformerEngine):
         stamps: List[List[List[int]]] = [[] for _ in waves]
         scores = [0.0 for _ in waves]
         self.last_token_num = [0 for _ in waves]
-        for batch, wave, lens in self.uploaded_batches(waves):
-            ids, logp, tok, rows, ts = self.forward_packed_ts(wave, lens)
-            ids_h = ids.cpu().numpy()
-            logp_h = logp.cpu().numpy() if with_scores else None
-            keep = ~np.isin(ids_h, self._drop_ids)
+        # Device -> host reads go to pinned buffers behind an event and are turned into Python lists one batch LATE: the
+        # host-side work of batch k (id filtering, time stamps) runs while the GPU is busy with batch k + 1.
+        def stage(batch, ids, logp, tok, rows, ts):
+            pinned = self.read_later
+            item = dict(batch=batch, tok=tok, rows=rows, ids=pinned(ids), logp=pinned(logp) if with_scores else None, ts=None)
             if ts is not None:
-                fire_idx, fire_count = ts["fire_idx"].cpu().numpy(), ts["fire_count"].cpu().numpy()
-                num_chars = ts["num_chars"].cpu().numpy()
+                item["ts"] = {k: pinned(ts[k]) for k in ("fire_idx", "fire_count", "num_chars")}
+            item["done"] = torch.cuda.Event()
+            item["done"].record()
+            return item
+
+        def finish(item):
+            item["done"].synchronize()
+            ids_h = item["ids"].numpy()
+            keep = ~np.isin(ids_h, self._drop_ids)
+            ts = item["ts"]
+            if ts is not None:
+                fire_idx, fire_count, num_chars = ts["fire_idx"].numpy(), ts["fire_count"].numpy(), ts["num_chars"].numpy()
             o = r0 = 0
-            for j, (i, n) in enumerate(zip(batch, tok)):
+            for j, (i, n) in enumerate(zip(item["batch"], item["tok"])):
                 self.last_token_num[i] = int(n)
                 results[i] = ids_h[o: o + n][keep[o: o + n]].tolist()
                 if with_scores:
-                    scores[i] = float(logp_h[o: o + n].sum())
+                    scores[i] = float(item["logp"].numpy()[o: o + n].sum())
                 if ts is not None and n > 0:
                     f0 = 3 * r0
-                    stamps[i] = timestamp.stamps_from_fires(fire_idx[f0: f0 + int(fire_count[j])], 3 * rows[j],
+                    stamps[i] = timestamp.stamps_from_fires(fire_idx[f0: f0 + int(fire_count[j])], 3 * item["rows"][j],
                                                             int(num_chars[j]), vad_offset=begin_time)
                 o += n
-                r0 += rows[j]
+                r0 += item["rows"][j]
+
+        pending = None
+        for batch, wave, lens in self.uploaded_batches(waves):
+            ids, logp, tok, rows, ts = self.forward_packed_ts(wave, lens)
+            cur = stage(batch, ids, logp, tok, rows, ts)
+            if pending is not None:
+                finish(pending)
+            pending = cur
+        if pending is not None:
+            finish(pending)
         return (results, stamps, scores) if with_scores else (results, stamps)

@@ -469,10 +469,13 @@ class ParaformerEngine:
         results: List[List[int]] = [[] for _ in waves]
         scores = [0.0 for _ in waves]
         self.last_token_num = [0 for _ in waves]  # predicted token counts of the last call (before id filtering)
-        for batch, wave, lens in self.uploaded_batches(waves):
-            ids, logp, tok = self.forward_packed(wave, lens)
-            ids_h = ids.cpu().numpy()
-            logp_h = logp.cpu().numpy() if with_scores else None
+        # Device -> host reads go to pinned buffers behind an event and become Python lists one batch LATE: the host-side
+        # work of batch k (id filtering) runs while the GPU is busy with batch k + 1.
+        def finish(item):
+            batch, tok, ids_p, logp_p, done = item
+            done.synchronize()
+            ids_h = ids_p.numpy()
+            logp_h = logp_p.numpy() if with_scores else None
             keep = ~np.isin(ids_h, self._drop_ids)
             o = 0
             for i, n in zip(batch, tok):
@@ -481,7 +484,25 @@ class ParaformerEngine:
                 if with_scores:
                     scores[i] = float(logp_h[o: o + n].sum())
                 o += n
+
+        pending = None
+        for batch, wave, lens in self.uploaded_batches(waves):
+            ids, logp, tok = self.forward_packed(wave, lens)
+            cur = (batch, tok, self.read_later(ids), self.read_later(logp) if with_scores else None, torch.cuda.Event())
+            cur[-1].record()
+            if pending is not None:
+                finish(pending)
+            pending = cur
+        if pending is not None:
+            finish(pending)
         return (results, scores) if with_scores else results
+
+    @staticmethod
+    def read_later(t: torch.Tensor) -> torch.Tensor:
+        """Asynchronous device -> host copy into pinned memory on the current stream (valid after a later event / sync)."""
+        h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+        h.copy_(t, non_blocking=True)
+        return h
 
 
 class SenseVoiceEngine:
