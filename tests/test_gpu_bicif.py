@@ -167,3 +167,44 @@ def test_too_short_and_ragged_inputs(eng, bicif_sd):
     assert ids[1] == alone_ids[0] and stamps[1] == alone_stamps[0]
     assert len(stamps[1]) == len(ids[1]) and all(b <= e for b, e in stamps[1])
     assert eng.recognize([]) == ([], [])
+
+
+def test_kernels_stay_inside_their_buffers():
+    """Guard bands around every output of the LSTM and fire kernels (compute-sanitizer is not available on the pool)."""
+    h, up, lens = 512, 3, [7, 1, 12]
+    w = _lstm_weights(3)
+    g = torch.Generator().manual_seed(6)
+    rows3, pad = up * sum(lens), 96
+    xg = torch.randn(rows3, 8 * h, generator=g).to(DEV)
+    cu = tables.cu_from_lengths(lens, torch.int32, DEV)
+    parts = ops.lstm_parts(h)
+    for impl in (0, 1):
+        part = torch.full((parts + 2, rows3), 7.5, device=DEV)
+        out_h = torch.full((rows3 + pad, 2 * h), 7.5, device=DEV)
+        ops.lstm_bidir(xg, cu, up, up * max(lens), torch.stack(w["w_hh"]).to(DEV), w["w_out"].to(DEV), part[1:-1], out_h=out_h[:rows3],
+                       impl=impl)
+        torch.cuda.synchronize()
+        assert bool((part[0] == 7.5).all()) and bool((part[-1] == 7.5).all())
+        assert bool((out_h[rows3:] == 7.5).all()) and bool((out_h[:rows3] != 7.5).all())
+        assert bool(torch.isfinite(part[1:-1]).all()) and bool((part[1:-1] != 7.5).all())
+    token_num = torch.tensor([3, 1, 5], dtype=torch.int32, device=DEV)
+    ids = torch.randint(3, 50, (9,), dtype=torch.int32, device=DEV)
+    cu_tok = tables.cu_from_lengths([3, 1, 5], torch.int32, DEV)
+    fbuf = torch.full((rows3 + 2 * pad,), 7.5, device=DEV)
+    pbuf = torch.full((rows3 + 2 * pad,), 7.5, device=DEV)
+    ibuf = torch.full((rows3 + 2 * pad,), -7, dtype=torch.int32, device=DEV)
+    cbuf = torch.full((len(lens) + 2,), -7, dtype=torch.int32, device=DEV)
+    nbuf = torch.full((len(lens) + 2,), -7, dtype=torch.int32, device=DEV)
+    ops.us_fires(part[1:-1], 0.1, 0.25, 0.01, THR, cu, up, token_num, ids, cu_tok, (0, 1, 2), fbuf[pad: pad + rows3],
+                 ibuf[pad: pad + rows3], cbuf[1:-1], nbuf[1:-1], us_peaks=pbuf[pad: pad + rows3])
+    torch.cuda.synchronize()
+    for buf, fill in ((fbuf, 7.5), (pbuf, 7.5), (ibuf, -7)):
+        assert bool((buf[:pad] == fill).all()) and bool((buf[pad + rows3:] == fill).all())
+    assert cbuf[0] == -7 and cbuf[-1] == -7 and nbuf[0] == -7 and nbuf[-1] == -7
+    assert nbuf[1:-1].cpu().tolist() == [3, 1, 5]
+    o = 0
+    for i, n in enumerate(lens):  # fired frames are inside the utterance and increasing; the rest of the slot is untouched
+        c = int(cbuf[1 + i])
+        got = ibuf[pad + o: pad + o + up * n].cpu().tolist()
+        assert 0 <= c <= up * n and all(0 <= a < b < up * n for a, b in zip(got[:c], got[1:c])) and all(v == -7 for v in got[c:])
+        o += up * n

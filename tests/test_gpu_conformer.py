@@ -217,3 +217,29 @@ def test_bf16_mode_within_stated_tolerance(golden_dir, conformer_sd):
     e16.forward_packed(wave, lens, taps=taps)
     torch.cuda.synchronize()
     assert rel(taps["enc"], g["enc_1"]) < 5e-2
+
+
+def test_gemm_heads_and_glu_dwconv_stay_inside_their_buffers(conformer_sd):
+    """Guard rows around the outputs of the grouped GEMM and the depthwise kernel (ragged batch, last tile partial)."""
+    g = torch.Generator().manual_seed(11)
+    heads, dk, np_, wrows, m, n_group = 4, 64, 2, 1024, 333, 300
+    a_s = ops.split_rows(torch.randn(m, 4 * heads * dk, generator=g).to(DEV), np_)
+    w_s = torch.cat([ops.split_rows((torch.randn(wrows, dk, generator=g) * 0.3).to(DEV), np_) for _ in range(heads)], dim=0)
+    pitch = (n_group + 255) // 256 * 256
+    out = torch.full((m + 64, heads * pitch), 7.5, device=DEV)
+    ops.gemm_heads(a_s, np_, w_s, wrows, m, n_group, heads, dk, out[32: 32 + m], lda=np_ * 4 * heads * dk,
+                   a_part_stride=4 * heads * dk, a_col0=heads * dk, a_col_step=dk)
+    torch.cuda.synchronize()
+    assert bool((out[:32] == 7.5).all()) and bool((out[32 + m:] == 7.5).all())
+    c, k, lens = 256, 15, [70, 3, 131]
+    r = sum(lens)
+    x = torch.randn(r, 2 * c, generator=g).to(DEV)
+    cu = tables.cu_from_lengths(lens, torch.int32, DEV)
+    dw = (torch.randn(c, k, generator=g) * 0.2).to(DEV)
+    vec = lambda: torch.randn(c, generator=g).to(DEV)
+    width = ops.split_width(c, np_)
+    buf = torch.full((r + 64, width), 3.0, dtype=torch.bfloat16, device=DEV)
+    ops.glu_dwconv(x, cu, max(lens), c, dw, vec(), vec().abs() + 0.5, vec(), buf[32: 32 + r], np_)
+    torch.cuda.synchronize()
+    assert bool((buf[:32] == 3.0).all()) and bool((buf[32 + r:] == 3.0).all())
+    assert bool(torch.isfinite(buf[32: 32 + r].float()).all())
