@@ -130,6 +130,26 @@ def bicif_paraformer_shapes(vocab_size: int = 8404, enc_blocks: int = 50, dec_bl
     return s
 
 
+def seaco_paraformer_shapes(vocab_size: int = 8404, enc_blocks: int = 50, dec_blocks: int = 16, inner_dim: int = 512,
+                            seaco_layers: int = 6, seaco_units: int = 1024, seaco_kernel: int = 21) -> Shapes:
+    """SeacoParaformer (funasr/models/seaco_paraformer/template.yaml): BiCifParaformer plus the 2-layer bias-encoder LSTM
+    (model.py:66-74), the SeACo decoder (a ParaformerSANMDecoder with `wo_input_layer`, no output layer; `num_blocks: 4`
+    leaves `att_layer_num` at its default 6, so it has 6 attention layers + the FFN-only layer, decoder.py:303-351) and
+    `hotword_output_layer` (:96)."""
+    s = bicif_paraformer_shapes(vocab_size, enc_blocks, dec_blocks)
+    for layer in range(2):
+        s["bias_encoder.weight_ih_l%d" % layer] = (4 * inner_dim, inner_dim)
+        s["bias_encoder.weight_hh_l%d" % layer] = (4 * inner_dim, inner_dim)
+        s["bias_encoder.bias_ih_l%d" % layer] = (4 * inner_dim,)
+        s["bias_encoder.bias_hh_l%d" % layer] = (4 * inner_dim,)
+    dec = paraformer_decoder_shapes(vocab_size, inner_dim, seaco_units, seaco_layers, seaco_layers, seaco_kernel, prefix="seaco_decoder.")
+    for k, v in dec.items():
+        if not k.startswith(("seaco_decoder.embed.", "seaco_decoder.output_layer.")):
+            s[k] = v
+    _linear(s, "hotword_output_layer", inner_dim, vocab_size)
+    return s
+
+
 def sense_voice_small_shapes(vocab_size: int = 25055, enc_blocks: int = 50, tp_blocks: int = 20) -> Shapes:
     """SenseVoiceSmall (funasr/models/sense_voice/model.py:598-660): SenseVoiceEncoderSmall, the CTC
     projection (funasr/models/ctc/ctc.py:28) and the 16 x 560 query embedding (:646-648)."""

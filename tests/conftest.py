@@ -71,3 +71,14 @@ def bicif_sd():
 
     sd = synth.synth_state_dict(params.bicif_paraformer_shapes(), seed=0)
     return {k: torch.from_numpy(v) for k, v in sd.items()}
+
+
+@pytest.fixture(scope="session")
+def seaco_sd():
+    """Seeded SeacoParaformer weights: BiCifParaformer + bias-encoder LSTM, SeACo decoder, hot-word output layer."""
+    import torch
+
+    from funasr_b200 import params, synth
+
+    sd = synth.synth_state_dict(params.seaco_paraformer_shapes(), seed=0)
+    return {k: torch.from_numpy(v) for k, v in sd.items()}
