@@ -82,6 +82,10 @@ class BiCifParaformerEngine(ParaformerEngine):
         with torch.cuda.device(self.device):
             self.stamper = TimestampPack(state_dict, self.device, nparts=self.nparts)
 
+    def decode(self, enc, cu_rows, embeds, cu_tok, max_l, taps=None):
+        """Decoder + greedy pick -> (ids, logp, logits or None); `seaco.SeacoParaformerEngine` adds the hot-word branch."""
+        return self.decoder.run(enc, cu_rows, embeds, cu_tok, max_l, want_logits=taps is not None)
+
     def forward_packed_ts(self, wave: torch.Tensor, lens: Sequence[int], taps: Optional[dict] = None):
         """-> (ids i32 [L] device, logp, token_num list, rows list, time-stamp dict or None)."""
         inner = {} if taps is None else taps
@@ -96,7 +100,7 @@ class BiCifParaformerEngine(ParaformerEngine):
             if max(tok) < 1:
                 empty = torch.empty(0, dtype=torch.int32, device=self.device)
                 return empty, torch.empty(0, dtype=torch.float32, device=self.device), tok, rows, None
-            ids, logp, logits = self.decoder.run(enc, cu_rows, pred["embeds"], pred["cu_tok"], max(tok), want_logits=taps is not None)
+            ids, logp, logits = self.decode(enc, cu_rows, pred["embeds"], pred["cu_tok"], max(tok), taps)
             ts = self.stamper.run(enc, cu_rows, max(rows), pred["token_num_dev"], ids, pred["cu_tok"], self.DROP_IDS,
                                   want_taps=taps is not None)
             inner.update(logits=logits, ids=ids, logp=logp, **ts)

@@ -576,3 +576,27 @@ extern "C" __attribute__((visibility("default"))) int fb200_us_fires(
   FB_CHECK_LAUNCH("us_fires");
   return FB200_OK;
 }
+
+// ---------------------------------------------------------------- SeACo: `_merge_res` on the greedy picks
+// funasr/models/seaco_paraformer/model.py:312-322 with seaco_weight = 1: a token keeps the plain decoder's distribution when
+// the hot-word distribution's argmax is NO_BIAS, else it takes the hot-word distribution; on the greedy path only the argmax
+// and its log-probability of the chosen distribution are needed.
+__global__ void merge_hotword_ids_kernel(const int32_t* __restrict__ dec_ids, const float* __restrict__ dec_logp,
+                                         const int32_t* __restrict__ hw_ids, const float* __restrict__ hw_logp, int no_bias, int n,
+                                         int32_t* __restrict__ out_ids, float* __restrict__ out_logp) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const bool keep = hw_ids[i] == no_bias;
+  out_ids[i] = keep ? dec_ids[i] : hw_ids[i];
+  if (out_logp != nullptr) out_logp[i] = keep ? dec_logp[i] : hw_logp[i];
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_merge_hotword_ids(
+    const int32_t* dec_ids, const float* dec_logp, const int32_t* hw_ids, const float* hw_logp, int no_bias, int n, int32_t* out_ids,
+    float* out_logp, void* stream) {
+  FB_CHECK_ARG(n >= 0 && dec_ids && hw_ids && out_ids && (out_logp == nullptr || (dec_logp && hw_logp)), "merge_hotword_ids: bad arguments");
+  if (n == 0) return FB200_OK;
+  merge_hotword_ids_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(dec_ids, dec_logp, hw_ids, hw_logp, no_bias, n, out_ids, out_logp);
+  FB_CHECK_LAUNCH("merge_hotword_ids");
+  return FB200_OK;
+}

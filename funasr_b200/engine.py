@@ -291,9 +291,11 @@ class DecoderPack:
             for i in range(_count(sd, prefix + group)):
                 self.layers.append(_DecLayer(sd, prefix + group + "%d." % i, nparts, self.device))
         self.after_norm = _Norm(sd, prefix + "after_norm.", self.device)
-        self.output = _Linear(sd[prefix + "output_layer.weight"], sd[prefix + "output_layer.bias"], nparts, self.device)
-        self.d = self.output.k
-        self.vocab = self.output.n
+        self.output = None  # the SeACo decoder has no output layer (`use_output_layer: false`)
+        if prefix + "output_layer.weight" in sd:
+            self.output = _Linear(sd[prefix + "output_layer.weight"], sd[prefix + "output_layer.bias"], nparts, self.device)
+        self.d = self.layers[0].w1.k
+        self.vocab = self.output.n if self.output is not None else 0
         self.ff = self.layers[0].w1.n
         # K/V projections of the memory for every cross-attention layer as ONE contraction
         src = [i for i, ly in enumerate(self.layers) if ly.has_src]
@@ -308,6 +310,22 @@ class DecoderPack:
     def run(self, enc: torch.Tensor, cu_rows: torch.Tensor, embeds: torch.Tensor, cu_tok: torch.Tensor,
             max_l: int, enc_split: Optional[torch.Tensor] = None, want_logits: bool = False):
         """Returns (ids i32 [L], logp f32 [L], logits or None)."""
+        _, xs = self.hidden(enc, cu_rows, embeds, cu_tok, max_l, enc_split=enc_split)
+        return self.head(xs, want_logits=want_logits)
+
+    def head(self, xs: torch.Tensor, want_logits: bool = False):
+        """`output_layer` + log-softmax argmax over the split hidden states -> (ids, logp, logits or None)."""
+        l, dev = xs.shape[0], self.device
+        logits = torch.empty(l, self.vocab, dtype=torch.float32, device=dev)
+        ops.gemm(xs, self.nparts, self.output.w, self.nparts, l, self.vocab, self.d, bias=self.output.bias, out_f32=logits)
+        ids = torch.empty(l, dtype=torch.int32, device=dev)
+        logp = torch.empty(l, dtype=torch.float32, device=dev)
+        ops.argmax_logprob(logits, self.vocab, ids, logp)
+        return ids, logp, (logits if want_logits else None)
+
+    def hidden(self, enc: torch.Tensor, cu_rows: torch.Tensor, embeds: torch.Tensor, cu_tok: torch.Tensor,
+               max_l: int, enc_split: Optional[torch.Tensor] = None, want_f32: bool = False):
+        """The decoder up to `after_norm` (decoder.py:395-404) -> (hidden fp32 [L, d] or None, its bf16 split)."""
         dev, np_, d, eps = self.device, self.nparts, self.d, self.eps
         r, l = enc.shape[0], embeds.shape[0]
         bf = torch.bfloat16
@@ -347,13 +365,10 @@ class DecoderPack:
                 x = xo
             else:
                 x = y
-        ops.layernorm(x, self.after_norm.g, self.after_norm.b, eps, out_split=xs, nparts=np_)
-        logits = torch.empty(l, self.vocab, dtype=torch.float32, device=dev)
-        ops.gemm(xs, np_, self.output.w, np_, l, self.vocab, d, bias=self.output.bias, out_f32=logits)
-        ids = torch.empty(l, dtype=torch.int32, device=dev)
-        logp = torch.empty(l, dtype=torch.float32, device=dev)
-        ops.argmax_logprob(logits, self.vocab, ids, logp)
-        return ids, logp, (logits if want_logits else None)
+        hid = torch.empty(l, d, dtype=torch.float32, device=dev) if want_f32 else None
+        out = torch.empty(l, ops.split_width(d, np_), dtype=bf, device=dev)  # `xs` is scratch of the layers above
+        ops.layernorm(x, self.after_norm.g, self.after_norm.b, eps, out_f32=hid, out_split=out, nparts=np_)
+        return hid, out
 
 
 class ParaformerEngine:

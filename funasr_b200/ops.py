@@ -229,6 +229,11 @@ def us_fires(part, bias, smooth, noise, threshold, cu_rows, upsample, token_num,
               _stream())
 
 
+def merge_hotword_ids(dec_ids, dec_logp, hw_ids, hw_logp, no_bias, out_ids, out_logp=None):
+    _lib.call("fb200_merge_hotword_ids", _p(dec_ids), _p(dec_logp), _p(hw_ids), _p(hw_logp), int(no_bias), dec_ids.numel(),
+              _p(out_ids), _p(out_logp), _stream())
+
+
 def argmax_logprob(logits, vocab, ids, score=None, rows=None):
     rows = logits.shape[0] if rows is None else rows
     _lib.call("fb200_argmax_logprob", _p(logits), logits.stride(0), rows, vocab, _p(ids), _p(score), _stream())

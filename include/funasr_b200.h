@@ -337,6 +337,11 @@ int fb200_us_fires(const float* part, int nparts, int rows3, float bias, float s
                    const int32_t* cu_tok, const int32_t* drop_ids, float* us_alphas, float* us_peaks, int32_t* fire_idx,
                    int32_t* fire_count, int32_t* num_chars, void* stream);
 
+/* SeacoParaformer `_merge_res` on the greedy picks (funasr/models/seaco_paraformer/model.py:312-322, seaco_weight = 1):
+ * out[i] = hw_ids[i] == no_bias ? dec : hw, for the ids and (when out_logp != NULL) their log-probabilities. */
+int fb200_merge_hotword_ids(const int32_t* dec_ids, const float* dec_logp, const int32_t* hw_ids, const float* hw_logp,
+                            int no_bias, int n, int32_t* out_ids, float* out_logp, void* stream);
+
 /* ------------------------------------------------------------------ decoding ----------- */
 
 /* Per row: id = argmax(logits), score = max(log_softmax) -- the greedy branch of
