@@ -517,6 +517,8 @@ class ParaformerInference:
             sd = {k: v.detach() for k, v in self.state_dict().items()}
             self._fb200_engine = self._fb200_engine_cls(sd, dev, precision=PRECISION, cmvn=getattr(frontend, "cmvn", None),
                                                         window=getattr(frontend, "window", "hamming"))
+            if hasattr(self._fb200_engine, "NO_BIAS") and hasattr(self, "NO_BIAS"):
+                self._fb200_engine.NO_BIAS = int(self.NO_BIAS)
             self._fb200_engine_key = key
         return self._fb200_engine
 
@@ -526,8 +528,11 @@ class ParaformerInference:
         off_path = (kwargs.get("decoding_ctc_weight", 0.0) > 0.00001 and getattr(self, "ctc", None) is not None) or (
             kwargs.get("lm_weight", 0.0) > 0.00001 and kwargs.get("lm_file") is not None) or (
             kwargs.get("pred_timestamp", False) and not self._fb200_timestamps) or kwargs.get(
-            "data_type", "sound") == "fbank" or getattr(self, "beam_search", None) is not None or (
-            self._fb200_hotwords and kwargs.get("hotword") is not None)
+            "data_type", "sound") == "fbank" or getattr(self, "beam_search", None) is not None
+        hot_ids = None
+        if self._fb200_hotwords and kwargs.get("hotword") is not None and not off_path:
+            hot_ids = self._fb200_hotword_ids(kwargs.get("hotword"), tokenizer, frontend)
+            off_path = hot_ids is not None and len(hot_ids) > 50  # the reference's ASF filter (model.py:268-295) is not on the path
         if off_path:
             ref = getattr(super(), "inference", None)
             if ref is None:
@@ -541,7 +546,9 @@ class ParaformerInference:
         meta_data["load_data"] = f"{t2 - t1:0.3f}"
         eng = self._engine_for(frontend)
         stamps = None
-        if self._fb200_timestamps:
+        if self._fb200_hotwords:
+            ids, stamps, scores = eng.recognize(waves, with_scores=True, begin_time=kwargs.get("begin_time", 0), hotwords=hot_ids)
+        elif self._fb200_timestamps:
             ids, stamps, scores = eng.recognize(waves, with_scores=True, begin_time=kwargs.get("begin_time", 0))
         else:
             ids, scores = eng.recognize(waves, with_scores=True)
@@ -890,23 +897,65 @@ class SeacoParaformerInference(BiCifParaformerInference):
     """`SeacoParaformer.inference` (funasr/models/seaco_paraformer/model.py:361-510; the class the hub alias
     `paraformer-zh` resolves to) WITHOUT hot words: `_seaco_decode_with_ASF` then returns the plain decoder's log-softmax
     (:252-254, :325-327) and the rest is BiCifParaformer's inference -- pinned by tests/golden/seaco.npz (the unmodified
-    reference's SeACo results equal its BiCif results on the same weights).  A call WITH `hotword=` goes to the
-    reference's own method (bias encoder, SeACo decoder and ASF are not on the accelerated path); without the reference
-    package it raises NotImplementedError."""
+    reference's SeACo results equal its BiCif results on the same weights).  WITH `hotword=` (up to 50 hot words incl.
+    the trailing [sos]) the hot-word branch runs in `seaco.SeacoParaformerEngine` (bias-encoder LSTM, SeACo decoder,
+    merge); longer lists need the reference's ASF filter and go to the reference's own method (NotImplementedError
+    without the reference package)."""
 
     _fb200_hotwords = True
     _fb200_empty = ([],)  # model.py:417-418
 
+    @property
+    def _fb200_engine_cls(self):
+        from . import seaco
+
+        return seaco.SeacoParaformerEngine
+
+    def _fb200_hotword_ids(self, hotword, tokenizer, frontend):
+        """Hot words as token-id lists, the last one [sos]: the reference's `generate_hotwords_list` (model.py:512-617:
+        string, .txt file or URL, optional seg_dict) when this class wraps the reference model; stand-alone: a list of
+        id lists, or a blank-separated string looked up in the tokenizer."""
+        gen = getattr(super(), "generate_hotwords_list", None)
+        if gen is not None:
+            return gen(hotword, tokenizer=tokenizer, frontend=frontend)
+        if isinstance(hotword, str):
+            if tokenizer is None:
+                raise RuntimeError("funasr_b200.SeacoParaformer: a hot-word string needs the tokenizer")
+            return [tokenizer.tokens2ids([w]) for w in hotword.strip().split()] + [[self.sos]]
+        return [list(map(int, w)) for w in hotword] + [[self.sos]]
+
+
+class _HotwordTensors(_ParamTree):
+    """`bias_encoder.*`, `seaco_decoder.*`, `hotword_output_layer.*` under the reference's names (model.py:66-96)."""
+
+    def __init__(self, shapes):
+        super().__init__()
+        self._declare(shapes, "")
+
 
 class SeacoParaformer(SeacoParaformerInference, Paraformer):
-    """Stand-alone `SeacoParaformer` for hosts without the reference package: BiCifParaformer's tensors only -- load a
-    SeACo checkpoint with `strict=False` (its `bias_encoder.*`, `seaco_decoder.*`, `hotword_output_layer.*` tensors serve
-    hot-word calls, which this class does not take)."""
+    """Stand-alone `SeacoParaformer` (funasr/models/seaco_paraformer/model.py:44-105) for hosts without the reference
+    package: BiCifParaformer's modules plus the hot-word tensors under the reference's state_dict keys; inference only."""
 
-    def __init__(self, *args, inner_dim=None, bias_encoder_type=None, bias_encoder_bid=None, bias_encoder_dropout_rate=None,
-                 seaco_lsm_weight=None, seaco_length_normal=None, seaco_length_normalized_loss=None, train_decoder=None,
-                 NO_BIAS=None, seaco_decoder=None, seaco_decoder_conf=None, seaco_weight=None, **kwargs):
+    def __init__(self, *args, inner_dim=512, bias_encoder_type="lstm", bias_encoder_bid=False, bias_encoder_dropout_rate=0.0,
+                 seaco_lsm_weight=0.0, seaco_length_normal=True, seaco_length_normalized_loss=True, train_decoder=True,
+                 NO_BIAS=8377, seaco_decoder=None, seaco_decoder_conf=None, seaco_weight=0.01, **kwargs):
         super().__init__(*args, **kwargs)
+        if bias_encoder_type != "lstm" or bias_encoder_bid:
+            raise NotImplementedError("funasr_b200.SeacoParaformer: only a unidirectional LSTM bias encoder")
+        conf = dict(seaco_decoder_conf or {})
+        blocks = max(int(conf.get("att_layer_num", 6)), int(conf.get("num_blocks", 6)))
+        extra = {k: v for k, v in params.seaco_paraformer_shapes(self.vocab_size, 1, 1, inner_dim, blocks,
+                                                                 int(conf.get("linear_units", 2048)),
+                                                                 int(conf.get("kernel_size", 21))).items()
+                 if k.startswith(("bias_encoder.", "seaco_decoder.", "hotword_output_layer."))}
+        groups = {}
+        for k, v in extra.items():
+            head, rest = k.split(".", 1)
+            groups.setdefault(head, {})[rest] = v
+        for head, shapes in groups.items():
+            self.add_module(head, _HotwordTensors(shapes))
+        self.NO_BIAS = NO_BIAS
 
 
 DROPIN_CLASSES[("model_classes", "SeacoParaformer")] = SeacoParaformer

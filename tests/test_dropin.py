@@ -546,16 +546,23 @@ def test_seaco_golden_equals_bicif_golden(golden_dir):
     assert all(k.startswith(("bias_encoder.", "seaco_decoder.", "hotword_output_layer.")) for k in s["extra_keys"].tolist())
 
 
-def test_standalone_seaco_model_takes_the_reference_keywords():
+SEACO = dict(inner_dim=512, bias_encoder_type="lstm", bias_encoder_bid=False, seaco_lsm_weight=0.1, seaco_length_normal=True,
+             train_decoder=False, NO_BIAS=8377, seaco_decoder="ParaformerSANMDecoder",
+             seaco_decoder_conf=dict(attention_heads=4, linear_units=1024, num_blocks=4, kernel_size=21, sanm_shfit=0,
+                                     use_output_layer=False, wo_input_layer=True))
+
+
+def test_standalone_seaco_model_has_the_reference_state_dict():
     conf = dict(MODEL, predictor="CifPredictorV3", predictor_conf=PRED_V3, encoder_conf=dict(ENC, num_blocks=1),
-                decoder_conf=dict(DEC, num_blocks=1, att_layer_num=1), inner_dim=512, bias_encoder_type="lstm",
-                bias_encoder_bid=False, seaco_lsm_weight=0.1, seaco_length_normal=True, train_decoder=False, NO_BIAS=8377,
-                seaco_decoder="ParaformerSANMDecoder", seaco_decoder_conf=dict(num_blocks=4))
+                decoder_conf=dict(DEC, num_blocks=1, att_layer_num=1), **SEACO)
     model = dropin.SeacoParaformer(**conf)
-    assert set(model.state_dict()) == set(params.bicif_paraformer_shapes(enc_blocks=1, dec_blocks=1))
+    want = params.seaco_paraformer_shapes(enc_blocks=1, dec_blocks=1)
+    assert {k: tuple(v.shape) for k, v in model.state_dict().items()} == dict(want)
     frontend = dropin.WavFrontend(lfr_m=7, lfr_n=6, dither=0.0)
-    with pytest.raises(NotImplementedError):  # hot words leave the accelerated path; no reference method to fall back to
+    with pytest.raises(RuntimeError, match="tokenizer"):  # a hot-word string cannot be looked up without the tokenizer
         model.inference([synth.synth_waveform(0, 16000)], key=["a"], frontend=frontend, hotword="some words")
+    with pytest.raises(NotImplementedError):  # more than 50 hot words: the reference's ASF filter, no reference method here
+        model.inference([synth.synth_waveform(0, 16000)], key=["a"], frontend=frontend, hotword=[[5 + i] for i in range(60)])
 
 
 @pytest.mark.skipif(not reference_available(), reason="reference tree not present (GPU box)")
@@ -580,7 +587,8 @@ def test_install_wraps_the_reference_seaco_model_class():
 
 
 @pytest.mark.gpu
-def test_seaco_model_inference_without_hotwords_matches_golden(bicif_sd, golden_dir, tmp_path):
+def test_seaco_model_inference_matches_golden(seaco_sd, golden_dir, tmp_path):
+    """`SeacoParaformer.inference` through the packed engine, without and with hot words, == the unmodified reference."""
     g = np.load(os.path.join(golden_dir, "seaco.npz"))
     dev = torch.device("cuda:0")
     shift, scale = synth.synth_cmvn()
@@ -588,16 +596,24 @@ def test_seaco_model_inference_without_hotwords_matches_golden(bicif_sd, golden_
     synth.write_cmvn_file(cmvn_file, shift, scale)
     frontend = dropin.WavFrontend(cmvn_file=cmvn_file, fs=16000, window="hamming", n_mels=80, frame_length=25,
                                   frame_shift=10, lfr_m=7, lfr_n=6, dither=0.0)
-    model = dropin.SeacoParaformer(**dict(MODEL, predictor="CifPredictorV3", predictor_conf=PRED_V3, inner_dim=512,
-                                          seaco_decoder="ParaformerSANMDecoder")).to(dev)
-    sd = dict(bicif_sd)
-    sd["hotword_output_layer.weight"] = torch.zeros(8404, 512)  # a SeACo checkpoint's extra tensors are ignored
-    missing = model.load_state_dict(sd, strict=False)
-    assert not missing.missing_keys and missing.unexpected_keys == ["hotword_output_layer.weight"]
+    model = dropin.SeacoParaformer(**dict(MODEL, predictor="CifPredictorV3", predictor_conf=PRED_V3, **SEACO)).to(dev)
+    model.load_state_dict(seaco_sd, strict=True)
     waves = [synth.synth_waveform(int(g["seeds"][ci]), int(g["num_samples"][ci])) for ci in range(3)]
     results, _ = model.inference(waves, key=["a", "b", "c"], tokenizer=None, frontend=frontend, device="cuda:0")
     assert [r["token_int"] for r in results] == [g["ids_%d" % ci].tolist() for ci in range(3)]
-    results, _ = model.inference(waves, key=["a", "b", "c"], tokenizer=_Tokenizer(), frontend=frontend, device="cuda:0")
+    tok = _Tokenizer()
+    tok.tokens2ids = lambda tokens: [tok.token_list.index(t) for t in tokens]
+    results, _ = model.inference(waves, key=["a", "b", "c"], tokenizer=tok, frontend=frontend, device="cuda:0")
     if not reference_available():
         assert [r["timestamp"] for r in results] == [g["timestamp_%d" % ci].tolist() for ci in range(3)]
+    # hot words as id lists (what the reference's generate_hotwords_list produces, without the trailing [sos])
+    flat, lens, hot, o = g["hotwords_flat"].tolist(), g["hotwords_len"].tolist(), [], 0
+    for n in lens[:-1]:
+        hot.append(flat[o: o + n])
+        o += n
+    results, _ = model.inference(waves[:2], key=["a", "b"], tokenizer=None, frontend=frontend, device="cuda:0", hotword=hot)
+    assert [r["token_int"] for r in results] == [g["hot_ids_%d" % ci].tolist() for ci in range(2)]
+    # a hot-word string: one single-token hot word per blank-separated item (model.py:595-605)
+    results, _ = model.inference([waves[0]], key=["a"], tokenizer=tok, frontend=frontend, device="cuda:0", hotword="t5 t77")
+    assert results[0]["text"]
     assert model.inference([np.zeros(200, dtype=np.float32)], key=["z"], frontend=frontend, device="cuda:0") == ([],)
