@@ -2,7 +2,8 @@
 
     python tools/configs_bench.py --config 3     # SenseVoiceSmall (50 + 20 SAN-M blocks, V = 25055), CTC greedy
     python tools/configs_bench.py --config 5     # Paraformer-large long-audio sweep: 60 / 120 / 300 / 600 s x 8 each
-    python tools/configs_bench.py --config 6     # BiCifParaformer (what `paraformer-zh` resolves to): ids + time stamps
+    python tools/configs_bench.py --config 6     # BiCifParaformer: ids + time stamps
+    python tools/configs_bench.py --config 7     # SeacoParaformer (what `paraformer-zh` resolves to) with 20 hot words
 
 Prints ONE JSON line: throughput with waveforms resident in HBM, end to end from pinned host memory, per-kernel-kind
 device times of one step (fb200_profile_*), and the oracle timed on the host cores over a bounded sample.
@@ -23,7 +24,7 @@ from funasr_b200 import _lib, engine, params, synth  # noqa: E402
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--config", type=int, required=True, choices=[3, 5, 6])
+    ap.add_argument("--config", type=int, required=True, choices=[3, 5, 6, 7])
     ap.add_argument("--utts", type=int, default=256)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
@@ -51,6 +52,22 @@ def main():
         name = "BiCifParaformer (SURVEY 8f rank 3): Paraformer-large + CifPredictorV3 time-stamp head, %d synthetic utterances U(2,30) s" % args.utts
         metric = "BiCifParaformer RTFx (audio s / wall s), token ids + time stamps"
         cpu_fn, cpu_n = (lambda w: BO.recognize(torch.from_numpy(w), sd, cmvn)), 2
+    elif args.config == 7:
+        import numpy as np
+
+        from funasr_b200 import seaco
+        from oracle import seaco_oracle as SO
+
+        sd = {k: torch.from_numpy(v) for k, v in synth.synth_state_dict(params.seaco_paraformer_shapes(), seed=0).items()}
+        eng = seaco.SeacoParaformerEngine(sd, dev, "fp32", cmvn=cmvn, max_rows=args.max_rows)
+        rng = np.random.default_rng(5)
+        hot = [rng.integers(3, 8000, size=int(rng.integers(2, 5))).tolist() for _ in range(20)]
+        plain = eng.recognize
+        eng.recognize = lambda src: plain(src, hotwords=hot)
+        durs = synth.synth_durations(args.utts)
+        name = "SeacoParaformer (SURVEY 8f rank 3) with 20 hot words of 2-4 tokens: BiCifParaformer + bias-encoder LSTM + SeACo decoder, %d synthetic utterances U(2,30) s" % args.utts
+        metric = "SeacoParaformer RTFx (audio s / wall s), 20 hot words, token ids + time stamps"
+        cpu_fn, cpu_n = (lambda w: SO.recognize(torch.from_numpy(w), sd, cmvn, hotwords=hot + [[1]])), 2
     else:
         sd = {k: torch.from_numpy(v) for k, v in synth.synth_state_dict(params.paraformer_large_shapes(), seed=0).items()}
         eng = engine.ParaformerEngine(sd, dev, "fp32", cmvn=cmvn, max_rows=args.max_rows)
