@@ -12,7 +12,8 @@ What the branch adds to BiCifParaformer (funasr/models/seaco_paraformer/model.py
     embeddings as memory: over the CIF embeddings and over the decoder's hidden states; the two results are added (:178-179);
   * `hotword_output_layer` -> log-softmax; where its argmax is NO_BIAS the plain decoder's log-softmax is kept, elsewhere
     the hot-word distribution replaces it (`_merge_res`, :312-322, with seaco_weight = 1).
-The attention-score filter (ASF, :268-295) only runs with more than `nfilter` = 50 hot words and is not restated.
+  * with more than `nfilter` = 50 hot words the attention-score filter (ASF, :268-295) first keeps the 50 hot words the
+    decoder's hidden states attend to most, plus the trailing [sos].
 """
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -52,6 +53,34 @@ def decoder_hidden(memory: torch.Tensor, x: torch.Tensor, sd: SD, prefix: str, h
     return P.layer_norm(x, sd, prefix + "after_norm.", eps)
 
 
+def asf_filter(ctx: torch.Tensor, hidden: torch.Tensor, sd: SD, heads: int = 4, eps: float = 1e-12, nfilter: int = NFILTER,
+               prefix: str = "seaco_decoder.") -> List[int]:
+    """The attention-score filter (model.py:268-295; `forward_asf6`, paraformer/decoder.py:439-458; `get_attn_mat`, :123-137):
+    the decoder's hidden states go through SeACo decoder layers 0-4 with ALL hot words as memory; the attention
+    probabilities of layer 5's cross-attention are summed over heads and tokens; the `nfilter` best hot words (never
+    the trailing [sos]... which is always appended) are kept.  Returns the kept row indices: top-k order, then N - 1.
+    (In a padded batch the reference scores utterance 0 only and applies its choice to every utterance; this is the
+    batch-1 form.)"""
+    x = hidden
+    for i in range(5):
+        x = P.decoder_layer(x, ctx, sd, prefix + "decoders.%d." % i, heads, eps)
+    p = prefix + "decoders.5."
+    t = P.decoder_ffn(P.layer_norm(x, sd, p + "norm1.", eps), sd, p + "feed_forward.", eps)
+    y = x + P.fsmn_memory(P.layer_norm(t, sd, p + "norm2.", eps), sd[p + "self_attn.fsmn_block.weight"])
+    q = F.linear(P.layer_norm(y, sd, p + "norm3.", eps), sd[p + "src_attn.linear_q.weight"], sd[p + "src_attn.linear_q.bias"])
+    kv = F.linear(ctx, sd[p + "src_attn.linear_k_v.weight"], sd[p + "src_attn.linear_k_v.bias"])
+    k = kv[:, : kv.shape[-1] // 2]
+    dk = q.shape[-1] // heads
+    scores = torch.zeros(ctx.shape[0])
+    for h in range(heads):
+        att = torch.softmax((q[:, h * dk:(h + 1) * dk] * dk ** -0.5) @ k[:, h * dk:(h + 1) * dk].T, dim=-1)
+        scores = scores + att.sum(0)
+    n = ctx.shape[0]
+    keep = torch.topk(scores, min(nfilter, n - 1))[1].tolist()
+    keep.append(n - 1)
+    return keep
+
+
 def seaco_decode(enc: torch.Tensor, embeds: torch.Tensor, sd: SD, hotwords: Optional[Sequence[Sequence[int]]], heads: int = 4,
                  taps: Optional[dict] = None) -> torch.Tensor:
     """`_seaco_decode_with_ASF` (model.py:233-327) -> merged log-probabilities [L, V]."""
@@ -59,9 +88,12 @@ def seaco_decode(enc: torch.Tensor, embeds: torch.Tensor, sd: SD, hotwords: Opti
     dec_pred = torch.log_softmax(F.linear(hidden, sd["decoder.output_layer.weight"], sd["decoder.output_layer.bias"]), dim=-1)
     if hotwords is None:
         return dec_pred
-    if len(hotwords) > NFILTER:
-        raise NotImplementedError("more than %d hot words: the reference's ASF filter is not restated" % NFILTER)
     ctx = hotword_embeddings(hotwords, sd)
+    if len(hotwords) > NFILTER:
+        keep_rows = asf_filter(ctx, hidden, sd, heads)
+        if taps is not None:
+            taps.update(asf_keep=keep_rows)
+        ctx = ctx[keep_rows]
     cif_att = decoder_hidden(ctx, embeds, sd, "seaco_decoder.", heads)
     dec_att = decoder_hidden(ctx, hidden, sd, "seaco_decoder.", heads)
     merged = cif_att + dec_att

@@ -133,6 +133,35 @@ def main():
         out["mixed_keep_0"] = (dha2.argmax(dim=-1) == 8377).numpy()
         model.hotword_output_layer.bias.data[8377] -= shift
         print("mixed: shift %.4f, %d of %d tokens keep the decoder's distribution" % (shift, int(out["mixed_keep_0"].sum()), int(tok_len[0])))
+    # ---- more than nfilter = 50 hot words: the attention-score filter (model.py:268-295) -----------------------------
+    rng = np.random.default_rng(11)
+    many_path = os.path.join(tmp, "many.txt")
+    many = [["t%d" % int(v) for v in rng.integers(0, 8000, size=int(rng.integers(1, 4)))] for _ in range(64)]
+    with open(many_path, "w") as f:
+        f.write("\n".join(" ".join(w) for w in many) + "\n")
+    with torch.no_grad():
+        hw_many = model.generate_hotwords_list(many_path, tokenizer=tokenizer, frontend=frontend)
+        out["many_flat"] = np.asarray([i for hw in hw_many for i in hw], dtype=np.int32)
+        out["many_len"] = np.asarray([len(hw) for hw in hw_many], dtype=np.int32)
+        hw_pad = pad_list([torch.Tensor(i).long() for i in hw_many], 0)
+        selected = model._hotword_representation(hw_pad, torch.Tensor([len(i) for i in hw_many]).int())
+        wave = synth.synth_waveform(*CASES[0])
+        speech, lens = extract_fbank([torch.from_numpy(wave)], data_type="sound", frontend=frontend)
+        enc, enc_lens = model.encode(speech, lens)
+        embeds, tok_len = model.calc_predictor(enc, enc_lens)[:2]
+        tok_len = tok_len.round().long()
+        _, hidden, _ = model.decoder(enc, enc_lens, embeds, tok_len, return_hidden=True, return_both=True)
+        n_hw = torch.tensor([selected.shape[0]], dtype=torch.int32)
+        att = model.seaco_decoder.forward_asf6(selected.unsqueeze(0), n_hw, hidden, tok_len)
+        scores = att[0].sum(0).sum(0)
+        out["many_scores"] = scores.numpy()
+        out["many_keep"] = np.asarray(torch.topk(scores, 50)[1].tolist() + [selected.shape[0] - 1], dtype=np.int32)
+        pred = model._seaco_decode_with_ASF(enc, enc_lens, embeds, tok_len, hw_list=hw_many)
+        top = pred[0, : tok_len[0]].topk(2, dim=-1)
+        out["many_top2_ids_0"] = top.indices.numpy().astype(np.int32)
+        out["many_top2_logp_0"] = top.values.numpy()
+        srt = np.sort(out["many_scores"][:-1])[::-1]
+        print("many hot words:", len(hw_many), "kept", len(out["many_keep"]), "score gap at the cut %.3e (scores ~ %.3f)" % (srt[49] - srt[50], srt[49]))
     bicif = np.load(os.path.join(HERE, "bicif.npz"))
     for ci in range(len(CASES)):
         assert np.array_equal(out["ids_%d" % ci], bicif["ids_%d" % ci]), "SeACo without hot words differs from BiCif (ids)"

@@ -89,3 +89,27 @@ def test_recognize_with_hot_words_matches_reference_inference(golden, seaco_sd):
     ids, stamps = S.recognize(wave, seaco_sd, cmvn, hotwords=hotwords_of(golden))
     assert ids == golden["hot_ids_0"].tolist()
     assert stamps == golden["hot_timestamp_0"].tolist()
+
+
+def many_hotwords_of(g):
+    flat, lens = g["many_flat"].tolist(), g["many_len"].tolist()
+    out, o = [], 0
+    for n in lens:
+        out.append(flat[o: o + n])
+        o += n
+    return out
+
+
+def test_attention_score_filter_matches_reference(golden_dir, golden, seaco_sd):
+    """65 hot words: the 50 the decoder's hidden states attend to most are kept (+ the trailing [sos]), then the
+    decode goes on with those (model.py:268-295)."""
+    b = np.load(os.path.join(golden_dir, "bicif.npz"))
+    hw = many_hotwords_of(golden)
+    assert len(hw) == 65 and hw[-1] == [1]
+    taps = {}
+    with torch.no_grad():
+        pred = S.seaco_decode(torch.from_numpy(b["enc_0"]), torch.from_numpy(b["embeds_0"]), seaco_sd, hw, taps=taps)
+    assert taps["asf_keep"] == golden["many_keep"].tolist()
+    top = pred.topk(2, dim=-1)
+    assert np.array_equal(top.indices.numpy().astype(np.int32), golden["many_top2_ids_0"])
+    assert _rel(top.values, golden["many_top2_logp_0"]) < 1e-4
