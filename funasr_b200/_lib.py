@@ -33,6 +33,7 @@ SIGNATURES = {
     "fb200_lstm_parts": [_I, _P],
     "fb200_lstm_bidir": [_P, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, ctypes.c_longlong, _P, _P, _I, _P],
     "fb200_us_fires": [_P, _I, _I, _F, _F, _F, _F, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
+    "fb200_asf_scores": [_P, _I, _P, _I, _P, _P, _I, _I, _I, _I, _F, _P, _P],
     "fb200_merge_hotword_ids": [_P, _P, _P, _P, _I, _I, _P, _P, _P],
     "fb200_conv2d_sub1": [_P, _I, _P, _P, _I, _I, _I, _P, _P, _I, _P, _I, _P],
     "fb200_gather_rows": [_P, _I, _P, _P, _I, _P, _I, _I, _I, _P],

@@ -600,3 +600,85 @@ extern "C" __attribute__((visibility("default"))) int fb200_merge_hotword_ids(
   FB_CHECK_LAUNCH("merge_hotword_ids");
   return FB200_OK;
 }
+
+// ---------------------------------------------------------------- SeACo: attention-score filter
+// `hotword_scores` of `_seaco_decode_with_ASF` (funasr/models/seaco_paraformer/model.py:268-274): the cross-attention
+// probabilities of SeACo decoder layer 5 (`get_attn_mat`, funasr/models/paraformer/decoder.py:123-137) summed over heads and
+// tokens, per hot word.  One CTA per utterance walks (head, token) in a fixed order -- deterministic sums, the top-k that
+// follows must not depend on scheduling.  fp32 on the CUDA cores: a few MFLOP per utterance.
+namespace fb200 {
+namespace lstm {
+constexpr int kAsfThreads = 256;
+constexpr int kAsfMaxWords = 2048;
+
+__global__ void __launch_bounds__(kAsfThreads) asf_scores_kernel(const float* __restrict__ q, int ld_q, const float* __restrict__ k,
+                                                                 int ld_k, const int32_t* __restrict__ cu_tok,
+                                                                 const int32_t* __restrict__ cu_mem, int heads, int head_dim,
+                                                                 float scale, float* __restrict__ scores) {
+  __shared__ float s_q[128];
+  __shared__ float s_p[kAsfMaxWords];
+  __shared__ float s_acc[kAsfMaxWords];
+  __shared__ float s_red[kAsfThreads / 32];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int t0 = cu_tok[b], nt = cu_tok[b + 1] - t0;
+  const int m0 = cu_mem[b], nm = cu_mem[b + 1] - m0;
+  for (int n = tid; n < nm; n += kAsfThreads) s_acc[n] = 0.f;
+  __syncthreads();
+  for (int h = 0; h < heads; ++h) {
+    for (int l = 0; l < nt; ++l) {
+      if (tid < head_dim) s_q[tid] = q[(size_t)(t0 + l) * ld_q + h * head_dim + tid] * scale;
+      __syncthreads();
+      float mx = -INFINITY;
+      for (int n = tid; n < nm; n += kAsfThreads) {
+        const float* kr = k + (size_t)(m0 + n) * ld_k + h * head_dim;
+        float d = 0.f;
+        for (int c = 0; c < head_dim; c += 4) {
+          const float4 kv = *reinterpret_cast<const float4*>(kr + c);
+          d = fmaf(s_q[c], kv.x, d);
+          d = fmaf(s_q[c + 1], kv.y, d);
+          d = fmaf(s_q[c + 2], kv.z, d);
+          d = fmaf(s_q[c + 3], kv.w, d);
+        }
+        s_p[n] = d;
+        mx = fmaxf(mx, d);
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+      if (lane == 0) s_red[warp] = mx;
+      __syncthreads();
+      mx = s_red[0];
+      for (int w = 1; w < kAsfThreads / 32; ++w) mx = fmaxf(mx, s_red[w]);
+      __syncthreads();
+      float sum = 0.f;
+      for (int n = tid; n < nm; n += kAsfThreads) {
+        const float e = expf(s_p[n] - mx);
+        s_p[n] = e;
+        sum += e;
+      }
+      sum = warp_sum(sum);
+      if (lane == 0) s_red[warp] = sum;
+      __syncthreads();
+      sum = 0.f;
+      for (int w = 0; w < kAsfThreads / 32; ++w) sum += s_red[w];
+      const float inv = 1.f / sum;
+      for (int n = tid; n < nm; n += kAsfThreads) s_acc[n] += s_p[n] * inv;
+      __syncthreads();
+    }
+  }
+  for (int n = tid; n < nm; n += kAsfThreads) scores[m0 + n] = s_acc[n];
+}
+}  // namespace lstm
+}  // namespace fb200
+
+extern "C" __attribute__((visibility("default"))) int fb200_asf_scores(
+    const float* q, int ld_q, const float* k, int ld_k, const int32_t* cu_tok, const int32_t* cu_mem, int batch, int max_words, int heads,
+    int head_dim, float scale, float* scores, void* stream) {
+  FB_CHECK_ARG(batch > 0 && heads > 0 && head_dim > 0 && head_dim <= 128 && head_dim % 4 == 0 && ld_q % 4 == 0 && ld_k % 4 == 0,
+               "asf_scores: batch %d / heads %d / head_dim %d", batch, heads, head_dim);
+  FB_CHECK_ARG(max_words >= 1 && max_words <= fb200::lstm::kAsfMaxWords, "asf_scores: %d hot words per utterance (1..%d)", max_words,
+               fb200::lstm::kAsfMaxWords);
+  fb200::lstm::asf_scores_kernel<<<batch, fb200::lstm::kAsfThreads, 0, (cudaStream_t)stream>>>(q, ld_q, k, ld_k, cu_tok, cu_mem, heads, head_dim,
+                                                                                             scale, scores);
+  FB_CHECK_LAUNCH("asf_scores");
+  return FB200_OK;
+}

@@ -532,7 +532,6 @@ class ParaformerInference:
         hot_ids = None
         if self._fb200_hotwords and kwargs.get("hotword") is not None and not off_path:
             hot_ids = self._fb200_hotword_ids(kwargs.get("hotword"), tokenizer, frontend)
-            off_path = hot_ids is not None and len(hot_ids) > 50  # the reference's ASF filter (model.py:268-295) is not on the path
         if off_path:
             ref = getattr(super(), "inference", None)
             if ref is None:
@@ -897,10 +896,8 @@ class SeacoParaformerInference(BiCifParaformerInference):
     """`SeacoParaformer.inference` (funasr/models/seaco_paraformer/model.py:361-510; the class the hub alias
     `paraformer-zh` resolves to) WITHOUT hot words: `_seaco_decode_with_ASF` then returns the plain decoder's log-softmax
     (:252-254, :325-327) and the rest is BiCifParaformer's inference -- pinned by tests/golden/seaco.npz (the unmodified
-    reference's SeACo results equal its BiCif results on the same weights).  WITH `hotword=` (up to 50 hot words incl.
-    the trailing [sos]) the hot-word branch runs in `seaco.SeacoParaformerEngine` (bias-encoder LSTM, SeACo decoder,
-    merge); longer lists need the reference's ASF filter and go to the reference's own method (NotImplementedError
-    without the reference package)."""
+    reference's SeACo results equal its BiCif results on the same weights).  WITH `hotword=` the hot-word branch runs in
+    `seaco.SeacoParaformerEngine` (bias-encoder LSTM, attention-score filter above 50 hot words, SeACo decoder, merge)."""
 
     _fb200_hotwords = True
     _fb200_empty = ([],)  # model.py:417-418

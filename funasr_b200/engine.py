@@ -324,8 +324,10 @@ class DecoderPack:
         return ids, logp, (logits if want_logits else None)
 
     def hidden(self, enc: torch.Tensor, cu_rows: torch.Tensor, embeds: torch.Tensor, cu_tok: torch.Tensor,
-               max_l: int, enc_split: Optional[torch.Tensor] = None, want_f32: bool = False):
-        """The decoder up to `after_norm` (decoder.py:395-404) -> (hidden fp32 [L, d] or None, its bf16 split)."""
+               max_l: int, enc_split: Optional[torch.Tensor] = None, want_f32: bool = False, query_layer: Optional[int] = None):
+        """The decoder up to `after_norm` (decoder.py:395-404) -> (hidden fp32 [L, d] or None, its bf16 split).
+        With `query_layer` the walk stops at that layer's cross-attention and returns its projected queries and keys in
+        fp32, (q [L, d], k [R, d]) -- `get_attn_mat` (decoder.py:123-137), for the SeACo attention-score filter."""
         dev, np_, d, eps = self.device, self.nparts, self.d, self.eps
         r, l = enc.shape[0], embeds.shape[0]
         bf = torch.bfloat16
@@ -356,8 +358,15 @@ class DecoderPack:
             ops.fsmn(n2, cu_tok, ly.fsmn, y, residual=x)  # x + conv(n2) + n2
             if ly.has_src:
                 ops.layernorm(y, ly.norm3.g, ly.norm3.b, eps, out_split=xs, nparts=np_)
-                ops.gemm(xs, np_, ly.q.w, np_, l, d, d, bias=ly.q.bias, out_split=qs, out_parts=np_)
                 j = self.src_index[li]
+                if li == query_layer:
+                    q32 = torch.empty(l, d, dtype=torch.float32, device=dev)
+                    ops.gemm(xs, np_, ly.q.w, np_, l, d, d, bias=ly.q.bias, out_f32=q32)
+                    k32 = torch.empty(r, d, dtype=torch.float32, device=dev)
+                    ops.gemm(enc_split, np_, self.kv.w[j * 2 * d: j * 2 * d + d], np_, r, d, d, bias=self.kv.bias[j * 2 * d: j * 2 * d + d],
+                             out_f32=k32)
+                    return q32, k32
+                ops.gemm(xs, np_, ly.q.w, np_, l, d, d, bias=ly.q.bias, out_split=qs, out_parts=np_)
                 ops.attention(qs, 0, d, kv, j * 2 * d, kv, j * 2 * d + d, self.kv.n, np_, cu_tok, cu_rows, max_l,
                               self.heads, float(d // self.heads) ** -0.5, out_split=xs, plan=plan)
                 xo = bufs[0] if y is not bufs[0] else bufs[1]

@@ -229,6 +229,14 @@ def us_fires(part, bias, smooth, noise, threshold, cu_rows, upsample, token_num,
               _stream())
 
 
+def asf_scores(q, k, cu_tok, cu_mem, max_words, heads, scale, scores):
+    """Per hot-word row: attention probabilities summed over heads and tokens (fb200_asf_scores); q / k fp32."""
+    _chk(q, torch.float32, "asf_scores")
+    _chk(k, torch.float32, "asf_scores")
+    _lib.call("fb200_asf_scores", _p(q), q.stride(0), _p(k), k.stride(0), _p(cu_tok), _p(cu_mem), cu_tok.numel() - 1, max_words,
+              heads, q.shape[1] // heads, float(scale), _p(scores), _stream())
+
+
 def merge_hotword_ids(dec_ids, dec_logp, hw_ids, hw_logp, no_bias, out_ids, out_logp=None):
     _lib.call("fb200_merge_hotword_ids", _p(dec_ids), _p(dec_logp), _p(hw_ids), _p(hw_logp), int(no_bias), dec_ids.numel(),
               _p(out_ids), _p(out_logp), _stream())

@@ -9,8 +9,8 @@ Per packed batch, when hot words are given:
   SeACo decoder twice, memory = the hot-word embeddings of every utterance `DecoderPack.hidden` (prefix `seaco_decoder.`)
   hotword_output_layer(cif_attended + dec_attended)                        two GEMMs, the second adding the first (linearity)
   `_merge_res`                                                             `fb200_merge_hotword_ids` on the two greedy picks
-More than `nfilter` = 50 hot words would need the reference's attention-score filter (ASF, :268-295): not on this path
-(`recognize` raises; the drop-in sends such calls to the reference's own method).
+With more than `nfilter` = 50 hot words the attention-score filter (ASF, :268-295) first keeps, per utterance, the 50 hot
+words its decoder states attend to most (`fb200_asf_scores` over SeACo layer 5's projected queries / keys, top-k on the host).
 """
 from typing import Dict, List, Optional, Sequence
 
@@ -90,8 +90,8 @@ class SeacoParaformerEngine(BiCifParaformerEngine):
         hw = [list(map(int, w)) for w in hotwords]
         if not hw or hw[-1] != [1]:
             hw.append([1])
-        if len(hw) > NFILTER:
-            raise NotImplementedError("funasr_b200: %d hot words need the reference's ASF filter (more than %d)" % (len(hw), NFILTER))
+        if len(hw) > 2048:
+            raise NotImplementedError("funasr_b200: %d hot words (at most 2048)" % len(hw))
         self.hotwords = hw
 
     def _hot_embeddings(self) -> torch.Tensor:
@@ -113,6 +113,22 @@ class SeacoParaformerEngine(BiCifParaformerEngine):
         memory = ctx.repeat(b, 1)  # every utterance attends to the same hot-word embeddings
         cu_mem = tables.cu_from_lengths([nh] * b, torch.int32, dev)
         mem_split = ops.split_rows(memory, np_)
+        if nh > NFILTER:
+            # attention-score filter (model.py:268-295): per utterance, the NFILTER hot words its decoder states attend to most
+            # in SeACo layer 5, plus the trailing [sos].  (The reference scores utterance 0 of a padded batch for all of them;
+            # this is its batch-1 behaviour.)
+            heads = self.seaco_decoder.heads
+            q32, k32 = self.seaco_decoder.hidden(memory, cu_mem, hidden, cu_tok, max_l, enc_split=mem_split, query_layer=5)
+            scores = torch.empty(b * nh, dtype=torch.float32, device=dev)
+            ops.asf_scores(q32, k32, cu_tok, cu_mem, nh, heads, float(d // heads) ** -0.5, scores)
+            top = torch.topk(scores.cpu().view(b, nh), min(NFILTER, nh - 1), dim=1)[1]  # the reference's own CPU top-k (:274)
+            keep = torch.cat([top, torch.full((b, 1), nh - 1, dtype=top.dtype)], dim=1)  # + the trailing [sos] (:276)
+            memory = ctx.index_select(0, keep.reshape(-1).to(dev))
+            nh = keep.shape[1]
+            cu_mem = tables.cu_from_lengths([nh] * b, torch.int32, dev)
+            mem_split = ops.split_rows(memory, np_)
+            if taps is not None:
+                taps.update(asf_scores=scores.view(b, -1), asf_keep=keep)
         _, cif_att = self.seaco_decoder.hidden(memory, cu_mem, embeds, cu_tok, max_l, enc_split=mem_split)
         _, dec_att = self.seaco_decoder.hidden(memory, cu_mem, hidden, cu_tok, max_l, enc_split=mem_split)
         v = self.hot_output.n

@@ -342,6 +342,13 @@ int fb200_us_fires(const float* part, int nparts, int rows3, float bias, float s
 int fb200_merge_hotword_ids(const int32_t* dec_ids, const float* dec_logp, const int32_t* hw_ids, const float* hw_logp,
                             int no_bias, int n, int32_t* out_ids, float* out_logp, void* stream);
 
+/* SeacoParaformer attention-score filter (funasr/models/seaco_paraformer/model.py:268-274; `get_attn_mat`,
+ * funasr/models/paraformer/decoder.py:123-137): scores[m] = sum over heads and the utterance's tokens of
+ * softmax_m(scale * q_token,head . k_m,head) for the hot-word rows m of utterance b ([cu_mem[b], cu_mem[b+1]), at most 2048).
+ * q f32 [tokens, ld_q], k f32 [rows, ld_k] (projected queries / keys, heads side by side); fixed summation order. */
+int fb200_asf_scores(const float* q, int ld_q, const float* k, int ld_k, const int32_t* cu_tok, const int32_t* cu_mem, int batch,
+                     int max_words, int heads, int head_dim, float scale, float* scores, void* stream);
+
 /* ------------------------------------------------------------------ decoding ----------- */
 
 /* Per row: id = argmax(logits), score = max(log_softmax) -- the greedy branch of

@@ -561,7 +561,7 @@ def test_standalone_seaco_model_has_the_reference_state_dict():
     frontend = dropin.WavFrontend(lfr_m=7, lfr_n=6, dither=0.0)
     with pytest.raises(RuntimeError, match="tokenizer"):  # a hot-word string cannot be looked up without the tokenizer
         model.inference([synth.synth_waveform(0, 16000)], key=["a"], frontend=frontend, hotword="some words")
-    with pytest.raises(NotImplementedError):  # more than 50 hot words: the reference's ASF filter, no reference method here
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
         model.inference([synth.synth_waveform(0, 16000)], key=["a"], frontend=frontend, hotword=[[5 + i] for i in range(60)])
 
 

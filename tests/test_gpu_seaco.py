@@ -94,7 +94,7 @@ def test_keep_branch_matches_reference(seaco_sd, golden):
     assert rel(logp, golden["mixed_top2_logp_0"][:, 0]) < 1e-3
 
 
-def test_matches_oracle_on_another_utterance_and_rejects_long_lists(eng, seaco_sd):
+def test_matches_oracle_on_another_utterance(eng, seaco_sd):
     shift, scale = synth.synth_cmvn()
     cmvn = (torch.from_numpy(shift), torch.from_numpy(scale))
     hot = [[40, 41], [900], [17, 18, 19, 20, 21, 22, 23]]
@@ -102,5 +102,27 @@ def test_matches_oracle_on_another_utterance_and_rejects_long_lists(eng, seaco_s
     ids, stamps = eng.recognize([wave], hotwords=hot)
     want_ids, want_stamps = S.recognize(torch.from_numpy(wave), seaco_sd, cmvn, hotwords=hot + [[1]])
     assert ids[0] == want_ids and stamps[0] == want_stamps
-    with pytest.raises(NotImplementedError):
-        eng.recognize([wave], hotwords=[[5 + i] for i in range(60)])
+
+
+def test_attention_score_filter_matches_reference(eng, golden, seaco_sd):
+    """65 hot words: scores, the kept 50 + [sos] and the merged picks of the reference; in a ragged batch every utterance
+    gets its OWN filter (= the reference's batch-1 results; the oracle is the check for the second utterance)."""
+    flat, lens, hot, o = golden["many_flat"].tolist(), golden["many_len"].tolist(), [], 0
+    for n in lens:
+        hot.append(flat[o: o + n])
+        o += n
+    waves = [synth.synth_waveform(int(golden["seeds"][0]), int(golden["num_samples"][0])), synth.synth_waveform(321, 16000 * 4)]
+    eng.set_hotwords(hot)
+    taps = {}
+    dev_wave, wl = eng.upload(waves)
+    ids, logp, tok, rows, ts = eng.forward_packed_ts(dev_wave, wl, taps=taps)
+    torch.cuda.synchronize()
+    eng.set_hotwords(None)
+    assert rel(taps["asf_scores"][0], golden["many_scores"]) < 1e-4
+    assert taps["asf_keep"][0].tolist() == golden["many_keep"].tolist()
+    n0 = tok[0]
+    assert ids[:n0].cpu().tolist() == golden["many_top2_ids_0"][:, 0].tolist()
+    assert rel(logp[:n0], golden["many_top2_logp_0"][:, 0]) < 1e-3
+    shift, scale = synth.synth_cmvn()
+    want, _ = S.recognize(torch.from_numpy(waves[1]), seaco_sd, (torch.from_numpy(shift), torch.from_numpy(scale)), hotwords=hot)
+    assert [i for i in ids[n0:].cpu().tolist() if i not in (0, 1, 2)] == want
