@@ -411,24 +411,30 @@ extern "C" __attribute__((visibility("default"))) int fb200_fsmn(const float* v,
   FB_CHECK_ARG(residual == nullptr || ld_res % 4 == 0, "fsmn: ld_res must be a multiple of 4");
   if (total_rows == 0) return FB200_OK;
   ProfScope prof(kProfFsmn, stream, (double)total_rows * dim * 4.0 * (residual ? 3.0 : 2.0));
-  if (ksize == 11) {
-    static bool attr_set = false;  // per process; idempotent
-    if (!attr_set) {
-      cudaError_t e = cudaFuncSetAttribute(fsmn_stream_kernel<11>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFsmnSmemBytes);
-      if (e != cudaSuccess) {
-        set_error("fsmn: cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-        return FB200_ECUDA;
-      }
-      attr_set = true;
-    }
+  if (ksize == 11 || ksize == 21) {  // 11: Paraformer / SenseVoice; 21: the SeACo decoder (seaco_paraformer/template.yaml)
     // rows per CTA: 64 when that fills the GPU (two CTAs per SM), fewer for small batches (a CTA walks its rows
-    // serially, so short walks are what keeps a small launch short; the halo re-read grows to (rows + 10) / rows)
+    // serially, so short walks are what keeps a small launch short; the halo re-read grows to (rows + K - 1) / rows)
     int cta_rows = (total_rows + 2 * 148 - 1) / (2 * 148);
     cta_rows = (cta_rows + kFsmnBlock - 1) / kFsmnBlock * kFsmnBlock;
     cta_rows = cta_rows < 16 ? 16 : (cta_rows > kFsmnRows ? kFsmnRows : cta_rows);
     const dim3 grid((total_rows + cta_rows - 1) / cta_rows, (dim + kFsmnCols - 1) / kFsmnCols);
-    fsmn_stream_kernel<11><<<grid, kFsmnThreads, kFsmnSmemBytes, (cudaStream_t)stream>>>(
-        v, ld_v, cu_rows, batch, total_rows, dim, weight, residual, ld_res, out, ld_out, cta_rows);
+#define FSMN_STREAM(KS)                                                                                                      \
+  do {                                                                                                                       \
+    static bool attr_set = false; /* per process; idempotent */                                                              \
+    if (!attr_set) {                                                                                                         \
+      cudaError_t e = cudaFuncSetAttribute(fsmn_stream_kernel<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kFsmnSmemBytes); \
+      if (e != cudaSuccess) {                                                                                                \
+        set_error("fsmn: cudaFuncSetAttribute: %s", cudaGetErrorString(e));                                                  \
+        return FB200_ECUDA;                                                                                                  \
+      }                                                                                                                      \
+      attr_set = true;                                                                                                       \
+    }                                                                                                                        \
+    fsmn_stream_kernel<KS><<<grid, kFsmnThreads, kFsmnSmemBytes, (cudaStream_t)stream>>>(                                    \
+        v, ld_v, cu_rows, batch, total_rows, dim, weight, residual, ld_res, out, ld_out, cta_rows);                          \
+  } while (0)
+    if (ksize == 11) FSMN_STREAM(11);
+    else FSMN_STREAM(21);
+#undef FSMN_STREAM
   }
   else
     fsmn_generic_kernel<<<total_rows, 128, 0, (cudaStream_t)stream>>>(v, ld_v, cu_rows, batch, total_rows, dim, weight,

@@ -151,17 +151,18 @@ def test_fsmn_matches_oracle(with_res):
         o += n
 
 
-@pytest.mark.parametrize("dim", [512, 320, 1024])
-def test_fsmn_streams_across_cta_and_sequence_boundaries(dim):
+@pytest.mark.parametrize("dim,ks", [(512, 11), (320, 11), (1024, 11), (512, 21), (512, 5)])
+def test_fsmn_streams_across_cta_and_sequence_boundaries(dim, ks):
     """64-row CTAs x 512-channel column blocks: sequences that start / end anywhere inside a CTA's rows, a
-    sequence spanning many CTAs, single-row sequences at CTA edges; channel counts below / above one column block."""
+    sequence spanning many CTAs, single-row sequences at CTA edges; channel counts below / above one column block.
+    Kernel 11 (Paraformer) and 21 (the SeACo decoder) stream; other sizes take the generic kernel."""
     lens = [63, 1, 1, 70, 3, 64, 129, 1, 500, 5, 187]
-    g = torch.Generator().manual_seed(dim)
+    g = torch.Generator().manual_seed(dim + ks)
     v = torch.randn(sum(lens), dim, generator=g)
-    w = torch.randn(dim, 1, 11, generator=g) * 0.3
+    w = torch.randn(dim, 1, ks, generator=g) * 0.3
     res = torch.randn(sum(lens), dim, generator=g)
     out = torch.full((sum(lens), dim), float("nan"), device=DEV)
-    ops.fsmn(v.to(DEV), cu(lens), w.reshape(dim, 11).to(DEV), out, residual=res.to(DEV))
+    ops.fsmn(v.to(DEV), cu(lens), w.reshape(dim, ks).to(DEV), out, residual=res.to(DEV))
     o = 0
     for n in lens:
         ref = O.fsmn_memory(v[o: o + n], w) + res[o: o + n]
