@@ -81,13 +81,21 @@ def gather_transcripts(local: dict, world_size: int, rank: int, group=None):
 
 def recognize_sharded(engine, waves, rank: int, world_size: int, group=None):
     """Data-parallel recognition of `waves` (every rank holds or can index all of them): this rank
-    runs its shard through `engine.recognize`, rank 0 returns the token ids of ALL utterances."""
+    runs its shard through `engine.recognize`, rank 0 returns the token ids of ALL utterances -- or (ids, stamps) when
+    the engine has a time-stamp head (`bicif.BiCifParaformerEngine`, `seaco.SeacoParaformerEngine`)."""
     lens = [int(w.shape[0]) for w in waves]
     mine = shard(lens, world_size)[rank]
     out = engine.recognize([waves[i] for i in mine])
-    merged = gather_transcripts({i: ids for i, ids in zip(mine, out)}, world_size, rank, group)
+    paired = isinstance(out, tuple)  # engines with a time-stamp head return (ids, stamps)
+    items = list(zip(*out)) if paired else out
+    merged = gather_transcripts({i: item for i, item in zip(mine, items)}, world_size, rank, group)
     if merged is None:
         return None
+    if paired:
+        n_out = len(out)
+        empty = tuple([] for _ in range(n_out))
+        rows = [merged.get(i, empty) for i in range(len(waves))]
+        return tuple([row[k] for row in rows] for k in range(n_out))
     return [merged[i] for i in range(len(waves))]
 
 

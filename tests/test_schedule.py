@@ -46,15 +46,24 @@ class _FakeEngine:
         return [[int(w.shape[0]) % 97, int(abs(float(w[0])) * 1e6) % 89] for w in waves]
 
 
+class _FakeStampEngine(_FakeEngine):
+    """Stands in for BiCifParaformerEngine: (ids, stamps) per utterance."""
+
+    def recognize(self, waves):
+        ids = super().recognize(waves)
+        return ids, [[[i, i + 10] for i in row] for row in ids]
+
+
 def _worker(rank, world, port, lens, out_path):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     waves = [synth.synth_waveform(i, n) for i, n in enumerate(lens)]
     got = schedule.recognize_sharded(_FakeEngine(), waves, rank, world)
+    got2 = schedule.recognize_sharded(_FakeStampEngine(), waves, rank, world)
     if rank == 0:
-        torch.save(got, out_path)
+        torch.save((got, got2), out_path)
     else:
-        assert got is None
+        assert got is None and got2 is None
     dist.barrier()
     dist.destroy_process_group()
 
@@ -67,9 +76,10 @@ def test_recognize_sharded_two_ranks_gloo(tmp_path):
     lens = [16000, 24000, 700, 52000, 8000, 31000, 399]
     out_path = str(tmp_path / "out.pt")
     mp.spawn(_worker, args=(2, port, lens, out_path), nprocs=2, join=True)
-    got = torch.load(out_path)
+    got, got2 = torch.load(out_path)
     waves = [synth.synth_waveform(i, n) for i, n in enumerate(lens)]
     assert got == _FakeEngine().recognize(waves)
+    assert got2 == _FakeStampEngine().recognize(waves)  # (ids, stamps) of every utterance, in order, on rank 0
 
 
 def test_slice_segments_matches_reference_slicing():
