@@ -308,12 +308,28 @@ class ConformerCTCEngine:
         """CTC-greedy token ids per utterance.  Utterances too short for the input layer (fewer than 7 frames: the
         reference raises TooShortUttError and AutoModel returns no result for them) give []."""
         results: List[List[int]] = [[] for _ in waves]
-        lens_all = [int(w.shape[0]) for w in waves]
-        with torch.cuda.device(self.device):
-            for batch in self.plan_batches(lens_all):
-                wave, lens = self.upload([waves[i] for i in batch])
-                ids, counts, cu_rows, _ = self.forward_packed(wave, lens)
-                ids_h, cnt_h, cu_h = ids.cpu().numpy(), counts.cpu().numpy(), cu_rows.cpu().numpy()
-                for j, i in enumerate(batch):
-                    results[i] = ids_h[cu_h[j]: cu_h[j] + cnt_h[j]].tolist()
+
+        # uploads of batch k + 1 on a copy stream under the kernels of batch k; results read into pinned memory behind an
+        # event and unpacked one batch late (engine.ParaformerEngine.uploaded_batches / read_later)
+        def finish(item):
+            batch, ids_p, cnt_p, cu_p, done = item
+            done.synchronize()
+            ids_h, cnt_h, cu_h = ids_p.numpy(), cnt_p.numpy(), cu_p.numpy()
+            for j, i in enumerate(batch):
+                results[i] = ids_h[cu_h[j]: cu_h[j] + cnt_h[j]].tolist()
+
+        pending = None
+        for batch, wave, lens in self.uploaded_batches(waves):
+            ids, counts, cu_rows, _ = self.forward_packed(wave, lens)
+            cur = (batch, self.read_later(ids), self.read_later(counts), self.read_later(cu_rows), torch.cuda.Event())
+            cur[-1].record()
+            if pending is not None:
+                finish(pending)
+            pending = cur
+        if pending is not None:
+            finish(pending)
         return results
+
+    _copy_stream = None
+    uploaded_batches = ParaformerEngine.uploaded_batches
+    read_later = staticmethod(ParaformerEngine.read_later)
