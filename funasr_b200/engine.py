@@ -613,9 +613,30 @@ class SenseVoiceEngine:
                   ban_ids: Sequence[int] = ()) -> List[List[int]]:
         """CTC-greedy token ids per utterance (blank dropped).  Utterances shorter than one frame give []."""
         results: List[List[int]] = [[] for _ in waves]
-        lens_all = [int(w.shape[0]) for w in waves]
-        _, rows = self.frontend.plan(lens_all)
-        order = sorted(range(len(waves)), key=lambda i: -rows[i])
+
+        def finish(item):
+            batch, ids_p, cnt_p, cu_p, done = item
+            done.synchronize()
+            ids_h, cnt_h, cu_h = ids_p.numpy(), cnt_p.numpy(), cu_p.numpy()
+            for j, i in enumerate(batch):
+                results[i] = ids_h[cu_h[j]: cu_h[j] + cnt_h[j]].tolist()
+
+        pending = None
+        for batch, wave, lens in self.uploaded_batches(waves):  # uploads under the previous batch, results one batch late
+            ids, counts, cu_rows, _ = self.forward_packed(wave, lens, language, textnorm, ban_ids=ban_ids)
+            cur = (batch, self.read_later(ids), self.read_later(counts), self.read_later(cu_rows), torch.cuda.Event())
+            cur[-1].record()
+            if pending is not None:
+                finish(pending)
+            pending = cur
+        if pending is not None:
+            finish(pending)
+        return results
+
+    def plan_batches(self, lens: Sequence[int]) -> List[List[int]]:
+        """Indices grouped longest-first under the packed-row budget (every utterance also carries its 4 prompt rows)."""
+        _, rows = self.frontend.plan(lens)
+        order = sorted(range(len(lens)), key=lambda i: -rows[i])
         batches, cur, cur_rows = [], [], 0
         for i in order:
             if rows[i] < 1:
@@ -628,17 +649,9 @@ class SenseVoiceEngine:
             cur_rows += need
         if cur:
             batches.append(cur)
-        with torch.cuda.device(self.device):
-            for batch in batches:
-                lens = [lens_all[i] for i in batch]
-                wave = torch.empty(sum(lens), dtype=torch.float32, device=self.device)
-                o = 0
-                for i, n in zip(batch, lens):
-                    src = torch.from_numpy(waves[i]) if isinstance(waves[i], np.ndarray) else waves[i]
-                    wave[o: o + n].copy_(src, non_blocking=True)
-                    o += n
-                ids, counts, cu_rows, _ = self.forward_packed(wave, lens, language, textnorm, ban_ids=ban_ids)
-                ids_h, cnt_h, cu_h = ids.cpu().numpy(), counts.cpu().numpy(), cu_rows.cpu().numpy()
-                for j, i in enumerate(batch):
-                    results[i] = ids_h[cu_h[j]: cu_h[j] + cnt_h[j]].tolist()
-        return results
+        return batches
+
+    _copy_stream = None
+    upload = ParaformerEngine.upload
+    uploaded_batches = ParaformerEngine.uploaded_batches
+    read_later = staticmethod(ParaformerEngine.read_later)
