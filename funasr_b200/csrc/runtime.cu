@@ -26,6 +26,7 @@
 #include <sstream>
 #include <string>
 #include <thread>
+#include <tuple>
 #include <vector>
 
 #include "common.cuh"
@@ -125,6 +126,7 @@ static void stamps_from_fires(const int32_t* fire_idx, int n, int num_frames, in
 class Recognizer {
  public:
   ~Recognizer() {
+    for (auto& g : graphs_) cudaGraphExecDestroy(g.second);
     for (void* p : owned_) cudaFree(p);
     if (arena_.base) cudaFree(arena_.base);
     for (int i = 0; i < 2; ++i) {
@@ -180,6 +182,17 @@ class Recognizer {
   Norm dec_after_;
   Linear dec_out_, dec_kv_;
   std::vector<std::string> tokens_;
+  // CUDA graphs of the launch-bound stretch (frontend + encoder + predictor: ~470 launches) for shapes that come back --
+  // a request of one short utterance is bound by the host's launch rate (13 us per launch, 5.6 of 7.7 ms for 10 s of audio),
+  // not by the GPU.  Key = everything the launches' host-side arguments depend on; the per-utterance prefix arrays and the
+  // waveforms live at fixed device addresses for a key and are refreshed outside the graph.  A key is captured the second
+  // time it is seen (the first, eager pass also performs the one-time cudaFuncSetAttribute calls).
+  typedef std::tuple<int, int, int, int, int> GraphKey;  // slot, utterances, frames, rows, longest utterance
+  std::map<GraphKey, cudaGraphExec_t> graphs_;
+  std::map<GraphKey, int> graph_seen_;
+  bool use_graphs_ = true;
+  template <typename F>
+  int run_graphed(const GraphKey& key, bool allowed, F&& issue);
   // CifPredictorV3 time-stamp head (BiCifParaformer), present when the checkpoint holds predictor.blstm.*
   bool has_stamps_ = false;
   Linear ts_up_, ts_proj_;
@@ -351,6 +364,8 @@ int Recognizer::init(const std::string& dir, int device, int nparts, int max_row
   device_ = device;
   np_ = nparts;
   max_rows_ = max_rows;
+  const char* genv = getenv("FB200_RT_GRAPHS");  // FB200_RT_GRAPHS=0: always launch kernel by kernel
+  use_graphs_ = genv == nullptr || atoi(genv) != 0;
   RT_CUDA(cudaSetDevice(device_));
   RT_CUDA(cudaStreamCreate(&stream_));
   RT_CUDA(cudaStreamCreate(&copy_stream_));
@@ -508,6 +523,8 @@ int Recognizer::reserve_wave(size_t samples) {
   if (samples <= wave_cap_) return FB200_OK;
   RT_CUDA(cudaStreamSynchronize(copy_stream_));
   RT_CUDA(cudaStreamSynchronize(stream_));
+  for (auto& g : graphs_) cudaGraphExecDestroy(g.second);  // the captured launches read the old waveform buffers
+  graphs_.clear();
   for (int i = 0; i < 2; ++i) {
     if (dwave_[i]) cudaFree(dwave_[i]);
     dwave_[i] = nullptr;
@@ -530,6 +547,35 @@ int Recognizer::stage(const std::vector<int>& batch, int slot, const float* cons
 
 static double now_ms() {
   return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+template <typename F>
+int Recognizer::run_graphed(const GraphKey& key, bool allowed, F&& issue) {
+  if (!allowed || !use_graphs_) return issue();
+  auto it = graphs_.find(key);
+  if (it != graphs_.end()) {
+    RT_CUDA(cudaGraphLaunch(it->second, stream_));
+    return FB200_OK;
+  }
+  if (++graph_seen_[key] < 2 || graphs_.size() >= 64) return issue();
+  if (cudaStreamBeginCapture(stream_, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+    cudaGetLastError();
+    return issue();
+  }
+  const int rc = issue();
+  cudaGraph_t graph = nullptr;
+  const cudaError_t e = cudaStreamEndCapture(stream_, &graph);
+  cudaGraphExec_t exec = nullptr;
+  if (rc != FB200_OK || e != cudaSuccess || graph == nullptr || cudaGraphInstantiate(&exec, graph, 0) != cudaSuccess) {
+    if (graph) cudaGraphDestroy(graph);
+    cudaGetLastError();
+    use_graphs_ = false;  // something on the stretch cannot be captured here: stay eager from now on
+    return rc != FB200_OK ? rc : issue();
+  }
+  cudaGraphDestroy(graph);
+  graphs_[key] = exec;
+  RT_CUDA(cudaGraphLaunch(exec, stream_));
+  return FB200_OK;
 }
 
 int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens, Result* res, const std::vector<int>* next,
@@ -589,12 +635,13 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   RT_CUDA(cudaMemcpyAsync(d_cus, cu_samples.data(), (B + 1) * 8, cudaMemcpyHostToDevice, stream_));
   RT_CUDA(cudaMemcpyAsync(d_cuf, cu_frames.data(), (B + 1) * 4, cudaMemcpyHostToDevice, stream_));
   RT_CUDA(cudaMemcpyAsync(d_cur, cu_rows.data(), (B + 1) * 4, cudaMemcpyHostToDevice, stream_));
+  const float scale = 1.f / sqrtf((float)(d / heads_));
+  auto issue_encoder = [&]() -> int {
   // frontend + encoder prologue (x * sqrt(d) + PE)
   RT_OK(fb200_fbank(wave, d_cus, d_cuf, B, F, window_, frame_len_, frame_shift_, nfft_, mel_, n_mels_, 32768.f, 0.97f, fb, st));
   RT_OK(fb200_lfr_cmvn(fb, d_cuf, d_cur, B, R, n_mels_, lfr_m_, lfr_n_, shift_, scale_, pe_inv_, sqrtf((float)d), 0, feats, din_, st));
   // encoder
   RT_OK(fb200_attention_plan(d_cur, d_cur, B, plan, plan_cap, st));
-  const float scale = 1.f / sqrtf((float)(d / heads_));
   const float* x = feats;
   int ldx = din_;
   for (const EncLayer& ly : enc_) {
@@ -616,6 +663,9 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   RT_OK(fb200_gemm(halo, R + B + 1, np, cif_conv_.w, np, R + B - 1, d, d, 3, cif_conv_.bias, 1, nullptr, 0, conv, d, 0, nullptr, np, 0, st));
   RT_OK(fb200_cif_alpha(conv, d, d_cur, B, R, d, cif_w_, cif_b_, 1.f, 0.f, alphas, st));
   RT_OK(fb200_cif_scan(alphas, d_cur, B, tail_, token_num, fire_pos, fire_rem, nullptr, st));
+  return FB200_OK;
+  };
+  RT_OK(run_graphed(GraphKey(slot, B, F, R, max_t), next == nullptr, issue_encoder));
   std::vector<int32_t> tok(B), cu_tok(B + 1, 0);
   RT_CUDA(cudaMemcpyAsync(tok.data(), token_num, B * 4, cudaMemcpyDeviceToHost, stream_));
   t_launched = now_ms();

@@ -87,6 +87,35 @@ def test_native_runtime_time_stamps_match_reference_golden(tmp_path, bicif_sd, g
     rec.close()
 
 
+@pytest.mark.gpu
+def test_native_runtime_graph_replay_matches_eager(tmp_path, cmvn, monkeypatch):
+    """Requests whose shape comes back are replayed from a CUDA graph (third call on): same ids as the eager calls, for
+    the same waveform and for ANOTHER waveform of the same length (the graph holds no data of the request), and as a
+    runtime with graphs switched off."""
+    sd = _small_sd()
+    runtime.export_model(sd, str(tmp_path), cmvn=synth.synth_cmvn())
+    a, b = synth.synth_waveform(70, 40000), synth.synth_waveform(71, 40000)
+    monkeypatch.setenv("FB200_RT_GRAPHS", "0")
+    eager = runtime.OfflineRecognizer(str(tmp_path))
+    want_a, want_b = eager.recognize([a])[0], eager.recognize([b])[0]
+    want_pair = eager.recognize([a, b])
+    eager.close()
+    monkeypatch.delenv("FB200_RT_GRAPHS")
+    rec = runtime.OfflineRecognizer(str(tmp_path))
+    for _ in range(4):
+        assert rec.recognize([a])[0] == want_a
+        assert rec.recognize([b])[0] == want_b
+    for _ in range(3):
+        assert rec.recognize([a, b]) == want_pair
+    big = synth.synth_waveform(72, 16000 * 20)  # grows the waveform buffers: the graphs are rebuilt
+    first = rec.recognize([big])[0]
+    for _ in range(3):
+        assert rec.recognize([big])[0] == first
+        assert rec.recognize([a])[0] == want_a
+    assert want_a != want_b
+    rec.close()
+
+
 def _example_binary():
     """examples/offline_recognize, built with g++ against the in-tree library when missing or stale."""
     import subprocess
