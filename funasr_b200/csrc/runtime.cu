@@ -683,7 +683,6 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   if (L == 0 || max_l < 1) return FB200_OK;  // no utterance has a token (paraformer/model.py:514-515)
   RT_CUDA(cudaMemcpyAsync(d_cut, cu_tok.data(), (B + 1) * 4, cudaMemcpyHostToDevice, stream_));
   float* embeds = arena_.get<float>((size_t)L * d);
-  RT_OK(fb200_cif_integrate(enc, d, alphas, d_cur, d_cut, B, L, d, tail_, fire_pos, fire_rem, embeds, d, st));
   // decoder
   const int wkv = np * kp64(dec_kv_.n);
   bf16 *encs = arena_.get<bf16>((size_t)R * wd), *kv = arena_.get<bf16>((size_t)R * wkv), *qs = arena_.get<bf16>((size_t)L * wd),
@@ -700,6 +699,8 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
     set_error("runtime: activation slab too small for %d tokens", L);
     return FB200_EINVAL;
   }
+  auto issue_decoder = [&]() -> int {  // CIF integration + decoder + greedy pick: ~110 launches, graph-replayed like the encoder
+  RT_OK(fb200_cif_integrate(enc, d, alphas, d_cur, d_cut, B, L, d, tail_, fire_pos, fire_rem, embeds, d, st));
   RT_OK(fb200_split_rows(enc, d, R, d, encs, np, st));
   RT_OK(fb200_gemm(encs, R, np, dec_kv_.w, np, R, dec_kv_.n, d, 1, dec_kv_.bias, 0, nullptr, 0, nullptr, 0, 0, kv, np, 0, st));
   RT_OK(fb200_attention_plan(d_cut, d_cur, B, dplan, dplan_cap, st));
@@ -733,6 +734,9 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   RT_OK(fb200_layernorm(y, d, L, d, dec_after_.g, dec_after_.b, eps_, nullptr, 0, ys, np, 0, nullptr, 0, st));
   RT_OK(fb200_gemm(ys, L, np, dec_out_.w, np, L, vocab_, d, 1, dec_out_.bias, 0, nullptr, 0, logits, ldv, 0, nullptr, np, 0, st));
   RT_OK(fb200_argmax_logprob(logits, ldv, L, vocab_, ids, logp, st));
+  return FB200_OK;
+  };
+  RT_OK(run_graphed(GraphKey(slot | 0x100, B, R, L, max_l), next == nullptr, issue_decoder));
   std::vector<int32_t> h_ids(L);
   RT_CUDA(cudaMemcpyAsync(h_ids.data(), ids, (size_t)L * 4, cudaMemcpyDeviceToHost, stream_));
   std::vector<int32_t> h_fire, h_fire_count, h_chars;
