@@ -32,6 +32,7 @@ SIGNATURES = {
     "fb200_lstm_workspace_bytes": [_I, _I, _P],
     "fb200_lstm_parts": [_I, _P],
     "fb200_lstm_bidir": [_P, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, ctypes.c_longlong, _P, _P, _I, _P],
+    "fb200_lstm_bidir_static": [_P, _I, _P, _I, _I, _I, _I, _I, _P, _P, _P, _P, _I, _P],
     "fb200_us_fires": [_P, _I, _I, _F, _F, _F, _F, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P],
     "fb200_asf_scores": [_P, _I, _P, _I, _P, _P, _I, _I, _I, _I, _F, _P, _P],
     "fb200_merge_hotword_ids": [_P, _P, _P, _P, _I, _I, _P, _P, _P],
@@ -63,7 +64,7 @@ RUNTIME_SIGNATURES = {
     "fb200_free_result": ([_P], None),
     "fb200_offline_uninit": ([_P], None),
 }
-EXPORTS = sorted(list(SIGNATURES) + list(RUNTIME_SIGNATURES) + ["fb200_version", "fb200_last_error", "fb200_launch_count",
+EXPORTS = sorted(list(SIGNATURES) + list(RUNTIME_SIGNATURES) + ["fb200_version", "fb200_lstm_static_max_batch", "fb200_last_error", "fb200_launch_count",
                   "fb200_profile_enable", "fb200_profile_read"])
 PROFILE_KINDS = ["fbank", "lfr_cmvn", "scale_add_pe", "layernorm", "split_rows", "fsmn", "gemm", "attention",
                  "cif_alpha", "cif_scan", "cif_integrate", "argmax_logprob", "ctc_collapse", "conv2d_sub1", "glu_dwconv",
@@ -91,6 +92,8 @@ def load():
         fn.argtypes = args
         fn.restype = ret
     lib.fb200_version.restype = c_int
+    lib.fb200_lstm_static_max_batch.argtypes = []
+    lib.fb200_lstm_static_max_batch.restype = c_int
     lib.fb200_last_error.restype = ctypes.c_char_p
     lib.fb200_launch_count.argtypes = [c_int]
     lib.fb200_launch_count.restype = ctypes.c_longlong

@@ -6,6 +6,8 @@
 //   * fb200_us_fires    -- sigmoid / smooth / noise / length scaling of the upsampled alphas (:270-283), the sequential
 //     fp32 integrate-and-fire of `cif_wo_hidden` (:71-93) and the re-normalised second scan of
 //     `ts_prediction_lfr6_standard` (funasr/utils/timestamp_tools.py:46-53), one warp per utterance.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace fb200 {
@@ -537,6 +539,107 @@ extern "C" __attribute__((visibility("default"))) int fb200_lstm_workspace_bytes
 extern "C" __attribute__((visibility("default"))) int fb200_lstm_parts(int hidden, int* parts) {
   FB_CHECK_ARG(parts != nullptr && hidden == fb200::lstm::H, "lstm_parts: hidden size %d unsupported (512 only)", hidden);
   *parts = 2 * fb200::lstm::CTAS;
+  return FB200_OK;
+}
+
+// ---------------------------------------------------------------- fb200_lstm_bidir without any allocation
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): the
+// LSTM's scratch (state double buffer, cell state, step counters) lives in a file-scope device array instead of a
+// caller-provided workspace.  No counterpart in the reference.
+//   * the array is sized for kStaticMaxBatch utterances (6 * 64 * 512 * 4 + 256 = 786 688 bytes); every GPU that loads
+//     the library holds it until the process exits;
+//   * in HOST code `g_lstm_static_scratch` is only a stand-in for the symbol, not a device address: the address is taken
+//     once per device with cudaGetSymbolAddress (that device current) and handed to the kernel through Params;
+//   * every call shares the array and finds the previous call's contents in it: the part the kernel needs at zero is
+//     cleared by a cudaMemsetAsync on the caller's stream ahead of the launch.  Two calls that overlap on the GPU
+//     (different streams, no dependency) race on it.
+namespace fb200 {
+namespace lstm {
+constexpr int kStaticMaxBatch = 64;
+constexpr size_t kStaticScratchBytes = (size_t)6 * kStaticMaxBatch * H * sizeof(float) + 256;
+static __device__ __align__(256) unsigned char g_lstm_static_scratch[kStaticScratchBytes];
+
+constexpr int kStaticMaxDevices = 64;
+static float* s_static_ptr[kStaticMaxDevices] = {};  // per device: address of the array, set once under s_static_mu
+static std::mutex s_static_mu;
+
+// Per-device set-up with that device current: the symbol's address and the kernels' shared-memory opt-in.
+static int static_scratch(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kStaticMaxDevices) {
+    set_error("lstm_bidir_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return FB200_ECUDA;
+  }
+  std::lock_guard<std::mutex> lock(s_static_mu);
+  float* ptr = s_static_ptr[dev];
+  if (ptr == nullptr) {
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_lstm_static_scratch);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(lstm_bidir_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(lstm_bidir_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemMma);
+    if (e != cudaSuccess || sym == nullptr) {
+      set_error("lstm_bidir_static: set-up on device %d: %s", dev, cudaGetErrorString(e));
+      return FB200_ECUDA;
+    }
+    ptr = s_static_ptr[dev] = static_cast<float*>(sym);
+  }
+  *out = ptr;
+  return FB200_OK;
+}
+}  // namespace lstm
+}  // namespace fb200
+
+extern "C" __attribute__((visibility("default"))) int fb200_lstm_static_max_batch(void) { return fb200::lstm::kStaticMaxBatch; }
+
+extern "C" __attribute__((visibility("default"))) int fb200_lstm_bidir_static(
+    const float* xg, int ld_xg, const int32_t* cu_rows, int upsample, int batch, int rows3, int max_len3, int hidden,
+    const float* w_hh, const float* w_out, float* part, float* out_h, int impl, void* stream) {
+  using namespace fb200::lstm;
+  FB_CHECK_ARG(impl == 0 || impl == 1, "lstm_bidir_static: impl must be 0 (tensor cores) or 1 (fp32 SIMT check kernel)");
+  FB_CHECK_ARG(hidden == H, "lstm_bidir_static: hidden size %d unsupported (512 only)", hidden);
+  FB_CHECK_ARG(batch > 0, "lstm_bidir_static: batch %d", batch);
+  FB_CHECK_ARG(batch <= kStaticMaxBatch,
+               "lstm_bidir_static: batch %d exceeds the static scratch (at most %d utterances, %zu bytes); use fb200_lstm_bidir "
+               "with a caller-provided workspace",
+               batch, kStaticMaxBatch, kStaticScratchBytes);
+  FB_CHECK_ARG(upsample >= 1 && ld_xg >= 8 * H, "lstm_bidir_static: upsample %d / ld_xg %d", upsample, ld_xg);
+  float* scratch = nullptr;
+  const int rc = static_scratch(&scratch);
+  if (rc != FB200_OK) return rc;
+  if (rows3 == 0 || max_len3 == 0) return FB200_OK;  // set-up only (e.g. ahead of a graph capture)
+  const size_t need = (size_t)6 * batch * H * sizeof(float) + 256;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e = cudaMemsetAsync(scratch, 0, need, st);  // the last call's state and counters are still in there
+  if (e != cudaSuccess) {
+    set_error("lstm_bidir_static: cudaMemsetAsync: %s", cudaGetErrorString(e));
+    return FB200_ECUDA;
+  }
+  Params p;
+  p.xg = xg;
+  p.ld_xg = ld_xg;
+  p.cu_rows = cu_rows;
+  p.up = upsample;
+  p.batch = batch;
+  p.rows3 = rows3;
+  p.max_len3 = max_len3;
+  p.w_hh = w_hh;
+  p.w_out = w_out;
+  p.hbuf = scratch;
+  p.cbuf = scratch + (size_t)2 * 2 * batch * H;
+  p.counters = reinterpret_cast<unsigned int*>(scratch + (size_t)2 * 2 * batch * H + (size_t)2 * batch * H);
+  p.part = part;
+  p.out_h = out_h;
+  void* args[] = {(void*)&p};
+  if (impl == 0)
+    e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_mma_kernel, dim3(2 * CTAS), dim3(MMA_THREADS), args, kSmemMma, st);
+  else
+    e = cudaLaunchCooperativeKernel((const void*)lstm_bidir_kernel, dim3(2 * CTAS), dim3(THREADS), args, kSmem, st);
+  if (e != cudaSuccess) {
+    set_error("lstm_bidir_static: cooperative launch: %s", cudaGetErrorString(e));
+    return FB200_ECUDA;
+  }
+  count_launch();
   return FB200_OK;
 }
 

@@ -326,6 +326,22 @@ int fb200_lstm_bidir(const float* xg, int ld_xg, const int32_t* cu_rows, int ups
                      int hidden, const float* w_hh, const float* w_out, float* workspace, long long workspace_bytes,
                      float* part, float* out_h, int impl, void* stream);
 
+/* fb200_lstm_bidir for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, kernels and results as fb200_lstm_bidir, minus the workspace: the scratch (state double buffer, cell
+ * state, step counters) is a file-scope device array inside the library, sized for fb200_lstm_static_max_batch() = 64
+ * utterances (786 688 bytes, held by every GPU that loads the library until the process exits).  The call allocates
+ * nothing -- no cudaMalloc / cudaFree, no allocating library routine: it takes the array's device address once per
+ * device (cudaGetSymbolAddress, with that device current), clears the part it needs with cudaMemsetAsync on `stream`
+ * and launches.  batch > 64 is rejected with FB200_EINVAL (use fb200_lstm_bidir).  rows3 == 0 performs the per-device
+ * set-up only (call it once ahead of a graph capture).  Every call shares the one array, which still holds the previous
+ * call's contents: calls that overlap on the GPU (different streams without a dependency, or two threads) RACE --
+ * serialise them on one stream or with events. */
+int fb200_lstm_static_max_batch(void);
+int fb200_lstm_bidir_static(const float* xg, int ld_xg, const int32_t* cu_rows, int upsample, int batch, int rows3,
+                            int max_len3, int hidden, const float* w_hh, const float* w_out, float* part, float* out_h,
+                            int impl, void* stream);
+
 /* alphas2 = relu(sigmoid(bias + sum(part)) * smooth - noise), scaled so each utterance sums to token_num[b]
  * (cif_predictor.py:270-283) -> us_alphas [rows3]; then the sequential fp32 integrate-and-fire of cif_wo_hidden with
  * `threshold` (:71-93) -> us_peaks (optional) and the fired frame indices, relative to the utterance, in fire_idx from
