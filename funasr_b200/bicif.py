@@ -77,6 +77,8 @@ class TimestampPack:
 class BiCifParaformerEngine(ParaformerEngine):
     """BiCifParaformer.inference for packed batches: token ids and [begin ms, end ms] per token."""
 
+    max_utts = 1024  # fb200_lstm_bidir takes at most 1024 utterances per launch (many short VAD segments fit the row budget)
+
     def __init__(self, state_dict, device="cuda:0", precision: str = "fp32", **kw):
         super().__init__(state_dict, device, precision, **kw)
         with torch.cuda.device(self.device):

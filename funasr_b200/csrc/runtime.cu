@@ -13,7 +13,7 @@
 //                 text is the space-separated token ids
 //
 // The op sequence is the one of funasr_b200/engine.py (ParaformerEngine.forward_packed), which cites the reference
-// model code line by line; tests/test_gpu_runtime.py checks that both produce identical token ids.
+// model code line by line; tests/test_runtime.py checks that both produce identical token ids.
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
@@ -187,7 +187,8 @@ class Recognizer {
   // not by the GPU.  Key = everything the launches' host-side arguments depend on; the per-utterance prefix arrays and the
   // waveforms live at fixed device addresses for a key and are refreshed outside the graph.  A key is captured the second
   // time it is seen (the first, eager pass also performs the one-time cudaFuncSetAttribute calls).
-  typedef std::tuple<int, int, int, int, int> GraphKey;  // slot, utterances, frames, rows, longest utterance
+  typedef std::tuple<int, int, int, int, int, int, int> GraphKey;  // slot, utterances, frames, rows, longest utterance, tokens, longest token run
+  // (every arena offset behind the fbank buffer depends on the frame count F through the 256-byte rounding, so BOTH stretches key on F)
   std::map<GraphKey, cudaGraphExec_t> graphs_;
   std::map<GraphKey, int> graph_seen_;
   bool use_graphs_ = true;
@@ -195,6 +196,7 @@ class Recognizer {
   int run_graphed(const GraphKey& key, bool allowed, F&& issue);
   // CifPredictorV3 time-stamp head (BiCifParaformer), present when the checkpoint holds predictor.blstm.*
   bool has_stamps_ = false;
+  static constexpr int kMaxStampBatch = 1024;
   Linear ts_up_, ts_proj_;
   float *ts_whh_ = nullptr, *ts_wout_ = nullptr, ts_bout_ = 0.f;
   int ts_parts_ = 0;
@@ -207,6 +209,9 @@ int Recognizer::load_file(const std::string& path) {
     set_error("runtime: cannot open %s", path.c_str());
     return FB200_EINVAL;
   }
+  f.seekg(0, std::ios::end);
+  const std::streamoff file_bytes = f.tellg();
+  f.seekg(0, std::ios::beg);
   char magic[8];
   uint32_t count = 0;
   f.read(magic, 8);
@@ -225,7 +230,23 @@ int Recognizer::load_file(const std::string& path) {
     HostTensor t;
     t.shape.resize(ndim);
     f.read(reinterpret_cast<char*>(t.shape.data()), 8 * ndim);
-    t.data.resize((size_t)t.numel());
+    // a corrupt header must not turn into a huge or negative allocation: every extent non-negative, the element count
+    // bounded by what is left of the file
+    bool sane = (bool)f && ndim <= 8;
+    unsigned long long numel = 1;
+    for (size_t a = 0; sane && a < t.shape.size(); ++a) {
+      sane = t.shape[a] >= 0 && (t.shape[a] == 0 || numel <= (unsigned long long)file_bytes / (unsigned long long)t.shape[a]);
+      if (sane) numel *= (unsigned long long)t.shape[a];
+    }
+    if (sane) {
+      const std::streamoff at = f.tellg();
+      sane = at >= 0 && numel * 4ull <= (unsigned long long)(file_bytes - at);
+    }
+    if (!sane) {
+      set_error("runtime: %s: bad shape at tensor %u (%s)", path.c_str(), i, name.c_str());
+      return FB200_EINVAL;
+    }
+    t.data.resize((size_t)numel);
     f.read(reinterpret_cast<char*>(t.data.data()), 4 * (std::streamsize)t.data.size());
     if (!f) {
       set_error("runtime: %s is truncated at tensor %u (%s)", path.c_str(), i, name.c_str());
@@ -366,12 +387,12 @@ int Recognizer::init(const std::string& dir, int device, int nparts, int max_row
   max_rows_ = max_rows;
   const char* genv = getenv("FB200_RT_GRAPHS");  // FB200_RT_GRAPHS=0: always launch kernel by kernel
   use_graphs_ = genv == nullptr || atoi(genv) != 0;
+  RT_OK(load_file(dir + "/model.fb200"));  // host only: a bad model directory is reported before any CUDA call
+  load_tokens(dir + "/tokens.json");
   RT_CUDA(cudaSetDevice(device_));
   RT_CUDA(cudaStreamCreate(&stream_));
   RT_CUDA(cudaStreamCreate(&copy_stream_));
   for (int i = 0; i < 2; ++i) RT_CUDA(cudaEventCreateWithFlags(&copied_[i], cudaEventDisableTiming));
-  RT_OK(load_file(dir + "/model.fb200"));
-  load_tokens(dir + "/tokens.json");
   const HostTensor *win = find("frontend.window"), *mel = find("frontend.mel"), *pe = find("frontend.pe_inv");
   const HostTensor* meta = find("frontend.meta");  // [lfr_m, lfr_n, frame_shift, nfft, heads, tail_threshold]
   if (!win || !mel || !pe || !meta || meta->data.size() < 6) {
@@ -429,13 +450,22 @@ int Recognizer::init(const std::string& dir, int device, int nparts, int max_row
   RT_OK(make_norm("encoder.after_norm.", &enc_after_));
   // predictor
   RT_OK(make_linear("predictor.cif_conv1d.weight", "predictor.cif_conv1d.bias", &cif_conv_));
-  RT_OK(upload(find("predictor.cif_output.weight")->data, &cif_w_));
-  RT_OK(upload(find("predictor.cif_output.bias")->data, &cif_b_));
+  const HostTensor *cow = find("predictor.cif_output.weight"), *cob = find("predictor.cif_output.bias");
+  if (!cow || !cob || (int)cow->data.size() < d_ || cob->data.empty()) {
+    set_error("runtime: missing predictor.cif_output.weight / bias");
+    return FB200_EINVAL;
+  }
+  RT_OK(upload(cow->data, &cif_w_));
+  RT_OK(upload(cob->data, &cif_b_));
   if (has("predictor.blstm.weight_hh_l0") && has("predictor.upsample_cnn.weight") && has("predictor.cif_output2.weight")) {
     // bicif_paraformer/cif_predictor.py:139-145: ConvTranspose1d [in, out, k] (stride k) as a GEMM with weight rows (j, o),
     // both directions' input projections stacked, recurrent weights and the Linear(2H -> 1) kept in fp32
     const HostTensor* uw = find("predictor.upsample_cnn.weight");
     const HostTensor* ub = find("predictor.upsample_cnn.bias");
+    if (uw->shape.size() != 3 || !ub) {
+      set_error("runtime: predictor.upsample_cnn.weight must be [in, out, k] with a bias");
+      return FB200_EINVAL;
+    }
     const int cin = (int)uw->shape[0], cout = (int)uw->shape[1], k = (int)uw->shape[2];
     if (k != 3 || cout != 512 || cin != d_) {
       set_error("runtime: time-stamp head with upsample %d / hidden %d unsupported (3 / 512)", k, cout);
@@ -462,8 +492,13 @@ int Recognizer::init(const std::string& dir, int device, int nparts, int max_row
     }
     RT_OK(make_linear_from(wih, 8 * cout, cout, 1, &bih, &ts_proj_));
     RT_OK(upload(whh, &ts_whh_));
-    RT_OK(upload(find("predictor.cif_output2.weight")->data, &ts_wout_));
-    ts_bout_ = find("predictor.cif_output2.bias")->data[0];
+    const HostTensor *o2w = find("predictor.cif_output2.weight"), *o2b = find("predictor.cif_output2.bias");
+    if (!ub || !o2w || !o2b || (int)ub->data.size() < cout || (int)o2w->data.size() < 2 * cout || o2b->data.empty()) {
+      set_error("runtime: incomplete time-stamp head (predictor.upsample_cnn.bias / cif_output2.*)");
+      return FB200_EINVAL;
+    }
+    RT_OK(upload(o2w->data, &ts_wout_));
+    ts_bout_ = o2b->data[0];
     RT_OK(fb200_lstm_parts(cout, &ts_parts_));
     has_stamps_ = true;
   }
@@ -492,6 +527,10 @@ int Recognizer::init(const std::string& dir, int device, int nparts, int max_row
         RT_OK(make_linear(p + "src_attn.linear_q.weight", p + "src_attn.linear_q.bias", &ly.q));
         RT_OK(make_linear(p + "src_attn.linear_out.weight", p + "src_attn.linear_out.bias", &ly.out));
         const HostTensor *w = find(p + "src_attn.linear_k_v.weight"), *b = find(p + "src_attn.linear_k_v.bias");
+        if (!w || !b) {
+          set_error("runtime: missing %ssrc_attn.linear_k_v.weight / bias", p.c_str());
+          return FB200_EINVAL;
+        }
         kvw.insert(kvw.end(), w->data.begin(), w->data.end());
         kvb.insert(kvb.end(), b->data.begin(), b->data.end());
         ly.src_index = n_src++;
@@ -665,7 +704,7 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   RT_OK(fb200_cif_scan(alphas, d_cur, B, tail_, token_num, fire_pos, fire_rem, nullptr, st));
   return FB200_OK;
   };
-  RT_OK(run_graphed(GraphKey(slot, B, F, R, max_t), next == nullptr, issue_encoder));
+  RT_OK(run_graphed(GraphKey(slot, B, F, R, max_t, 0, 0), next == nullptr, issue_encoder));
   std::vector<int32_t> tok(B), cu_tok(B + 1, 0);
   RT_CUDA(cudaMemcpyAsync(tok.data(), token_num, B * 4, cudaMemcpyDeviceToHost, stream_));
   t_launched = now_ms();
@@ -736,7 +775,7 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   RT_OK(fb200_argmax_logprob(logits, ldv, L, vocab_, ids, logp, st));
   return FB200_OK;
   };
-  RT_OK(run_graphed(GraphKey(slot | 0x100, B, R, L, max_l), next == nullptr, issue_decoder));
+  RT_OK(run_graphed(GraphKey(slot | 0x100, B, F, R, max_t, L, max_l), next == nullptr, issue_decoder));
   std::vector<int32_t> h_ids(L);
   RT_CUDA(cudaMemcpyAsync(h_ids.data(), ids, (size_t)L * 4, cudaMemcpyDeviceToHost, stream_));
   std::vector<int32_t> h_fire, h_fire_count, h_chars;
@@ -810,7 +849,8 @@ int Recognizer::recognize(const float* const* waves, const int* lens, int n, Res
       set_error("runtime: an utterance of %d encoder rows exceeds max_rows %d", rows[i], max_rows_);
       return FB200_EINVAL;
     }
-    if (!cur.empty() && cur_rows + rows[i] > max_rows_) {
+    // the time-stamp head's LSTM launch takes at most kMaxStampBatch utterances (fb200_lstm_bidir: batch <= 1024)
+    if (!cur.empty() && (cur_rows + rows[i] > max_rows_ || (has_stamps_ && (int)cur.size() >= kMaxStampBatch))) {
       batches.push_back(cur);
       cur.clear();
       cur_rows = 0;
@@ -853,8 +893,15 @@ RT_API void* fb200_offline_init(const char* model_dir, int device, int precision
     fb200::set_error("offline_init: model_dir / precision (0 = fp32 parity, 1 = bf16)");
     return nullptr;
   }
-  Recognizer* r = new Recognizer();
-  if (r->init(model_dir, device, precision == 0 ? 2 : 1, max_rows > 0 ? max_rows : 18944) != FB200_OK) {
+  Recognizer* r = nullptr;
+  try {
+    r = new Recognizer();
+    if (r->init(model_dir, device, precision == 0 ? 2 : 1, max_rows > 0 ? max_rows : 18944) != FB200_OK) {
+      delete r;
+      return nullptr;
+    }
+  } catch (const std::exception& ex) {  // nothing may unwind through the C boundary
+    fb200::set_error("offline_init: %s", ex.what());
     delete r;
     return nullptr;
   }
@@ -866,8 +913,20 @@ RT_API void* fb200_offline_infer(void* handle, const float* const* waves, const 
     fb200::set_error("offline_infer: bad arguments");
     return nullptr;
   }
-  Result* res = new Result();
-  if (static_cast<Recognizer*>(handle)->recognize(waves, lens, count, res) != FB200_OK) {
+  for (int i = 0; i < count; ++i)
+    if (lens[i] < 0 || (lens[i] > 0 && waves[i] == nullptr)) {
+      fb200::set_error("offline_infer: utterance %d has length %d / a null waveform", i, lens[i]);
+      return nullptr;
+    }
+  Result* res = nullptr;
+  try {
+    res = new Result();
+    if (static_cast<Recognizer*>(handle)->recognize(waves, lens, count, res) != FB200_OK) {
+      delete res;
+      return nullptr;
+    }
+  } catch (const std::exception& ex) {
+    fb200::set_error("offline_infer: %s", ex.what());
     delete res;
     return nullptr;
   }
@@ -880,7 +939,13 @@ RT_API void* fb200_offline_infer_buffer(void* handle, const char* pcm16, int n_b
     return nullptr;
   }
   const int n = n_bytes / 2;
-  std::vector<float> wave(n);
+  std::vector<float> wave;
+  try {
+    wave.resize(n);
+  } catch (const std::exception& ex) {
+    fb200::set_error("offline_infer_buffer: %s", ex.what());
+    return nullptr;
+  }
   const int16_t* s = reinterpret_cast<const int16_t*>(pcm16);
   for (int i = 0; i < n; ++i) wave[i] = (float)s[i] / 32768.f;  // the frontend scales by 1 << 15 again (wav_frontend.py:130)
   const float* w = wave.data();

@@ -451,7 +451,7 @@ class ParaformerEngine:
         for i in order:
             if rows[i] < 1:
                 continue
-            if cur and cur_rows + rows[i] > self.max_rows:
+            if cur and (cur_rows + rows[i] > self.max_rows or (self.max_utts and len(cur) >= self.max_utts)):
                 batches.append(cur)
                 cur, cur_rows = [], 0
             cur.append(i)
@@ -459,6 +459,9 @@ class ParaformerEngine:
         if cur:
             batches.append(cur)
         return batches
+
+    # utterances per batch (None: the row budget alone); engines with a time-stamp head set it to the LSTM launch's limit
+    max_utts = None
 
     def uploaded_batches(self, waves: Sequence[np.ndarray]):
         """Yields (utterance indices, packed device waveforms, sample counts) per planned batch, inside this engine's

@@ -43,16 +43,17 @@ def shard(num_samples: Sequence[int], world_size: int) -> List[List[int]]:
     return out
 
 
-def batches(num_samples: Sequence[int], indices: Sequence[int], max_rows: int) -> List[List[int]]:
-    """Indices (into `num_samples`) grouped longest-first under the packed-row budget; utterances
-    shorter than one frame are left out (they produce no tokens)."""
+def batches(num_samples: Sequence[int], indices: Sequence[int], max_rows: int, max_utts: int = 0) -> List[List[int]]:
+    """Indices (into `num_samples`) grouped longest-first under the packed-row budget (and at most `max_utts`
+    utterances per batch when given: 1024 for engines with a time-stamp head); utterances shorter than one frame are
+    left out (they produce no tokens)."""
     rows = {i: encoder_rows(int(num_samples[i])) for i in indices}
     order = sorted(indices, key=lambda i: (-rows[i], i))
     out, cur, cur_rows = [], [], 0
     for i in order:
         if rows[i] < 1:
             continue
-        if cur and cur_rows + rows[i] > max_rows:
+        if cur and (cur_rows + rows[i] > max_rows or (max_utts and len(cur) >= max_utts)):
             out.append(cur)
             cur, cur_rows = [], 0
         cur.append(i)
@@ -62,41 +63,115 @@ def batches(num_samples: Sequence[int], indices: Sequence[int], max_rows: int) -
     return out
 
 
-def gather_transcripts(local: dict, world_size: int, rank: int, group=None):
-    """Collect {utterance index: token ids} from every rank on rank 0 (the path's only collective:
-    a few hundred KB, latency-bound).  Returns the merged dict on rank 0, None elsewhere."""
+def _encode_items(local: dict) -> "np.ndarray":
+    """{utterance index: ids | (ids, stamps)} -> int32 [1 + sum(3 + len(ids) + 2 len(stamps))]:
+    count, then per utterance: index, n_ids, n_stamps, ids..., begin/end pairs..."""
+    import numpy as np
+
+    flat = [len(local)]
+    for index, item in local.items():
+        ids, stamps = (item[0], item[1]) if isinstance(item, tuple) else (item, None)
+        flat += [int(index), len(ids), -1 if stamps is None else len(stamps)]
+        flat += [int(t) for t in ids]
+        if stamps is not None:
+            for b, e in stamps:
+                flat += [int(b), int(e)]
+    return np.asarray(flat, dtype=np.int32)
+
+
+def _decode_items(buf) -> dict:
+    out, n, o = {}, int(buf[0]), 1
+    for _ in range(n):
+        index, n_ids, n_st = int(buf[o]), int(buf[o + 1]), int(buf[o + 2])
+        o += 3
+        ids = [int(t) for t in buf[o: o + n_ids]]
+        o += n_ids
+        if n_st < 0:
+            out[index] = ids
+        else:
+            out[index] = (ids, [[int(buf[o + 2 * k]), int(buf[o + 2 * k + 1])] for k in range(n_st)])
+            o += 2 * n_st
+    return out
+
+
+def payload_capacity(num_samples: Sequence[int], world_size: int, with_stamps: bool = False) -> int:
+    """int32 slots per rank of the transcript gather, from the plan alone (every rank computes the same number, nothing
+    is exchanged): an utterance of T encoder rows has at most T + 1 tokens (the CIF tail frame)."""
+    per_tok = 3 if with_stamps else 1
+    cap = 1
+    for mine in shard(num_samples, world_size):
+        cap = max(cap, 1 + sum(3 + per_tok * (encoder_rows(int(num_samples[i])) + 1) for i in mine))
+    return cap
+
+
+def gather_transcripts(local: dict, world_size: int, rank: int, group=None, capacity: int = 0, device=None, stats=None):
+    """Collect {utterance index: token ids (or (ids, stamps))} from every rank on rank 0 -- the path's only collective
+    (SURVEY.md 8e): ONE all_gather of a fixed-size int32 buffer per rank (ids + lengths, a few hundred KB in total) over
+    NCCL (device buffers) or gloo (host buffers, the CPU tests).  `capacity` = int32 slots per rank (payload_capacity());
+    0: agreed on first with one MAX all-reduce.  Returns the merged dict on rank 0, None elsewhere."""
     if world_size == 1:
         return dict(local)
+    import numpy as np
+    import torch
     import torch.distributed as dist
 
-    bucket = [None] * world_size if rank == 0 else None
-    dist.gather_object(local, bucket, dst=0, group=group)
+    flat = _encode_items(local)
+    dev = torch.device(device) if device is not None else torch.device("cpu")
+    if capacity <= 0:
+        need = torch.tensor([flat.size], dtype=torch.int64, device=dev)
+        dist.all_reduce(need, op=dist.ReduceOp.MAX, group=group)
+        capacity = int(need.item())
+    if flat.size > capacity:
+        raise RuntimeError("gather_transcripts: %d int32 slots needed, capacity %d" % (flat.size, capacity))
+    host = torch.zeros(capacity, dtype=torch.int32, pin_memory=dev.type == "cuda")
+    host[: flat.size] = torch.from_numpy(flat)
+    mine = host.to(dev, non_blocking=True)
+    everyone = torch.empty(world_size * capacity, dtype=torch.int32, device=dev)
+    dist.all_gather(list(everyone.view(world_size, capacity).unbind(0)), mine, group=group)
+    if stats is not None:
+        stats["gather_bytes"] = int(world_size * capacity * 4)
     if rank != 0:
         return None
     merged = {}
-    for part in bucket:
-        merged.update(part)
+    table = everyone.cpu().numpy().reshape(world_size, capacity)
+    for r in range(world_size):
+        merged.update(_decode_items(table[r]))
     return merged
 
 
-def recognize_sharded(engine, waves, rank: int, world_size: int, group=None):
-    """Data-parallel recognition of `waves` (every rank holds or can index all of them): this rank
-    runs its shard through `engine.recognize`, rank 0 returns the token ids of ALL utterances -- or (ids, stamps) when
-    the engine has a time-stamp head (`bicif.BiCifParaformerEngine`, `seaco.SeacoParaformerEngine`)."""
+def recognize_sharded(engine, waves, rank: int, world_size: int, group=None, stats=None):
+    """Data-parallel recognition of `waves` (every rank holds or can index all of them; entries of other ranks' shards may
+    be None as long as `lens` can be told -- pass objects with `.shape`): this rank runs its shard through
+    `engine.recognize`, rank 0 returns the token ids of ALL utterances -- or (ids, stamps) when the engine has a
+    time-stamp head (`bicif.BiCifParaformerEngine`, `seaco.SeacoParaformerEngine`)."""
+    import time
+
     lens = [int(w.shape[0]) for w in waves]
     mine = shard(lens, world_size)[rank]
+    t0 = time.perf_counter()
     out = engine.recognize([waves[i] for i in mine])
+    t1 = time.perf_counter()
     paired = isinstance(out, tuple)  # engines with a time-stamp head return (ids, stamps)
     items = list(zip(*out)) if paired else out
-    merged = gather_transcripts({i: item for i, item in zip(mine, items)}, world_size, rank, group)
+    local = {i: ((list(item[0]), list(item[1])) if paired else list(item)) for i, item in zip(mine, items)}
+    dev = getattr(engine, "device", None)
+    use_dev = dev if (dev is not None and world_size > 1 and _backend(group) == "nccl") else None
+    merged = gather_transcripts(local, world_size, rank, group, payload_capacity(lens, world_size, paired), use_dev, stats)
+    if stats is not None:  # host clocks around this rank's share and the gather (diagnostics for bench.py)
+        stats.setdefault("local_ms", []).append((t1 - t0) * 1e3)
+        stats.setdefault("gather_ms", []).append((time.perf_counter() - t1) * 1e3)
     if merged is None:
         return None
     if paired:
-        n_out = len(out)
-        empty = tuple([] for _ in range(n_out))
-        rows = [merged.get(i, empty) for i in range(len(waves))]
-        return tuple([row[k] for row in rows] for k in range(n_out))
-    return [merged[i] for i in range(len(waves))]
+        rows = [merged.get(i, ([], [])) for i in range(len(waves))]
+        return tuple([row[k] for row in rows] for k in range(2))
+    return [merged.get(i, []) for i in range(len(waves))]
+
+
+def _backend(group=None) -> str:
+    import torch.distributed as dist
+
+    return str(dist.get_backend(group)) if dist.is_initialized() else ""
 
 
 def slice_segments(speech, segments_ms):

@@ -1,8 +1,9 @@
 """Import the UNMODIFIED reference (`/root/reference`, read-only) in this container.
 
-Only used by `tests/golden/make_golden.py` (fixture generation) and by the optional
-CPU-side cross-checks that skip when `/root/reference` is absent (it does not exist on
-the GPU box).  Four third-party modules the reference imports at package-import time are
+Used by `tests/golden/make_golden*.py` (fixture generation), by the tests that drive the reference's own
+`AutoModel` (CPU cross-checks here; on the GPU box the drop-in test and the large-sample parity gate) and by
+`bench.py --impl reference`.  `/root/reference` does not exist on the GPU box: there the unmodified copy under
+`oracle/_ref/pyref` (written by `make -C oracle`, git-ignored) is imported instead.  Four third-party modules the reference imports at package-import time are
 not installed here (omegaconf, hydra, kaldiio, librosa); none is touched on the offline
 Paraformer path when the config is passed inline, so empty stubs are injected
 (SURVEY.md section 8c, Appendix A).
@@ -11,7 +12,12 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = os.environ.get("FUNASR_REFERENCE_ROOT", "/root/reference")
+_HERE = os.path.dirname(os.path.abspath(__file__))
+# /root/reference in the build container; on the GPU box the unmodified copy that `make -C oracle` put under
+# oracle/_ref/pyref (git-ignored, travels with the snapshot)
+_CANDIDATES = [os.environ.get("FUNASR_REFERENCE_ROOT", ""), "/root/reference",
+               os.path.join(os.path.dirname(os.path.dirname(_HERE)), "oracle", "_ref", "pyref")]
+REFERENCE_ROOT = next((c for c in _CANDIDATES if c and os.path.isdir(os.path.join(c, "funasr"))), "/root/reference")
 
 
 def reference_available() -> bool:

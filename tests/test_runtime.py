@@ -116,6 +116,71 @@ def test_native_runtime_graph_replay_matches_eager(tmp_path, cmvn, monkeypatch):
     rec.close()
 
 
+@pytest.mark.gpu
+def test_native_runtime_graph_replay_same_rows_other_frame_count(tmp_path, cmvn, monkeypatch):
+    """Two request shapes with the SAME encoder rows, token counts apart or not, but different fbank frame counts
+    (40000 vs 40160 samples: F = 248 / 249, R = 42 both): the activation layout behind the fbank buffer depends on F, so a
+    decoder graph captured for one must never be replayed for the other (both graphs key on F)."""
+    sd = _small_sd()
+    runtime.export_model(sd, str(tmp_path), cmvn=synth.synth_cmvn())
+    a, b = synth.synth_waveform(73, 40000), synth.synth_waveform(73, 40160)
+    b[:40000] = a  # same audio plus 10 ms: most likely the same token count as well
+    monkeypatch.setenv("FB200_RT_GRAPHS", "0")
+    eager = runtime.OfflineRecognizer(str(tmp_path))
+    want_a, want_b = eager.recognize([a])[0], eager.recognize([b])[0]
+    eager.close()
+    monkeypatch.delenv("FB200_RT_GRAPHS")
+    rec = runtime.OfflineRecognizer(str(tmp_path))
+    for _ in range(4):  # graphs captured on the second sighting, replayed afterwards, the two shapes alternating
+        assert rec.recognize([a])[0] == want_a
+        assert rec.recognize([b])[0] == want_b
+    rec.close()
+
+
+@pytest.mark.gpu
+def test_native_runtime_more_than_1024_short_utterances_with_stamps(tmp_path):
+    """A time-stamp model directory and 1100 half-second utterances: they fit one packed batch by rows (9 rows each), but the
+    LSTM launch takes at most 1024 utterances -- the batcher must cut there instead of failing after the ids were computed."""
+    shapes = params.bicif_paraformer_shapes(enc_blocks=2, dec_blocks=1)
+    sd = synth.synth_state_dict(shapes, seed=0)
+    runtime.export_model(sd, str(tmp_path), cmvn=synth.synth_cmvn())
+    rec = runtime.OfflineRecognizer(str(tmp_path))
+    base = [synth.synth_waveform(200 + i, 8000) for i in range(4)]
+    waves = [base[i % 4] for i in range(1100)]
+    ids, stamps = rec.recognize(waves, with_stamps=True)
+    want_ids, want_stamps = rec.recognize(base, with_stamps=True)
+    rec.close()
+    assert len(ids) == 1100
+    for i in range(1100):
+        assert ids[i] == want_ids[i % 4] and stamps[i] == want_stamps[i % 4]
+    from funasr_b200 import bicif
+
+    eng = bicif.BiCifParaformerEngine({k: torch.from_numpy(v) for k, v in sd.items()}, "cuda:0", "fp32",
+                                      cmvn=tuple(torch.from_numpy(x) for x in synth.synth_cmvn()))
+    assert max(len(b) for b in eng.plan_batches([8000] * 1100)) <= 1024
+    e_ids, e_stamps = eng.recognize(waves)
+    assert e_ids == ids and e_stamps == stamps
+
+
+def test_corrupt_model_file_is_rejected_not_fatal(tmp_path):
+    """Header fields of model.fb200 are validated: a negative or absurd extent gives an error string, not an exception
+    through the C boundary (std::terminate)."""
+    sd = _small_sd()
+    path = runtime.export_model(sd, str(tmp_path), cmvn=synth.synth_cmvn())
+    raw = bytearray(open(path, "rb").read())
+    (nlen,) = struct.unpack("<H", raw[12:14])
+    at = 14 + nlen  # ndim byte of the first tensor, then int64 extents
+    for bad in (-5, 1 << 40):
+        broken = bytearray(raw)
+        broken[at + 1: at + 9] = struct.pack("<q", bad)
+        d = tmp_path / ("bad%d" % (bad > 0))
+        d.mkdir()
+        open(d / "model.fb200", "wb").write(bytes(broken))
+        lib = _lib.load()
+        assert not lib.fb200_offline_init(str(d).encode(), 0, 0, 0)
+        assert "bad shape" in lib.fb200_last_error().decode()
+
+
 def _example_binary():
     """examples/offline_recognize, built with g++ against the in-tree library when missing or stale."""
     import subprocess

@@ -82,6 +82,24 @@ def test_recognize_sharded_two_ranks_gloo(tmp_path):
     assert got2 == _FakeStampEngine().recognize(waves)  # (ids, stamps) of every utterance, in order, on rank 0
 
 
+def test_transcript_payload_round_trip_and_capacity():
+    """The gather's int32 payload: plain id lists and (ids, stamps) pairs survive encode/decode; the capacity computed
+    from the plan alone bounds every rank's payload (tokens <= rows + 1 per utterance)."""
+    local = {5: [3, 9, 4], 0: [], 7: [8404 - 1]}
+    assert schedule._decode_items(schedule._encode_items(local)) == local
+    paired = {2: ([5, 6], [[0, 120], [130, 300]]), 9: ([], [])}
+    assert schedule._decode_items(schedule._encode_items(paired)) == paired
+    lens = [16000, 24000, 700, 52000, 8000, 31000, 399]
+    for world in (1, 2, 3):
+        for stamped in (False, True):
+            cap = schedule.payload_capacity(lens, world, stamped)
+            for mine in schedule.shard(lens, world):
+                full = {i: [1] * (schedule.encoder_rows(lens[i]) + 1) for i in mine}
+                if stamped:
+                    full = {i: (v, [[0, 1]] * len(v)) for i, v in full.items()}
+                assert schedule._encode_items(full).size <= cap
+
+
 def test_slice_segments_matches_reference_slicing():
     speech = np.arange(16000 * 3, dtype=np.float32)
     segs = [[0, 500], [480, 1999], [2500, 3500], [100, 100]]
