@@ -77,6 +77,7 @@ class TimestampPack:
 class BiCifParaformerEngine(ParaformerEngine):
     """BiCifParaformer.inference for packed batches: token ids and [begin ms, end ms] per token."""
 
+    RETURNS_ARRAYS = False  # recognize() here returns (id lists, time-stamp lists)
     max_utts = 1024  # fb200_lstm_bidir takes at most 1024 utterances per launch (many short VAD segments fit the row budget)
 
     def __init__(self, state_dict, device="cuda:0", precision: str = "fp32", **kw):

@@ -490,7 +490,9 @@ class ParaformerEngine:
                     nxt = start_upload(batches[bi + 1])
                 yield batch, wave, lens
 
-    def recognize(self, waves: Sequence[np.ndarray], with_scores: bool = False):
+    RETURNS_ARRAYS = True  # recognize(as_arrays=True): int32 arrays instead of lists (schedule.recognize_sharded's payload)
+
+    def recognize(self, waves: Sequence[np.ndarray], with_scores: bool = False, as_arrays: bool = False):
         """Token ids per utterance (sos/eos/blank dropped).  Utterances shorter than one frame or
         with no predicted token give [] (model.py:514-515)."""
         results: List[List[int]] = [[] for _ in waves]
@@ -507,7 +509,8 @@ class ParaformerEngine:
             o = 0
             for i, n in zip(batch, tok):
                 self.last_token_num[i] = int(n)
-                results[i] = ids_h[o: o + n][keep[o: o + n]].tolist()
+                row = ids_h[o: o + n][keep[o: o + n]]
+                results[i] = row if as_arrays else row.tolist()
                 if with_scores:
                     scores[i] = float(logp_h[o: o + n].sum())
                 o += n

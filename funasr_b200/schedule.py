@@ -64,33 +64,41 @@ def batches(num_samples: Sequence[int], indices: Sequence[int], max_rows: int, m
 
 
 def _encode_items(local: dict) -> "np.ndarray":
-    """{utterance index: ids | (ids, stamps)} -> int32 [1 + sum(3 + len(ids) + 2 len(stamps))]:
-    count, then per utterance: index, n_ids, n_stamps, ids..., begin/end pairs..."""
+    """{utterance index: ids | (ids, stamps)} -> int32 payload: [n, index[n], n_ids[n], n_stamps[n] (-1: no stamps), every
+    utterance's ids back to back, every utterance's (begin, end) pairs back to back] -- 3 n + 1 header slots, then one slot
+    per token and two per stamp.  Built with numpy (a Python loop over 10^5 tokens costs more than the collective)."""
     import numpy as np
 
-    flat = [len(local)]
-    for index, item in local.items():
-        ids, stamps = (item[0], item[1]) if isinstance(item, tuple) else (item, None)
-        flat += [int(index), len(ids), -1 if stamps is None else len(stamps)]
-        flat += [int(t) for t in ids]
-        if stamps is not None:
-            for b, e in stamps:
-                flat += [int(b), int(e)]
-    return np.asarray(flat, dtype=np.int32)
+    n = len(local)
+    index = np.fromiter(local.keys(), dtype=np.int32, count=n)
+    paired = [isinstance(v, tuple) for v in local.values()]
+    ids = [np.asarray(v[0] if p else v, dtype=np.int32).reshape(-1) for v, p in zip(local.values(), paired)]
+    stamps = [np.asarray(v[1], dtype=np.int32).reshape(-1) if p else np.empty(0, np.int32) for v, p in zip(local.values(), paired)]
+    n_ids = np.fromiter((a.size for a in ids), dtype=np.int32, count=n)
+    n_st = np.fromiter((a.size // 2 if p else -1 for a, p in zip(stamps, paired)), dtype=np.int32, count=n)
+    return np.concatenate([np.asarray([n], np.int32), index, n_ids, n_st] + ids + stamps)
 
 
 def _decode_items(buf) -> dict:
-    out, n, o = {}, int(buf[0]), 1
-    for _ in range(n):
-        index, n_ids, n_st = int(buf[o]), int(buf[o + 1]), int(buf[o + 2])
-        o += 3
-        ids = [int(t) for t in buf[o: o + n_ids]]
-        o += n_ids
-        if n_st < 0:
-            out[index] = ids
+    import numpy as np
+
+    buf = np.asarray(buf)
+    n = int(buf[0])
+    used = 1 + 3 * n + int(buf[1 + n: 1 + 2 * n].sum()) + 2 * int(np.maximum(buf[1 + 2 * n: 1 + 3 * n], 0).sum())
+    flat = buf[:used].tolist()  # ONE conversion of the used prefix (the buffer is capacity-sized); list slices from here on
+    index, n_ids, n_st = flat[1: 1 + n], flat[1 + n: 1 + 2 * n], flat[1 + 2 * n: 1 + 3 * n]
+    o = 1 + 3 * n
+    so = o + sum(n_ids)
+    out = {}
+    for k in range(n):
+        ids = flat[o: o + n_ids[k]]
+        o += n_ids[k]
+        if n_st[k] < 0:
+            out[index[k]] = ids
         else:
-            out[index] = (ids, [[int(buf[o + 2 * k]), int(buf[o + 2 * k + 1])] for k in range(n_st)])
-            o += 2 * n_st
+            e = so + 2 * n_st[k]
+            out[index[k]] = (ids, [flat[t: t + 2] for t in range(so, e, 2)])
+            so = e
     return out
 
 
@@ -149,11 +157,13 @@ def recognize_sharded(engine, waves, rank: int, world_size: int, group=None, sta
     lens = [int(w.shape[0]) for w in waves]
     mine = shard(lens, world_size)[rank]
     t0 = time.perf_counter()
-    out = engine.recognize([waves[i] for i in mine])
+    # engines that can hand the ids over as int32 arrays do (no Python list per utterance on the way into the payload)
+    kw = {"as_arrays": True} if getattr(engine, "RETURNS_ARRAYS", False) else {}
+    out = engine.recognize([waves[i] for i in mine], **kw)
     t1 = time.perf_counter()
     paired = isinstance(out, tuple)  # engines with a time-stamp head return (ids, stamps)
     items = list(zip(*out)) if paired else out
-    local = {i: ((list(item[0]), list(item[1])) if paired else list(item)) for i, item in zip(mine, items)}
+    local = {i: ((item[0], item[1]) if paired else item) for i, item in zip(mine, items)}
     dev = getattr(engine, "device", None)
     use_dev = dev if (dev is not None and world_size > 1 and _backend(group) == "nccl") else None
     merged = gather_transcripts(local, world_size, rank, group, payload_capacity(lens, world_size, paired), use_dev, stats)
