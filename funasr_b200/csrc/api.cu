@@ -1,5 +1,6 @@
 // Library-level entry points: version, thread-local error text, launch counter.
 #include <stdarg.h>
+#include <stdlib.h>
 
 #include <vector>
 
@@ -16,6 +17,14 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 void count_launch(int n) { g_launches += n; }
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("FB200_PDL");
+    return e == nullptr || atoi(e) != 0;
+  }();
+  return on;
+}
 
 // ---- optional per-entry-point device timing (CUDA events on the caller's stream) ----------
 struct ProfRec {

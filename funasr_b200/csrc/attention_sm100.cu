@@ -146,9 +146,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                          const __grid_constant__ CUtensorMap map_v, const __grid_constant__ CUtensorMap map_o,
                          const AttnParams p) {
-  const int n_items = p.plan[0] * p.heads;
-  if ((int)blockIdx.x >= n_items) return;
-
   constexpr uint32_t kKBlk = TK * 128;           // one 64-column block of a K / V tile (bytes)
   constexpr uint32_t kKBytes = NP * 2 * kKBlk;   // one stage: all parts, both column blocks
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -224,8 +221,15 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
   const uint32_t tmem_o = tmem_base + kTmemO, tmem_q = tmem_base + kTmemQ;
   auto tmem_s = [&](int i) { return tmem_base + kTmemS + 64u * i; };  // fp32 scores of a tile: 64 columns
   auto tmem_p = [&](int i) { return tmem_base + kTmemP + 64u * i; };  // bf16 pairs: 32 columns per part
+  // Everything above (barriers, tensor memory, descriptor prefetch) ran under the previous kernel's tail; the plan, Q, K
+  // and V are other kernels' outputs and are visible from here on.
+  pdl_trigger();  // after the tensor-memory allocation (see gemm_sm100.cu): the next kernel's CTAs may be scheduled now
+  pdl_wait();
+  const int n_items = p.plan[0] * p.heads;
+  const bool idle = (int)blockIdx.x >= n_items;  // CTA-uniform: nothing to do but hand the tensor memory back
 
-  if (warp >= 8) {
+  if (idle) {
+  } else if (warp >= 8) {
     asm volatile("setmaxnreg.dec.sync.aligned.u32 88;");
     if (warp == 8 || warp == 11) {
     // ------------------------------------------------------------------ TMA producers -----

@@ -46,6 +46,47 @@ class ProfScope {
     fb200::count_launch();                                                           \
   } while (0)
 
+// ---- programmatic dependent launch (PDL) ------------------------------------------------------------------------
+// The path is ~26 000 short launches per 1024-utterance step: back to back on one stream, each kernel used to start
+// only after the previous one had drained and its completion had travelled through the front end.  Kernels launched
+// through launch_pdl() carry cudaLaunchAttributeProgrammaticStreamSerialization: the NEXT kernel's CTAs are scheduled
+// as soon as every CTA of the current one has executed pdl_trigger() (all of them do so first thing), run their
+// prologue (barrier init, tensor-memory allocation, descriptor prefetch, static weight loads) under the current
+// kernel's tail, and block in pdl_wait() until the current kernel has completed and its writes are visible.
+// RULE: a kernel launched with launch_pdl() executes pdl_wait() in every thread before it reads or writes any memory
+// another kernel of the stream may write (only launch parameters and static weights may be touched before it).
+// FB200_PDL=0 in the environment launches everything fully serialised (the instructions are then no-ops).
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+bool pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, void* stream, int cluster_x,
+                              Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[2];
+  unsigned n = 0;
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = (unsigned)cluster_x;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 constexpr int kWarp = 32;
 
 __device__ __forceinline__ float warp_sum(float v) {

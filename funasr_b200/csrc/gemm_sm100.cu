@@ -164,6 +164,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   tcgen05_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+  // Everything above ran under the previous kernel's tail.  The trigger comes AFTER the tensor-memory allocation: a CTA
+  // of the next kernel that lands on this SM must find this CTA's columns already taken (it would otherwise hold them while
+  // blocked in its own pdl_wait, and a CTA of THIS grid still waiting for columns would never get them).
+  pdl_trigger();
+  pdl_wait();  // the previous kernels' outputs (A, the residual) are visible from here
 
   if (warp == 0) {
     if (elect_one()) {  // ===== TMA producer =====

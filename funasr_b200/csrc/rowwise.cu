@@ -15,6 +15,8 @@ layernorm_kernel(const float* __restrict__ x, int ld_x, int rows, int dim, const
                  const float* __restrict__ beta, float eps, float* __restrict__ out_f32, int ld_f32,
                  __nv_bfloat16* __restrict__ out_split, int nparts, int halo,
                  const int32_t* __restrict__ cu_rows, int batch) {
+  pdl_trigger();
+  pdl_wait();  // x comes from the previous kernel
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row = blockIdx.x * kLnWarps + warp;
   if (row >= rows) return;
@@ -90,6 +92,8 @@ layernorm_kernel(const float* __restrict__ x, int ld_x, int rows, int dim, const
 __global__ void split_rows_kernel(const float* __restrict__ x, int ld_x, int rows, int dim,
                                   __nv_bfloat16* __restrict__ out, int nparts, const int32_t* __restrict__ cu_rows,
                                   int batch) {
+  pdl_trigger();
+  pdl_wait();
   const int kp = round_up(dim, 64);
   const size_t total = (size_t)rows * kp;
   const size_t ld = (size_t)nparts * kp;
@@ -129,6 +133,8 @@ fsmn_stream_kernel(const float* __restrict__ v, int ld_v, const int32_t* __restr
                    int ld_res, float* __restrict__ out, int ld_out, int cta_rows) {
   constexpr int LEFT = (KS - 1) / 2;
   constexpr uint32_t FULL = (1u << KS) - 1u;
+  pdl_trigger();
+  pdl_wait();  // v and the residual come from the previous kernels
   extern __shared__ __align__(128) uint8_t fsmn_smem[];
   __shared__ uint32_t s_mask[kFsmnRows];  // bit j: tap j of this output row lies inside its sequence
   __shared__ __align__(8) uint64_t s_bar[2 * kFsmnStages];
@@ -362,8 +368,8 @@ extern "C" __attribute__((visibility("default"))) int fb200_layernorm(const floa
   cudaStream_t st = (cudaStream_t)stream;
   __nv_bfloat16* sp = (__nv_bfloat16*)out_split;
 #define LN_LAUNCH(NV)                                                                                            \
-  layernorm_kernel<NV><<<grid, kLnWarps * 32, 0, st>>>(x, ld_x, rows, dim, gamma, beta, eps, out_f32, ld_f32, sp, \
-                                                       nparts, halo, cu_rows, batch)
+  launch_pdl(layernorm_kernel<NV>, dim3(grid), dim3(kLnWarps * 32), 0, st, 1, x, ld_x, rows, dim, gamma, beta, eps, out_f32, \
+             ld_f32, sp, nparts, halo, cu_rows, batch)
   if (dim <= 512) LN_LAUNCH(4);
   else if (dim <= 640) LN_LAUNCH(5);
   else LN_LAUNCH(16);
@@ -380,8 +386,8 @@ static int split_rows_impl(const float* x, int ld_x, int rows, int dim, void* ou
   const size_t total = (size_t)rows * round_up(dim, 64);
   int grid = (int)((total + 255) / 256);
   if (grid > 148 * 16) grid = 148 * 16;
-  split_rows_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, ld_x, rows, dim, (__nv_bfloat16*)out_split, nparts,
-                                                            cu_rows, batch);
+  launch_pdl(split_rows_kernel, dim3(grid), dim3(256), 0, stream, 1, x, ld_x, rows, dim, (__nv_bfloat16*)out_split, nparts,
+             cu_rows, batch);
   FB_CHECK_LAUNCH("split_rows");
   return FB200_OK;
 }
@@ -429,8 +435,8 @@ extern "C" __attribute__((visibility("default"))) int fb200_fsmn(const float* v,
       }                                                                                                                      \
       attr_set = true;                                                                                                       \
     }                                                                                                                        \
-    fsmn_stream_kernel<KS><<<grid, kFsmnThreads, kFsmnSmemBytes, (cudaStream_t)stream>>>(                                    \
-        v, ld_v, cu_rows, batch, total_rows, dim, weight, residual, ld_res, out, ld_out, cta_rows);                          \
+    launch_pdl(fsmn_stream_kernel<KS>, grid, dim3(kFsmnThreads), kFsmnSmemBytes, stream, 1,                                 \
+               v, ld_v, cu_rows, batch, total_rows, dim, weight, residual, ld_res, out, ld_out, cta_rows);                  \
   } while (0)
     if (ksize == 11) FSMN_STREAM(11);
     else FSMN_STREAM(21);
