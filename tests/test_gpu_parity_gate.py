@@ -41,6 +41,19 @@ def _workload(count, first_seed=0):
     return [(i, first_seed + i, int(n)) for i, n in enumerate(durs)]
 
 
+def test_paraformer_1024_utterances_vs_committed_reference_golden(paraformer_sd, cmvn, golden_dir):
+    """The same gate against tests/golden/configs1_ids_1024.npz -- ids and CIF counts the unmodified reference's CPU
+    AutoModel produced for all 1024 utterances (tests/golden/make_golden_configs1.py, run on the GPU box's host cores)."""
+    g = np.load(os.path.join(golden_dir, "configs1_ids_1024.npz"))
+    specs = _workload(1024)
+    assert [n for _, _, n in specs] == g["num_samples"].tolist()
+    eng = engine.ParaformerEngine(paraformer_sd, DEV, "fp32", cmvn=cmvn)
+    got = eng.recognize([synth.synth_waveform(seed, n) for _, seed, n in specs])
+    want = {i: (g["ids"][g["offsets"][i]: g["offsets"][i + 1]].tolist(), int(g["token_num"][i])) for i in range(1024)}
+    st = _stats("paraformer-large fp32 mode vs committed reference golden", got, list(eng.last_token_num), want)
+    assert st["counts_identical"] == 1024 and st["ids_identical_pct"] >= 99.9
+
+
 def test_paraformer_1024_utterances_fp32_mode_token_identity(paraformer_sd, cmvn):
     specs = _workload(1024)
     eng = engine.ParaformerEngine(paraformer_sd, DEV, "fp32", cmvn=cmvn)
