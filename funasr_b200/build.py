@@ -8,6 +8,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfunasr_b200.so")
+COMPAT_LIB = os.path.join(HERE, "libfunasr_b200_compat.so")
 SOURCES = ["api.cu", "frontend.cu", "rowwise.cu", "gemm_sm100.cu", "attention_sm100.cu", "cif_decode.cu", "conformer.cu", "relpos_attention_sm100.cu", "bicif.cu", "runtime.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
@@ -47,6 +48,11 @@ def build(force: bool = False, verbose: bool = False) -> str:
         list(ex.map(run, jobs))
     if jobs or force or _stale(LIB, objs):
         run([_nvcc(), "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"])
+    # the reference's C++ offline-stream API (funasrruntime.h names and signatures) over the library: plain C++, no CUDA
+    compat_src = os.path.join(CSRC, "funasr_compat.cpp")
+    if force or _stale(COMPAT_LIB, [compat_src, LIB, headers[-1]]):
+        run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", compat_src, "-o", COMPAT_LIB, "-L" + HERE,
+             "-lfunasr_b200", "-Wl,-rpath,$ORIGIN"])
     return LIB
 
 

@@ -129,7 +129,7 @@ __global__ void attention_plan_kernel(const int32_t* __restrict__ cu_q, const in
   int pos = s_count[tid] - cnt;
   if (tid == nth - 1) {
     plan[0] = min(s_count[tid], capacity);
-    plan[1] = s_count[tid];  // > capacity: the caller's buffer was too small (checked by nobody but tests)
+    plan[1] = s_count[tid];  // > capacity: the caller's buffer was too small -- the attention kernels trap on it
     plan[2] = plan[3] = 0;
   }
   int4* tiles = reinterpret_cast<int4*>(plan) + 1;
@@ -225,6 +225,12 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
   // and V are other kernels' outputs and are visible from here on.
   pdl_trigger();  // after the tensor-memory allocation (see gemm_sm100.cu): the next kernel's CTAs may be scheduled now
   pdl_wait();
+  if (p.plan[1] > p.plan[0]) {  // the plan was cut at its capacity: query blocks would silently go missing -- fail loudly
+    if (threadIdx.x == 0 && blockIdx.x == 0)
+      printf("fb200_attention: the plan needs %d entries but was built with capacity %d (fb200_attention_plan: capacity >= "
+             "q_rows / 128 + batch always suffices)\n", p.plan[1], p.plan[0]);
+    __trap();
+  }
   const int n_items = p.plan[0] * p.heads;
   const bool idle = (int)blockIdx.x >= n_items;  // CTA-uniform: nothing to do but hand the tensor memory back
 

@@ -63,6 +63,11 @@ __global__ void __launch_bounds__(kThreads, 1)
 relpos_attention_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_k,
                            const __grid_constant__ CUtensorMap map_v, const Params p) {
   const int item = blockIdx.x / p.heads, head = blockIdx.x % p.heads;
+  if (p.plan[1] > p.plan[0]) {  // truncated plan: fail loudly (see attention_sm100.cu)
+    if (threadIdx.x == 0 && blockIdx.x == 0)
+      printf("fb200_attention_relpos: the plan needs %d entries but was built with capacity %d\n", p.plan[1], p.plan[0]);
+    __trap();
+  }
   if (item >= p.plan[0]) return;
   const int4 it = __ldg(reinterpret_cast<const int4*>(p.plan) + 1 + item);
   const int q_row = it.x, q_valid = it.y, beg = it.z, T = it.w;

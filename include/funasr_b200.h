@@ -207,7 +207,9 @@ int fb200_split_weight(const float* w, int n, int k, void* out_split, int nparts
 /* Work list of fb200_attention for one (cu_q, cu_kv) pair: every 128-row query block of every
  * utterance that has keys.  Built on the device (one small kernel), reused by every attention call
  * over the same batch (all layers).  plan: int32 [4 + 4 * capacity]; capacity >= q_rows / 128 + batch
- * always suffices.  plan[0] = entries written, plan[1] = entries needed. */
+ * always suffices.  plan[0] = entries written, plan[1] = entries needed; a plan cut short (plan[1] > plan[0]) makes
+ * fb200_attention / fb200_attention_relpos print the two numbers and trap (a sticky CUDA error on the stream) instead of
+ * silently skipping query blocks. */
 int fb200_attention_plan(const int32_t* cu_q, const int32_t* cu_kv, int batch, int32_t* plan,
                          int capacity, void* stream);
 
