@@ -9,6 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfunasr_b200.so")
 COMPAT_LIB = os.path.join(HERE, "libfunasr_b200_compat.so")
+TORCH_LIB = os.path.join(HERE, "libfunasr_b200_torch.so")
 SOURCES = ["api.cu", "frontend.cu", "rowwise.cu", "gemm_sm100.cu", "attention_sm100.cu", "cif_decode.cu", "conformer.cu", "relpos_attention_sm100.cu", "bicif.cu", "runtime.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
@@ -53,6 +54,18 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if force or _stale(COMPAT_LIB, [compat_src, LIB, headers[-1]]):
         run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", compat_src, "-o", COMPAT_LIB, "-L" + HERE,
              "-lfunasr_b200", "-Wl,-rpath,$ORIGIN"])
+    # TORCH_LIBRARY(funasr_b200, ...): the torch custom-op layer over the C-ABI (csrc/torch_shim.cpp; g++ with torch's headers)
+    shim_src = os.path.join(CSRC, "torch_shim.cpp")
+    if force or _stale(TORCH_LIB, [shim_src, LIB, headers[-1]]):
+        import torch
+
+        tdir = os.path.dirname(torch.__file__)
+        cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+        run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden",
+             "-D_GLIBCXX_USE_CXX11_ABI=%d" % int(torch._C._GLIBCXX_USE_CXX11_ABI), "-DUSE_CUDA",
+             "-I" + os.path.join(tdir, "include"), "-I" + os.path.join(tdir, "include", "torch", "csrc", "api", "include"),
+             "-I" + cuda_inc, shim_src, "-o", TORCH_LIB, "-L" + HERE, "-lfunasr_b200", "-L" + os.path.join(tdir, "lib"),
+             "-ltorch", "-ltorch_cpu", "-lc10", "-lc10_cuda", "-Wl,-rpath,$ORIGIN", "-Wl,-rpath," + os.path.join(tdir, "lib")])
     return LIB
 
 

@@ -490,6 +490,19 @@ def _as_waveforms(data_in, data_lengths, fs: int, kwargs) -> List["np.ndarray"]:
     return [one(x) for x in (loaded if isinstance(loaded, (list, tuple)) else [loaded])]
 
 
+def _check_frontend_geometry(frontend, who: str) -> None:
+    """The packed engines are built for the templates' frontend geometry (16 kHz, 80 mel bins, 25 / 10 ms frames, LFR 7 / 6,
+    x 32768 upscaling) and take only the CMVN statistics and the window from the frontend object: anything else must fail
+    loudly instead of being silently ignored.  `dither` is NOT honoured by the `inference` overrides -- they behave as
+    dither = 0 (deterministic; the reference's default 1.0 adds noise per frame element, funasr/frontends/wav_frontend.py:94)."""
+    want = dict(fs=16000, n_mels=80, frame_length=25, frame_shift=10, lfr_m=7, lfr_n=6, upsacle_samples=True, snip_edges=True)
+    for name, value in want.items():
+        got = getattr(frontend, name, value)
+        if got != value:
+            raise NotImplementedError("funasr_b200.%s: frontend.%s = %r is outside the accelerated path (only %r)"
+                                      % (who, name, got, value))
+
+
 class ParaformerInference:
     """`Paraformer.inference` (funasr/models/paraformer/model.py:443-596) as ONE call into the packed
     engine: no padded tensors, no per-utterance device->host reads, no Python loop over frames.  Mixed
@@ -511,6 +524,7 @@ class ParaformerInference:
         if dev.type != "cuda":
             raise RuntimeError("funasr_b200.Paraformer: the model lives on %s -- this path runs on a CUDA device only "
                                "(no CPU fallback); build the model with device='cuda'" % dev)
+        _check_frontend_geometry(frontend, "Paraformer.inference")
         key = (tuple((p.data_ptr(), p._version) for p in self.parameters()), str(dev), PRECISION,
                getattr(frontend, "cmvn_file", None), getattr(frontend, "window", "hamming"))
         if self._fb200_engine is None or self._fb200_engine_key != key:
@@ -671,6 +685,7 @@ class SenseVoiceInference:
         if dev.type != "cuda":
             raise RuntimeError("funasr_b200.SenseVoiceSmall: the model lives on %s -- this path runs on a CUDA device "
                                "only (no CPU fallback); build the model with device='cuda'" % dev)
+        _check_frontend_geometry(frontend, "SenseVoiceSmall.inference")
         key = (tuple((p.data_ptr(), p._version) for p in self.parameters()), str(dev), PRECISION,
                getattr(frontend, "cmvn_file", None), getattr(frontend, "window", "hamming"))
         if self._fb200_engine is None or self._fb200_engine_key != key:
