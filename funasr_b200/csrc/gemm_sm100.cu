@@ -307,6 +307,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 #pragma unroll
           for (int j = 0; j < 32; ++j) y[j] = __uint_as_float(r[j]);
         }
+        if (warp == 2 && lane == 0) GTRACE(2, 22);
         if (c + 32 >= BN) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
           tcgen05_fence_before();
           __syncwarp();
@@ -317,6 +318,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));  // the leader issues the MMAs of both CTAs
           }
         }
+        if (warp == 2 && lane == 0) GTRACE(2, 26);
         if (!live) continue;
         if (bias != nullptr) {
           if (full) {
@@ -331,6 +333,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
               if (col0 + j < n) y[j] += __ldg(bias + col0 + j);
           }
         }
+        if (warp == 2 && lane == 0) GTRACE(2, 27);
 #pragma unroll
         for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], lo);
         if (swish) {
@@ -380,9 +383,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           for (int j = 0; j < 32; ++j)
             if (col0 + j >= n) y[j] = 0.f;
         }
+        if (warp == 2 && lane == 0) GTRACE(2, 23);
         // the boxes of the previous chunk must have been read by the TMA engine before they are overwritten
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();
+        if (warp == 2 && lane == 0) GTRACE(2, 24);
         const bool do_f32 = has_f32 && col0 >= f32_col0;
         if (do_f32) {
 #pragma unroll
@@ -415,6 +420,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
         fence_proxy_async_smem();
         __syncwarp();
+        if (warp == 2 && lane == 0) GTRACE(2, 25);
         if (lane == 0) {
           const int r0 = m0 + lg * 32;
           if (do_f32) tma_store_2d(&map_f32, fbuf, col0 - f32_col0, r0);
