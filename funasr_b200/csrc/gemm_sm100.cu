@@ -114,6 +114,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * STAGES + 2 + a); };
   const uint32_t tmem_slot = bar_base + 8u * (2 * STAGES + 4);
+  const uint32_t bias_sm = bar_base + 256u;  // the current tile's BN bias values (fp32), shared by the four epilogue warps
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // work unit = (group of CL row blocks, column block); cluster g takes units g, g + #clusters, ...; CTA rank r
@@ -285,11 +286,38 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
 #pragma unroll
       for (int i = 0; i < 32; ++i) rv[i] = (col_ok && r0 + i < m) ? __ldg(rp + (size_t)i * p.ld_res1) : 0.f;
     };
+    // Bias: the BN values of a tile's columns are staged ONCE per tile in shared memory by the 128 epilogue threads (fetched
+    // into registers a whole tile early) and every chunk reads its 32 values with 8 broadcast LDS.128.  Fetched from global
+    // memory where they are used -- 8 broadcast LDG.128 per chunk and warp -- they kept the load/store unit busy for ~300 of
+    // the ~1350 cycles a chunk takes, and the epilogue, not the MMAs, bounds the K = 512 products (profiles/r02_gemm_epilogue.md).
+    constexpr int kBiasPerThread = BN / 128 > 0 ? BN / 128 : 1;
+    const int et = (warp - 2) * 32 + lane;  // 0..127
+    float bnext[kBiasPerThread];
+    auto fetch_bias = [&](int tile) {
+      const int n0 = (tile % p.tiles_n) * BN;
+#pragma unroll
+      for (int u = 0; u < kBiasPerThread; ++u) {
+        const int cc = et * kBiasPerThread + u;
+        bnext[u] = (bias != nullptr && cc < BN && n0 + cc < n) ? __ldg(bias + n0 + cc) : 0.f;
+      }
+    };
+    auto epi_sync = [&]() { asm volatile("bar.sync 1, 128;" ::: "memory"); };
     int tl = 0;
+    if (unit0 < total_tiles) fetch_bias(unit0);
     if (res_coal && unit0 < total_tiles) load_res(unit0, 0);
     for (int tile = unit0; tile < total_tiles; tile += unit_step, ++tl) {
       const int acc = tl & 1;
       const int m0 = ((tile / p.tiles_n) * CL + cta_rank) * BM, n0 = (tile % p.tiles_n) * BN;
+      if (bias != nullptr) {
+        epi_sync();  // every warp has read the previous tile's values
+        if (et * kBiasPerThread < BN) {
+#pragma unroll
+          for (int u = 0; u < kBiasPerThread; ++u)
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_sm + (uint32_t)(et * kBiasPerThread + u) * 4u), "f"(bnext[u]) : "memory");
+        }
+        epi_sync();  // staged
+        if (tile + unit_step < total_tiles) fetch_bias(tile + unit_step);  // the next tile's values: in flight under this tile
+      }
       mbar_wait(tfull_bar(acc), ((uint32_t)tl >> 1) & 1u);
       if (warp == 2 && lane == 0) GTRACE(2, 20);
       tcgen05_fence_after();
@@ -320,17 +348,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         }
         if (warp == 2 && lane == 0) GTRACE(2, 26);
         if (!live) continue;
-        if (bias != nullptr) {
-          if (full) {
+        if (bias != nullptr) {  // columns >= n hold zeros in the staged tile
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-              const float4 b4 = __ldg(reinterpret_cast<const float4*>(bias + col0) + j);
-              y[4 * j] += b4.x; y[4 * j + 1] += b4.y; y[4 * j + 2] += b4.z; y[4 * j + 3] += b4.w;
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (col0 + j < n) y[j] += __ldg(bias + col0 + j);
+          for (int j = 0; j < 8; ++j) {
+            float4 b4;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(b4.x), "=f"(b4.y), "=f"(b4.z), "=f"(b4.w)
+                         : "r"(bias_sm + (uint32_t)(c + 4 * j) * 4u)
+                         : "memory");
+            y[4 * j] += b4.x; y[4 * j + 1] += b4.y; y[4 * j + 2] += b4.z; y[4 * j + 3] += b4.w;
           }
         }
         if (warp == 2 && lane == 0) GTRACE(2, 27);
