@@ -10,7 +10,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfunasr_b200.so")
 COMPAT_LIB = os.path.join(HERE, "libfunasr_b200_compat.so")
 TORCH_LIB = os.path.join(HERE, "libfunasr_b200_torch.so")
-SOURCES = ["api.cu", "frontend.cu", "rowwise.cu", "gemm_sm100.cu", "attention_sm100.cu", "cif_decode.cu", "conformer.cu", "relpos_attention_sm100.cu", "bicif.cu", "runtime.cu"]
+SOURCES = ["api.cu", "frontend.cu", "rowwise.cu", "gemm_sm100.cu", "attention_sm100.cu", "cif_decode.cu", "conformer.cu", "relpos_attention_sm100.cu", "bicif.cu", "runtime.cu", "stack_sm100.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden"]
 
@@ -28,7 +28,7 @@ def _stale(target: str, deps) -> bool:
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "gemm_host.inc"), os.path.join(CSRC, "attention_host.inc"), os.path.join(CSRC, "attention_softmax.inc"), os.path.join(CSRC, "attention_output.inc"), os.path.join(CSRC, "sm100_ptx.cuh"), os.path.join(os.path.dirname(HERE), "include", "funasr_b200.h")]
+    headers = [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "gemm_host.inc"), os.path.join(CSRC, "attention_host.inc"), os.path.join(CSRC, "attention_softmax.inc"), os.path.join(CSRC, "attention_output.inc"), os.path.join(CSRC, "sm100_ptx.cuh"), os.path.join(CSRC, "stack.cuh"), os.path.join(os.path.dirname(HERE), "include", "funasr_b200.h")]
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
     objs, jobs = [], []

@@ -30,6 +30,7 @@
 
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include "stack.cuh"
 
 namespace fb200 {
 

@@ -18,6 +18,7 @@
 
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include "stack.cuh"
 
 namespace fb200 {
 
@@ -25,30 +26,6 @@ constexpr int BM = 128;
 constexpr int BK = 64;  // bf16 elements = 128 bytes = one swizzle row
 constexpr int kGemmThreads = 192;
 constexpr int kEpiWarpBytes = 8192;  // per epilogue warp: fp32 box 32x32 (4 KB, SW128) + 2 bf16 part boxes 32x32 (2 KB each, SW64)
-constexpr int kMaxTerms = 6;
-constexpr int kMaxTaps = 24;
-
-struct GemmParams {
-  int m, n, k_blocks, kp_a, kp_w;
-  int taps, nterms;
-  int term_a[kMaxTerms], term_b[kMaxTerms];
-  int a_col0;                                // first A column; tap j reads A row m + tap_row[j], columns + tap_col[j]
-  int tap_row[kMaxTaps], tap_col[kMaxTaps];
-  // Column groups (0 = none): output columns [g * group_n, (g + 1) * group_n) are an independent product of the A
-  // columns shifted by g * a_col_step with the weight rows starting at g * w_group_rows -- the per-head (q+v).p^T
-  // products of the rel-pos attention as ONE launch.
-  int group_n, a_col_step, w_group_rows;
-  int tiles_m, tiles_n;
-  const float* bias;
-  int act;  // 0 none, 1 ReLU, 2 swish y * sigmoid(y)
-  const float* res1;
-  int ld_res1;
-  float* out_f32;
-  int ld_out, f32_col0;  // out_f32 holds columns [f32_col0, n) only
-  __nv_bfloat16* out_split;
-  int out_parts, out_kp;
-};
-
 // swish y * sigmoid(y) on the SFU (ex2.approx + rcp.approx: ~2 ulp, far inside the 16-bit-mantissa operand rounding that
 // follows); the IEEE expf + division made the epilogue of the K = 256 FFN contractions longer than their mainloop
 __device__ __forceinline__ float swish_fast(float y) { return __fdividef(y, 1.f + __expf(-y)); }

@@ -2,6 +2,7 @@
 // splitting, FSMN depthwise conv with per-sequence zero halos.
 #include "common.cuh"
 #include "sm100_ptx.cuh"
+#include "stack.cuh"
 
 namespace fb200 {
 
@@ -363,6 +364,8 @@ extern "C" __attribute__((visibility("default"))) int fb200_layernorm(const floa
   FB_CHECK_ARG(nparts >= 1 && nparts <= 3, "layernorm: nparts must be 1, 2 or 3");
   FB_CHECK_ARG(!halo || (cu_rows != nullptr && batch > 0), "layernorm: halo output needs cu_rows");
   if (rows == 0) return FB200_OK;
+  if (stack_recording())
+    return stack_record_layernorm(x, ld_x, rows, dim, gamma, beta, eps, out_f32, ld_f32, out_split, nparts, halo, cu_rows, batch);
   ProfScope prof(kProfLayerNorm, stream, (double)rows * dim * (4.0 + (out_f32 ? 4.0 : 0.0) + (out_split ? 2.0 * nparts : 0.0)));
   const int grid = (rows + kLnWarps - 1) / kLnWarps;
   cudaStream_t st = (cudaStream_t)stream;
@@ -416,6 +419,8 @@ extern "C" __attribute__((visibility("default"))) int fb200_fsmn(const float* v,
   FB_CHECK_ARG(ksize >= 1 && ksize <= kFsmnMaxK, "fsmn: ksize %d unsupported", ksize);
   FB_CHECK_ARG(residual == nullptr || ld_res % 4 == 0, "fsmn: ld_res must be a multiple of 4");
   if (total_rows == 0) return FB200_OK;
+  if (stack_recording())
+    return stack_record_fsmn(v, ld_v, cu_rows, batch, total_rows, dim, weight, ksize, residual, ld_res, out, ld_out);
   ProfScope prof(kProfFsmn, stream, (double)total_rows * dim * 4.0 * (residual ? 3.0 : 2.0));
   if (ksize == 11 || ksize == 21) {  // 11: Paraformer / SenseVoice; 21: the SeACo decoder (seaco_paraformer/template.yaml)
     // rows per CTA: 64 when that fills the GPU (two CTAs per SM), fewer for small batches (a CTA walks its rows

@@ -19,6 +19,8 @@ precision = "fp32": every dense contraction runs on a 2-way bf16 split of both o
 """
 from typing import Dict, List, Optional, Sequence, Tuple
 
+import os
+
 import numpy as np
 import torch
 
@@ -128,7 +130,7 @@ class FrontendPack:
         return frames, rows
 
     def run(self, wave: torch.Tensor, num_samples: Sequence[int], pe_scale: Optional[float] = None,
-            fbank_out: Optional[list] = None, row_skip: int = 0):
+            fbank_out: Optional[list] = None, row_skip: int = 0, feats_out: Optional[torch.Tensor] = None):
         """wave: packed fp32 [sum N] on the device.  Returns (feats [R, dim], cu_rows i32 dev, rows list).
         pe_scale given: feats = cmvn(lfr(fbank)) * pe_scale + PE(pos)  (the encoder input).
         row_skip > 0: every utterance gets that many extra rows at its head (counted in `rows`, positions
@@ -147,7 +149,8 @@ class FrontendPack:
             fbank_out.append(fb)
         feats = ops.lfr_cmvn(fb, cu_frames, cu_rows, int(sum(rows)), self.lfr_m, self.lfr_n, self.shift, self.scale,
                              self.pe_inv if pe_scale is not None else None, 1.0 if pe_scale is None else pe_scale,
-                             row_skip=row_skip)
+                             row_skip=row_skip,
+                             out=None if feats_out is None or feats_out.shape[0] < sum(rows) else feats_out[: int(sum(rows))])
         return feats, cu_rows, rows
 
 
@@ -195,6 +198,20 @@ class EncoderPack:
         xo = ws["x0"]
         ops.gemm(ws["h"], np_, ly.w2.w, np_, r, d, self.ff, bias=ly.w2.bias, res1=x1, out_f32=xo)
         return xo
+
+    def record(self, x: torch.Tensor, cu_rows: torch.Tensor, enc: torch.Tensor, halo: Optional[torch.Tensor],
+               split: Optional[torch.Tensor]):
+        """The layer walk of `run` over capacity-sized buffers, for an open `ops.StackProgram` recording: x [R, din] in,
+        after_norm(x) -> enc fp32 [R, d], its split in the CIF halo layout and / or as a plain split (the decoder's memory)."""
+        ws = self.workspace(x.shape[0])
+        ws["plan"] = None
+        for ly in self.layers:
+            x = self._layer(ly, x, cu_rows, x.shape[0], ws)
+        an = self.after_norm
+        ops.layernorm(x, an.g, an.b, self.eps, out_f32=enc, out_split=halo, nparts=self.nparts, halo=halo is not None,
+                      cu_rows=cu_rows if halo is not None else None)
+        if split is not None:
+            ops.layernorm(x, an.g, an.b, self.eps, out_split=split, nparts=self.nparts)
 
     def workspace(self, r: int):
         dev, np_, d = self.device, self.nparts, self.d
@@ -257,7 +274,7 @@ class PredictorPack:
         return torch.empty(r + b + 1, ops.split_width(self.d, self.nparts), dtype=torch.bfloat16, device=self.device)
 
     def run(self, enc: torch.Tensor, enc_halo: torch.Tensor, cu_rows: torch.Tensor, batch: int,
-            want_fires: bool = False):
+            want_fires: bool = False, embeds_out: Optional[torch.Tensor] = None):
         """enc fp32 [R, d]; enc_halo its bf16 split in halo layout.  Returns dict with alphas [R],
         token_num (host list), cu_tok (device i32), embeds [L, d], fires [R + B] or None."""
         r, d, dev = enc.shape[0], self.d, self.device
@@ -275,7 +292,10 @@ class PredictorPack:
         tok = token_num.cpu().tolist()  # the one D2H of the batch: [B] token counts
         cu_tok = tables.cu_from_lengths(tok, torch.int32, dev)
         total = int(sum(tok))
-        embeds = torch.empty(total, d, dtype=torch.float32, device=dev)
+        if embeds_out is not None and embeds_out.shape[0] >= total:
+            embeds = embeds_out[:total]
+        else:
+            embeds = torch.empty(total, d, dtype=torch.float32, device=dev)
         ops.cif_integrate(enc, alphas, cu_rows, cu_tok, total, self.tail, fire_pos, fire_rem, embeds)
         return dict(alphas=alphas, token_num=tok, token_num_dev=token_num, cu_tok=cu_tok, embeds=embeds, fires=fires)
 
@@ -342,7 +362,8 @@ class DecoderPack:
         t = torch.empty(l, d, dtype=torch.float32, device=dev)
         n2 = torch.empty(l, d, dtype=torch.float32, device=dev)
         bufs = [torch.empty(l, d, dtype=torch.float32, device=dev) for _ in range(2)]
-        plan = ops.attention_plan(cu_tok, cu_rows, l) if np_ < 3 else None  # one work list for all cross-attentions
+        # one work list for all cross-attentions (a stack-program recording needs none)
+        plan = ops.attention_plan(cu_tok, cu_rows, l) if np_ < 3 and not ops.recording() else None
         x = embeds
         for li, ly in enumerate(self.layers):
             ops.layernorm(x, ly.norm1.g, ly.norm1.b, eps, out_split=xs, nparts=np_)
@@ -380,6 +401,51 @@ class DecoderPack:
         return hid, out
 
 
+class _SmallPath:
+    """Small requests (BASELINE configs[0]: one 10 s utterance = 167 encoder rows): the 50 encoder layers + after_norm and
+    the 16 decoder layers + vocabulary projection run as TWO persistent cooperative kernels (`ops.StackProgram`) instead of
+    ~570 launches.  Recorded once for capacities (rows, tokens, utterances); each request runs them with its own counts."""
+
+    def __init__(self, eng: "ParaformerEngine"):
+        dev, np_ = eng.device, eng.nparts
+        enc_, dec_ = eng.encoder, eng.decoder
+        rc, lc, bc = eng.STACK_ROWS, eng.STACK_TOKENS, eng.STACK_BATCH
+        self.eng = eng
+        d = enc_.d
+        f32, bf, i32 = torch.float32, torch.bfloat16, torch.int32
+        self.x = torch.zeros(rc, enc_.din, dtype=f32, device=dev)         # encoder input (the frontend writes it)
+        self.cu_rows = torch.zeros(bc + 1, dtype=i32, device=dev)
+        self.cu_tok = torch.zeros(bc + 1, dtype=i32, device=dev)
+        self.enc = torch.zeros(rc, d, dtype=f32, device=dev)
+        self.halo = torch.zeros(rc + bc + 1, ops.split_width(d, np_), dtype=bf, device=dev)
+        self.split = torch.zeros(rc, ops.split_width(d, np_), dtype=bf, device=dev)
+        self.embeds = torch.zeros(lc, d, dtype=f32, device=dev)           # CIF output (the predictor writes it)
+        self.logits = torch.zeros(lc, dec_.vocab, dtype=f32, device=dev)
+        self.enc_prog = ops.StackProgram([rc, bc])
+        with self.enc_prog:
+            enc_.record(self.x, self.cu_rows, self.enc, self.halo, self.split)
+        self.dec_prog = ops.StackProgram([lc, rc, bc])
+        with self.dec_prog:
+            _, xs = dec_.hidden(self.enc, self.cu_rows, self.embeds, self.cu_tok, lc, enc_split=self.split)
+            ops.gemm(xs, np_, dec_.output.w, np_, lc, dec_.vocab, dec_.d, bias=dec_.output.bias, out_f32=self.logits)
+
+    def encode(self, cu_rows: torch.Tensor, r: int, b: int):
+        """`self.x[:r]` holds the encoder input.  Returns (enc [r, d], halo split [r + b + 1, ...]) views of the buffers."""
+        self.cu_rows[: b + 1].copy_(cu_rows)
+        self.enc_prog.run([r, b])
+        return self.enc[:r], self.halo[: r + b + 1]
+
+    def decode(self, cu_tok: torch.Tensor, r: int, l: int, b: int):
+        """`self.embeds[:l]` holds the CIF output.  Returns (ids i32 [l], logp f32 [l])."""
+        self.cu_tok[: b + 1].copy_(cu_tok)
+        self.dec_prog.run([l, r, b])
+        dev = self.eng.device
+        ids = torch.empty(l, dtype=torch.int32, device=dev)
+        logp = torch.empty(l, dtype=torch.float32, device=dev)
+        ops.argmax_logprob(self.logits[:l], self.eng.decoder.vocab, ids, logp)
+        return ids, logp
+
+
 class ParaformerEngine:
     """Paraformer.inference (funasr/models/paraformer/model.py:443-596) for a packed batch:
     host float32 waveforms in, token-id lists out.  One instance per process / GPU."""
@@ -401,6 +467,7 @@ class ParaformerEngine:
         self.nparts = self.PRECISIONS[precision]
         self.max_rows = max_rows
         self._copy_stream = None
+        self._small = None
         self.last_token_num: List[int] = []
         self._drop_ids = np.array(sorted(self.DROP_IDS), dtype=np.int32)
         with torch.cuda.device(self.device):
@@ -408,6 +475,18 @@ class ParaformerEngine:
             self.encoder = EncoderPack(state_dict, self.device, heads=heads, nparts=self.nparts)
             self.predictor = PredictorPack(state_dict, self.device, nparts=self.nparts)
             self.decoder = DecoderPack(state_dict, self.device, heads=heads, nparts=self.nparts)
+
+    # ---- small requests: encoder and decoder stretches as ONE persistent kernel each (csrc/stack_sm100.cu) -----------
+    STACK_ROWS, STACK_TOKENS, STACK_BATCH = 256, 192, 8  # capacities the two programs are recorded with
+
+    def small_path(self):
+        """Buffers and programs of the request-stack path, recorded on first use (FB200_STACK=0 switches it off)."""
+        if self._small is None:
+            if os.environ.get("FB200_STACK", "1") == "0" or self.nparts > 2 or self.encoder.tp_layers:
+                self._small = False
+            else:
+                self._small = _SmallPath(self)
+        return self._small or None
 
     # ---- stage-level entry points (also used by the parity tests) ------------------------------
     def upload(self, waves: Sequence) -> Tuple[torch.Tensor, List[int]]:
@@ -425,17 +504,29 @@ class ParaformerEngine:
     def forward_packed(self, wave: torch.Tensor, lens: Sequence[int], taps: Optional[dict] = None):
         """Device-resident packed waveforms -> (ids i32 [L] device, logp, token_num list)."""
         with torch.cuda.device(self.device):
-            feats, cu_rows, rows = self.frontend.run(wave, lens, pe_scale=float(self.encoder.d) ** 0.5)
-            b, r = len(lens), feats.shape[0]
-            halo = self.predictor.halo_buffer(r, b)
-            enc = self.encoder.run(feats, cu_rows, max(rows), out_halo=halo)
-            pred = self.predictor.run(enc, halo, cu_rows, b, want_fires=taps is not None)
+            b = len(lens)
+            small = None
+            if taps is None and b <= self.STACK_BATCH and sum(self.frontend.plan(lens)[1]) <= self.STACK_ROWS:
+                small = self.small_path()
+            feats, cu_rows, rows = self.frontend.run(wave, lens, pe_scale=float(self.encoder.d) ** 0.5,
+                                                     feats_out=small.x if small else None)
+            r = feats.shape[0]
+            if small:
+                enc, halo = small.encode(cu_rows, r, b)
+            else:
+                halo = self.predictor.halo_buffer(r, b)
+                enc = self.encoder.run(feats, cu_rows, max(rows), out_halo=halo)
+            pred = self.predictor.run(enc, halo, cu_rows, b, want_fires=taps is not None,
+                                      embeds_out=small.embeds if small else None)
             if taps is not None:
                 taps.update(feats=feats, enc=enc, cu_rows=cu_rows, rows=rows, **pred)
             tok = pred["token_num"]
             if max(tok) < 1:
                 empty = torch.empty(0, dtype=torch.int32, device=self.device)
                 return empty, torch.empty(0, dtype=torch.float32, device=self.device), tok
+            if small and sum(tok) <= self.STACK_TOKENS:
+                ids, logp = small.decode(pred["cu_tok"], r, int(sum(tok)), b)
+                return ids, logp, tok
             ids, logp, logits = self.decoder.run(enc, cu_rows, pred["embeds"], pred["cu_tok"], max(tok),
                                                  want_logits=taps is not None)
             if taps is not None:

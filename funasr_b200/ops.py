@@ -4,6 +4,7 @@ torch is used for device memory and the current stream only; every function here
 hand-written CUDA kernels from libfunasr_b200.so and raises if the library is unavailable.
 Naming: `cu_*` are int32 prefix-sum tensors on the device ([batch + 1]).
 """
+import ctypes
 from typing import Optional
 
 import torch
@@ -27,6 +28,71 @@ def _chk(t: torch.Tensor, dtype, name: str):
     if t.dtype != dtype:
         raise RuntimeError("funasr_b200.%s: expected %s, got %s" % (name, dtype, t.dtype))
     return t
+
+
+class StackProgram:
+    """A stretch of the path recorded as ONE persistent cooperative kernel (csrc/stack_sm100.cu; fb200_stack_* in the
+    C-ABI) for small requests.  Inside `with prog:` the wrappers `gemm`, `layernorm`, `fsmn` and `attention` of this module
+    launch nothing: the calls are appended to the program (every tensor they name is kept alive by it).  `dim_values` are
+    the row / batch CAPACITIES the recording runs with (pairwise distinct); `run(dims)` launches the program for a request
+    with the actual counts."""
+
+    def __init__(self, dim_values):
+        self.dim_values = [int(v) for v in dim_values]
+        self.handle = ctypes.c_void_p()
+        self.keep = []
+        self.n_ops = self.n_barriers = 0
+        self._open = False
+
+    def __enter__(self):
+        global _recording
+        if _recording is not None:
+            raise RuntimeError("funasr_b200: a stack program is already being recorded")
+        arr = (ctypes.c_int32 * len(self.dim_values))(*self.dim_values)
+        _lib.call("fb200_stack_begin", ctypes.byref(self.handle), arr, len(self.dim_values))
+        _recording, self._open = self, True
+        return self
+
+    def __exit__(self, exc_type, exc, tb):
+        global _recording
+        _recording, self._open = None, False
+        if exc_type is not None:
+            _lib.call("fb200_stack_destroy", self.handle)
+            self.handle = ctypes.c_void_p()
+            return False
+        _lib.call("fb200_stack_end", self.handle)
+        a, b = ctypes.c_int32(), ctypes.c_int32()
+        _lib.call("fb200_stack_info", self.handle, ctypes.byref(a), ctypes.byref(b))
+        self.n_ops, self.n_barriers = a.value, b.value
+        return False
+
+    def run(self, dims):
+        arr = (ctypes.c_int32 * len(dims))(*[int(v) for v in dims])
+        _lib.call("fb200_stack_run", self.handle, arr, len(dims), _stream())
+
+    def close(self):
+        if self.handle:
+            _lib.call("fb200_stack_destroy", self.handle)
+            self.handle = ctypes.c_void_p()
+        self.keep = []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_recording: Optional[StackProgram] = None
+
+
+def recording() -> bool:
+    return _recording is not None
+
+
+def _keep(*tensors):
+    if _recording is not None:
+        _recording.keep.extend(t for t in tensors if t is not None)
 
 
 def round_up(x: int, m: int = BK) -> int:
@@ -83,6 +149,7 @@ def layernorm(x, gamma, beta, eps, out_f32=None, out_split=None, nparts=1, halo=
     _chk(x, torch.float32, "layernorm")
     rows = x.shape[0] if rows is None else rows
     batch = 0 if cu_rows is None else cu_rows.numel() - 1
+    _keep(x, gamma, beta, out_f32, out_split, cu_rows)
     _lib.call("fb200_layernorm", _p(x), x.stride(0), rows, x.shape[1], _p(gamma), _p(beta), eps, _p(out_f32),
               0 if out_f32 is None else out_f32.stride(0), _p(out_split), nparts, 1 if halo else 0, _p(cu_rows),
               batch, _stream())
@@ -134,6 +201,7 @@ def split_rows_halo(x, nparts, cu_rows):
 def fsmn(v, cu_rows, weight, out, residual=None, rows=None):
     """v fp32 [rows, dim] view (row stride allowed); weight fp32 [dim, k]; out fp32 [rows, dim]."""
     rows = v.shape[0] if rows is None else rows
+    _keep(v, cu_rows, weight, out, residual)
     _lib.call("fb200_fsmn", _p(v), v.stride(0), _p(cu_rows), cu_rows.numel() - 1, rows, v.shape[1], _p(weight),
               weight.shape[-1], _p(residual), 0 if residual is None else residual.stride(0), _p(out), out.stride(0),
               _stream())
@@ -147,6 +215,7 @@ def gemm(a_split, a_parts, w_split, w_parts, m, n, k, bias=None, relu=False, res
     _chk(a_split, torch.bfloat16, "gemm")
     _chk(w_split, torch.bfloat16, "gemm")
     a_rows = a_split.shape[0] if a_rows is None else a_rows
+    _keep(a_split, w_split, bias, res1, out_f32, out_split)
     _lib.call("fb200_gemm", _p(a_split), a_rows, a_parts, _p(w_split), w_parts, m, n, k, taps, _p(bias),
               1 if relu else 0, _p(res1), 0 if res1 is None else res1.stride(0), _p(out_f32),
               0 if out_f32 is None else out_f32.stride(0), f32_col0, _p(out_split), out_parts, impl, _stream())
@@ -169,7 +238,8 @@ def attention(q, q_col0, q_ps, k, k_col0, v, v_col0, kv_ps, nparts, cu_q, cu_kv,
     _chk(v, torch.bfloat16, "attention")
     q_rows = q.shape[0] if q_rows is None else q_rows
     kv_rows = k.shape[0] if kv_rows is None else kv_rows
-    if plan is None and impl == 0 and nparts < 3:
+    _keep(q, k, v, cu_q, cu_kv, out_f32, out_split)
+    if plan is None and impl == 0 and nparts < 3 and _recording is None:  # a recorded attention op needs no work list
         plan = attention_plan(cu_q, cu_kv, q_rows)
     _lib.call("fb200_attention", _p(q), q.stride(0), q_col0, q_ps, _p(k), k.stride(0), k_col0, _p(v), v.stride(0),
               v_col0, kv_ps, nparts, _p(cu_q), _p(cu_kv), _p(plan), cu_q.numel() - 1, q_rows, kv_rows, max_q, heads,

@@ -382,6 +382,31 @@ int fb200_argmax_logprob(const float* logits, int ld, int rows, int vocab, int32
 int fb200_ctc_collapse(const int32_t* ids, const int32_t* cu_rows, int batch, uint32_t drop_mask,
                        int collapse_repeats, int32_t* out_ids, int32_t* out_len, void* stream);
 
+/* ------------------------------------------------------------------ request stack ------ */
+
+/* SMALL requests (one or a few utterances: BASELINE configs[0]) as ONE persistent cooperative kernel instead of ~580
+ * launches: between fb200_stack_begin and fb200_stack_end the calls fb200_gemm (impl 0, <= 2 parts, <= 3 row taps),
+ * fb200_layernorm, fb200_fsmn and fb200_attention made by THIS thread launch nothing -- they are appended to a program
+ * (operand pointers, tensor maps and shapes baked in; any other fb200_* call still launches and is not part of it).
+ * fb200_stack_run launches the program: one CTA per SM, tensor memory / barriers / shared-memory rings set up once, the
+ * ops walked in order with a device-wide barrier wherever an op reads or overwrites what an op since the previous
+ * barrier wrote or read (decided from the byte ranges at record time; the FSMN and attention of a layer share a phase).
+ * GEMM / LayerNorm / FSMN results are bit-identical to the per-op kernels'; attention is an fp32 streaming-softmax
+ * SIMT kernel over (utterance, head, <= 8 query rows) items (last-bit differences to the tcgen05 kernel).
+ * Replaces, for small requests, the per-module walk of SANMEncoder.forward (funasr/models/sanm/encoder.py:361-430) and
+ * ParaformerSANMDecoder.forward (funasr/models/paraformer/decoder.py:395-404): the reference runs those as ~1700 eager
+ * torch kernels per request.
+ *   dim_values[ndims]  row / batch CAPACITIES used while recording (pairwise distinct, ndims <= 8): every row or batch
+ *                      count of a recorded call that equals dim_values[s] becomes run-time dimension s;
+ *                      fb200_stack_run(dims) then supplies the request's actual values (0 <= dims[s] <= dim_values[s]).
+ *                      Buffers must be sized for the capacities; rows past dims[s] hold garbage after a run.
+ * A program may not run concurrently with itself; the recorded buffers must outlive it. */
+int fb200_stack_begin(void** handle, const int32_t* dim_values, int ndims);
+int fb200_stack_end(void* handle);
+int fb200_stack_info(void* handle, int32_t* n_ops, int32_t* n_barriers);
+int fb200_stack_run(void* handle, const int32_t* dims, int ndims, void* stream);
+int fb200_stack_destroy(void* handle);
+
 /* ------------------------------------------------------------------ native offline runtime ---- */
 
 /* The packed Paraformer path orchestrated in C++ inside this library (csrc/runtime.cu) -- no Python, no torch: the
