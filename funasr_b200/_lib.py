@@ -56,6 +56,7 @@ SIGNATURES = {
     "fb200_stack_info": [_P, _P, _P],
     "fb200_stack_run": [_P, _P, _I, _P],
     "fb200_stack_destroy": [_P],
+    "fb200_stack_profile": [_P, _I],
 }
 # native offline runtime (csrc/runtime.cu): name -> (argument types, return type)
 RUNTIME_SIGNATURES = {
@@ -70,7 +71,7 @@ RUNTIME_SIGNATURES = {
     "fb200_offline_uninit": ([_P], None),
 }
 EXPORTS = sorted(list(SIGNATURES) + list(RUNTIME_SIGNATURES) + ["fb200_version", "fb200_lstm_static_max_batch", "fb200_last_error", "fb200_launch_count",
-                  "fb200_profile_enable", "fb200_profile_read"])
+                  "fb200_profile_enable", "fb200_profile_read", "fb200_stack_profile_read"])
 PROFILE_KINDS = ["fbank", "lfr_cmvn", "scale_add_pe", "layernorm", "split_rows", "fsmn", "gemm", "attention",
                  "cif_alpha", "cif_scan", "cif_integrate", "argmax_logprob", "ctc_collapse", "conv2d_sub1", "glu_dwconv",
                  "attention_relpos", "lstm_bidir", "us_fires"]
@@ -97,6 +98,8 @@ def load():
         fn.argtypes = args
         fn.restype = ret
     lib.fb200_version.restype = c_int
+    lib.fb200_stack_profile_read.argtypes = [_P, _P, _P, _P, _I, _P]
+    lib.fb200_stack_profile_read.restype = c_int  # number of ops (>= 0) or a negative error code
     lib.fb200_lstm_static_max_batch.argtypes = []
     lib.fb200_lstm_static_max_batch.restype = c_int
     lib.fb200_last_error.restype = ctypes.c_char_p

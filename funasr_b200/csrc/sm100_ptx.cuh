@@ -49,6 +49,12 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "l"(map), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, int c0, int c1, int c2, int c3, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
 // ---- thread-block clusters: operand tiles shared by TMA multicast
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;
@@ -263,6 +269,8 @@ int make_tma_map(CUtensorMap* map, const void* base, int elem_bytes, uint64_t ro
 inline int make_tma_map_bf16(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint32_t box_rows) {
   return make_tma_map(map, base, 2, rows, cols, cols, 64, box_rows, 128);
 }
+int make_tma_map_operand4(CUtensorMap* map, const void* base, uint64_t rows, uint64_t ld, uint64_t k_blocks, uint64_t parts,
+                          uint64_t part_stride, uint32_t box_rows, uint32_t box_kb);
 int sm_count();
 
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }

@@ -37,31 +37,33 @@ namespace fb200 {
 
 constexpr int kStackThreads = 256;
 constexpr int SBK = 64;
-constexpr int kStStages = 4;
-constexpr uint32_t kStAPart = 128 * 128;     // 128 rows x 128 B
-constexpr uint32_t kStBPart = 64 * 128;      // at most 64 weight rows
-constexpr uint32_t kStStageBytes = 2 * (kStAPart + kStBPart);
-constexpr uint32_t kStRingBytes = kStStages * kStStageBytes;  // 196608
+// The operand ring is cut per op into as many stages as fit (a stage = all parts of a [bm x 64] A block and a [bn x 64]
+// W block: 12 KB..48 KB): a TMA load takes ~2.5 us to land here, so what sets a small-tile CTA's rate is the BYTES IN
+// FLIGHT, not the stage count -- 4 stages of 16 KB measured 23 GB/s per SM.
+constexpr int kStMaxStages = 16;
+constexpr uint32_t kStRingBytes = 196608;
 constexpr uint32_t kStEpiWarpBytes = 8192;
 constexpr uint32_t kStEpiBytes = 4 * kStEpiWarpBytes;
-constexpr uint32_t kStMiscBytes = 1024;      // barriers, tensor-memory slot, bias tile
+constexpr uint32_t kStMiscBytes = 1024;      // barriers, tensor-memory slot (0..511), bias tile (512..767), attention split (768..)
 constexpr uint32_t kStOpBytes = 256;
 constexpr uint32_t kStSmemBytes = kStRingBytes + kStEpiBytes + kStMiscBytes + kStOpBytes + 1024;
 constexpr int kStTmemCols = 128;             // two accumulator buffers of 64 columns
 constexpr int kStackMaxDims = 8;
 
-// attention overlay on the ring + epilogue staging (229376 bytes)
+// attention overlay: the ring holds three 64-key tiles (K hi | K mid | V hi | V mid, each two [64 rows x 128 B] TMA boxes
+// in the 128-byte swizzle, which also makes the per-key 16-byte reads of the score loop conflict-free); the epilogue
+// staging area holds the query rows, the probabilities, the partial scores and the row statistics
 constexpr int kAtTile = 64;                         // keys per tile
-constexpr uint32_t kAtKRow = 272;                   // 128 bf16 + 16 B: conflict-free LDS.128 across keys
-constexpr uint32_t kAtKPart = kAtTile * kAtKRow;    // 17408
-constexpr uint32_t kAtVPart = kAtTile * 256;        // 16384
-constexpr uint32_t kAtSlot = 2 * kAtKPart + 2 * kAtVPart;  // 67584
+constexpr uint32_t kAtBox = 64 * 128;               // one [64 x 64] bf16 box
+constexpr uint32_t kAtPart = 2 * kAtBox;            // one part of K or V of a tile: dims 0..63 | 64..127
+constexpr uint32_t kAtSlot = 4 * kAtPart;           // 65536
 constexpr int kAtSlots = 3;
 constexpr uint32_t kAtQ = kAtSlots * kAtSlot;       // fp32 [8][128]
 constexpr uint32_t kAtP = kAtQ + 8 * 128 * 4;       // fp32 [8][64]
 constexpr uint32_t kAtSp = kAtP + 8 * 64 * 4;       // fp32 [4][8][64]
 constexpr uint32_t kAtStat = kAtSp + 4 * 8 * 64 * 4;  // fp32 corr[8], linv[8]
 constexpr uint32_t kAtEnd = kAtStat + 64;
+static_assert(kAtSlots * kAtSlot <= kStRingBytes, "attention tiles live in the ring");
 static_assert(kAtEnd <= kStRingBytes + kStEpiBytes, "attention overlay must fit the ring + epilogue staging");
 static_assert(8 * 8 * 128 * 4 <= kAtSlot, "output partials alias tile slot 0");
 static_assert(kStSmemBytes <= 232448, "shared memory budget");
@@ -71,7 +73,11 @@ enum StackOpKind { kStGemm = 0, kStLayerNorm = 1, kStFsmn = 2, kStAttention = 3 
 struct StackGemmOp {
   int n, k_blocks, kp_a, kp_w, nparts, a_col0, act, taps;
   int tap_row[4];
-  int ld_res1, ld_out, f32_col0, out_parts, out_kp, map0, pad0, pad1;
+  int ld_res1, ld_out, f32_col0, out_parts, out_kp, map0;
+  // split-K (set by the recorder when a LayerNorm op consumes this product): up to ksplit_max K ranges per output tile, each
+  // range writes its raw fp32 accumulators to rows [ks * part_rows, ...) of the scratch matrix behind map0 / out_f32; bias
+  // and residual move into the LayerNorm op
+  int ksplit_max, part_rows;
   const float* bias;
   const float* res1;
   float* out_f32;
@@ -88,6 +94,14 @@ struct StackLnOp {
   const int32_t* cu_rows;
   int ld_x, dim, ld_f32, nparts, halo;
   float eps;
+  // fused reduction of a split-K product (part != nullptr): x = sum over the K ranges of part[ks] (+ bias) (+ res), stored
+  // to `x` (it stays the residual stream) before it is normalised; g_* restate the product so that this op derives the
+  // same ksplit as the GEMM op did
+  const float* part;
+  const float* p_bias;
+  const float* p_res;
+  long long part_stride;
+  int ld_part, ld_res, g_ncols, g_kblocks, g_nparts, ksplit_max;
 };
 struct StackFsmnOp {
   const float* v;
@@ -107,6 +121,7 @@ struct StackAttnOp {
   __nv_bfloat16* out_split;
   int ld_q, q_ps, ld_k, ld_v, kv_ps, nparts, heads, ld_out, out_parts, out_kp;
   float scale;
+  int map0, k_col0, v_col0;  // maps[map0] / maps[map0 + 1]: [64 x 64] boxes over the whole key / value matrices
 };
 struct __align__(16) StackOp {
   int kind, barrier_after, rows, rows_slot, batch, batch_slot, next_gemm, pad;
@@ -133,13 +148,12 @@ __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.pr
 // Device-wide barrier: every thread's global writes of the phase (generic and, through the waits on the bulk groups,
 // TMA stores) are ordered before thread 0's release; the waiting side acquires and re-orders the async proxy (the next
 // phase reads through TMA / bulk copies what other SMs wrote with plain stores, and the other way round).
-__device__ __forceinline__ void grid_barrier(unsigned int* counter, unsigned int& gen) {
-  fence_proxy_async_all();
+__device__ __forceinline__ void grid_barrier(unsigned int* counter, unsigned int& gen, int flags) {
+  if (!(flags & 4)) fence_proxy_async_all();
   __syncthreads();
+  ++gen;
   if (threadIdx.x == 0) {
-    ++gen;
-    __threadfence();
-    atomicAdd(counter, 1u);
+    asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(counter), "r"(1u) : "memory");
     const unsigned int target = gen * gridDim.x;
     unsigned int spins = 0;
     while (ld_acquire_u32(counter) < target) {
@@ -149,63 +163,154 @@ __device__ __forceinline__ void grid_barrier(unsigned int* counter, unsigned int
         __trap();
       }
     }
-    __threadfence();
-  } else {
-    ++gen;
   }
   __syncthreads();
   fence_proxy_async_all();
 }
 
-struct TileCfg {
-  int bm, bn, tiles_m, tiles_n;
+// Tile shapes of a GEMM op: [bm x bn] output tile, `kbs` k-blocks per TMA instruction / ring stage (a stage holds
+// <= 64 KB so that the ring always has >= 3 of them), and which of the op's pre-encoded operand maps has that box.
+// Map order of a GEMM op (from map0): fp32 out, split out, A maps (bm, kbs) = (32,4) (32,2) (64,2) (96,2) (96,1) (128,1),
+// W maps (bn, kbs) = (32,4) (32,2) (32,1) (64,2) (64,1).
+struct StackTile {
+  int bm, bn, kbs, a_map, w_map;
 };
-// Tile shape for a [m x ncols x K] product on `grid` CTAs: fewest rounds first, then the smallest per-CTA time estimate
-// max(ingest bytes / 41 B/clk, MMA cycles) + a fixed cost per tile.
-__device__ __forceinline__ TileCfg pick_tile_cfg(int m, int ncols, int k_iters, int nparts, int grid) {
-  TileCfg best = {128, 64, 1, 1};
-  long long best_cost = -1;
+constexpr int kStTiles = 8;
+__host__ __device__ constexpr StackTile stack_tile(int i) {
+  return i == 0 ? StackTile{128, 64, 1, 5, 4} : i == 1 ? StackTile{128, 32, 1, 5, 2} : i == 2 ? StackTile{96, 64, 1, 4, 4}
+       : i == 3 ? StackTile{96, 32, 2, 3, 1}  : i == 4 ? StackTile{64, 64, 2, 2, 3}  : i == 5 ? StackTile{64, 32, 2, 2, 1}
+       : i == 6 ? StackTile{32, 64, 2, 1, 3}  : StackTile{32, 32, 4, 0, 0};
+}
+constexpr int kStMapsPerGemm = 13, kStAMap0 = 2, kStWMap0 = 8;
+static const int kHostAMaps[6][2] = {{32, 4}, {32, 2}, {64, 2}, {96, 2}, {96, 1}, {128, 1}};
+static const int kHostWMaps[5][2] = {{32, 4}, {32, 2}, {32, 1}, {64, 2}, {64, 1}};
+
+struct TileCfg {
+  int idx, tiles_m, tiles_n, ksplit;
+};
+// Tile shape (and K split) for a [m x ncols x K] product on `grid` CTAs: the smallest estimate of
+//   rounds * (max(ingest bytes / 64 B/clk, MMA issue) + fixed cost per unit)
+// where one MMA costs its issuing thread max(40, bn / 2) cycles: with <= 64-column tiles the per-CTA time is set by the
+// NUMBER of MMAs (k-blocks x 4 K-slices x terms), which only a K split shortens.
+__device__ __noinline__ TileCfg pick_tile_cfg(int m, int ncols, int k_blocks, int nparts, int grid, int ksplit_max) {
+  TileCfg best = {0, 1, 1, 1};
+  int best_cost = 0x7fffffff;
+  const int terms = nparts == 1 ? 1 : 3;
 #pragma unroll
-  for (int bi = 0; bi < 4; ++bi) {
-    const int bm = 128 - 32 * bi;
+  for (int pass = 0; pass < 2; ++pass) {  // unsplit, then the full split (everything below is division by constants)
+    const int ks = pass == 0 ? 1 : ksplit_max;
+    if (pass == 1 && (ksplit_max <= 1 || (k_blocks & (ksplit_max - 1)) != 0)) break;
+    const int kb_unit = pass == 0 ? k_blocks : k_blocks / ksplit_max;
 #pragma unroll
-    for (int ni = 0; ni < 2; ++ni) {
-      const int bn = ni == 0 ? 64 : 32;
-      const int tm = (m + bm - 1) / bm, tn = (ncols + bn - 1) / bn;
-      const int tiles = tm * tn;
-      const int rounds = (tiles + grid - 1) / grid;
-      const int rows = m < bm ? m : bm;
-      const long long ingest = (long long)(((rows + 31) / 32) * 32 + bn) * 128 * nparts * k_iters / 41;
-      const long long mma = (long long)k_iters * 4 * (nparts == 1 ? 1 : 3) * (bn / 2);
-      const long long cost = (long long)rounds * ((ingest > mma ? ingest : mma) + 1500);
-      if (best_cost < 0 || cost < best_cost) {
+    for (int ci = 0; ci < kStTiles; ++ci) {
+      constexpr StackTile t0 = stack_tile(0);
+      (void)t0;
+      const StackTile t = stack_tile(ci);
+      if ((kb_unit & (t.kbs - 1)) != 0) continue;
+      const int tm = (m + t.bm - 1) / t.bm, tn = (ncols + t.bn - 1) / t.bn;
+      const int units = tm * tn * ks;
+      const int rounds = units <= grid ? 1 : (units <= 2 * grid ? 2 : (units + grid - 1) / grid);
+      const int ingest = (t.bm + t.bn) * nparts * kb_unit * 2;  // cycles: 128 B per row and k-block at ~64 B/clk
+      const int per_mma = (t.bn >> 1) > 40 ? (t.bn >> 1) : 40;
+      const int mma = kb_unit * 4 * terms * per_mma;
+      const int cost = rounds * ((ingest > mma ? ingest : mma) + 1500) + (ks > 1 ? 300 * ks : 0);  // + the reduction's reads
+      if (cost < best_cost) {
         best_cost = cost;
-        best.bm = bm;
-        best.bn = bn;
+        best.idx = ci;
         best.tiles_m = tm;
         best.tiles_n = tn;
+        best.ksplit = ks;
       }
     }
   }
   return best;
 }
+__device__ __forceinline__ StackTile stack_tile_rt(int i) {  // run-time index -> table entry (selects, no memory)
+  StackTile t = stack_tile(0);
+#pragma unroll
+  for (int c = 1; c < kStTiles; ++c)
+    if (i == c) t = stack_tile(c);
+  return t;
+}
 
 // ---------------------------------------------------------------- LayerNorm rows ---------
 // Same arithmetic as layernorm_kernel<NV> (rowwise.cu): warp per row, row in registers, two-pass variance.
-template <int NV>
-__device__ __forceinline__ void stack_ln_rows(const StackLnOp& o, int rows, int batch, int warp_global, int warp_stride,
-                                              int lane) {
+template <int NV, bool FUSED>
+__device__ __noinline__ void stack_ln_rows(const StackLnOp& o, int rows, int batch, int warp_global, int warp_stride,
+                                           int lane, int ksplit) {
   const int dim = o.dim, nvec = dim >> 2, nparts = o.nparts;
   const int kp = round_up(dim, 64);
   for (int row = warp_global; row < rows; row += warp_stride) {
     const float4* xr = reinterpret_cast<const float4*>(o.x + (size_t)row * o.ld_x);
     float4 v[NV];
     float s = 0.f;
+    if (FUSED) {
+      // the split-K product's epilogue: K ranges summed in order, then + bias, then + residual; x is written back.
+      // Every load of the row is issued before the first sum (NV * ksplit 16-byte loads per lane in flight: one L2 round
+      // trip instead of NV of them); rows wider than 640 go range by range.
+      const float4* rr = o.p_res ? reinterpret_cast<const float4*>(o.p_res + (size_t)row * o.ld_res) : nullptr;
+      const float* prow = o.part + (size_t)row * o.ld_part;
+      if (NV <= 5) {
+        float4 t[NV <= 5 ? NV : 1][8];
 #pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const int idx = lane + i * 32;
-      v[i] = idx < nvec ? __ldcg(xr + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
-      s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+        for (int i = 0; i < (NV <= 5 ? NV : 1); ++i) {
+          const int idx = lane + i * 32;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            t[i][ks] = (idx < nvec && ks < ksplit) ? __ldcg(reinterpret_cast<const float4*>(prow + (size_t)ks * o.part_stride) + idx)
+                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int i = 0; i < (NV <= 5 ? NV : 1); ++i) {
+          float4 a = t[i][0];
+#pragma unroll
+          for (int ks = 1; ks < 8; ++ks) {
+            if (ks < ksplit) {
+              a.x += t[i][ks].x; a.y += t[i][ks].y; a.z += t[i][ks].z; a.w += t[i][ks].w;
+            }
+          }
+          v[i] = a;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const int idx = lane + i * 32;
+          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (idx < nvec) {
+            a = __ldcg(reinterpret_cast<const float4*>(prow) + idx);
+            for (int ks = 1; ks < ksplit; ++ks) {
+              const float4 b = __ldcg(reinterpret_cast<const float4*>(prow + (size_t)ks * o.part_stride) + idx);
+              a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+            }
+          }
+          v[i] = a;
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int idx = lane + i * 32;
+        float4 a = v[i];
+        if (idx < nvec) {
+          if (o.p_bias) {
+            const float4 b = __ldg(reinterpret_cast<const float4*>(o.p_bias) + idx);
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+          }
+          if (rr) {
+            const float4 b = __ldcg(rr + idx);
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+          }
+          reinterpret_cast<float4*>(const_cast<float*>(o.x) + (size_t)row * o.ld_x)[idx] = a;
+        }
+        v[i] = a;
+        s += (a.x + a.y) + (a.z + a.w);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        const int idx = lane + i * 32;
+        v[i] = idx < nvec ? __ldcg(xr + idx) : make_float4(0.f, 0.f, 0.f, 0.f);
+        s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
+      }
     }
     const float mean = warp_sum(s) / (float)dim;
     float q = 0.f;
@@ -290,20 +395,23 @@ __device__ __forceinline__ uint2 ld_shared_u2(uint32_t addr) {
 // ---------------------------------------------------------------- the kernel -------------
 __global__ void __launch_bounds__(kStackThreads, 1)
 stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ maps, int n_ops, const StackDims dims,
-             unsigned int* __restrict__ sync_words) {
+             unsigned int* __restrict__ sync_words, unsigned long long* __restrict__ trace, const int flags) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t epi_base = smem_base + kStRingBytes;
   const uint32_t bar_base = epi_base + kStEpiBytes;
   const uint32_t op_base = bar_base + kStMiscBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (kStStages + s); };
-  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStStages + a); };
-  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStStages + 2 + a); };
-  auto att_bar = [&](int s) { return bar_base + 8u * (2 * kStStages + 4 + s); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kStStages + 4 + kAtSlots);
-  const uint32_t bias_sm = bar_base + 256u;  // 64 fp32
-  const uint32_t item_sm = bar_base + 512u;  // attention work split: [0] query rows per item, [1] items
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStMaxStages + s); };
+  auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kStMaxStages + a); };
+  auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kStMaxStages + 2 + a); };
+  auto att_bar = [&](int s) { return bar_base + 8u * (2 * kStMaxStages + 4 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kStMaxStages + 4 + kAtSlots);
+  const uint32_t bias_sm = bar_base + 512u;  // 64 fp32
+  const uint32_t item_sm = bar_base + 768u;  // attention work split: [0] query rows per item, [1] items
+  const uint32_t cfg_sm = bar_base + 784u;   // 2 x {tile index, tiles_m, tiles_n, ksplit, op index}: the NEXT GEMM op's shape,
+                                             // worked out by warp 7 while the current op runs (slot = GEMM ordinal & 1)
+  const uint32_t att_sm = bar_base + 848u;   // next attention op: {aq, items, op index, b, q_beg, q_len, kv_beg, kv_len, rem}
   const StackOp* s_op = reinterpret_cast<const StackOp*>(smem_raw + (op_base - smem_u32(smem_raw)));
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -311,7 +419,7 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
 
   if (warp == 1) {
     if (lane == 0) {
-      for (int s = 0; s < kStStages; ++s) {
+      for (int s = 0; s < kStMaxStages; ++s) {
         mbar_init(full_bar(s), 1);
         mbar_init(empty_bar(s), 1);
       }
@@ -332,40 +440,124 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
   uint32_t tmem_base;
   asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  int it = 0;   // k-block stages issued / consumed so far (warps 0 and 1 advance it identically)
+  // fb200_stack_profile: CTA 0's clock at points of every op (slot 8 * op + k: 0 start, 1 producer done, 2 first stage
+  // landed, 3 last MMA committed, 4 the LAST CTA's body done, 5 stores landed, 6 phase body done, 7 barrier passed)
+  const bool tracing = trace != nullptr && blockIdx.x == 0 && lane == 0;
+  auto stamp = [&](int slot) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    trace[slot] = t;
+  };
+  // bit s: parity of the next phase to wait for on stage s's barrier -- the producer's view of `empty` (a fresh barrier
+  // lets parity 1 through), the MMA thread's view of `full`; per barrier, so ops may cut the ring into different stage counts
+  uint32_t par_empty = 0xffffffffu, par_full = 0u;
   int tl = 0;   // tiles so far (warps 1..5)
   uint32_t att_par = 0;  // bit s: parity of the next phase of attention slot barrier s (all threads advance it alike)
   unsigned int gen = 0;
   int prefetched = -1;  // index of the last GEMM op whose weights were sent towards L2
+  int gemm_count = 0;   // GEMM ops so far (all threads)
+  int last_ksplit = 1;  // K split of the last GEMM op (the LayerNorm op behind a split product sums that many ranges)
+  int cfg_done = -1;    // warp 7: op index whose tile shape sits in cfg_sm
+  if (tid == 0) {
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(cfg_sm + 16u), "r"(-1) : "memory");
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(cfg_sm + 48u), "r"(-1) : "memory");
+    asm volatile("st.shared.b32 [%0], %1;" ::"r"(att_sm + 8u), "r"(-1) : "memory");
+  }
 
+  if (tracing && tid == 0) trace[8 * n_ops] = (unsigned long long)clock64();  // SM clock over the run (with the time stamps: MHz)
+  constexpr int kOpVecs = (int)(sizeof(StackOp) / 16);
+  uint4 op_next = make_uint4(0u, 0u, 0u, 0u);  // the next op record, fetched while the current op runs
+  if (tid < kOpVecs) op_next = __ldg(reinterpret_cast<const uint4*>(ops) + tid);
   for (int oi = 0; oi < n_ops; ++oi) {
-    if (tid < (int)(sizeof(StackOp) / 16))
-      reinterpret_cast<uint4*>(smem_raw + (op_base - smem_u32(smem_raw)))[tid] = __ldg(reinterpret_cast<const uint4*>(ops + oi) + tid);
+    if (tid < kOpVecs) reinterpret_cast<uint4*>(smem_raw + (op_base - smem_u32(smem_raw)))[tid] = op_next;
     __syncthreads();
+    if (tid < kOpVecs && oi + 1 < n_ops) op_next = __ldg(reinterpret_cast<const uint4*>(ops + oi + 1) + tid);
+    if (tracing && tid == 0) stamp(8 * oi);
     const StackOp& op = *s_op;
     const int rows = op.rows_slot >= 0 ? dims.v[op.rows_slot] : op.rows;
     const int batch = op.batch_slot >= 0 ? dims.v[op.batch_slot] : op.batch;
 
-    // weights of the next GEMM op towards L2 while this op runs (each CTA its share; a hint, nothing waits for it)
-    if (op.next_gemm > prefetched && op.next_gemm < n_ops) {
-      prefetched = op.next_gemm;
-      if (warp == 7) {
-        const StackOp* nx = ops + op.next_gemm;
-        const char* wb = nx->u.g.w_base;
-        const unsigned long long total = nx->u.g.w_bytes;
+    // towards L2 while this op runs (hints; nothing waits for them): the weights of the next GEMM op, and the small
+    // parameter vectors (bias, LayerNorm gamma / beta, FSMN taps) of the next op -- every one of them is a cold HBM line
+    // on a path that streams 880 MB of weights per request
+    if (warp == 7 && !(flags & 1)) {
+      auto l2_prefetch = [&](const void* base, unsigned long long total) {
+        const char* b = (const char*)base;
         const unsigned long long chunk = 4096;
         for (unsigned long long off = ((unsigned long long)blockIdx.x * 32 + lane) * chunk; off < total;
              off += (unsigned long long)grid * 32 * chunk) {
           const unsigned long long left = total - off;
           const uint32_t nbytes = (uint32_t)(left < chunk ? (left & ~15ull) : chunk);
-          if (nbytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(wb + off), "r"(nbytes) : "memory");
+          if (nbytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(b + off), "r"(nbytes) : "memory");
         }
-        if (lane == 0) {
-          asm volatile("prefetch.tensormap [%0];" ::"l"(maps + nx->u.g.map0) : "memory");
-          asm volatile("prefetch.tensormap [%0];" ::"l"(maps + nx->u.g.map0 + 1) : "memory");
-          asm volatile("prefetch.tensormap [%0];" ::"l"(maps + nx->u.g.map0 + 2) : "memory");
-          asm volatile("prefetch.tensormap [%0];" ::"l"(maps + nx->u.g.map0 + 3) : "memory");
+      };
+      if (op.next_gemm > prefetched && op.next_gemm < n_ops) {
+        const StackOp* nx = ops + op.next_gemm;
+        l2_prefetch(nx->u.g.w_base, nx->u.g.w_bytes);
+        if (nx->u.g.bias) l2_prefetch(nx->u.g.bias, (unsigned long long)nx->u.g.n * 4ull);
+        if (lane < kStMapsPerGemm) asm volatile("prefetch.tensormap [%0];" ::"l"(maps + nx->u.g.map0 + lane) : "memory");
+      }
+      if (oi + 1 < n_ops) {
+        const StackOp* nx = ops + oi + 1;
+        const int kind = nx->kind;
+        if (kind == kStLayerNorm) {
+          l2_prefetch(nx->u.ln.gamma, (unsigned long long)nx->u.ln.dim * 4ull);
+          l2_prefetch(nx->u.ln.beta, (unsigned long long)nx->u.ln.dim * 4ull);
+          if (nx->u.ln.p_bias) l2_prefetch(nx->u.ln.p_bias, (unsigned long long)nx->u.ln.dim * 4ull);
+        } else if (kind == kStFsmn) {
+          l2_prefetch(nx->u.f.weight, (unsigned long long)nx->u.f.dim * nx->u.f.ksize * 4ull);
+        } else if (kind == kStAttention && lane < 2) {
+          asm volatile("prefetch.tensormap [%0];" ::"l"(maps + nx->u.a.map0 + lane) : "memory");
         }
+      }
+    }
+    if (op.next_gemm > prefetched && op.next_gemm < n_ops) prefetched = op.next_gemm;
+    // look-ahead on an otherwise idle thread: the tile shape of the next GEMM op (a few hundred dependent instructions
+    // that used to sit in front of every product's first load) and the work split of an attention op right behind this one
+    if (warp == 7 && lane == 0) {
+      const int target = op.next_gemm;
+      if (target < n_ops && target != cfg_done) {
+        const StackOp* nx = ops + target;
+        const int nrows = nx->rows_slot >= 0 ? dims.v[nx->rows_slot] : nx->rows;
+        const int ncols_n = nx->u.g.out_split ? nx->u.g.out_kp : nx->u.g.n;
+        const TileCfg c = pick_tile_cfg(nrows, ncols_n, nx->u.g.taps * nx->u.g.k_blocks, nx->u.g.nparts, grid,
+                                        nx->u.g.taps == 1 ? nx->u.g.ksplit_max : 1);
+        const uint32_t slot = cfg_sm + (uint32_t)((gemm_count + (op.kind == kStGemm ? 1 : 0)) & 1) * 32u;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "r"(c.idx), "r"(c.tiles_m), "r"(c.tiles_n), "r"(c.ksplit) : "memory");
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(slot + 16u), "r"(target) : "memory");
+        cfg_done = target;
+      }
+      if (oi + 1 < n_ops && ops[oi + 1].kind == kStAttention) {
+        const StackOp* nx = ops + oi + 1;
+        const StackAttnOp& na = nx->u.a;
+        const int nb = nx->batch_slot >= 0 ? dims.v[nx->batch_slot] : nx->batch;
+        const int total_q = __ldg(na.cu_q + nb);
+        int aq = (na.heads * total_q + grid - 1) / grid;
+        aq = aq < 1 ? 1 : (aq > 8 ? 8 : aq);
+        int items = 0;
+        for (;;) {
+          items = 0;
+          for (int b = 0; b < nb; ++b) {
+            const int len = __ldg(na.cu_q + b + 1) - __ldg(na.cu_q + b);
+            const int kv = __ldg(na.cu_kv + b + 1) - __ldg(na.cu_kv + b);
+            if (kv > 0) items += ((len + aq - 1) / aq) * na.heads;
+          }
+          if (items <= grid || aq >= 8) break;
+          ++aq;
+        }
+        int b = 0, rem = blockIdx.x, q_beg = 0, q_len = 0, kv_beg = 0, kv_len = 0;
+        for (; b < nb; ++b) {
+          q_beg = __ldg(na.cu_q + b);
+          q_len = __ldg(na.cu_q + b + 1) - q_beg;
+          kv_beg = __ldg(na.cu_kv + b);
+          kv_len = __ldg(na.cu_kv + b + 1) - kv_beg;
+          const int n_it = kv_len > 0 ? ((q_len + aq - 1) / aq) * na.heads : 0;
+          if (rem < n_it) break;
+          rem -= n_it;
+        }
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(att_sm), "r"(aq), "r"(items), "r"(oi + 1), "r"(b) : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(att_sm + 16u), "r"(q_beg), "r"(q_len), "r"(kv_beg), "r"(kv_len) : "memory");
+        asm volatile("st.shared.b32 [%0], %1;" ::"r"(att_sm + 32u), "r"(rem) : "memory");
       }
     }
 
@@ -374,79 +566,117 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
       const StackGemmOp& g = op.u.g;
       const int m = rows, n = g.n, nparts = g.nparts;
       const int ncols = g.out_split ? g.out_kp : n;
-      const int k_iters = g.taps * g.k_blocks;
-      const TileCfg cfg = pick_tile_cfg(m, ncols, k_iters, nparts, grid);
-      const int bm = cfg.bm, bn = cfg.bn;
-      const int total_tiles = cfg.tiles_m * cfg.tiles_n;
-      const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - (int)blockIdx.x + grid - 1) / grid : 0;
-      const CUtensorMap* map_a = maps + g.map0;
-      const CUtensorMap* map_w = maps + g.map0 + 1;
-      const CUtensorMap* map_f32 = maps + g.map0 + 2;
-      const CUtensorMap* map_split = maps + g.map0 + 3;
-      const int nterms = nparts == 1 ? 1 : 3;
+      TileCfg cfg;
+      {
+        const uint32_t slot = cfg_sm + (uint32_t)(gemm_count & 1) * 32u;
+        int tag;
+        asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(cfg.idx), "=r"(cfg.tiles_m), "=r"(cfg.tiles_n), "=r"(cfg.ksplit) : "r"(slot) : "memory");
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tag) : "r"(slot + 16u) : "memory");
+        if (tag != oi) cfg = pick_tile_cfg(m, ncols, g.taps * g.k_blocks, nparts, grid, g.taps == 1 ? g.ksplit_max : 1);
+      }
+      ++gemm_count;
+      last_ksplit = cfg.ksplit;
+      const int ksplit = cfg.ksplit, kb_unit = g.k_blocks / ksplit;  // unit = (tile, K range)
+      const StackTile tc = stack_tile_rt(cfg.idx);
+      const int bm = tc.bm, bn = tc.bn, kbs = tc.kbs;
+      const int total_tiles = cfg.tiles_m * cfg.tiles_n * ksplit;  // units
+      const CUtensorMap* map_f32 = maps + g.map0;
+      const CUtensorMap* map_split = maps + g.map0 + 1;
+      const CUtensorMap* map_a = maps + g.map0 + kStAMap0 + tc.a_map;
+      const CUtensorMap* map_w = maps + g.map0 + kStWMap0 + tc.w_map;
+      const uint32_t a_blk = (uint32_t)bm * 128u, b_blk = (uint32_t)bn * 128u;  // one [rows x 64] block of one part
+      const uint32_t a_bytes = (uint32_t)(nparts * kbs) * a_blk, b_bytes = (uint32_t)(nparts * kbs) * b_blk;
+      const uint32_t stage_bytes = a_bytes + b_bytes;
+      const int n_stages = (int)(kStRingBytes / stage_bytes) < kStMaxStages ? (int)(kStRingBytes / stage_bytes) : kStMaxStages;
 
-      if (warp == 0) {
-        if (lane == 0) {  // ===== TMA producer =====
-          int i = it;
-          const int w_boxes = bn / 32;
-          for (int tile = blockIdx.x; tile < total_tiles; tile += grid) {
+      if (warp == 0 || warp == 6) {
+        // ===== TMA producers: warp 0 brings the A blocks (and arms the barrier for the whole stage), warp 6 the W blocks --
+        // two issuing warps because an instruction occupies its warp for ~200 cycles
+        // (elect.sync, not `lane == 0`: the compiler then keeps descriptors and barrier addresses in uniform registers --
+        // with a lane test every UTMALDG / UTCHMMA was wrapped in an ELECT + 7 x R2UR loop, ~100 cycles apiece)
+        const bool leader = elect_one();
+        if (leader) {
+          const bool a_role = warp == 0;
+          int s = 0;
+          for (int unit = blockIdx.x; unit < total_tiles; unit += grid) {
+            const int tile = unit / ksplit, kb_lo = (unit - tile * ksplit) * kb_unit;
             const int m0 = (tile / cfg.tiles_n) * bm, n0 = (tile % cfg.tiles_n) * bn;
-            const int rows_here = m - m0 < bm ? m - m0 : bm;
-            const int a_boxes = (rows_here + 31) / 32;
             for (int tap = 0; tap < g.taps; ++tap) {
-              const int a_r = m0 + g.tap_row[tap];
-              for (int kb = 0; kb < g.k_blocks; ++kb, ++i) {
-                const int s = i % kStStages;
-                const uint32_t ph = (uint32_t)(i / kStStages) & 1u;
-                mbar_wait(empty_bar(s), ph ^ 1u);
-                const uint32_t sa = smem_base + s * kStStageBytes;
-                mbar_expect_tx(full_bar(s), (uint32_t)(nparts * (a_boxes + w_boxes)) * 4096u);
-                for (int pa = 0; pa < nparts; ++pa)
-                  for (int b = 0; b < a_boxes; ++b)
-                    tma_load_2d(sa + pa * kStAPart + b * 4096u, map_a, g.a_col0 + pa * g.kp_a + kb * SBK, a_r + b * 32, full_bar(s));
-                for (int pb = 0; pb < nparts; ++pb)
-                  for (int b = 0; b < w_boxes; ++b)
-                    tma_load_2d(sa + 2 * kStAPart + pb * kStBPart + b * 4096u, map_w, pb * g.kp_w + kb * SBK, tap * n + n0 + b * 32,
-                                full_bar(s));
+              for (int kb0 = kb_lo; kb0 < kb_lo + kb_unit; kb0 += kbs) {
+                mbar_wait(empty_bar(s), (par_empty >> s) & 1u);
+                par_empty ^= 1u << s;
+                const uint32_t sa = smem_base + (uint32_t)s * stage_bytes;
+                if (a_role) {
+                  mbar_expect_tx(full_bar(s), stage_bytes);
+                  tma_load_4d(sa, map_a, 0, m0 + g.tap_row[tap], kb0, 0, full_bar(s));
+                } else {
+                  tma_load_4d(sa + a_bytes, map_w, 0, tap * n + n0, kb0, 0, full_bar(s));
+                }
+                s = s + 1 == n_stages ? 0 : s + 1;
               }
             }
           }
+          if (trace != nullptr && blockIdx.x == 0 && a_role) stamp(8 * oi + 1);
         }
-        it += my_tiles * k_iters;
-        __syncwarp();
+        {  // the barrier parities live in every lane: take the elected lane's copy
+          const unsigned who = __ballot_sync(0xffffffffu, leader);
+          par_empty = __shfl_sync(0xffffffffu, par_empty, __ffs(who) - 1);
+        }
       } else if (warp == 1) {
-        if (lane == 0) {  // ===== MMA issuer =====
+        const bool leader = elect_one();
+        if (leader) {  // ===== MMA issuer =====
           const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(bn >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-          int i = it, t = tl;
-          for (int tile = blockIdx.x; tile < total_tiles; tile += grid, ++t) {
+          int s = 0, t = tl;
+          bool first = true;
+          for (int unit = blockIdx.x; unit < total_tiles; unit += grid, ++t) {
+            const int kb_lo = (unit % ksplit) * kb_unit;
             const int acc = t & 1;
             mbar_wait(tempty_bar(acc), (((uint32_t)t >> 1) & 1u) ^ 1u);
             tcgen05_fence_after();
             const uint32_t tmem_d = tmem_base + (uint32_t)(acc * 64);
-            for (int j = 0; j < k_iters; ++j, ++i) {
-              const int s = i % kStStages;
-              const uint32_t ph = (uint32_t)(i / kStStages) & 1u;
-              mbar_wait(full_bar(s), ph);
-              tcgen05_fence_after();
-              const uint32_t sa = smem_base + s * kStStageBytes;
-              const uint32_t sb = sa + 2 * kStAPart;
-              for (int tt = 0; tt < nterms; ++tt) {
-                const int ta = (nparts == 2 && tt == 1) ? 1 : 0, tb = (nparts == 2 && tt == 0) ? 1 : 0;
+            bool fresh = true;  // the tile's first MMA overwrites the accumulator
+            for (int tap = 0; tap < g.taps; ++tap) {
+              for (int kb0 = kb_lo; kb0 < kb_lo + kb_unit; kb0 += kbs) {
+                mbar_wait(full_bar(s), (par_full >> s) & 1u);
+                par_full ^= 1u << s;
+                if (trace != nullptr && blockIdx.x == 0 && first) stamp(8 * oi + 2);
+                first = false;
+                tcgen05_fence_after();
+                const uint32_t sa = smem_base + (uint32_t)s * stage_bytes;
+                const uint32_t sb = sa + a_bytes;
+                const int kb_here = kb_lo + kb_unit - kb0 < kbs ? kb_lo + kb_unit - kb0 : kbs;
+                // The issue loop is the critical path of a small-tile product (one thread, ~100 dependent-instruction cycles
+                // per MMA when each descriptor is rebuilt): descriptors of a k-block are built once (hi / mid of A and W)
+                // and stepped by adding the 16-byte-unit offset of the next 16-element K slice to their address field.
+                for (int kb = 0; kb < ((flags & 2) ? 0 : kb_here); ++kb) {  // flags bit 1: timing experiment without the MMAs
+                  const uint64_t da0 = umma_desc_sw128(sa + (uint32_t)kb * a_blk), db0 = umma_desc_sw128(sb + (uint32_t)kb * b_blk);
+                  if (nparts == 2 && !(flags & 16)) {  // flags bit 4: timing experiment with one term per k-block
+                    const uint64_t da1 = da0 + (uint64_t)((uint32_t)kbs * a_blk >> 4), db1 = db0 + (uint64_t)((uint32_t)kbs * b_blk >> 4);
 #pragma unroll
-                for (int k = 0; k < SBK / 16; ++k) {
-                  const uint64_t da = umma_desc_sw128(sa + ta * kStAPart + k * 32);
-                  const uint64_t db = umma_desc_sw128(sb + tb * kStBPart + k * 32);
-                  umma_bf16(tmem_d, da, db, idesc, (j > 0 || tt > 0 || k > 0) ? 1u : 0u);
+                    for (int k = 0; k < SBK / 16; ++k) umma_bf16(tmem_d, da0 + 2 * k, db1 + 2 * k, idesc, (fresh && k == 0) ? 0u : 1u);
+#pragma unroll
+                    for (int k = 0; k < SBK / 16; ++k) umma_bf16(tmem_d, da1 + 2 * k, db0 + 2 * k, idesc, 1u);
+#pragma unroll
+                    for (int k = 0; k < SBK / 16; ++k) umma_bf16(tmem_d, da0 + 2 * k, db0 + 2 * k, idesc, 1u);
+                  } else {
+#pragma unroll
+                    for (int k = 0; k < SBK / 16; ++k) umma_bf16(tmem_d, da0 + 2 * k, db0 + 2 * k, idesc, (fresh && k == 0) ? 0u : 1u);
+                  }
+                  fresh = false;
                 }
+                umma_commit(empty_bar(s));
+                s = s + 1 == n_stages ? 0 : s + 1;
               }
-              umma_commit(empty_bar(s));
             }
             umma_commit(tfull_bar(acc));
           }
+          if (trace != nullptr && blockIdx.x == 0) stamp(8 * oi + 3);
         }
-        it += my_tiles * k_iters;
-        tl += my_tiles;
-        __syncwarp();
+        for (int unit = blockIdx.x; unit < total_tiles; unit += grid) ++tl;  // (every lane keeps the count)
+        {
+          const unsigned who = __ballot_sync(0xffffffffu, leader);
+          par_full = __shfl_sync(0xffffffffu, par_full, __ffs(who) - 1);
+        }
       } else if (warp < 6) {
         // ===== epilogue warps 2..5: TMEM lane group = warp % 4, lane = output row =====
         const int lg = warp & 3;
@@ -461,7 +691,9 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
         const uint32_t sw128 = (uint32_t)(lane & 7), sw64 = (uint32_t)((lane >> 1) & 3);
         const int et = (warp - 2) * 32 + lane;
         int t = tl;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += grid, ++t) {
+        for (int unit = blockIdx.x; unit < total_tiles; unit += grid, ++t) {
+          const int tile = unit / ksplit;
+          const int part_r0 = (unit - tile * ksplit) * g.part_rows;  // split-K: this K range's rows of the scratch matrix
           const int acc = t & 1;
           const int m0 = (tile / cfg.tiles_n) * bm, n0 = (tile % cfg.tiles_n) * bn;
           const int rows_here = m - m0 < bm ? m - m0 : bm;
@@ -559,9 +791,9 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
             }
             fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) {
+            if (elect_one()) {
               const int r0 = m0 + lg * 32;
-              if (do_f32) tma_store_2d(map_f32, fbuf, col0 - f32_col0, r0);
+              if (do_f32) tma_store_2d(map_f32, fbuf, col0 - f32_col0, part_r0 + r0);
               if (has_split) {
                 tma_store_2d(map_split, sbuf, col0, r0);
                 if (out_parts > 1) tma_store_2d(map_split, sbuf + 2048u, out_kp + col0, r0);
@@ -570,17 +802,21 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
             }
           }
         }
-        tl += my_tiles;
+        tl = t;
         if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // this warp's stores have landed
+        if (tracing && warp == 2) stamp(8 * oi + 5);
         __syncwarp();
       }
     } else if (op.kind == kStLayerNorm) {
       // ================================================================ LayerNorm =======
       const StackLnOp& o = op.u.ln;
       const int wg = blockIdx.x + grid * warp, ws = grid * (kStackThreads / 32);
-      if (o.dim <= 512) stack_ln_rows<4>(o, rows, batch, wg, ws, lane);
-      else if (o.dim <= 640) stack_ln_rows<5>(o, rows, batch, wg, ws, lane);
-      else stack_ln_rows<16>(o, rows, batch, wg, ws, lane);
+      const int ksplit = o.part != nullptr ? last_ksplit : 1;  // the split-K GEMM op right before this op chose it
+      // (the recorder fuses a split-K reduction only into LayerNorms of at most 512 columns)
+      if (o.part != nullptr) stack_ln_rows<4, true>(o, rows, batch, wg, ws, lane, ksplit);
+      else if (o.dim <= 512) stack_ln_rows<4, false>(o, rows, batch, wg, ws, lane, ksplit);
+      else if (o.dim <= 640) stack_ln_rows<5, false>(o, rows, batch, wg, ws, lane, ksplit);
+      else stack_ln_rows<16, false>(o, rows, batch, wg, ws, lane, ksplit);
     } else if (op.kind == kStFsmn) {
       // ================================================================ FSMN ============
       // out[r, c] = (v[r, c] (+ res[r, c])) + sum_j w[c, j] v[r + j - left, c]  (taps inside the utterance of r, in tap
@@ -618,29 +854,37 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
       // 64-key tiles (bulk copies of the bf16 parts as they lie in the split matrices); fp32 streaming softmax.
       const StackAttnOp& o = op.u.a;
       const int heads = o.heads, nparts = o.nparts;
-      if (tid == 0) {  // query rows per item: the smallest AQ whose item count fits one round (capped at 8)
-        const int total_q = __ldg(o.cu_q + batch);
-        int aq = (heads * total_q + grid - 1) / grid;
-        aq = aq < 1 ? 1 : (aq > 8 ? 8 : aq);
-        int items = 0;
-        for (;;) {
-          items = 0;
-          for (int b = 0; b < batch; ++b) {
-            const int len = __ldg(o.cu_q + b + 1) - __ldg(o.cu_q + b);
-            const int kv = __ldg(o.cu_kv + b + 1) - __ldg(o.cu_kv + b);
-            if (kv > 0) items += ((len + aq - 1) / aq) * heads;
+      int aq, items, pre_tag, pre_b, pre_qb, pre_ql, pre_kb, pre_kl, pre_rem;
+      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(aq), "=r"(items), "=r"(pre_tag), "=r"(pre_b) : "r"(att_sm) : "memory");
+      asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(pre_qb), "=r"(pre_ql), "=r"(pre_kb), "=r"(pre_kl) : "r"(att_sm + 16u) : "memory");
+      asm volatile("ld.shared.b32 %0, [%1];" : "=r"(pre_rem) : "r"(att_sm + 32u) : "memory");
+      if (pre_tag != oi) {  // not looked ahead (first op of a program): work it out here
+        if (tid == 0) {  // query rows per item: the smallest AQ whose item count fits one round (capped at 8)
+          const int total_q = __ldg(o.cu_q + batch);
+          int a = (heads * total_q + grid - 1) / grid;
+          a = a < 1 ? 1 : (a > 8 ? 8 : a);
+          int n_items = 0;
+          for (;;) {
+            n_items = 0;
+            for (int b = 0; b < batch; ++b) {
+              const int len = __ldg(o.cu_q + b + 1) - __ldg(o.cu_q + b);
+              const int kv = __ldg(o.cu_kv + b + 1) - __ldg(o.cu_kv + b);
+              if (kv > 0) n_items += ((len + a - 1) / a) * heads;
+            }
+            if (n_items <= grid || a >= 8) break;
+            ++a;
           }
-          if (items <= grid || aq >= 8) break;
-          ++aq;
+          asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(item_sm), "r"(a), "r"(n_items) : "memory");
         }
-        asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(item_sm), "r"(aq), "r"(items) : "memory");
+        __syncthreads();
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(aq), "=r"(items) : "r"(item_sm) : "memory");
       }
-      __syncthreads();
-      int aq, items;
-      asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(aq), "=r"(items) : "r"(item_sm) : "memory");
       for (int item = blockIdx.x; item < items; item += grid) {
         // item -> (utterance, chunk, head)
         int b = 0, rem = item, q_beg = 0, q_len = 0, kv_beg = 0, kv_len = 0;
+        if (pre_tag == oi && item == (int)blockIdx.x) {  // this CTA's first item was decoded ahead of time
+          b = pre_b; rem = pre_rem; q_beg = pre_qb; q_len = pre_ql; kv_beg = pre_kb; kv_len = pre_kl;
+        } else
         for (; b < batch; ++b) {
           q_beg = __ldg(o.cu_q + b);
           q_len = __ldg(o.cu_q + b + 1) - q_beg;
@@ -654,29 +898,23 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
         const int nq = q_len - q0 < aq ? q_len - q0 : aq;
         const int hoff = head * 128;
         const int ntiles = (kv_len + kAtTile - 1) / kAtTile;
-        auto issue_tile = [&](int t) {  // warp 0: bulk copies of tile t into slot t % 3
-          const int s = t % kAtSlots;
-          const int nvalid = kv_len - t * kAtTile < kAtTile ? kv_len - t * kAtTile : kAtTile;
-          if (lane == 0) mbar_expect_tx(att_bar(s), (uint32_t)(nvalid * nparts * 2) * 256u);
-          __syncwarp();
-          const uint32_t slot = smem_base + (uint32_t)s * kAtSlot;
-          for (int j = lane; j < nvalid; j += 32) {
-            const size_t row = (size_t)(kv_beg + t * kAtTile + j);
-            for (int pp = 0; pp < nparts; ++pp) {
-              const __nv_bfloat16* ks = o.k + row * o.ld_k + hoff + pp * o.kv_ps;
-              const __nv_bfloat16* vs = o.v + row * o.ld_v + hoff + pp * o.kv_ps;
-              asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                               slot + (uint32_t)pp * kAtKPart + (uint32_t)j * kAtKRow),
-                           "l"(ks), "r"(256u), "r"(att_bar(s))
-                           : "memory");
-              asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                               slot + 2 * kAtKPart + (uint32_t)pp * kAtVPart + (uint32_t)j * 256u),
-                           "l"(vs), "r"(256u), "r"(att_bar(s))
-                           : "memory");
+        const CUtensorMap* map_k = maps + o.map0;
+        const CUtensorMap* map_v = maps + o.map0 + 1;
+        auto issue_tile = [&](int t) {  // warps 0 / 1: the K / V blocks of tile t into slot t % 3, ONE instruction each
+          if (elect_one()) {              // (box = [part][half of the head dim][64 keys][64 dims])
+            const int s = t % kAtSlots;
+            const uint32_t slot = smem_base + (uint32_t)s * kAtSlot;
+            const int row = kv_beg + t * kAtTile;
+            if (warp == 0) {
+              mbar_expect_tx(att_bar(s), (uint32_t)(nparts * 4) * kAtBox);
+              tma_load_4d(slot, map_k, 0, row, head * 2, 0, att_bar(s));
+            } else {
+              tma_load_4d(slot + 2 * kAtPart, map_v, 0, row, head * 2, 0, att_bar(s));
             }
           }
+          __syncwarp();
         };
-        if (warp == 0)
+        if (warp < 2)
           for (int t = 0; t < ntiles && t < kAtSlots; ++t) issue_tile(t);
         // Q rows, pre-scaled like the reference (q * d_k^-0.5 before the product)
         if (tid < 8 * 32) {
@@ -691,12 +929,17 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
             }
             val.x *= o.scale; val.y *= o.scale; val.z *= o.scale; val.w *= o.scale;
           }
-          asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_base + kAtQ + (uint32_t)(i * 128 + c) * 4u), "f"(val.x),
-                       "f"(val.y), "f"(val.z), "f"(val.w)
-                       : "memory");
+          // Qt[d][row]: the eight rows' values of one dimension side by side (two LDS.128 per dimension in the score loop)
+          st_shared_f32(smem_base + kAtQ + (uint32_t)((c + 0) * 8 + i) * 4u, val.x);
+          st_shared_f32(smem_base + kAtQ + (uint32_t)((c + 1) * 8 + i) * 4u, val.y);
+          st_shared_f32(smem_base + kAtQ + (uint32_t)((c + 2) * 8 + i) * 4u, val.z);
+          st_shared_f32(smem_base + kAtQ + (uint32_t)((c + 3) * 8 + i) * 4u, val.w);
         }
         __syncthreads();
+        if (tracing && tid == 0 && item == (int)blockIdx.x) stamp(8 * oi + 1);
 
+        const uint8_t* sm = smem_raw + (smem_base - smem_u32(smem_raw));  // generic view of the overlay (plain loads: the
+                                                                          // compiler may batch and hoist them)
         float oacc[8][4];
 #pragma unroll
         for (int i = 0; i < 8; ++i)
@@ -711,58 +954,50 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
           const int nvalid = kv_len - t * kAtTile < kAtTile ? kv_len - t * kAtTile : kAtTile;
           mbar_wait(att_bar(s), (att_par >> s) & 1u);
           att_par ^= 1u << s;
-          const uint32_t slot = smem_base + (uint32_t)s * kAtSlot;
+          if (tracing && tid == 0 && item == (int)blockIdx.x && t == 0) stamp(8 * oi + 2);
+          const uint8_t* slot = sm + (uint32_t)s * kAtSlot;
           // ---- partial scores: S[i][key] over dims [dq*32, dq*32+32)
           {
             float sp[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) sp[i] = 0.f;
             if (key < nvalid) {
-#pragma unroll
+#pragma unroll 2
               for (int d8 = 0; d8 < 4; ++d8) {
-                const uint32_t koff = (uint32_t)key * kAtKRow + (uint32_t)(dq * 64 + d8 * 16);
-                uint4 raw;
+                // dims [dq*32 + d8*8, +8) of key `key`: box dq/2, 16-byte chunk (dq%2)*4 + d8, swizzled by the row
+                const uint32_t koff = (uint32_t)(dq >> 1) * kAtBox + (uint32_t)key * 128u +
+                                      ((((uint32_t)(dq & 1) * 4u + (uint32_t)d8) ^ ((uint32_t)key & 7u)) << 4);
                 float kf[8];
-                ld_shared_v4(slot + koff, raw);
-                bf16x8_to_f32(raw, kf);
+                bf16x8_to_f32(*reinterpret_cast<const uint4*>(slot + koff), kf);
                 if (nparts > 1) {
                   float km[8];
-                  ld_shared_v4(slot + kAtKPart + koff, raw);
-                  bf16x8_to_f32(raw, km);
+                  bf16x8_to_f32(*reinterpret_cast<const uint4*>(slot + kAtPart + koff), km);
 #pragma unroll
                   for (int u = 0; u < 8; ++u) kf[u] += km[u];
                 }
+                // all eight rows in lock step (rows past aq hold zeros): eight independent FMA chains per thread
+                const float4* qt = reinterpret_cast<const float4*>(sm + kAtQ) + (dq * 32 + d8 * 8) * 2;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                  if (i < aq) {
-                    const uint32_t qa = smem_base + kAtQ + (uint32_t)(i * 128 + dq * 32 + d8 * 8) * 4u;
-                    const float4 q0v = ld_shared_f4(qa), q1v = ld_shared_f4(qa + 16u);
-                    sp[i] = fmaf(q0v.x, kf[0], sp[i]); sp[i] = fmaf(q0v.y, kf[1], sp[i]);
-                    sp[i] = fmaf(q0v.z, kf[2], sp[i]); sp[i] = fmaf(q0v.w, kf[3], sp[i]);
-                    sp[i] = fmaf(q1v.x, kf[4], sp[i]); sp[i] = fmaf(q1v.y, kf[5], sp[i]);
-                    sp[i] = fmaf(q1v.z, kf[6], sp[i]); sp[i] = fmaf(q1v.w, kf[7], sp[i]);
-                  }
+                for (int u = 0; u < 8; ++u) {
+                  const float4 qa = qt[u * 2], qb = qt[u * 2 + 1];
+                  sp[0] = fmaf(qa.x, kf[u], sp[0]); sp[1] = fmaf(qa.y, kf[u], sp[1]);
+                  sp[2] = fmaf(qa.z, kf[u], sp[2]); sp[3] = fmaf(qa.w, kf[u], sp[3]);
+                  sp[4] = fmaf(qb.x, kf[u], sp[4]); sp[5] = fmaf(qb.y, kf[u], sp[5]);
+                  sp[6] = fmaf(qb.z, kf[u], sp[6]); sp[7] = fmaf(qb.w, kf[u], sp[7]);
                 }
               }
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i)
-              if (i < aq) st_shared_f32(smem_base + kAtSp + (uint32_t)((dq * 8 + i) * 64 + key) * 4u, sp[i]);
+            for (int i = 0; i < 8; ++i) st_shared_f32(smem_base + kAtSp + (uint32_t)((dq * 8 + i) * 64 + key) * 4u, sp[i]);
           }
           __syncthreads();
           // ---- softmax of row `warp` over this tile (lanes: keys lane, lane + 32), running max / sum
           if (warp < aq) {
+            const float* spp = reinterpret_cast<const float*>(sm + kAtSp);
             float s0 = -INFINITY, s1 = -INFINITY;
-            if (lane < nvalid) {
-              s0 = 0.f;
-#pragma unroll
-              for (int d = 0; d < 4; ++d) s0 += ld_shared_f32(smem_base + kAtSp + (uint32_t)((d * 8 + warp) * 64 + lane) * 4u);
-            }
-            if (lane + 32 < nvalid) {
-              s1 = 0.f;
-#pragma unroll
-              for (int d = 0; d < 4; ++d) s1 += ld_shared_f32(smem_base + kAtSp + (uint32_t)((d * 8 + warp) * 64 + lane + 32) * 4u);
-            }
+            if (lane < nvalid) s0 = ((spp[(0 * 8 + warp) * 64 + lane] + spp[(1 * 8 + warp) * 64 + lane]) + spp[(2 * 8 + warp) * 64 + lane]) + spp[(3 * 8 + warp) * 64 + lane];
+            if (lane + 32 < nvalid)
+              s1 = ((spp[(0 * 8 + warp) * 64 + lane + 32] + spp[(1 * 8 + warp) * 64 + lane + 32]) + spp[(2 * 8 + warp) * 64 + lane + 32]) + spp[(3 * 8 + warp) * 64 + lane + 32];
             const float mx = warp_max(fmaxf(s0, s1));
             const float m_new = fmaxf(m_run, mx);
             const float corr = expf(m_run - m_new);  // exp(-inf) = 0 on the first tile
@@ -771,53 +1006,60 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
             const float sum = warp_sum(p0 + p1);
             l_run = l_run * corr + sum;
             m_run = m_new;
-            st_shared_f32(smem_base + kAtP + (uint32_t)(warp * 64 + lane) * 4u, p0);
-            st_shared_f32(smem_base + kAtP + (uint32_t)(warp * 64 + lane + 32) * 4u, p1);
+            st_shared_f32(smem_base + kAtP + (uint32_t)(lane * 8 + warp) * 4u, p0);  // Pt[key][row]
+            st_shared_f32(smem_base + kAtP + (uint32_t)((lane + 32) * 8 + warp) * 4u, p1);
             if (lane == 0) st_shared_f32(smem_base + kAtStat + (uint32_t)warp * 4u, corr);
+          } else {  // rows past aq: keep their (never stored) accumulators finite
+            st_shared_f32(smem_base + kAtP + (uint32_t)(lane * 8 + warp) * 4u, 0.f);
+            st_shared_f32(smem_base + kAtP + (uint32_t)((lane + 32) * 8 + warp) * 4u, 0.f);
+            if (lane == 0) st_shared_f32(smem_base + kAtStat + (uint32_t)warp * 4u, 0.f);
           }
           __syncthreads();
           // ---- O[i][c4*4 .. +3] (partial over this thread's eighth of the keys) = O * corr + P . V
           {
+            const float4* stat4 = reinterpret_cast<const float4*>(sm + kAtStat);
+            const float4* pt4 = reinterpret_cast<const float4*>(sm + kAtP);
+            {
+              const float4 ca = stat4[0], cb = stat4[1];
+              const float cr[8] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              if (i < aq) {
-                const float corr = ld_shared_f32(smem_base + kAtStat + (uint32_t)i * 4u);
+              for (int i = 0; i < 8; ++i)
 #pragma unroll
-                for (int u = 0; u < 4; ++u) oacc[i][u] *= corr;
-              }
+                for (int u = 0; u < 4; ++u) oacc[i][u] *= cr[i];
             }
 #pragma unroll 2
             for (int kk = 0; kk < 8; ++kk) {
               const int ky = kq * 8 + kk;
               if (ky < nvalid) {
-                const uint32_t voff = slot + 2 * kAtKPart + (uint32_t)ky * 256u + (uint32_t)c4 * 8u;
-                uint2 raw = ld_shared_u2(voff);
+                // columns [c4*4, +4) of value row ky: box c4/16, byte (c4%16)*8 of the 128-byte row, chunk swizzled by the row
+                const uint8_t* vp = slot + 2 * kAtPart + (uint32_t)(c4 >> 4) * kAtBox + (uint32_t)ky * 128u +
+                                    (((((uint32_t)c4 & 15u) >> 1) ^ ((uint32_t)ky & 7u)) << 4) + ((uint32_t)c4 & 1u) * 8u;
+                uint2 raw = *reinterpret_cast<const uint2*>(vp);
                 float v0 = __uint_as_float(raw.x << 16), v1 = __uint_as_float(raw.x & 0xffff0000u);
                 float v2 = __uint_as_float(raw.y << 16), v3 = __uint_as_float(raw.y & 0xffff0000u);
                 if (nparts > 1) {
-                  raw = ld_shared_u2(voff + kAtVPart);
+                  raw = *reinterpret_cast<const uint2*>(vp + kAtPart);
                   v0 += __uint_as_float(raw.x << 16); v1 += __uint_as_float(raw.x & 0xffff0000u);
                   v2 += __uint_as_float(raw.y << 16); v3 += __uint_as_float(raw.y & 0xffff0000u);
                 }
+                const float4 pa = pt4[ky * 2], pb = pt4[ky * 2 + 1];
+                const float pr[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                  if (i < aq) {
-                    const float p = ld_shared_f32(smem_base + kAtP + (uint32_t)(i * 64 + ky) * 4u);
-                    oacc[i][0] = fmaf(p, v0, oacc[i][0]); oacc[i][1] = fmaf(p, v1, oacc[i][1]);
-                    oacc[i][2] = fmaf(p, v2, oacc[i][2]); oacc[i][3] = fmaf(p, v3, oacc[i][3]);
-                  }
+                  oacc[i][0] = fmaf(pr[i], v0, oacc[i][0]); oacc[i][1] = fmaf(pr[i], v1, oacc[i][1]);
+                  oacc[i][2] = fmaf(pr[i], v2, oacc[i][2]); oacc[i][3] = fmaf(pr[i], v3, oacc[i][3]);
                 }
               }
             }
           }
           __syncthreads();  // tile consumed: its slot, the score partials and P may be overwritten
-          if (warp == 0 && t + kAtSlots < ntiles) issue_tile(t + kAtSlots);
+          if (warp < 2 && t + kAtSlots < ntiles) issue_tile(t + kAtSlots);
         }
+        if (tracing && tid == 0 && item == (int)blockIdx.x) stamp(8 * oi + 3);
         // ---- sum the eight key-eighths (fixed order), normalise, store
         if (warp < aq && lane == 0) st_shared_f32(smem_base + kAtStat + 32u + (uint32_t)warp * 4u, 1.f / l_run);
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          if (i < aq)
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_base + (uint32_t)(((kq * 8 + i) * 128) + c4 * 4) * 4u),
                          "f"(oacc[i][0]), "f"(oacc[i][1]), "f"(oacc[i][2]), "f"(oacc[i][3])
                          : "memory");
@@ -844,12 +1086,20 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
     }
 
     // ---- end of the op
+    if (tracing && tid == 0) stamp(8 * oi + 6);
+    if (trace != nullptr && tid == 0) {  // slot 4: the LAST CTA's arrival at the end of the op body
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      atomicMax(trace + 8 * oi + 4, t);
+    }
     if (op.barrier_after)
-      grid_barrier(sync_words, gen);
+      grid_barrier(sync_words, gen, flags);
     else
       __syncthreads();
+    if (tracing && tid == 0) stamp(8 * oi + 7);
   }
 
+  if (tracing && tid == 0) trace[8 * n_ops + 1] = (unsigned long long)clock64();
   tcgen05_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -883,6 +1133,9 @@ struct StackProgram {
   StackOp* d_ops = nullptr;
   CUtensorMap* d_maps = nullptr;
   unsigned int* d_sync = nullptr;
+  unsigned long long* d_trace = nullptr;  // fb200_stack_profile(handle, 1): n_ops + 1 time stamps of the last run
+  float* d_scratch[2] = {nullptr, nullptr};  // split-K partial sums (two buffers, taken in turn)
+  int fused = 0;
   int grid = 0;
 };
 static thread_local StackProgram* g_rec = nullptr;
@@ -952,20 +1205,20 @@ int stack_record_gemm(const void* a, int a_rows, int lda, int a_parts, const voi
   g.out_parts = p.out_parts;
   g.out_kp = p.out_kp;
   g.map0 = (int)pr.maps.size();
+  g.ksplit_max = 1;
+  g.part_rows = 0;
   g.bias = p.bias;
   g.res1 = p.res1;
   g.out_f32 = p.out_f32;
   g.out_split = p.out_split;
   g.w_base = (const char*)w;
   g.w_bytes = (unsigned long long)w_rows * ldw * 2ull;
-  // operand maps in 32-row boxes (the kernel picks the tile height and width per run); output boxes as in gemm_host.inc
-  CUtensorMap ma, mw, mf, ms;
-  int rc = make_tma_map(&ma, a, 2, (uint64_t)a_rows, (uint64_t)lda, (uint64_t)lda, 64, 32, 128);
+  // output boxes as in gemm_host.inc; operand maps for every tile shape the kernel may pick at run time
+  CUtensorMap mf, ms, mo;
+  int rc = make_tma_map(&mo, a, 2, (uint64_t)a_rows, (uint64_t)lda, (uint64_t)lda, 64, 32, 128);  // placeholder for absent outputs
   if (rc) return rc;
-  rc = make_tma_map(&mw, w, 2, (uint64_t)w_rows, (uint64_t)ldw, (uint64_t)ldw, 64, 32, 128);
-  if (rc) return rc;
-  mf = ma;
-  ms = ma;
+  mf = mo;
+  ms = mo;
   if (p.out_f32) {
     rc = make_tma_map(&mf, p.out_f32, 4, (uint64_t)p.m, (uint64_t)(p.n - p.f32_col0), (uint64_t)p.ld_out, 32, 32, 128);
     if (rc) return rc;
@@ -975,10 +1228,22 @@ int stack_record_gemm(const void* a, int a_rows, int lda, int a_parts, const voi
                       32, 64);
     if (rc) return rc;
   }
-  pr.maps.push_back(ma);
-  pr.maps.push_back(mw);
   pr.maps.push_back(mf);
   pr.maps.push_back(ms);
+  for (int i = 0; i < 6; ++i) {
+    CUtensorMap ma;
+    rc = make_tma_map_operand4(&ma, (const __nv_bfloat16*)a + p.a_col0, (uint64_t)a_rows, (uint64_t)lda, (uint64_t)p.k_blocks,
+                               (uint64_t)a_parts, (uint64_t)p.kp_a, (uint32_t)kHostAMaps[i][0], (uint32_t)kHostAMaps[i][1]);
+    if (rc) return rc;
+    pr.maps.push_back(ma);
+  }
+  for (int i = 0; i < 5; ++i) {
+    CUtensorMap mw;
+    rc = make_tma_map_operand4(&mw, w, (uint64_t)w_rows, (uint64_t)ldw, (uint64_t)p.k_blocks, (uint64_t)a_parts, (uint64_t)p.kp_w,
+                               (uint32_t)kHostWMaps[i][0], (uint32_t)kHostWMaps[i][1]);
+    if (rc) return rc;
+    pr.maps.push_back(mw);
+  }
   std::vector<ByteRange> rd, wr;
   rd.push_back(range_of(a, (size_t)a_rows * lda * 2));
   if (p.res1) rd.push_back(range_of(p.res1, (size_t)p.m * p.ld_res1 * 4));
@@ -1064,8 +1329,8 @@ int stack_record_attention(const void* q, int ld_q, int q_col0, int q_part_strid
   op.batch_slot = slot_of(pr, batch);
   StackAttnOp& o = op.u.a;
   o.q = (const __nv_bfloat16*)q + q_col0;
-  o.k = (const __nv_bfloat16*)k + k_col0;
-  o.v = (const __nv_bfloat16*)v + v_col0;
+  o.k = (const __nv_bfloat16*)k;
+  o.v = (const __nv_bfloat16*)v;
   o.cu_q = cu_q;
   o.cu_kv = cu_kv;
   o.out_f32 = out_f32;
@@ -1081,6 +1346,18 @@ int stack_record_attention(const void* q, int ld_q, int q_col0, int q_part_strid
   o.out_parts = out_split ? out_parts : 0;
   o.out_kp = round_up(heads * head_dim, 64);
   o.scale = scale;
+  o.map0 = (int)pr.maps.size();
+  o.k_col0 = k_col0;
+  o.v_col0 = v_col0;
+  CUtensorMap mk, mv;  // box = both 64-dim halves of one head, every part, 64 keys
+  int rc = make_tma_map_operand4(&mk, (const __nv_bfloat16*)k + k_col0, (uint64_t)kv_rows, (uint64_t)ld_k, (uint64_t)heads * 2,
+                                 (uint64_t)nparts, (uint64_t)kv_part_stride, 64, 2);
+  if (rc) return rc;
+  rc = make_tma_map_operand4(&mv, (const __nv_bfloat16*)v + v_col0, (uint64_t)kv_rows, (uint64_t)ld_v, (uint64_t)heads * 2,
+                             (uint64_t)nparts, (uint64_t)kv_part_stride, 64, 2);
+  if (rc) return rc;
+  pr.maps.push_back(mk);
+  pr.maps.push_back(mv);
   std::vector<ByteRange> rd, wr;
   rd.push_back(range_of(q, (size_t)q_rows * ld_q * 2));
   rd.push_back(range_of(k, (size_t)kv_rows * ld_k * 2));
@@ -1129,6 +1406,72 @@ extern "C" __attribute__((visibility("default"))) int fb200_stack_end(void* hand
     if (pr->ops[i].kind == kStGemm) next = i;
   }
   pr->ops.back().barrier_after = 0;
+  // Split-K fusion: a product whose only consumer is the LayerNorm op right behind it (out-projection -> norm2, FFN w2 ->
+  // the next layer's norm1, ...) may be cut into K ranges -- what bounds a small-tile product is the NUMBER of MMAs its
+  // one issuing thread walks through -- with the LayerNorm op summing the ranges (+ bias, + residual) as it reads its
+  // rows.  Both ops are separated from their neighbours by barriers, so the scratch matrix is never read and written in
+  // the same phase; two scratch buffers are used in turn all the same.
+  static int split_on = -1;
+  if (split_on < 0) {
+    const char* e = getenv("FB200_STACK_SPLITK");
+    split_on = e ? atoi(e) : 1;
+  }
+  size_t scratch_floats = 0;
+  std::vector<int> fuse_at;
+  for (size_t i = 0; split_on && i + 1 < pr->ops.size(); ++i) {
+    StackOp& a = pr->ops[i];
+    StackOp& b = pr->ops[i + 1];
+    if (a.kind != kStGemm || b.kind != kStLayerNorm) continue;
+    const StackGemmOp& g = a.u.g;
+    const StackLnOp& l = b.u.ln;
+    const bool last = i + 2 == pr->ops.size();
+    if (g.out_split != nullptr || g.out_f32 == nullptr || g.f32_col0 != 0 || g.act != 0 || g.taps != 1 || l.x != g.out_f32 ||
+        l.ld_x != g.ld_out || l.dim != g.n || a.rows != b.rows || a.rows_slot != b.rows_slot || !a.barrier_after ||
+        !(b.barrier_after || last) || g.k_blocks < 8 || g.k_blocks % 4 != 0 || g.n % 32 != 0 || g.n > 512)
+      continue;
+    fuse_at.push_back((int)i);
+    const int ksmax = (g.k_blocks % 8 == 0 && g.k_blocks >= 16) ? 8 : 4;
+    const size_t need = (size_t)ksmax * a.rows * g.n;
+    if (need > scratch_floats) scratch_floats = need;
+  }
+  if (!fuse_at.empty()) {
+    for (int j = 0; j < 2; ++j)
+      if (cudaMalloc(&pr->d_scratch[j], scratch_floats * sizeof(float)) != cudaSuccess) {
+        set_error("stack_end: cudaMalloc of the split-K scratch (%zu bytes) failed", scratch_floats * sizeof(float));
+        pr->failed = true;
+        return FB200_ECUDA;
+      }
+    for (size_t f = 0; f < fuse_at.size(); ++f) {
+      StackOp& a = pr->ops[fuse_at[f]];
+      StackOp& b = pr->ops[fuse_at[f] + 1];
+      StackGemmOp& g = a.u.g;
+      StackLnOp& l = b.u.ln;
+      float* scratch = pr->d_scratch[f & 1];
+      const int ksmax = (g.k_blocks % 8 == 0 && g.k_blocks >= 16) ? 8 : 4;
+      l.part = scratch;
+      l.p_bias = g.bias;
+      l.p_res = g.res1;
+      l.ld_res = g.ld_res1;
+      l.part_stride = (long long)a.rows * g.n;
+      l.ld_part = g.n;
+      l.g_ncols = g.n;
+      l.g_kblocks = g.k_blocks;
+      l.g_nparts = g.nparts;
+      l.ksplit_max = ksmax;
+      g.bias = nullptr;
+      g.res1 = nullptr;
+      g.out_f32 = scratch;
+      g.ld_out = g.n;
+      g.ksplit_max = ksmax;
+      g.part_rows = a.rows;
+      const int rc = make_tma_map(&pr->maps[g.map0], scratch, 4, (uint64_t)ksmax * a.rows, (uint64_t)g.n, (uint64_t)g.n, 32, 32, 128);
+      if (rc) {
+        pr->failed = true;
+        return rc;
+      }
+    }
+    pr->fused = (int)fuse_at.size();
+  }
   static int grid = 0;
   if (grid == 0) {
     cudaError_t e = cudaFuncSetAttribute(stack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStSmemBytes);
@@ -1179,7 +1522,14 @@ extern "C" __attribute__((visibility("default"))) int fb200_stack_run(void* hand
   const CUtensorMap* maps = pr->d_maps;
   int n_ops = (int)pr->ops.size();
   unsigned int* sync_words = pr->d_sync;
-  void* args[] = {(void*)&ops, (void*)&maps, (void*)&n_ops, (void*)&d, (void*)&sync_words};
+  unsigned long long* trace = pr->d_trace;
+  if (trace != nullptr) cudaMemsetAsync(trace, 0, (pr->ops.size() * 8 + 8) * sizeof(unsigned long long), (cudaStream_t)stream);
+  static int flags = -1;  // experiment switches (FB200_STACK_FLAGS): bit 0 = no L2 prefetch of the next op's weights / parameters
+  if (flags < 0) {
+    const char* e = getenv("FB200_STACK_FLAGS");
+    flags = e ? atoi(e) : 0;
+  }
+  void* args[] = {(void*)&ops, (void*)&maps, (void*)&n_ops, (void*)&d, (void*)&sync_words, (void*)&trace, (void*)&flags};
   const cudaError_t e = cudaLaunchCooperativeKernel((const void*)stack_kernel, dim3((unsigned)pr->grid), dim3(kStackThreads), args,
                                                     kStSmemBytes, (cudaStream_t)stream);
   if (e != cudaSuccess) {
@@ -1190,6 +1540,48 @@ extern "C" __attribute__((visibility("default"))) int fb200_stack_run(void* hand
   return FB200_OK;
 }
 
+extern "C" __attribute__((visibility("default"))) int fb200_stack_profile(void* handle, int enable) {
+  StackProgram* pr = (StackProgram*)handle;
+  FB_CHECK_ARG(pr != nullptr && !pr->open && pr->d_ops != nullptr, "stack_profile: program not finished");
+  if (enable && pr->d_trace == nullptr) {
+    const size_t bytes = (pr->ops.size() * 8 + 8) * sizeof(unsigned long long);
+    if (cudaMalloc(&pr->d_trace, bytes) != cudaSuccess || cudaMemset(pr->d_trace, 0, bytes) != cudaSuccess) {
+      set_error("stack_profile: cudaMalloc failed");
+      return FB200_ECUDA;
+    }
+  } else if (!enable && pr->d_trace != nullptr) {
+    cudaDeviceSynchronize();
+    cudaFree(pr->d_trace);
+    pr->d_trace = nullptr;
+  }
+  return FB200_OK;
+}
+
+extern "C" __attribute__((visibility("default"))) int fb200_stack_profile_read(void* handle, int32_t* kinds, int32_t* barrier_after,
+                                                                                double* stamp_us, int capacity, double* sm_mhz) {
+  StackProgram* pr = (StackProgram*)handle;
+  FB_CHECK_ARG(pr != nullptr && pr->d_trace != nullptr, "stack_profile_read: profiling is not enabled on this program");
+  const int n = (int)pr->ops.size();
+  FB_CHECK_ARG(capacity >= n, "stack_profile_read: capacity %d < %d ops", capacity, n);
+  std::vector<unsigned long long> t((size_t)n * 8 + 8);
+  if (cudaDeviceSynchronize() != cudaSuccess ||
+      cudaMemcpy(t.data(), pr->d_trace, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost) != cudaSuccess) {
+    set_error("stack_profile_read: device read failed");
+    return FB200_ECUDA;
+  }
+  for (int i = 0; i < n; ++i) {
+    if (kinds) kinds[i] = pr->ops[i].kind;
+    if (barrier_after) barrier_after[i] = pr->ops[i].barrier_after;
+    if (stamp_us)
+      for (int k = 0; k < 8; ++k) stamp_us[i * 8 + k] = t[i * 8 + k] ? (double)(t[i * 8 + k] - t[0]) * 1e-3 : -1.0;
+  }
+  if (sm_mhz) {  // SM cycles between the first and the last stamp of CTA 0 over the wall time between them
+    const double us = (double)(t[(size_t)(n - 1) * 8 + 7] - t[0]) * 1e-3;
+    *sm_mhz = us > 0.0 ? (double)(t[(size_t)n * 8 + 1] - t[(size_t)n * 8]) / us : 0.0;
+  }
+  return n;
+}
+
 extern "C" __attribute__((visibility("default"))) int fb200_stack_destroy(void* handle) {
   StackProgram* pr = (StackProgram*)handle;
   if (pr == nullptr) return FB200_OK;
@@ -1197,6 +1589,9 @@ extern "C" __attribute__((visibility("default"))) int fb200_stack_destroy(void* 
   if (pr->d_ops) cudaFree(pr->d_ops);
   if (pr->d_maps) cudaFree(pr->d_maps);
   if (pr->d_sync) cudaFree(pr->d_sync);
+  if (pr->d_trace) cudaFree(pr->d_trace);
+  for (int j = 0; j < 2; ++j)
+    if (pr->d_scratch[j]) cudaFree(pr->d_scratch[j]);
   delete pr;
   return FB200_OK;
 }

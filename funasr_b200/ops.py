@@ -70,6 +70,23 @@ class StackProgram:
         arr = (ctypes.c_int32 * len(dims))(*[int(v) for v in dims])
         _lib.call("fb200_stack_run", self.handle, arr, len(dims), _stream())
 
+    def profile(self, on: bool = True):
+        """Per-op time stamps of every following run (fb200_stack_profile)."""
+        _lib.call("fb200_stack_profile", self.handle, 1 if on else 0)
+
+    def profile_read(self):
+        """[(kind, barrier_after, [8 stamps in us since the program's start, -1 = not taken])] per op of the last run; kind
+        0 GEMM, 1 LayerNorm, 2 FSMN, 3 attention; stamps: 0 start, 1 producer done, 2 first stage landed, 3 last MMA
+        committed, 4 the last CTA's body done, 5 stores landed, 6 body done, 7 barrier passed."""
+        n = max(self.n_ops, 1)
+        kinds, bars, us = (ctypes.c_int32 * n)(), (ctypes.c_int32 * n)(), (ctypes.c_double * (8 * n))()
+        mhz = ctypes.c_double()
+        got = _lib.load().fb200_stack_profile_read(self.handle, kinds, bars, us, n, ctypes.byref(mhz))
+        self.sm_mhz = mhz.value  # SM clock of the profiled run
+        if got < 0:
+            raise RuntimeError("fb200_stack_profile_read failed (%d): %s" % (got, _lib.load().fb200_last_error().decode()))
+        return [(int(kinds[i]), int(bars[i]), [float(us[8 * i + k]) for k in range(8)]) for i in range(got)]
+
     def close(self):
         if self.handle:
             _lib.call("fb200_stack_destroy", self.handle)

@@ -406,6 +406,16 @@ int fb200_stack_end(void* handle);
 int fb200_stack_info(void* handle, int32_t* n_ops, int32_t* n_barriers);
 int fb200_stack_run(void* handle, const int32_t* dims, int ndims, void* stream);
 int fb200_stack_destroy(void* handle);
+/* Per-op timeline of a program: after fb200_stack_profile(handle, 1) every run leaves CTA 0's clock at eight points of
+ * each op (0 start, 1 TMA producer done, 2 first operand stage landed, 3 last MMA committed, 4 the last CTA's body
+ * done, 5 stores landed, 6 op body done, 7 barrier passed; 1..5 GEMM ops only).  fb200_stack_profile_read waits for
+ * the device and returns the number of ops n, their kinds (0 GEMM, 1 LayerNorm, 2 FSMN, 3 attention), whether a
+ * device-wide barrier follows, stamp_us[8 * n]: microseconds since the first op's start (-1: not taken), and the SM
+ * clock the run saw (sm_mhz: CTA 0's cycle counter over the stamped wall time).
+ * Measurement aid, no counterpart in the reference. */
+int fb200_stack_profile(void* handle, int enable);
+int fb200_stack_profile_read(void* handle, int32_t* kinds, int32_t* barrier_after, double* stamp_us, int capacity,
+                             double* sm_mhz);
 
 /* ------------------------------------------------------------------ native offline runtime ---- */
 

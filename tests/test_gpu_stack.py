@@ -174,7 +174,9 @@ def test_stack_encoder_matches_per_op_path():
     torch.cuda.synchronize()
     err = float((want - got[:r]).abs().max() / want.abs().max())
     assert err < 1e-4, err  # the two attention kernels differ in the last bits; everything else is identical
-    assert float((halo_want.float() - halo[: r + b + 1].float()).abs().max()) < 1e-2
+    d = enc.d  # hi | mid parts: compare the values they stand for (a last-bit difference may move a hi part by one ulp)
+    hw, hg = halo_want.float(), halo[: r + b + 1].float()
+    assert float(((hw[:, :d] + hw[:, d:]) - (hg[:, :d] + hg[:, d:])).abs().max() / want.abs().max()) < 1e-4
     prog.close()
 
 
