@@ -126,6 +126,8 @@ static void stamps_from_fires(const int32_t* fire_idx, int n, int num_frames, in
 class Recognizer {
  public:
   ~Recognizer() {
+    if (enc_prog_) fb200_stack_destroy(enc_prog_);
+    if (dec_prog_) fb200_stack_destroy(dec_prog_);
     for (auto& g : graphs_) cudaGraphExecDestroy(g.second);
     for (void* p : owned_) cudaFree(p);
     if (arena_.base) cudaFree(arena_.base);
@@ -194,6 +196,23 @@ class Recognizer {
   bool use_graphs_ = true;
   template <typename F>
   int run_graphed(const GraphKey& key, bool allowed, F&& issue);
+  // Small requests (<= kStackBatch utterances, <= kStackRows encoder rows: BASELINE configs[0]): the encoder and decoder
+  // stretches run as two persistent cooperative kernels (fb200_stack_*, csrc/stack_sm100.cu) recorded once over
+  // capacity-sized buffers of their own; FB200_STACK=0 keeps the per-op launches.
+  static constexpr int kStackRows = 256, kStackTokens = 192, kStackBatch = 8;
+  struct EncBufs {
+    float* feats; bf16 *xs0, *xs, *h, *qkv; float *v, *mem, *x0, *x1, *enc; bf16 *halo, *encs; int32_t *d_cur, *plan;
+  };
+  struct DecBufs {
+    bf16 *encs, *kv, *qs, *ys, *hs; float *hf, *t, *t2, *n2, *b0, *b1, *embeds, *logits; int32_t *d_cut, *d_cur, *dplan;
+  };
+  int encoder_ops(const EncBufs& b, int R, int B, int max_t, void* st);
+  int decoder_ops(const DecBufs& b, int R, int L, int B, int max_l, int ldv, void* st);
+  int small_init();
+  bool use_stack_ = true, small_ready_ = false;
+  EncBufs small_enc_ = {};
+  DecBufs small_dec_ = {};
+  void *enc_prog_ = nullptr, *dec_prog_ = nullptr;
   // CifPredictorV3 time-stamp head (BiCifParaformer), present when the checkpoint holds predictor.blstm.*
   bool has_stamps_ = false;
   static constexpr int kMaxStampBatch = 1024;
@@ -617,6 +636,141 @@ int Recognizer::run_graphed(const GraphKey& key, bool allowed, F&& issue) {
   return FB200_OK;
 }
 
+// The 50 SAN-M encoder layers + after_norm over packed rows (the per-op calls; inside fb200_stack_begin / _end they are
+// recorded instead of launched).  b.encs != nullptr: after_norm also as a plain split (the decoder's memory operand).
+int Recognizer::encoder_ops(const EncBufs& b, int R, int B, int max_t, void* st) {
+  const int np = np_, d = d_;
+  const int wqkv = np * kp64(3 * d);
+  const float scale = 1.f / sqrtf((float)(d / heads_));
+  const float* x = b.feats;
+  int ldx = din_;
+  for (const EncLayer& ly : enc_) {
+    bf16* a = ly.din == d ? b.xs : b.xs0;
+    RT_OK(fb200_layernorm(x, ldx, R, ly.din, ly.norm1.g, ly.norm1.b, eps_, nullptr, 0, a, np, 0, nullptr, 0, st));
+    RT_OK(fb200_gemm(a, R, np, ly.qkv.w, np, R, 3 * d, ly.din, 1, ly.qkv.bias, 0, nullptr, 0, b.v, d, 2 * d, b.qkv, np, 0, st));
+    RT_OK(fb200_fsmn(b.v, d, b.d_cur, B, R, d, ly.fsmn, ly.fsmn_k, ly.din == d ? x : nullptr, ldx, b.mem, d, st));
+    RT_OK(fb200_attention(b.qkv, wqkv, 0, wqkv / np, b.qkv, wqkv, d, b.qkv, wqkv, 2 * d, wqkv / np, np, b.d_cur, b.d_cur, b.plan, B, R, R,
+                          max_t, heads_, d / heads_, scale, nullptr, 0, b.xs, np, 0, st));
+    RT_OK(fb200_gemm(b.xs, R, np, ly.out.w, np, R, d, d, 1, ly.out.bias, 0, b.mem, d, b.x1, d, 0, nullptr, np, 0, st));
+    RT_OK(fb200_layernorm(b.x1, d, R, d, ly.norm2.g, ly.norm2.b, eps_, nullptr, 0, b.xs, np, 0, nullptr, 0, st));
+    RT_OK(fb200_gemm(b.xs, R, np, ly.w1.w, np, R, ff_, d, 1, ly.w1.bias, 1, nullptr, 0, nullptr, 0, 0, b.h, np, 0, st));
+    RT_OK(fb200_gemm(b.h, R, np, ly.w2.w, np, R, d, ff_, 1, ly.w2.bias, 0, b.x1, d, b.x0, d, 0, nullptr, np, 0, st));
+    x = b.x0;
+    ldx = d;
+  }
+  RT_OK(fb200_layernorm(x, d, R, d, enc_after_.g, enc_after_.b, eps_, b.enc, d, b.halo, np, 1, b.d_cur, B, st));
+  if (b.encs != nullptr) RT_OK(fb200_layernorm(x, d, R, d, enc_after_.g, enc_after_.b, eps_, nullptr, 0, b.encs, np, 0, nullptr, 0, st));
+  return FB200_OK;
+}
+
+// K / V projection of the memory, the 16 decoder layers, after_norm and the vocabulary projection over packed token rows.
+int Recognizer::decoder_ops(const DecBufs& b, int R, int L, int B, int max_l, int ldv, void* st) {
+  const int np = np_, d = d_;
+  const int wd = np * kp64(d), wkv = np * kp64(dec_kv_.n);
+  const float scale = 1.f / sqrtf((float)(d / heads_));
+  RT_OK(fb200_gemm(b.encs, R, np, dec_kv_.w, np, R, dec_kv_.n, d, 1, dec_kv_.bias, 0, nullptr, 0, nullptr, 0, 0, b.kv, np, 0, st));
+  const float* y = b.embeds;
+  for (const DecLayer& ly : dec_) {
+    RT_OK(fb200_layernorm(y, d, L, d, ly.norm1.g, ly.norm1.b, eps_, nullptr, 0, b.ys, np, 0, nullptr, 0, st));
+    RT_OK(fb200_gemm(b.ys, L, np, ly.w1.w, np, L, ff_, d, 1, ly.w1.bias, 1, nullptr, 0, b.hf, ff_, 0, nullptr, np, 0, st));
+    RT_OK(fb200_layernorm(b.hf, ff_, L, ff_, ly.ffn_norm.g, ly.ffn_norm.b, eps_, nullptr, 0, b.hs, np, 0, nullptr, 0, st));
+    float* tt = (y == b.t) ? b.t2 : b.t;
+    RT_OK(fb200_gemm(b.hs, L, np, ly.w2.w, np, L, d, ff_, 1, ly.w2.bias, 0, nullptr, 0, tt, d, 0, nullptr, np, 0, st));
+    if (!ly.has_fsmn) {  // decoders3: FFN only, no residual (paraformer/decoder.py:102-108)
+      y = tt;
+      continue;
+    }
+    RT_OK(fb200_layernorm(tt, d, L, d, ly.norm2.g, ly.norm2.b, eps_, b.n2, d, nullptr, np, 0, nullptr, 0, st));
+    float* yo = (y == b.b0) ? b.b1 : b.b0;
+    RT_OK(fb200_fsmn(b.n2, d, b.d_cut, B, L, d, ly.fsmn, ly.fsmn_k, y, d, yo, d, st));  // x + conv(n2) + n2
+    if (ly.has_src) {
+      RT_OK(fb200_layernorm(yo, d, L, d, ly.norm3.g, ly.norm3.b, eps_, nullptr, 0, b.ys, np, 0, nullptr, 0, st));
+      RT_OK(fb200_gemm(b.ys, L, np, ly.q.w, np, L, d, d, 1, ly.q.bias, 0, nullptr, 0, nullptr, 0, 0, b.qs, np, 0, st));
+      const int j = ly.src_index;
+      RT_OK(fb200_attention(b.qs, wd, 0, wd / np, b.kv, wkv, j * 2 * d, b.kv, wkv, j * 2 * d + d, wkv / np, np, b.d_cut, b.d_cur, b.dplan,
+                            B, L, R, max_l, heads_, d / heads_, scale, nullptr, 0, b.ys, np, 0, st));
+      float* xo = (yo == b.b0) ? b.b1 : b.b0;
+      RT_OK(fb200_gemm(b.ys, L, np, ly.out.w, np, L, d, d, 1, ly.out.bias, 0, yo, d, xo, d, 0, nullptr, np, 0, st));
+      y = xo;
+    } else {
+      y = yo;
+    }
+  }
+  RT_OK(fb200_layernorm(y, d, L, d, dec_after_.g, dec_after_.b, eps_, nullptr, 0, b.ys, np, 0, nullptr, 0, st));
+  RT_OK(fb200_gemm(b.ys, L, np, dec_out_.w, np, L, vocab_, d, 1, dec_out_.bias, 0, nullptr, 0, b.logits, ldv, 0, nullptr, np, 0, st));
+  return FB200_OK;
+}
+
+// Buffers (capacity-sized, zeroed once) and the two programs of the small-request path.
+int Recognizer::small_init() {
+  const int np = np_, d = d_, RC = kStackRows, LC = kStackTokens, BC = kStackBatch;
+  const int wd = np * kp64(d), wdin = np * kp64(din_), wff = np * kp64(ff_), wqkv = np * kp64(3 * d), wkv = np * kp64(dec_kv_.n);
+  const int ldv = (vocab_ + 3) / 4 * 4;
+  auto dev = [&](size_t bytes) -> void* {
+    void* p = nullptr;
+    if (cudaMalloc(&p, bytes) != cudaSuccess || cudaMemset(p, 0, bytes) != cudaSuccess) return nullptr;
+    owned_.push_back(p);
+    return p;
+  };
+  EncBufs& e = small_enc_;
+  DecBufs& c = small_dec_;
+  e.feats = (float*)dev((size_t)RC * din_ * 4);
+  e.xs0 = (bf16*)dev((size_t)RC * wdin * 2);
+  e.xs = (bf16*)dev((size_t)RC * wd * 2);
+  e.h = (bf16*)dev((size_t)RC * wff * 2);
+  e.qkv = (bf16*)dev((size_t)RC * wqkv * 2);
+  e.v = (float*)dev((size_t)RC * d * 4);
+  e.mem = (float*)dev((size_t)RC * d * 4);
+  e.x0 = (float*)dev((size_t)RC * d * 4);
+  e.x1 = (float*)dev((size_t)RC * d * 4);
+  e.enc = (float*)dev((size_t)RC * d * 4);
+  e.halo = (bf16*)dev((size_t)(RC + BC + 1) * wd * 2);
+  e.encs = (bf16*)dev((size_t)RC * wd * 2);
+  e.d_cur = (int32_t*)dev((BC + 1) * 4);
+  e.plan = nullptr;
+  c.encs = e.encs;
+  c.kv = (bf16*)dev((size_t)RC * wkv * 2);
+  c.qs = (bf16*)dev((size_t)LC * wd * 2);
+  c.ys = (bf16*)dev((size_t)LC * wd * 2);
+  c.hs = (bf16*)dev((size_t)LC * wff * 2);
+  c.hf = (float*)dev((size_t)LC * ff_ * 4);
+  c.t = (float*)dev((size_t)LC * d * 4);
+  c.t2 = (float*)dev((size_t)LC * d * 4);
+  c.n2 = (float*)dev((size_t)LC * d * 4);
+  c.b0 = (float*)dev((size_t)LC * d * 4);
+  c.b1 = (float*)dev((size_t)LC * d * 4);
+  c.embeds = (float*)dev((size_t)LC * d * 4);
+  c.logits = (float*)dev((size_t)LC * ldv * 4);
+  c.d_cut = (int32_t*)dev((BC + 1) * 4);
+  c.d_cur = e.d_cur;
+  c.dplan = nullptr;
+  if (!e.feats || !e.xs0 || !e.xs || !e.h || !e.qkv || !e.v || !e.mem || !e.x0 || !e.x1 || !e.enc || !e.halo || !e.encs || !e.d_cur ||
+      !c.kv || !c.qs || !c.ys || !c.hs || !c.hf || !c.t || !c.t2 || !c.n2 || !c.b0 || !c.b1 || !c.embeds || !c.logits || !c.d_cut) {
+    set_error("runtime: device memory for the small-request buffers");
+    return FB200_ECUDA;
+  }
+  const int32_t edims[2] = {RC, BC};
+  RT_OK(fb200_stack_begin(&enc_prog_, edims, 2));
+  int rc = encoder_ops(e, RC, BC, RC, stream_);
+  if (rc != FB200_OK) {
+    fb200_stack_destroy(enc_prog_);
+    enc_prog_ = nullptr;
+    return rc;
+  }
+  RT_OK(fb200_stack_end(enc_prog_));
+  const int32_t ddims[3] = {LC, RC, BC};
+  RT_OK(fb200_stack_begin(&dec_prog_, ddims, 3));
+  rc = decoder_ops(c, RC, LC, BC, LC, ldv, stream_);
+  if (rc != FB200_OK) {
+    fb200_stack_destroy(dec_prog_);
+    dec_prog_ = nullptr;
+    return rc;
+  }
+  RT_OK(fb200_stack_end(dec_prog_));
+  small_ready_ = true;
+  return FB200_OK;
+}
+
 int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens, Result* res, const std::vector<int>* next,
                         const float* const* waves) {
   static const bool trace = getenv("FB200_RT_TRACE") != nullptr;  // host-side phase times of every batch on stderr
@@ -651,6 +805,12 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
     max_t = std::max(max_t, rows);
   }
   const int F = cu_frames[B], R = cu_rows[B];
+  // small request: the encoder / decoder stretches run from the recorded programs over their own fixed buffers
+  bool small = use_stack_ && np_ <= 2 && B <= kStackBatch && R > 0 && R <= kStackRows;
+  if (small && !small_ready_) {
+    static const bool off = getenv("FB200_STACK") != nullptr && atoi(getenv("FB200_STACK")) == 0;
+    if (off || small_init() != FB200_OK) use_stack_ = small = false;
+  }
   const float* wave = dwave_[slot];
   int64_t* d_cus = arena_.get<int64_t>(B + 1);
   int32_t *d_cuf = arena_.get<int32_t>(B + 1), *d_cur = arena_.get<int32_t>(B + 1), *d_cut = arena_.get<int32_t>(B + 1);
@@ -670,6 +830,14 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
     set_error("runtime: activation slab too small for a batch of %d rows", R);
     return FB200_EINVAL;
   }
+  EncBufs eb = {feats, xs0, xs, h, qkv, v, mem, x0, x1, enc, halo, nullptr, d_cur, plan};
+  if (small) {
+    eb = small_enc_;
+    feats = eb.feats;
+    enc = eb.enc;
+    halo = eb.halo;
+    d_cur = eb.d_cur;
+  }
   RT_CUDA(cudaStreamWaitEvent(stream_, copied_[slot], 0));  // this batch's waveforms are on the device
   RT_CUDA(cudaMemcpyAsync(d_cus, cu_samples.data(), (B + 1) * 8, cudaMemcpyHostToDevice, stream_));
   RT_CUDA(cudaMemcpyAsync(d_cuf, cu_frames.data(), (B + 1) * 4, cudaMemcpyHostToDevice, stream_));
@@ -680,31 +848,20 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   RT_OK(fb200_fbank(wave, d_cus, d_cuf, B, F, window_, frame_len_, frame_shift_, nfft_, mel_, n_mels_, 32768.f, 0.97f, fb, st));
   RT_OK(fb200_lfr_cmvn(fb, d_cuf, d_cur, B, R, n_mels_, lfr_m_, lfr_n_, shift_, scale_, pe_inv_, sqrtf((float)d), 0, feats, din_, st));
   // encoder
-  RT_OK(fb200_attention_plan(d_cur, d_cur, B, plan, plan_cap, st));
-  const float* x = feats;
-  int ldx = din_;
-  for (const EncLayer& ly : enc_) {
-    bf16* a = ly.din == d ? xs : xs0;
-    RT_OK(fb200_layernorm(x, ldx, R, ly.din, ly.norm1.g, ly.norm1.b, eps_, nullptr, 0, a, np, 0, nullptr, 0, st));
-    RT_OK(fb200_gemm(a, R, np, ly.qkv.w, np, R, 3 * d, ly.din, 1, ly.qkv.bias, 0, nullptr, 0, v, d, 2 * d, qkv, np, 0, st));
-    RT_OK(fb200_fsmn(v, d, d_cur, B, R, d, ly.fsmn, ly.fsmn_k, ly.din == d ? x : nullptr, ldx, mem, d, st));
-    RT_OK(fb200_attention(qkv, wqkv, 0, wqkv / np, qkv, wqkv, d, qkv, wqkv, 2 * d, wqkv / np, np, d_cur, d_cur, plan, B, R, R, max_t,
-                          heads_, d / heads_, scale, nullptr, 0, xs, np, 0, st));
-    RT_OK(fb200_gemm(xs, R, np, ly.out.w, np, R, d, d, 1, ly.out.bias, 0, mem, d, x1, d, 0, nullptr, np, 0, st));
-    RT_OK(fb200_layernorm(x1, d, R, d, ly.norm2.g, ly.norm2.b, eps_, nullptr, 0, xs, np, 0, nullptr, 0, st));
-    RT_OK(fb200_gemm(xs, R, np, ly.w1.w, np, R, ff_, d, 1, ly.w1.bias, 1, nullptr, 0, nullptr, 0, 0, h, np, 0, st));
-    RT_OK(fb200_gemm(h, R, np, ly.w2.w, np, R, d, ff_, 1, ly.w2.bias, 0, x1, d, x0, d, 0, nullptr, np, 0, st));
-    x = x0;
-    ldx = d;
+  if (small) {
+    const int32_t dims[2] = {R, B};
+    RT_OK(fb200_stack_run(enc_prog_, dims, 2, st));
+  } else {
+    RT_OK(fb200_attention_plan(d_cur, d_cur, B, plan, plan_cap, st));
+    RT_OK(encoder_ops(eb, R, B, max_t, st));
   }
-  RT_OK(fb200_layernorm(x, d, R, d, enc_after_.g, enc_after_.b, eps_, enc, d, halo, np, 1, d_cur, B, st));
   // predictor: k = 3 conv over the halo layout, alpha head, integrate-and-fire scan
   RT_OK(fb200_gemm(halo, R + B + 1, np, cif_conv_.w, np, R + B - 1, d, d, 3, cif_conv_.bias, 1, nullptr, 0, conv, d, 0, nullptr, np, 0, st));
   RT_OK(fb200_cif_alpha(conv, d, d_cur, B, R, d, cif_w_, cif_b_, 1.f, 0.f, alphas, st));
   RT_OK(fb200_cif_scan(alphas, d_cur, B, tail_, token_num, fire_pos, fire_rem, nullptr, st));
   return FB200_OK;
   };
-  RT_OK(run_graphed(GraphKey(slot, B, F, R, max_t, 0, 0), next == nullptr, issue_encoder));
+  RT_OK(run_graphed(GraphKey(slot, B, F, R, max_t, 0, 0), next == nullptr && !small, issue_encoder));
   std::vector<int32_t> tok(B), cu_tok(B + 1, 0);
   RT_CUDA(cudaMemcpyAsync(tok.data(), token_num, B * 4, cudaMemcpyDeviceToHost, stream_));
   t_launched = now_ms();
@@ -720,6 +877,8 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   for (int i = 0; i < B; ++i) cu_tok[i + 1] = cu_tok[i] + tok[i], max_l = std::max(max_l, tok[i]);
   const int L = cu_tok[B];
   if (L == 0 || max_l < 1) return FB200_OK;  // no utterance has a token (paraformer/model.py:514-515)
+  const bool small_dec = small && L <= kStackTokens;
+  if (small_dec) d_cut = small_dec_.d_cut;
   RT_CUDA(cudaMemcpyAsync(d_cut, cu_tok.data(), (B + 1) * 4, cudaMemcpyHostToDevice, stream_));
   float* embeds = arena_.get<float>((size_t)L * d);
   // decoder
@@ -738,44 +897,27 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
     set_error("runtime: activation slab too small for %d tokens", L);
     return FB200_EINVAL;
   }
+  DecBufs db = {encs, kv, qs, ys, hs, hf, t, t2, n2, b0, b1, embeds, logits, d_cut, d_cur, dplan};
+  if (small_dec) {
+    db = small_dec_;
+    embeds = db.embeds;
+    logits = db.logits;
+    encs = db.encs;  // (the time-stamp head reads the split of the encoder output too)
+  }
   auto issue_decoder = [&]() -> int {  // CIF integration + decoder + greedy pick: ~110 launches, graph-replayed like the encoder
   RT_OK(fb200_cif_integrate(enc, d, alphas, d_cur, d_cut, B, L, d, tail_, fire_pos, fire_rem, embeds, d, st));
-  RT_OK(fb200_split_rows(enc, d, R, d, encs, np, st));
-  RT_OK(fb200_gemm(encs, R, np, dec_kv_.w, np, R, dec_kv_.n, d, 1, dec_kv_.bias, 0, nullptr, 0, nullptr, 0, 0, kv, np, 0, st));
-  RT_OK(fb200_attention_plan(d_cut, d_cur, B, dplan, dplan_cap, st));
-  const float* y = embeds;
-  for (const DecLayer& ly : dec_) {
-    RT_OK(fb200_layernorm(y, d, L, d, ly.norm1.g, ly.norm1.b, eps_, nullptr, 0, ys, np, 0, nullptr, 0, st));
-    RT_OK(fb200_gemm(ys, L, np, ly.w1.w, np, L, ff_, d, 1, ly.w1.bias, 1, nullptr, 0, hf, ff_, 0, nullptr, np, 0, st));
-    RT_OK(fb200_layernorm(hf, ff_, L, ff_, ly.ffn_norm.g, ly.ffn_norm.b, eps_, nullptr, 0, hs, np, 0, nullptr, 0, st));
-    float* tt = (y == t) ? t2 : t;
-    RT_OK(fb200_gemm(hs, L, np, ly.w2.w, np, L, d, ff_, 1, ly.w2.bias, 0, nullptr, 0, tt, d, 0, nullptr, np, 0, st));
-    if (!ly.has_fsmn) {  // decoders3: FFN only, no residual (paraformer/decoder.py:102-108)
-      y = tt;
-      continue;
-    }
-    RT_OK(fb200_layernorm(tt, d, L, d, ly.norm2.g, ly.norm2.b, eps_, n2, d, nullptr, np, 0, nullptr, 0, st));
-    float* yo = (y == b0) ? b1 : b0;
-    RT_OK(fb200_fsmn(n2, d, d_cut, B, L, d, ly.fsmn, ly.fsmn_k, y, d, yo, d, st));  // x + conv(n2) + n2
-    if (ly.has_src) {
-      RT_OK(fb200_layernorm(yo, d, L, d, ly.norm3.g, ly.norm3.b, eps_, nullptr, 0, ys, np, 0, nullptr, 0, st));
-      RT_OK(fb200_gemm(ys, L, np, ly.q.w, np, L, d, d, 1, ly.q.bias, 0, nullptr, 0, nullptr, 0, 0, qs, np, 0, st));
-      const int j = ly.src_index;
-      RT_OK(fb200_attention(qs, wd, 0, wd / np, kv, wkv, j * 2 * d, kv, wkv, j * 2 * d + d, wkv / np, np, d_cut, d_cur, dplan, B, L, R,
-                            max_l, heads_, d / heads_, scale, nullptr, 0, ys, np, 0, st));
-      float* xo = (yo == b0) ? b1 : b0;
-      RT_OK(fb200_gemm(ys, L, np, ly.out.w, np, L, d, d, 1, ly.out.bias, 0, yo, d, xo, d, 0, nullptr, np, 0, st));
-      y = xo;
-    } else {
-      y = yo;
-    }
+  if (small_dec) {
+    const int32_t dims[3] = {L, R, B};
+    RT_OK(fb200_stack_run(dec_prog_, dims, 3, st));
+  } else {
+    RT_OK(fb200_split_rows(enc, d, R, d, encs, np, st));
+    RT_OK(fb200_attention_plan(d_cut, d_cur, B, dplan, dplan_cap, st));
+    RT_OK(decoder_ops(db, R, L, B, max_l, ldv, st));
   }
-  RT_OK(fb200_layernorm(y, d, L, d, dec_after_.g, dec_after_.b, eps_, nullptr, 0, ys, np, 0, nullptr, 0, st));
-  RT_OK(fb200_gemm(ys, L, np, dec_out_.w, np, L, vocab_, d, 1, dec_out_.bias, 0, nullptr, 0, logits, ldv, 0, nullptr, np, 0, st));
   RT_OK(fb200_argmax_logprob(logits, ldv, L, vocab_, ids, logp, st));
   return FB200_OK;
   };
-  RT_OK(run_graphed(GraphKey(slot | 0x100, B, F, R, max_t, L, max_l), next == nullptr, issue_decoder));
+  RT_OK(run_graphed(GraphKey(slot | 0x100, B, F, R, max_t, L, max_l), next == nullptr && !small_dec, issue_decoder));
   std::vector<int32_t> h_ids(L);
   RT_CUDA(cudaMemcpyAsync(h_ids.data(), ids, (size_t)L * 4, cudaMemcpyDeviceToHost, stream_));
   std::vector<int32_t> h_fire, h_fire_count, h_chars;

@@ -233,78 +233,26 @@ __device__ __forceinline__ StackTile stack_tile_rt(int i) {  // run-time index -
   return t;
 }
 
+__device__ __forceinline__ float ld_shared_f32_raw(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_shared_f32_raw(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
 // ---------------------------------------------------------------- LayerNorm rows ---------
 // Same arithmetic as layernorm_kernel<NV> (rowwise.cu): warp per row, row in registers, two-pass variance.
-template <int NV, bool FUSED>
-__device__ __noinline__ void stack_ln_rows(const StackLnOp& o, int rows, int batch, int warp_global, int warp_stride,
-                                           int lane, int ksplit) {
+template <int NV>
+__device__ __noinline__ void stack_ln_rows(const StackLnOp& o, int rows, int batch, int warp_global, int warp_stride, int lane) {
   const int dim = o.dim, nvec = dim >> 2, nparts = o.nparts;
   const int kp = round_up(dim, 64);
   for (int row = warp_global; row < rows; row += warp_stride) {
     const float4* xr = reinterpret_cast<const float4*>(o.x + (size_t)row * o.ld_x);
     float4 v[NV];
     float s = 0.f;
-    if (FUSED) {
-      // the split-K product's epilogue: K ranges summed in order, then + bias, then + residual; x is written back.
-      // Every load of the row is issued before the first sum (NV * ksplit 16-byte loads per lane in flight: one L2 round
-      // trip instead of NV of them); rows wider than 640 go range by range.
-      const float4* rr = o.p_res ? reinterpret_cast<const float4*>(o.p_res + (size_t)row * o.ld_res) : nullptr;
-      const float* prow = o.part + (size_t)row * o.ld_part;
-      if (NV <= 5) {
-        float4 t[NV <= 5 ? NV : 1][8];
-#pragma unroll
-        for (int i = 0; i < (NV <= 5 ? NV : 1); ++i) {
-          const int idx = lane + i * 32;
-#pragma unroll
-          for (int ks = 0; ks < 8; ++ks)
-            t[i][ks] = (idx < nvec && ks < ksplit) ? __ldcg(reinterpret_cast<const float4*>(prow + (size_t)ks * o.part_stride) + idx)
-                                                   : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-#pragma unroll
-        for (int i = 0; i < (NV <= 5 ? NV : 1); ++i) {
-          float4 a = t[i][0];
-#pragma unroll
-          for (int ks = 1; ks < 8; ++ks) {
-            if (ks < ksplit) {
-              a.x += t[i][ks].x; a.y += t[i][ks].y; a.z += t[i][ks].z; a.w += t[i][ks].w;
-            }
-          }
-          v[i] = a;
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < NV; ++i) {
-          const int idx = lane + i * 32;
-          float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (idx < nvec) {
-            a = __ldcg(reinterpret_cast<const float4*>(prow) + idx);
-            for (int ks = 1; ks < ksplit; ++ks) {
-              const float4 b = __ldcg(reinterpret_cast<const float4*>(prow + (size_t)ks * o.part_stride) + idx);
-              a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-            }
-          }
-          v[i] = a;
-        }
-      }
-#pragma unroll
-      for (int i = 0; i < NV; ++i) {
-        const int idx = lane + i * 32;
-        float4 a = v[i];
-        if (idx < nvec) {
-          if (o.p_bias) {
-            const float4 b = __ldg(reinterpret_cast<const float4*>(o.p_bias) + idx);
-            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-          }
-          if (rr) {
-            const float4 b = __ldcg(rr + idx);
-            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
-          }
-          reinterpret_cast<float4*>(const_cast<float*>(o.x) + (size_t)row * o.ld_x)[idx] = a;
-        }
-        v[i] = a;
-        s += (a.x + a.y) + (a.z + a.w);
-      }
-    } else {
+    {
 #pragma unroll
       for (int i = 0; i < NV; ++i) {
         const int idx = lane + i * 32;
@@ -363,6 +311,70 @@ __device__ __noinline__ void stack_ln_rows(const StackLnOp& o, int rows, int bat
       for (int c = dim + lane; c < kp; c += 32)
         for (int pp = 0; pp < nparts; ++pp) srow[pp * kp + c] = __float2bfloat16_rn(0.f);
     }
+  }
+}
+
+// LayerNorm behind a split-K product (dim <= 512, no halo): x = sum of the K ranges (in order) + bias + residual is
+// written back (it stays the residual stream) and normalised.  FOUR warps share a row -- a lane then has the 8 range loads
+// of ONE 16-byte vector in flight instead of 32 loads queued behind each other (the warp-per-row version spent 3 us in
+// four or five L2 round trips) -- and the row statistics meet in shared memory (fixed order).  Two rows per CTA at a time.
+__device__ __noinline__ void stack_ln_fused_rows(const StackLnOp& o, int rows, int ksplit, uint32_t red_sm) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int group = warp >> 2, wq = warp & 3;
+  const int dim = o.dim, nvec = dim >> 2, nparts = o.nparts;
+  const int kp = round_up(dim, 64);
+  const int idx = wq * 32 + lane;
+  const bool live = idx < nvec;
+  const uint32_t red = red_sm + (uint32_t)group * 32u;  // 4 partial sums + 4 partial square sums per group
+  for (int row = blockIdx.x + gridDim.x * group; row < rows; row += gridDim.x * 2) {
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (live) {
+      const float4* pr = reinterpret_cast<const float4*>(o.part + (size_t)row * o.ld_part) + idx;
+      float4 t[8];
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks)
+        t[ks] = ks < ksplit ? __ldcg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(pr) + (size_t)ks * o.part_stride))
+                            : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 bb = make_float4(0.f, 0.f, 0.f, 0.f), rr = bb;
+      if (o.p_bias) bb = __ldg(reinterpret_cast<const float4*>(o.p_bias) + idx);
+      if (o.p_res) rr = __ldcg(reinterpret_cast<const float4*>(o.p_res + (size_t)row * o.ld_res) + idx);
+      a = t[0];
+#pragma unroll
+      for (int ks = 1; ks < 8; ++ks)
+        if (ks < ksplit) {
+          a.x += t[ks].x; a.y += t[ks].y; a.z += t[ks].z; a.w += t[ks].w;
+        }
+      a.x += bb.x; a.y += bb.y; a.z += bb.z; a.w += bb.w;
+      a.x += rr.x; a.y += rr.y; a.z += rr.z; a.w += rr.w;
+      reinterpret_cast<float4*>(const_cast<float*>(o.x) + (size_t)row * o.ld_x)[idx] = a;
+    }
+    const float s = warp_sum((a.x + a.y) + (a.z + a.w));
+    if (lane == 0) st_shared_f32_raw(red + (uint32_t)wq * 4u, s);
+    asm volatile("bar.sync %0, 128;" ::"r"(2 + group) : "memory");
+    const float mean = ((ld_shared_f32_raw(red) + ld_shared_f32_raw(red + 4u)) + (ld_shared_f32_raw(red + 8u) + ld_shared_f32_raw(red + 12u))) / (float)dim;
+    float q = 0.f;
+    if (live) {
+      const float d0 = a.x - mean, d1 = a.y - mean, d2 = a.z - mean, d3 = a.w - mean;
+      q = (d0 * d0 + d1 * d1) + (d2 * d2 + d3 * d3);
+    }
+    q = warp_sum(q);
+    if (lane == 0) st_shared_f32_raw(red + 16u + (uint32_t)wq * 4u, q);
+    asm volatile("bar.sync %0, 128;" ::"r"(2 + group) : "memory");
+    const float var = ((ld_shared_f32_raw(red + 16u) + ld_shared_f32_raw(red + 20u)) + (ld_shared_f32_raw(red + 24u) + ld_shared_f32_raw(red + 28u))) / (float)dim;
+    const float rstd = rsqrtf(var + o.eps);
+    if (live) {
+      const float4 g = __ldg(reinterpret_cast<const float4*>(o.gamma) + idx);
+      const float4 b = __ldg(reinterpret_cast<const float4*>(o.beta) + idx);
+      const float yy[4] = {(a.x - mean) * rstd * g.x + b.x, (a.y - mean) * rstd * g.y + b.y, (a.z - mean) * rstd * g.z + b.z,
+                           (a.w - mean) * rstd * g.w + b.w};
+      if (o.out_f32) reinterpret_cast<float4*>(o.out_f32 + (size_t)row * o.ld_f32)[idx] = make_float4(yy[0], yy[1], yy[2], yy[3]);
+      if (o.out_split) store_split4(o.out_split + (size_t)row * (nparts * kp), kp, idx * 4, yy, nparts);
+    }
+    if (o.out_split) {
+      for (int c = dim + wq * 32 + lane; c < kp; c += 128)
+        for (int pp = 0; pp < nparts; ++pp) o.out_split[(size_t)row * (nparts * kp) + pp * kp + c] = __float2bfloat16_rn(0.f);
+    }
+    asm volatile("bar.sync %0, 128;" ::"r"(2 + group) : "memory");  // the statistics slots are free for the group's next row
   }
 }
 
@@ -812,11 +824,11 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
       const StackLnOp& o = op.u.ln;
       const int wg = blockIdx.x + grid * warp, ws = grid * (kStackThreads / 32);
       const int ksplit = o.part != nullptr ? last_ksplit : 1;  // the split-K GEMM op right before this op chose it
-      // (the recorder fuses a split-K reduction only into LayerNorms of at most 512 columns)
-      if (o.part != nullptr) stack_ln_rows<4, true>(o, rows, batch, wg, ws, lane, ksplit);
-      else if (o.dim <= 512) stack_ln_rows<4, false>(o, rows, batch, wg, ws, lane, ksplit);
-      else if (o.dim <= 640) stack_ln_rows<5, false>(o, rows, batch, wg, ws, lane, ksplit);
-      else stack_ln_rows<16, false>(o, rows, batch, wg, ws, lane, ksplit);
+      // (the recorder fuses a split-K reduction only into LayerNorms of at most 512 columns without the halo layout)
+      if (o.part != nullptr) stack_ln_fused_rows(o, rows, ksplit, bias_sm);
+      else if (o.dim <= 512) stack_ln_rows<4>(o, rows, batch, wg, ws, lane);
+      else if (o.dim <= 640) stack_ln_rows<5>(o, rows, batch, wg, ws, lane);
+      else stack_ln_rows<16>(o, rows, batch, wg, ws, lane);
     } else if (op.kind == kStFsmn) {
       // ================================================================ FSMN ============
       // out[r, c] = (v[r, c] (+ res[r, c])) + sum_j w[c, j] v[r + j - left, c]  (taps inside the utterance of r, in tap
@@ -1427,7 +1439,7 @@ extern "C" __attribute__((visibility("default"))) int fb200_stack_end(void* hand
     const bool last = i + 2 == pr->ops.size();
     if (g.out_split != nullptr || g.out_f32 == nullptr || g.f32_col0 != 0 || g.act != 0 || g.taps != 1 || l.x != g.out_f32 ||
         l.ld_x != g.ld_out || l.dim != g.n || a.rows != b.rows || a.rows_slot != b.rows_slot || !a.barrier_after ||
-        !(b.barrier_after || last) || g.k_blocks < 8 || g.k_blocks % 4 != 0 || g.n % 32 != 0 || g.n > 512)
+        !(b.barrier_after || last) || g.k_blocks < 8 || g.k_blocks % 4 != 0 || g.n % 32 != 0 || g.n > 512 || l.halo)
       continue;
     fuse_at.push_back((int)i);
     const int ksmax = (g.k_blocks % 8 == 0 && g.k_blocks >= 16) ? 8 : 4;
