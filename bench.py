@@ -272,10 +272,46 @@ def other_configs(job, eng, args):
         eng.recognize(wave10)
         lat.append((time.perf_counter() - t0) * 1e3)
     entry = {"workload": "one synthetic 10 s utterance, host waveform -> token ids, ParaformerEngine.recognize",
-             "ms_per_utterance": float(np.median(lat)), "value": 10.0 / (float(np.median(lat)) * 1e-3), "unit": "audio_s/s"}
+             "ms_per_utterance": float(np.median(lat)), "value": 10.0 / (float(np.median(lat)) * 1e-3), "unit": "audio_s/s",
+             "path": "request-stack (two persistent cooperative kernels)" if getattr(eng, "_small", None) else "per-op launches"}
     golden = os.path.join(ROOT, "tests", "golden", "stages_10s.npz")
     if os.path.exists(golden) and args.precision == "fp32":
         entry["ids_equal_reference_golden"] = bool(ids10 == np.load(golden)["token_int"].tolist())
+    # the same request through the native runtime (fb200_offline_infer: no Python between the kernels), and the weight
+    # stream it implies: every request reads all contraction weights once (hi + mid bf16 = 4 bytes per parameter)
+    try:
+        import tempfile
+
+        from funasr_b200 import runtime
+
+        d = tempfile.mkdtemp(prefix="fb200_bench_")
+        sd_t = state_dict()
+        runtime.export_model({k: v.numpy() for k, v in sd_t.items()}, d, cmvn=synth.synth_cmvn())
+        rec = runtime.OfflineRecognizer(d, device=job.local, precision="bf16" if args.precision == "bf16" else "fp32")
+        w10 = [wave10[0].numpy()]
+        for _ in range(5):
+            rec.recognize(w10)
+        nat = []
+        for _ in range(12):
+            t0 = time.perf_counter()
+            ids_n = rec.recognize(w10)
+            nat.append((time.perf_counter() - t0) * 1e3)
+        rec.close()
+        wbytes = (2.0 if args.precision == "bf16" else 4.0) * sum(v.numel() for k, v in sd_t.items()
+                                                                   if v.dim() >= 2 and not k.startswith("decoder.embed"))
+        del sd_t
+        ms = float(np.median(nat))
+        entry["native_runtime_ms"] = ms
+        entry["native_ids_equal"] = bool(list(ids_n[0]) == list(ids10))
+        peak = peaks().get("hbm_gbs")
+        entry["roofline"] = {"bound": "hbm", "achieved": wbytes / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                             "frac": (wbytes / (ms * 1e-3) / 1e9 / peak) if peak else None,
+                             "bytes": wbytes, "note": "weights streamed once per request / host-to-ids time of the native runtime"}
+        import shutil
+
+        shutil.rmtree(d, ignore_errors=True)
+    except Exception as exc:  # the sub-result is additional: never fail the bench line over it
+        entry["native_runtime_error"] = str(exc)[:200]
     out["configs[0]"] = entry
     # configs[4]: long-audio sweep through the same engine
     long_durs = [int(s * synth.SAMPLE_RATE) for s in (60, 120, 300, 600) for _ in range(8)]

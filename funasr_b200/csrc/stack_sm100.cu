@@ -12,17 +12,27 @@
 // (one release/acquire counter in global memory); independent neighbours (FSMN and attention of a layer) are not -- the
 // recorder derives that from the byte ranges each op reads and writes.
 //
-// Arithmetic: the GEMM, LayerNorm and FSMN ops compute bit for bit what the per-op kernels compute (same bf16 split
+// Arithmetic: GEMM (unsplit), LayerNorm and FSMN ops compute bit for bit what the per-op kernels compute (same bf16 split
 // operands, same term order per k-block, same epilogue, same two-pass LayerNorm, same tap order) -- the tile shapes
-// differ, the sums do not.  Attention is a streaming-softmax fp32 SIMT kernel over (utterance, head, <= 8 query rows)
-// items -- at this size spreading a few query rows over every SM beats eight 128-row tensor-core items -- so its
-// results differ from the tcgen05 attention kernel's in the last bits (both are checked against the oracle).
+// differ, the sums do not.  A product whose only consumer is the LayerNorm op behind it (out-projection, FFN w2) is cut
+// into K ranges, summed in a fixed order by that LayerNorm op (last-bit differences to the per-op path).  Attention runs
+// on the legacy tensor-core path (mma.sync m16n8k16, bf16 hi / mid operands, the same hi.mid + mid.hi + hi.hi products
+// as the tcgen05 kernel) over (utterance, head, <= 16 query rows) items: at this size spreading a few query rows over
+// every SM beats eight 128-row tcgen05 items.
 //
-// Small-M tiling: an SM takes in ~41 B/clk, so what bounds a phase is the bytes ONE CTA must ingest: the A tile
-// [bm x K] hi+mid and the W tile [bn x K] hi+mid.  bm (32..128 rows, in 32-row TMA boxes) and bn (32 / 64 columns) are
-// picked on the device per op from the ACTUAL row count so that the tiles cover the SMs in one round with the smallest
-// per-CTA ingest; programs are recorded once for a row CAPACITY and run with the request's row counts (`dims`).
-// The next GEMM's weights are prefetched into L2 (cp.async.bulk.prefetch.L2) while the current op runs.
+// What bounds a phase here (all measured, tools/stack_bench.py, tools/micro/*.cu, profiles/r02_request_stack.md):
+//   * a TMA instruction occupies its issuing warp for ~180-240 cycles whatever it moves -> operands are fetched as 4-d
+//     boxes (k-blocks x parts per instruction) by two producer warps;
+//   * tcgen05.mma with a <= 64-column tile costs ~41-55 cycles (A is re-read from shared memory), so the per-CTA time of
+//     a product is set by the NUMBER of MMAs (k-blocks x 4 x terms): only a K split shortens it;
+//   * TMA / MMA issue must sit behind elect.sync -- behind `lane == 0` the compiler wraps every UTMALDG / UTCHMMA in an
+//     ELECT + 7 x R2UR loop (~100 cycles apiece);
+//   * a device-wide barrier costs ~1.25 us (release, L2 atomic, acquire poll) + the skew between CTAs.
+//
+// Small-M tiling: bm (32..128 rows), bn (32 / 64 columns) and the K split are picked on the device per op from the
+// ACTUAL row count (by an otherwise idle warp, one op ahead); programs are recorded once for a row CAPACITY and run with
+// the request's row counts (`dims`).  The next GEMM's weights and the next op's parameter vectors are prefetched into L2
+// (cp.async.bulk.prefetch.L2) while the current op runs.
 #include <cuda.h>
 #include <math.h>
 #include <stdlib.h>
@@ -58,14 +68,13 @@ constexpr uint32_t kAtBox = 64 * 128;               // one [64 x 64] bf16 box
 constexpr uint32_t kAtPart = 2 * kAtBox;            // one part of K or V of a tile: dims 0..63 | 64..127
 constexpr uint32_t kAtSlot = 4 * kAtPart;           // 65536
 constexpr int kAtSlots = 3;
-constexpr uint32_t kAtQ = kAtSlots * kAtSlot;       // fp32 [8][128]
-constexpr uint32_t kAtP = kAtQ + 8 * 128 * 4;       // fp32 [8][64]
-constexpr uint32_t kAtSp = kAtP + 8 * 64 * 4;       // fp32 [4][8][64]
-constexpr uint32_t kAtStat = kAtSp + 4 * 8 * 64 * 4;  // fp32 corr[8], linv[8]
-constexpr uint32_t kAtEnd = kAtStat + 64;
+constexpr int kAtRows = 16;                         // query rows per item at most (one m16 MMA row block)
+constexpr uint32_t kAtQ = kAtSlots * kAtSlot;       // bf16 [2 parts][16 rows][128 dims], 16-byte chunks XOR-swizzled by the row
+constexpr uint32_t kAtP = kAtQ + 2 * 16 * 256;      // bf16 [2 parts][16 rows][64 keys], swizzled alike
+constexpr uint32_t kAtStat = kAtP + 2 * 16 * 128;   // fp32 [8 warps][16 rows]: per-warp row maxima, later row sums
+constexpr uint32_t kAtEnd = kAtStat + 8 * 16 * 4;
 static_assert(kAtSlots * kAtSlot <= kStRingBytes, "attention tiles live in the ring");
 static_assert(kAtEnd <= kStRingBytes + kStEpiBytes, "attention overlay must fit the ring + epilogue staging");
-static_assert(8 * 8 * 128 * 4 <= kAtSlot, "output partials alias tile slot 0");
 static_assert(kStSmemBytes <= 232448, "shared memory budget");
 
 enum StackOpKind { kStGemm = 0, kStLayerNorm = 1, kStFsmn = 2, kStAttention = 3 };
@@ -404,6 +413,26 @@ __device__ __forceinline__ uint2 ld_shared_u2(uint32_t addr) {
   return v;
 }
 
+__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_shared_u32(uint32_t addr, uint32_t v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+// four 8 x 8 b16 matrices; lane l supplies the row address of matrix l / 8, row l % 8
+__device__ __forceinline__ void ldmatrix_x4(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t addr, uint32_t (&r)[4]) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0, %1, %2, %3}, [%4];" : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(addr) : "memory");
+}
+// D += A (16 x 16, row) * B (16 x 8, col), bf16 operands, fp32 accumulators
+__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], const uint32_t* b) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
 // ---------------------------------------------------------------- the kernel -------------
 __global__ void __launch_bounds__(kStackThreads, 1)
 stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ maps, int n_ops, const StackDims dims,
@@ -545,7 +574,7 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
         const int nb = nx->batch_slot >= 0 ? dims.v[nx->batch_slot] : nx->batch;
         const int total_q = __ldg(na.cu_q + nb);
         int aq = (na.heads * total_q + grid - 1) / grid;
-        aq = aq < 1 ? 1 : (aq > 8 ? 8 : aq);
+        aq = aq < 1 ? 1 : (aq > kAtRows ? kAtRows : aq);
         int items = 0;
         for (;;) {
           items = 0;
@@ -554,7 +583,7 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
             const int kv = __ldg(na.cu_kv + b + 1) - __ldg(na.cu_kv + b);
             if (kv > 0) items += ((len + aq - 1) / aq) * na.heads;
           }
-          if (items <= grid || aq >= 8) break;
+          if (items <= grid || aq >= kAtRows) break;
           ++aq;
         }
         int b = 0, rem = blockIdx.x, q_beg = 0, q_len = 0, kv_beg = 0, kv_len = 0;
@@ -874,7 +903,7 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
         if (tid == 0) {  // query rows per item: the smallest AQ whose item count fits one round (capped at 8)
           const int total_q = __ldg(o.cu_q + batch);
           int a = (heads * total_q + grid - 1) / grid;
-          a = a < 1 ? 1 : (a > 8 ? 8 : a);
+          a = a < 1 ? 1 : (a > kAtRows ? kAtRows : a);
           int n_items = 0;
           for (;;) {
             n_items = 0;
@@ -883,7 +912,7 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
               const int kv = __ldg(o.cu_kv + b + 1) - __ldg(o.cu_kv + b);
               if (kv > 0) n_items += ((len + a - 1) / a) * heads;
             }
-            if (n_items <= grid || a >= 8) break;
+            if (n_items <= grid || a >= kAtRows) break;
             ++a;
           }
           asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(item_sm), "r"(a), "r"(n_items) : "memory");
@@ -928,38 +957,37 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
         };
         if (warp < 2)
           for (int t = 0; t < ntiles && t < kAtSlots; ++t) issue_tile(t);
-        // Q rows, pre-scaled like the reference (q * d_k^-0.5 before the product)
-        if (tid < 8 * 32) {
-          const int i = tid >> 5, c = (tid & 31) * 4;
-          float4 val = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (i < nq) {
-            const __nv_bfloat16* qp = o.q + (size_t)(q_beg + q0 + i) * o.ld_q + hoff + c;
-            for (int pp = 0; pp < nparts; ++pp) {
-              const uint2 raw = __ldcg(reinterpret_cast<const uint2*>(qp + (size_t)pp * o.q_ps));
-              val.x += __uint_as_float(raw.x << 16); val.y += __uint_as_float(raw.x & 0xffff0000u);
-              val.z += __uint_as_float(raw.y << 16); val.w += __uint_as_float(raw.y & 0xffff0000u);
-            }
-            val.x *= o.scale; val.y *= o.scale; val.z *= o.scale; val.w *= o.scale;
-          }
-          // Qt[d][row]: the eight rows' values of one dimension side by side (two LDS.128 per dimension in the score loop)
-          st_shared_f32(smem_base + kAtQ + (uint32_t)((c + 0) * 8 + i) * 4u, val.x);
-          st_shared_f32(smem_base + kAtQ + (uint32_t)((c + 1) * 8 + i) * 4u, val.y);
-          st_shared_f32(smem_base + kAtQ + (uint32_t)((c + 2) * 8 + i) * 4u, val.z);
-          st_shared_f32(smem_base + kAtQ + (uint32_t)((c + 3) * 8 + i) * 4u, val.w);
+        // ---- query rows as they lie in the split matrix (bf16 hi | mid): 16-byte chunks into the swizzled staging tile
+        for (int id = tid; id < 2 * kAtRows * 16; id += kStackThreads) {
+          const int pp = id >> 8, r = (id >> 4) & 15, c = id & 15;
+          uint4 val = make_uint4(0u, 0u, 0u, 0u);
+          if (r < nq && pp < nparts)
+            val = __ldcg(reinterpret_cast<const uint4*>(o.q + (size_t)(q_beg + q0 + r) * o.ld_q + hoff + (size_t)pp * o.q_ps + c * 8));
+          st_shared_v4(smem_base + kAtQ + (uint32_t)pp * 4096u + (uint32_t)r * 256u + (uint32_t)((c ^ (r & 7)) << 4), val.x, val.y, val.z, val.w);
         }
         __syncthreads();
         if (tracing && tid == 0 && item == (int)blockIdx.x) stamp(8 * oi + 1);
 
-        const uint8_t* sm = smem_raw + (smem_base - smem_u32(smem_raw));  // generic view of the overlay (plain loads: the
-                                                                          // compiler may batch and hoist them)
-        float oacc[8][4];
+        // m16n8k16 fragments: g = row / key-in-tile index, tq = column pair
+        const int g = lane >> 2, tq = lane & 3;
+        uint32_t qa[2][8][4];  // A fragments of Q: [part][k-step of 16 dims]
+        {
+          const int r = (lane & 7) + ((lane >> 3) & 1) * 8;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
+          for (int pp = 0; pp < 2; ++pp)
 #pragma unroll
-          for (int u = 0; u < 4; ++u) oacc[i][u] = 0.f;
-        float m_run = -INFINITY, l_run = 0.f;  // of row `warp` (uniform across the warp)
-        const int key = tid & 63, dq = tid >> 6;  // S phase: one key, one quarter of the head dimension
-        const int c4 = tid & 31, kq = tid >> 5;   // PV phase: four output columns, one eighth of the tile's keys
+            for (int ks = 0; ks < 8; ++ks) {
+              const int c = ks * 2 + (lane >> 4);
+              ldmatrix_x4(smem_base + kAtQ + (uint32_t)pp * 4096u + (uint32_t)r * 256u + (uint32_t)((c ^ (r & 7)) << 4), qa[pp][ks]);
+            }
+        }
+        float oacc[2][4];  // O: rows g / g + 8, dims warp * 16 + j * 8 + 2 tq (+1)
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+#pragma unroll
+          for (int u = 0; u < 4; ++u) oacc[j][u] = 0.f;
+        float m_run[2] = {-INFINITY, -INFINITY};  // rows g, g + 8 (every thread of a row holds the same values)
+        float l_part[2] = {0.f, 0.f};             // this thread's share of the row sums (its two keys of every tile)
 
         for (int t = 0; t < ntiles; ++t) {
           const int s = t % kAtSlots;
@@ -967,133 +995,179 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
           mbar_wait(att_bar(s), (att_par >> s) & 1u);
           att_par ^= 1u << s;
           if (tracing && tid == 0 && item == (int)blockIdx.x && t == 0) stamp(8 * oi + 2);
-          const uint8_t* slot = sm + (uint32_t)s * kAtSlot;
-          // ---- partial scores: S[i][key] over dims [dq*32, dq*32+32)
+          const uint32_t slot = smem_base + (uint32_t)s * kAtSlot;
+          // ---- S[16 x 8 keys of this warp] = Q K^T over 128 dims: hi.mid + mid.hi + hi.hi per 16-dim step
+          // (one accumulator per cross term: three independent MMA chains of 8 instead of one of 24 -- the phase is bound
+          // by the MMA latency, not by its rate)
+          float sc[4] = {0.f, 0.f, 0.f, 0.f}, sc1[4] = {0.f, 0.f, 0.f, 0.f}, sc2[4] = {0.f, 0.f, 0.f, 0.f};
           {
-            float sp[8];
+            const int key = warp * 8 + g;
+            const uint32_t krow = slot + (uint32_t)key * 128u + (uint32_t)tq * 4u;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) sp[i] = 0.f;
-            if (key < nvalid) {
-#pragma unroll 2
-              for (int d8 = 0; d8 < 4; ++d8) {
-                // dims [dq*32 + d8*8, +8) of key `key`: box dq/2, 16-byte chunk (dq%2)*4 + d8, swizzled by the row
-                const uint32_t koff = (uint32_t)(dq >> 1) * kAtBox + (uint32_t)key * 128u +
-                                      ((((uint32_t)(dq & 1) * 4u + (uint32_t)d8) ^ ((uint32_t)key & 7u)) << 4);
-                float kf[8];
-                bf16x8_to_f32(*reinterpret_cast<const uint4*>(slot + koff), kf);
-                if (nparts > 1) {
-                  float km[8];
-                  bf16x8_to_f32(*reinterpret_cast<const uint4*>(slot + kAtPart + koff), km);
-#pragma unroll
-                  for (int u = 0; u < 8; ++u) kf[u] += km[u];
-                }
-                // all eight rows in lock step (rows past aq hold zeros): eight independent FMA chains per thread
-                const float4* qt = reinterpret_cast<const float4*>(sm + kAtQ) + (dq * 32 + d8 * 8) * 2;
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                  const float4 qa = qt[u * 2], qb = qt[u * 2 + 1];
-                  sp[0] = fmaf(qa.x, kf[u], sp[0]); sp[1] = fmaf(qa.y, kf[u], sp[1]);
-                  sp[2] = fmaf(qa.z, kf[u], sp[2]); sp[3] = fmaf(qa.w, kf[u], sp[3]);
-                  sp[4] = fmaf(qb.x, kf[u], sp[4]); sp[5] = fmaf(qb.y, kf[u], sp[5]);
-                  sp[6] = fmaf(qb.z, kf[u], sp[6]); sp[7] = fmaf(qb.w, kf[u], sp[7]);
-                }
+            for (int ks = 0; ks < 8; ++ks) {
+              const uint32_t kb = krow + (uint32_t)(ks >> 2) * kAtBox;
+              const uint32_t c0 = (uint32_t)((((ks & 3) * 2) ^ (key & 7)) << 4), c1 = (uint32_t)((((ks & 3) * 2 + 1) ^ (key & 7)) << 4);
+              uint32_t bh[2], bm[2] = {0u, 0u};
+              bh[0] = ld_shared_u32(kb + c0);
+              bh[1] = ld_shared_u32(kb + c1);
+              if (nparts > 1) {
+                bm[0] = ld_shared_u32(kb + kAtPart + c0);
+                bm[1] = ld_shared_u32(kb + kAtPart + c1);
+                mma_bf16_16816(sc1, qa[0][ks], bm);
+                mma_bf16_16816(sc2, qa[1][ks], bh);
               }
+              mma_bf16_16816(sc, qa[0][ks], bh);
             }
 #pragma unroll
-            for (int i = 0; i < 8; ++i) st_shared_f32(smem_base + kAtSp + (uint32_t)((dq * 8 + i) * 64 + key) * 4u, sp[i]);
+            for (int u = 0; u < 4; ++u) sc[u] = (sc1[u] + sc2[u]) + sc[u];  // small terms first
+          }
+          // ---- row maxima across the tile: quad, then the eight warps through shared memory
+          const int k0 = warp * 8 + tq * 2;
+          const bool v0 = k0 < nvalid, v1 = k0 + 1 < nvalid;
+          sc[0] = v0 ? sc[0] * o.scale : -INFINITY;
+          sc[1] = v1 ? sc[1] * o.scale : -INFINITY;
+          sc[2] = v0 ? sc[2] * o.scale : -INFINITY;
+          sc[3] = v1 ? sc[3] * o.scale : -INFINITY;
+          {
+            float mx0 = fmaxf(sc[0], sc[1]), mx1 = fmaxf(sc[2], sc[3]);
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+            mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+            mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+            if (tq == 0) {
+              st_shared_f32(smem_base + kAtStat + (uint32_t)(warp * 16 + g) * 4u, mx0);
+              st_shared_f32(smem_base + kAtStat + (uint32_t)(warp * 16 + g + 8) * 4u, mx1);
+            }
+          }
+          // (the last tile's value rows past the utterance may hold anything: zero them so that 0 * garbage stays 0)
+          if (nvalid < kAtTile) {
+            for (int id = tid; id < (kAtTile - nvalid) * 16 * nparts; id += kStackThreads) {
+              const int pp = id / ((kAtTile - nvalid) * 16), rem2 = id - pp * (kAtTile - nvalid) * 16;
+              const int r = nvalid + (rem2 >> 4), c = rem2 & 15;
+              st_shared_v4(slot + 2 * kAtPart + (uint32_t)pp * kAtPart + (uint32_t)(c >> 3) * kAtBox + (uint32_t)r * 128u + (uint32_t)((c & 7) << 4), 0u, 0u, 0u, 0u);
+            }
           }
           __syncthreads();
-          // ---- softmax of row `warp` over this tile (lanes: keys lane, lane + 32), running max / sum
-          if (warp < aq) {
-            const float* spp = reinterpret_cast<const float*>(sm + kAtSp);
-            float s0 = -INFINITY, s1 = -INFINITY;
-            if (lane < nvalid) s0 = ((spp[(0 * 8 + warp) * 64 + lane] + spp[(1 * 8 + warp) * 64 + lane]) + spp[(2 * 8 + warp) * 64 + lane]) + spp[(3 * 8 + warp) * 64 + lane];
-            if (lane + 32 < nvalid)
-              s1 = ((spp[(0 * 8 + warp) * 64 + lane + 32] + spp[(1 * 8 + warp) * 64 + lane + 32]) + spp[(2 * 8 + warp) * 64 + lane + 32]) + spp[(3 * 8 + warp) * 64 + lane + 32];
-            const float mx = warp_max(fmaxf(s0, s1));
-            const float m_new = fmaxf(m_run, mx);
-            const float corr = expf(m_run - m_new);  // exp(-inf) = 0 on the first tile
-            const float p0 = lane < nvalid ? expf(s0 - m_new) : 0.f;
-            const float p1 = lane + 32 < nvalid ? expf(s1 - m_new) : 0.f;
-            const float sum = warp_sum(p0 + p1);
-            l_run = l_run * corr + sum;
-            m_run = m_new;
-            st_shared_f32(smem_base + kAtP + (uint32_t)(lane * 8 + warp) * 4u, p0);  // Pt[key][row]
-            st_shared_f32(smem_base + kAtP + (uint32_t)((lane + 32) * 8 + warp) * 4u, p1);
-            if (lane == 0) st_shared_f32(smem_base + kAtStat + (uint32_t)warp * 4u, corr);
-          } else {  // rows past aq: keep their (never stored) accumulators finite
-            st_shared_f32(smem_base + kAtP + (uint32_t)(lane * 8 + warp) * 4u, 0.f);
-            st_shared_f32(smem_base + kAtP + (uint32_t)((lane + 32) * 8 + warp) * 4u, 0.f);
-            if (lane == 0) st_shared_f32(smem_base + kAtStat + (uint32_t)warp * 4u, 0.f);
+          float corr[2];
+          {
+            float mn0 = m_run[0], mn1 = m_run[1];
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+              mn0 = fmaxf(mn0, ld_shared_f32(smem_base + kAtStat + (uint32_t)(w * 16 + g) * 4u));
+              mn1 = fmaxf(mn1, ld_shared_f32(smem_base + kAtStat + (uint32_t)(w * 16 + g + 8) * 4u));
+            }
+            corr[0] = expf(m_run[0] - mn0);  // exp(-inf) = 0 on the first tile
+            corr[1] = expf(m_run[1] - mn1);
+            m_run[0] = mn0;
+            m_run[1] = mn1;
+          }
+          // ---- probabilities of this warp's keys -> bf16 hi / mid in the staging tile (the A operand of P V)
+          {
+            const float p0 = v0 ? expf(sc[0] - m_run[0]) : 0.f, p1 = v1 ? expf(sc[1] - m_run[0]) : 0.f;
+            const float p2 = v0 ? expf(sc[2] - m_run[1]) : 0.f, p3 = v1 ? expf(sc[3] - m_run[1]) : 0.f;
+            l_part[0] = l_part[0] * corr[0] + (p0 + p1);
+            l_part[1] = l_part[1] * corr[1] + (p2 + p3);
+            const __nv_bfloat162 h01 = __floats2bfloat162_rn(p0, p1), h23 = __floats2bfloat162_rn(p2, p3);
+            const __nv_bfloat162 m01 = __floats2bfloat162_rn(p0 - __low2float(h01), p1 - __high2float(h01));
+            const __nv_bfloat162 m23 = __floats2bfloat162_rn(p2 - __low2float(h23), p3 - __high2float(h23));
+            const uint32_t pa0 = smem_base + kAtP + (uint32_t)g * 128u + (uint32_t)((warp ^ (g & 7)) << 4) + (uint32_t)tq * 4u;
+            const uint32_t pa1 = smem_base + kAtP + (uint32_t)(g + 8) * 128u + (uint32_t)((warp ^ (g & 7)) << 4) + (uint32_t)tq * 4u;
+            st_shared_u32(pa0, *reinterpret_cast<const uint32_t*>(&h01));
+            st_shared_u32(pa1, *reinterpret_cast<const uint32_t*>(&h23));
+            st_shared_u32(pa0 + 2048u, *reinterpret_cast<const uint32_t*>(&m01));
+            st_shared_u32(pa1 + 2048u, *reinterpret_cast<const uint32_t*>(&m23));
           }
           __syncthreads();
-          // ---- O[i][c4*4 .. +3] (partial over this thread's eighth of the keys) = O * corr + P . V
-          {
-            const float4* stat4 = reinterpret_cast<const float4*>(sm + kAtStat);
-            const float4* pt4 = reinterpret_cast<const float4*>(sm + kAtP);
-            {
-              const float4 ca = stat4[0], cb = stat4[1];
-              const float cr[8] = {ca.x, ca.y, ca.z, ca.w, cb.x, cb.y, cb.z, cb.w};
+          // ---- O[16 x 16 dims of this warp] = O * corr + P V over the tile's 64 keys
 #pragma unroll
-              for (int i = 0; i < 8; ++i)
-#pragma unroll
-                for (int u = 0; u < 4; ++u) oacc[i][u] *= cr[i];
-            }
-#pragma unroll 2
-            for (int kk = 0; kk < 8; ++kk) {
-              const int ky = kq * 8 + kk;
-              if (ky < nvalid) {
-                // columns [c4*4, +4) of value row ky: box c4/16, byte (c4%16)*8 of the 128-byte row, chunk swizzled by the row
-                const uint8_t* vp = slot + 2 * kAtPart + (uint32_t)(c4 >> 4) * kAtBox + (uint32_t)ky * 128u +
-                                    (((((uint32_t)c4 & 15u) >> 1) ^ ((uint32_t)ky & 7u)) << 4) + ((uint32_t)c4 & 1u) * 8u;
-                uint2 raw = *reinterpret_cast<const uint2*>(vp);
-                float v0 = __uint_as_float(raw.x << 16), v1 = __uint_as_float(raw.x & 0xffff0000u);
-                float v2 = __uint_as_float(raw.y << 16), v3 = __uint_as_float(raw.y & 0xffff0000u);
-                if (nparts > 1) {
-                  raw = *reinterpret_cast<const uint2*>(vp + kAtPart);
-                  v0 += __uint_as_float(raw.x << 16); v1 += __uint_as_float(raw.x & 0xffff0000u);
-                  v2 += __uint_as_float(raw.y << 16); v3 += __uint_as_float(raw.y & 0xffff0000u);
-                }
-                const float4 pa = pt4[ky * 2], pb = pt4[ky * 2 + 1];
-                const float pr[8] = {pa.x, pa.y, pa.z, pa.w, pb.x, pb.y, pb.z, pb.w};
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                  oacc[i][0] = fmaf(pr[i], v0, oacc[i][0]); oacc[i][1] = fmaf(pr[i], v1, oacc[i][1]);
-                  oacc[i][2] = fmaf(pr[i], v2, oacc[i][2]); oacc[i][3] = fmaf(pr[i], v3, oacc[i][3]);
-                }
-              }
-            }
+          for (int j = 0; j < 2; ++j) {
+            oacc[j][0] *= corr[0]; oacc[j][1] *= corr[0];
+            oacc[j][2] *= corr[1]; oacc[j][3] *= corr[1];
           }
-          __syncthreads();  // tile consumed: its slot, the score partials and P may be overwritten
+          {
+            const int pr = (lane & 7) + ((lane >> 3) & 1) * 8;          // P: ldmatrix row of this lane
+            const int mi = lane >> 3;                                   // V: matrix index of this lane
+            const int vkey = ((mi & 1) << 3) + (lane & 7);              //    key within the 16-key step
+            const int vdim = warp * 16 + ((mi >> 1) << 3);              //    first dim of its 8 x 8 block
+            const uint32_t vbase = slot + 2 * kAtPart + (uint32_t)(vdim >> 6) * kAtBox;
+            const int vchunk = (vdim & 63) >> 3;
+            float t1[2][4], t2[2][4];  // the hi.mid and mid.hi terms of this tile (independent MMA chains)
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+              for (int u = 0; u < 4; ++u) t1[j][u] = t2[j][u] = 0.f;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              uint32_t ph[4], pm[4] = {0u, 0u, 0u, 0u}, vh[4], vm[4] = {0u, 0u, 0u, 0u};
+              const int pc = kk * 2 + (lane >> 4);
+              const uint32_t paddr = smem_base + kAtP + (uint32_t)pr * 128u + (uint32_t)((pc ^ (pr & 7)) << 4);
+              const int key = kk * 16 + vkey;
+              const uint32_t vaddr = vbase + (uint32_t)key * 128u + (uint32_t)((vchunk ^ (key & 7)) << 4);
+              ldmatrix_x4(paddr, ph);
+              ldmatrix_x4_trans(vaddr, vh);
+              if (nparts > 1) {
+                ldmatrix_x4(paddr + 2048u, pm);
+                ldmatrix_x4_trans(vaddr + kAtPart, vm);
+                mma_bf16_16816(t1[0], ph, vm);
+                mma_bf16_16816(t1[1], ph, vm + 2);
+                mma_bf16_16816(t2[0], pm, vh);
+                mma_bf16_16816(t2[1], pm, vh + 2);
+              }
+              mma_bf16_16816(oacc[0], ph, vh);
+              mma_bf16_16816(oacc[1], ph, vh + 2);
+            }
+#pragma unroll
+            for (int j = 0; j < 2; ++j)
+#pragma unroll
+              for (int u = 0; u < 4; ++u) oacc[j][u] += t1[j][u] + t2[j][u];
+          }
+          __syncthreads();  // tile consumed: its slot, the row maxima and P may be overwritten
           if (warp < 2 && t + kAtSlots < ntiles) issue_tile(t + kAtSlots);
         }
         if (tracing && tid == 0 && item == (int)blockIdx.x) stamp(8 * oi + 3);
-        // ---- sum the eight key-eighths (fixed order), normalise, store
-        if (warp < aq && lane == 0) st_shared_f32(smem_base + kAtStat + 32u + (uint32_t)warp * 4u, 1.f / l_run);
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_base + (uint32_t)(((kq * 8 + i) * 128) + c4 * 4) * 4u),
-                         "f"(oacc[i][0]), "f"(oacc[i][1]), "f"(oacc[i][2]), "f"(oacc[i][3])
-                         : "memory");
-        __syncthreads();
+        // ---- row sums: quad, then the eight warps (fixed order); normalise, store
         {
-          const int i = tid >> 5;  // row i, columns c4*4..+3
-          if (i < nq) {
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float4 pv = ld_shared_f4(smem_base + (uint32_t)(((e * 8 + i) * 128) + c4 * 4) * 4u);
-              acc.x += pv.x; acc.y += pv.y; acc.z += pv.z; acc.w += pv.w;
-            }
-            const float inv = ld_shared_f32(smem_base + kAtStat + 32u + (uint32_t)i * 4u);
-            const float yy[4] = {acc.x * inv, acc.y * inv, acc.z * inv, acc.w * inv};
-            const size_t row = (size_t)(q_beg + q0 + i);
-            const int col = hoff + c4 * 4;
-            if (o.out_f32) *reinterpret_cast<float4*>(o.out_f32 + row * o.ld_out + col) = make_float4(yy[0], yy[1], yy[2], yy[3]);
-            if (o.out_split) store_split4(o.out_split + row * (size_t)(o.out_parts * o.out_kp), o.out_kp, col, yy, o.out_parts);
+          float l0 = l_part[0], l1 = l_part[1];
+          l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+          l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+          l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+          l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+          if (tq == 0) {
+            st_shared_f32(smem_base + kAtStat + (uint32_t)(warp * 16 + g) * 4u, l0);
+            st_shared_f32(smem_base + kAtStat + (uint32_t)(warp * 16 + g + 8) * 4u, l1);
           }
         }
-        __syncthreads();  // the partials (tile slot 0) and the statistics are free for the next item
+        __syncthreads();
+        {
+          float l0 = 0.f, l1 = 0.f;
+#pragma unroll
+          for (int w = 0; w < 8; ++w) {
+            l0 += ld_shared_f32(smem_base + kAtStat + (uint32_t)(w * 16 + g) * 4u);
+            l1 += ld_shared_f32(smem_base + kAtStat + (uint32_t)(w * 16 + g + 8) * 4u);
+          }
+          const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+#pragma unroll
+          for (int j = 0; j < 2; ++j) {
+            const int col = hoff + warp * 16 + j * 8 + tq * 2;
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+              const int r = g + hf * 8;
+              if (r < nq) {
+                const float y0 = oacc[j][hf * 2] * (hf ? inv1 : inv0), y1 = oacc[j][hf * 2 + 1] * (hf ? inv1 : inv0);
+                const size_t row = (size_t)(q_beg + q0 + r);
+                if (o.out_f32) *reinterpret_cast<float2*>(o.out_f32 + row * o.ld_out + col) = make_float2(y0, y1);
+                if (o.out_split) {
+                  __nv_bfloat16* srow = o.out_split + row * (size_t)(o.out_parts * o.out_kp);
+                  const __nv_bfloat162 h = __floats2bfloat162_rn(y0, y1);
+                  *reinterpret_cast<__nv_bfloat162*>(srow + col) = h;
+                  if (o.out_parts > 1)
+                    *reinterpret_cast<__nv_bfloat162*>(srow + o.out_kp + col) = __floats2bfloat162_rn(y0 - __low2float(h), y1 - __high2float(h));
+                }
+              }
+            }
+          }
+        }
+        __syncthreads();  // the staging tiles and the statistics are free for the next item
       }
     }
 

@@ -391,8 +391,10 @@ int fb200_ctc_collapse(const int32_t* ids, const int32_t* cu_rows, int batch, ui
  * fb200_stack_run launches the program: one CTA per SM, tensor memory / barriers / shared-memory rings set up once, the
  * ops walked in order with a device-wide barrier wherever an op reads or overwrites what an op since the previous
  * barrier wrote or read (decided from the byte ranges at record time; the FSMN and attention of a layer share a phase).
- * GEMM / LayerNorm / FSMN results are bit-identical to the per-op kernels'; attention is an fp32 streaming-softmax
- * SIMT kernel over (utterance, head, <= 8 query rows) items (last-bit differences to the tcgen05 kernel).
+ * Unsplit GEMM, LayerNorm and FSMN results are bit-identical to the per-op kernels'; a product consumed only by the
+ * LayerNorm call right behind it is cut into K ranges which that LayerNorm sums in a fixed order; attention runs the same
+ * hi.mid + mid.hi + hi.hi bf16 products on mma.sync over (utterance, head, <= 16 query rows) items (last-bit differences
+ * to the tcgen05 kernel in both cases; tests/test_gpu_stack.py, ids of configs[0] == the reference's golden ids).
  * Replaces, for small requests, the per-module walk of SANMEncoder.forward (funasr/models/sanm/encoder.py:361-430) and
  * ParaformerSANMDecoder.forward (funasr/models/paraformer/decoder.py:395-404): the reference runs those as ~1700 eager
  * torch kernels per request.

@@ -1,6 +1,6 @@
 """Request-stack path (csrc/stack_sm100.cu): programs recorded from the per-op calls and run as ONE persistent
 cooperative kernel must reproduce the per-op kernels -- bit for bit for GEMM / LayerNorm / FSMN (same sums, other tiles),
-within fp32 rounding for attention (fp32 SIMT streaming softmax vs the SIMT check kernel) -- and the whole engine must
+within the 16-bit-mantissa operand rounding for attention (bf16 hi / mid products on mma.sync vs the fp32 SIMT check kernel) -- and the whole engine must
 return the reference's token ids for BASELINE configs[0] (tests/golden/stages_10s.npz) through it."""
 import os
 
@@ -105,7 +105,8 @@ def test_stack_layernorm_fsmn_equal_per_op_kernels():
     ([167], [167]),                 # one 10 s utterance, self-attention
     ([71], [167]),                  # its decoder cross-attention
     ([5, 130, 1, 64], [40, 200, 3, 13]),  # ragged batch, more than one key tile, a one-row utterance
-    ([256], [256]),                 # capacity: 8 query rows per item, two rounds
+    ([256], [256]),                 # capacity: 7 query rows per item
+    ([200, 56], [256, 1]),          # a one-key utterance; four full key tiles
 ])
 def test_stack_attention_matches_simt_check_kernel(q_lens, kv_lens):
     qcap, kcap, bcap, d = 256, 257, 8, 512
@@ -128,7 +129,7 @@ def test_stack_attention_matches_simt_check_kernel(q_lens, kv_lens):
     prog.run([lq, lk, b])
     torch.cuda.synchronize()
     err = float((want - got[:lq]).abs().max() / want.abs().max())
-    assert err < 2e-6, err
+    assert err < 3e-5, err  # hi.mid + mid.hi + hi.hi products on the tensor cores (mma.sync) against the fp32 check kernel
     hi, mid = got_s[:lq, :d].float(), got_s[:lq, d:].float()
     assert float((hi + mid - got[:lq]).abs().max() / got[:lq].abs().max()) < 2e-5
     prog.close()
