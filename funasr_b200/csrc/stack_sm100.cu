@@ -251,6 +251,41 @@ __device__ __forceinline__ void st_shared_f32_raw(uint32_t addr, float v) {
   asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
 }
 
+// pick_tile_cfg by a whole warp: lane = candidate (2 passes x 8 shapes), the cheapest wins, ties go to the earlier candidate
+// -- the same choice as the sequential walk, in ~1/10 of the dependent instructions (the look-ahead warp was the last to
+// reach the barrier of the short phases).
+__device__ __forceinline__ TileCfg pick_tile_cfg_warp(int m, int ncols, int k_blocks, int nparts, int grid, int ksplit_max, int lane) {
+  const int pass = (lane >> 3) & 1, ci = lane & 7;
+  const int terms = nparts == 1 ? 1 : 3;
+  const StackTile t = stack_tile_rt(ci);
+  const int ks = pass == 0 ? 1 : ksplit_max;
+  const bool pass_ok = pass == 0 || (ksplit_max > 1 && (k_blocks & (ksplit_max - 1)) == 0);
+  const int kb_unit = pass == 0 ? k_blocks : k_blocks / (ksplit_max > 0 ? ksplit_max : 1);
+  const int tm = (m + t.bm - 1) / t.bm, tn = (ncols + t.bn - 1) / t.bn;
+  unsigned key = 0xffffffffu;
+  if (lane < 16 && pass_ok && (kb_unit & (t.kbs - 1)) == 0) {
+    const int units = tm * tn * ks;
+    const int rounds = units <= grid ? 1 : (units <= 2 * grid ? 2 : (units + grid - 1) / grid);
+    const int ingest = (t.bm + t.bn) * nparts * kb_unit * 2;
+    const int per_mma = (t.bn >> 1) > 40 ? (t.bn >> 1) : 40;
+    const int mma = kb_unit * 4 * terms * per_mma;
+    const int cost = rounds * ((ingest > mma ? ingest : mma) + 1500) + (ks > 1 ? 300 * ks : 0);
+    key = ((unsigned)(cost < (1 << 27) ? cost : (1 << 27) - 1) << 4) | (unsigned)lane;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned other = __shfl_xor_sync(0xffffffffu, key, o);
+    key = other < key ? other : key;
+  }
+  const int win = (int)(key & 15u);
+  TileCfg best;
+  best.idx = win & 7;
+  best.tiles_m = __shfl_sync(0xffffffffu, tm, win);
+  best.tiles_n = __shfl_sync(0xffffffffu, tn, win);
+  best.ksplit = __shfl_sync(0xffffffffu, ks, win);
+  return best;
+}
+
 // ---------------------------------------------------------------- LayerNorm rows ---------
 // Same arithmetic as layernorm_kernel<NV> (rowwise.cu): warp per row, row in registers, two-pass variance.
 template <int NV>
@@ -555,19 +590,23 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
     if (op.next_gemm > prefetched && op.next_gemm < n_ops) prefetched = op.next_gemm;
     // look-ahead on an otherwise idle thread: the tile shape of the next GEMM op (a few hundred dependent instructions
     // that used to sit in front of every product's first load) and the work split of an attention op right behind this one
-    if (warp == 7 && lane == 0) {
+    if (warp == 7) {
       const int target = op.next_gemm;
-      if (target < n_ops && target != cfg_done) {
+      if (target < n_ops && target != cfg_done) {  // (warp-uniform)
         const StackOp* nx = ops + target;
         const int nrows = nx->rows_slot >= 0 ? dims.v[nx->rows_slot] : nx->rows;
         const int ncols_n = nx->u.g.out_split ? nx->u.g.out_kp : nx->u.g.n;
-        const TileCfg c = pick_tile_cfg(nrows, ncols_n, nx->u.g.taps * nx->u.g.k_blocks, nx->u.g.nparts, grid,
-                                        nx->u.g.taps == 1 ? nx->u.g.ksplit_max : 1);
-        const uint32_t slot = cfg_sm + (uint32_t)((gemm_count + (op.kind == kStGemm ? 1 : 0)) & 1) * 32u;
-        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "r"(c.idx), "r"(c.tiles_m), "r"(c.tiles_n), "r"(c.ksplit) : "memory");
-        asm volatile("st.shared.b32 [%0], %1;" ::"r"(slot + 16u), "r"(target) : "memory");
+        const TileCfg c = pick_tile_cfg_warp(nrows, ncols_n, nx->u.g.taps * nx->u.g.k_blocks, nx->u.g.nparts, grid,
+                                             nx->u.g.taps == 1 ? nx->u.g.ksplit_max : 1, lane);
+        if (lane == 0) {
+          const uint32_t slot = cfg_sm + (uint32_t)((gemm_count + (op.kind == kStGemm ? 1 : 0)) & 1) * 32u;
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(slot), "r"(c.idx), "r"(c.tiles_m), "r"(c.tiles_n), "r"(c.ksplit) : "memory");
+          asm volatile("st.shared.b32 [%0], %1;" ::"r"(slot + 16u), "r"(target) : "memory");
+        }
         cfg_done = target;
       }
+    }
+    if (warp == 7 && lane == 0) {
       if (oi + 1 < n_ops && ops[oi + 1].kind == kStAttention) {
         const StackOp* nx = ops + oi + 1;
         const StackAttnOp& na = nx->u.a;
@@ -657,8 +696,8 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
               }
             }
           }
-          if (trace != nullptr && blockIdx.x == 0 && a_role) stamp(8 * oi + 1);
         }
+        if (leader && trace != nullptr && blockIdx.x == 0 && warp == 0) stamp(8 * oi + 1);
         {  // the barrier parities live in every lane: take the elected lane's copy
           const unsigned who = __ballot_sync(0xffffffffu, leader);
           par_empty = __shfl_sync(0xffffffffu, par_empty, __ffs(who) - 1);
@@ -798,9 +837,48 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
               for (int j = 0; j < 32; ++j)
                 if (col0 + j >= n) y[j] = 0.f;
             }
+            const bool do_f32 = has_f32 && col0 >= f32_col0;
+            if (!(flags & 32)) {
+              // plain stores: a thread owns 32 consecutive columns of its row (128 B of fp32, 64 B per bf16 part).  The
+              // TMA-store version (staging boxes + cp.async.bulk) published its bytes ~1.2 us later at the barrier.
+              if (row_ok) {
+                if (do_f32) {
+                  float* dst = g.out_f32 + (size_t)(part_r0 + row) * g.ld_out + (col0 - f32_col0);
+                  if (full) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) reinterpret_cast<float4*>(dst)[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
+                  } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                      if (col0 + j < n) dst[j] = y[j];
+                  }
+                }
+                if (has_split) {
+                  __nv_bfloat16* dst = g.out_split + (size_t)row * (out_parts * out_kp) + col0;
+#pragma unroll
+                  for (int pp = 0; pp < 2; ++pp) {
+                    if (pp < out_parts) {
+#pragma unroll
+                      for (int q = 0; q < 4; ++q) {
+                        uint32_t w[4];
+#pragma unroll
+                        for (int u = 0; u < 4; ++u) {
+                          const int j = q * 8 + u * 2;
+                          const __nv_bfloat162 h = __floats2bfloat162_rn(y[j], y[j + 1]);
+                          w[u] = *reinterpret_cast<const uint32_t*>(&h);
+                          y[j] -= __low2float(h);
+                          y[j + 1] -= __high2float(h);
+                        }
+                        reinterpret_cast<uint4*>(dst + (size_t)pp * out_kp)[q] = make_uint4(w[0], w[1], w[2], w[3]);
+                      }
+                    }
+                  }
+                }
+              }
+              continue;
+            }
             if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             __syncwarp();
-            const bool do_f32 = has_f32 && col0 >= f32_col0;
             if (do_f32) {
 #pragma unroll
               for (int j = 0; j < 8; ++j)
@@ -846,6 +924,11 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
         tl = t;
         if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // this warp's stores have landed
         if (tracing && warp == 2) stamp(8 * oi + 5);
+        if (trace != nullptr && warp == 2 && lane == 0) {  // slot 4 of a GEMM op: the LAST CTA's stores landed
+          unsigned long long tt;
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(tt));
+          atomicMax(trace + 8 * oi + 4, tt);
+        }
         __syncwarp();
       }
     } else if (op.kind == kStLayerNorm) {
@@ -966,8 +1049,8 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
           st_shared_v4(smem_base + kAtQ + (uint32_t)pp * 4096u + (uint32_t)r * 256u + (uint32_t)((c ^ (r & 7)) << 4), val.x, val.y, val.z, val.w);
         }
         __syncthreads();
-        if (tracing && tid == 0 && item == (int)blockIdx.x) stamp(8 * oi + 1);
 
+        if (tracing && tid == 0 && item == (int)blockIdx.x) stamp(8 * oi + 1);
         // m16n8k16 fragments: g = row / key-in-tile index, tq = column pair
         const int g = lane >> 2, tq = lane & 3;
         uint32_t qa[2][8][4];  // A fragments of Q: [part][k-step of 16 dims]
@@ -1173,7 +1256,7 @@ stack_kernel(const StackOp* __restrict__ ops, const CUtensorMap* __restrict__ ma
 
     // ---- end of the op
     if (tracing && tid == 0) stamp(8 * oi + 6);
-    if (trace != nullptr && tid == 0) {  // slot 4: the LAST CTA's arrival at the end of the op body
+    if (trace != nullptr && tid == 0 && op.kind != kStGemm) {  // slot 4: the LAST CTA's arrival at the end of the op body
       unsigned long long t;
       asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
       atomicMax(trace + 8 * oi + 4, t);
