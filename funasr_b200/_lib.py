@@ -51,6 +51,8 @@ SIGNATURES = {
     "fb200_cif_integrate": [_P, _I, _P, _P, _P, _I, _I, _I, _F, _P, _P, _P, _I, _P],
     "fb200_argmax_logprob": [_P, _I, _I, _I, _P, _P, _P],
     "fb200_ctc_collapse": [_P, _P, _I, c_uint32, _I, _P, _P, _P],
+    "fb200_gemm_argmax_workspace": [_I, _I, _P],
+    "fb200_gemm_argmax": [_P, _I, _I, _P, _I, _I, _I, _I, _P, _P, ctypes.c_longlong, _P, _P, _P],
     "fb200_stack_begin": [_P, _P, _I],
     "fb200_stack_end": [_P],
     "fb200_stack_info": [_P, _P, _P],

@@ -93,17 +93,30 @@ class BiCifParaformerEngine(ParaformerEngine):
         """-> (ids i32 [L] device, logp, token_num list, rows list, time-stamp dict or None)."""
         inner = {} if taps is None else taps
         with torch.cuda.device(self.device):
-            feats, cu_rows, rows = self.frontend.run(wave, lens, pe_scale=float(self.encoder.d) ** 0.5)
-            b, r = len(lens), feats.shape[0]
-            halo = self.predictor.halo_buffer(r, b)
-            enc = self.encoder.run(feats, cu_rows, max(rows), out_halo=halo)
-            pred = self.predictor.run(enc, halo, cu_rows, b, want_fires=taps is not None)
+            b = len(lens)
+            small = None  # small requests: encoder / decoder stretches as persistent kernels (engine._SmallPath)
+            if taps is None and b <= self.STACK_BATCH and sum(self.frontend.plan(lens)[1]) <= self.STACK_ROWS:
+                small = self.small_path()
+            feats, cu_rows, rows = self.frontend.run(wave, lens, pe_scale=float(self.encoder.d) ** 0.5,
+                                                     feats_out=small.x if small else None)
+            r = feats.shape[0]
+            if small:
+                enc, halo = small.encode(cu_rows, r, b)
+            else:
+                halo = self.predictor.halo_buffer(r, b)
+                enc = self.encoder.run(feats, cu_rows, max(rows), out_halo=halo)
+            pred = self.predictor.run(enc, halo, cu_rows, b, want_fires=taps is not None,
+                                      embeds_out=small.embeds if small else None)
             inner.update(feats=feats, enc=enc, cu_rows=cu_rows, rows=rows, **pred)
             tok = pred["token_num"]
             if max(tok) < 1:
                 empty = torch.empty(0, dtype=torch.int32, device=self.device)
                 return empty, torch.empty(0, dtype=torch.float32, device=self.device), tok, rows, None
-            ids, logp, logits = self.decode(enc, cu_rows, pred["embeds"], pred["cu_tok"], max(tok), taps)
+            if small and sum(tok) <= self.STACK_TOKENS and type(self).decode is BiCifParaformerEngine.decode:
+                ids, logp = small.decode(pred["cu_tok"], r, int(sum(tok)), b)
+                logits = None
+            else:
+                ids, logp, logits = self.decode(enc, cu_rows, pred["embeds"], pred["cu_tok"], max(tok), taps)
             ts = self.stamper.run(enc, cu_rows, max(rows), pred["token_num_dev"], ids, pred["cu_tok"], self.DROP_IDS,
                                   want_taps=taps is not None)
             inner.update(logits=logits, ids=ids, logp=logp, **ts)

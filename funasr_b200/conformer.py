@@ -23,6 +23,7 @@ from typing import Dict, List, Optional, Sequence
 import numpy as np
 import torch
 
+from .engine import FUSED_ARGMAX
 from . import ops, tables
 from .engine import FrontendPack, ParaformerEngine, _dev, _Linear, _Norm
 
@@ -266,11 +267,14 @@ class ConformerCTCEngine:
                 taps.update(embed=x.clone())
             enc_split = torch.empty(r, ops.split_width(self.encoder.d, np_), dtype=torch.bfloat16, device=dev)
             enc = self.encoder.run(x, cu_rows, max(rows), taps=layer_taps, out_split=enc_split)
-            ld = (v + 3) // 4 * 4
-            logits = torch.empty(r, ld, dtype=torch.float32, device=dev)
-            ops.gemm(enc_split, np_, self.ctc.w, np_, r, v, self.ctc.k, bias=self.ctc.bias, out_f32=logits)
             frame_ids = torch.empty(r, dtype=torch.int32, device=dev)
-            ops.argmax_logprob(logits, v, frame_ids, rows=r)
+            if np_ < 3 and FUSED_ARGMAX:
+                ops.gemm_argmax(enc_split, np_, self.ctc.w, np_, r, v, self.ctc.k, frame_ids, bias=self.ctc.bias)
+            else:
+                ld = (v + 3) // 4 * 4
+                logits = torch.empty(r, ld, dtype=torch.float32, device=dev)
+                ops.gemm(enc_split, np_, self.ctc.w, np_, r, v, self.ctc.k, bias=self.ctc.bias, out_f32=logits)
+                ops.argmax_logprob(logits, v, frame_ids, rows=r)
             out_ids = torch.empty(r, dtype=torch.int32, device=dev)
             out_len = torch.empty(len(lens), dtype=torch.int32, device=dev)
             ops.ctc_collapse(frame_ids, cu_rows, self.DROP_MASK, True, out_ids, out_len)

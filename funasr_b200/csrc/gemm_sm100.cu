@@ -300,6 +300,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       tcgen05_fence_after();
       const int row = m0 + lg * 32 + lane;
       const bool row_ok = row < m;
+      float am = -INFINITY, asum = 0.f;  // fused greedy pick: this row's running maximum / sum(exp(y - max)) / first column
+      int ai = 0x7fffffff;
 #pragma unroll 1
       for (int c = 0; c < BN; c += 32) {
         const int col0 = n0 + c;
@@ -337,6 +339,30 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           }
         }
         if (warp == 2 && lane == 0) GTRACE(2, 27);
+        if (p.amax_part != nullptr) {  // logits never leave the SM: streaming (max, first argmax, sum of exponentials)
+          float cm = -INFINITY;
+          int ci = 0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if ((full || col0 + j < n) && y[j] > cm) {
+              cm = y[j];
+              ci = j;
+            }
+          if (cm > am) {
+            asum *= __expf(am - cm);  // exp(-inf) = 0 on the first chunk
+            am = cm;
+            ai = col0 + ci;
+          }
+          float cs = 0.f;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (full || col0 + j < n) cs += __expf(y[j] - am);
+          asum += cs;
+          if (c + 32 >= BN || col0 + 32 >= ncols) {
+            if (row_ok) p.amax_part[(size_t)row * p.tiles_n + (tile % p.tiles_n)] = make_float4(am, asum, __int_as_float(ai), 0.f);
+          }
+          continue;
+        }
 #pragma unroll
         for (int j = 0; j < 32; ++j) y[j] = fmaxf(y[j], lo);
         if (swish) {

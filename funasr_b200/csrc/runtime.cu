@@ -697,7 +697,8 @@ int Recognizer::decoder_ops(const DecBufs& b, int R, int L, int B, int max_l, in
     }
   }
   RT_OK(fb200_layernorm(y, d, L, d, dec_after_.g, dec_after_.b, eps_, nullptr, 0, b.ys, np, 0, nullptr, 0, st));
-  RT_OK(fb200_gemm(b.ys, L, np, dec_out_.w, np, L, vocab_, d, 1, dec_out_.bias, 0, nullptr, 0, b.logits, ldv, 0, nullptr, np, 0, st));
+  if (b.logits != nullptr)  // (recorded stack programs: the logits are written, the pick is a launch of its own)
+    RT_OK(fb200_gemm(b.ys, L, np, dec_out_.w, np, L, vocab_, d, 1, dec_out_.bias, 0, nullptr, 0, b.logits, ldv, 0, nullptr, np, 0, st));
   return FB200_OK;
 }
 
@@ -890,7 +891,10 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   const int dplan_cap = L / 128 + B;
   int32_t* dplan = arena_.get<int32_t>(4 + 4 * (size_t)dplan_cap);
   const int ldv = (vocab_ + 3) / 4 * 4;
-  float* logits = arena_.get<float>((size_t)L * ldv);
+  // per-op path: vocabulary projection fused with the greedy pick (fb200_gemm_argmax: the [L, V] logits are never written)
+  long long pick_bytes = 0;
+  fb200_gemm_argmax_workspace(L, vocab_, &pick_bytes);
+  float* logits = small_dec ? nullptr : arena_.get<float>((size_t)(pick_bytes + 3) / 4);
   int32_t* ids = arena_.get<int32_t>(L);
   float* logp = arena_.get<float>(L);
   if (!arena_.ok()) {
@@ -912,7 +916,11 @@ int Recognizer::forward(const std::vector<int>& batch, int slot, const int* lens
   } else {
     RT_OK(fb200_split_rows(enc, d, R, d, encs, np, st));
     RT_OK(fb200_attention_plan(d_cut, d_cur, B, dplan, dplan_cap, st));
-    RT_OK(decoder_ops(db, R, L, B, max_l, ldv, st));
+    DecBufs nb = db;
+    nb.logits = nullptr;
+    RT_OK(decoder_ops(nb, R, L, B, max_l, ldv, st));
+    RT_OK(fb200_gemm_argmax(db.ys, L, np, dec_out_.w, np, L, vocab_, d, dec_out_.bias, logits, pick_bytes, ids, logp, st));
+    return FB200_OK;
   }
   RT_OK(fb200_argmax_logprob(logits, ldv, L, vocab_, ids, logp, st));
   return FB200_OK;

@@ -29,6 +29,9 @@ struct GemmParams {
   int ld_out, f32_col0;  // out_f32 holds columns [f32_col0, n) only
   __nv_bfloat16* out_split;
   int out_parts, out_kp;
+  // fused greedy pick (fb200_gemm_argmax): no matrix is written; every column tile leaves, per row, its maximum, the first
+  // column that reaches it and sum(exp(y - max)) in amax_part[row * tiles_n + tile] = (max, sum, column as bits, -)
+  float4* amax_part;
 };
 
 // true while fb200_stack_begin() ... fb200_stack_end() is open on this thread

@@ -26,6 +26,8 @@ import torch
 
 from . import ops, tables
 
+# vocabulary / CTC projections fused with the greedy pick (fb200_gemm_argmax); FB200_FUSED_ARGMAX=0 keeps logits + argmax kernels
+FUSED_ARGMAX = os.environ.get("FB200_FUSED_ARGMAX", "1") != "0"
 FRAME_LEN = 400
 FRAME_SHIFT = 160
 NFFT = 512
@@ -336,10 +338,14 @@ class DecoderPack:
     def head(self, xs: torch.Tensor, want_logits: bool = False):
         """`output_layer` + log-softmax argmax over the split hidden states -> (ids, logp, logits or None)."""
         l, dev = xs.shape[0], self.device
-        logits = torch.empty(l, self.vocab, dtype=torch.float32, device=dev)
-        ops.gemm(xs, self.nparts, self.output.w, self.nparts, l, self.vocab, self.d, bias=self.output.bias, out_f32=logits)
         ids = torch.empty(l, dtype=torch.int32, device=dev)
         logp = torch.empty(l, dtype=torch.float32, device=dev)
+        if not want_logits and self.nparts < 3 and FUSED_ARGMAX:
+            # the [L, V] logits never exist: the projection's epilogue keeps (max, first argmax, sum of exponentials) per row
+            ops.gemm_argmax(xs, self.nparts, self.output.w, self.nparts, l, self.vocab, self.d, ids, logp, bias=self.output.bias)
+            return ids, logp, None
+        logits = torch.empty(l, self.vocab, dtype=torch.float32, device=dev)
+        ops.gemm(xs, self.nparts, self.output.w, self.nparts, l, self.vocab, self.d, bias=self.output.bias, out_f32=logits)
         ops.argmax_logprob(logits, self.vocab, ids, logp)
         return ids, logp, (logits if want_logits else None)
 
@@ -692,13 +698,17 @@ class SenseVoiceEngine:
             enc_split = ops.split_rows(enc, self.nparts)
             frame_ids = torch.empty(r, dtype=torch.int32, device=self.device)
             bias = self._bias(ban_ids)
-            ld = (v + 3) // 4 * 4
-            logits = torch.empty(min(r, self.LOGIT_ROWS), ld, dtype=torch.float32, device=self.device)
-            for r0 in range(0, r, self.LOGIT_ROWS):
-                n = min(self.LOGIT_ROWS, r - r0)
-                ops.gemm(enc_split[r0: r0 + n], self.nparts, self.ctc.w, self.nparts, n, v, self.ctc.k, bias=bias,
-                         out_f32=logits[:n])
-                ops.argmax_logprob(logits[:n], v, frame_ids[r0: r0 + n], rows=n)
+            if self.nparts < 3 and FUSED_ARGMAX:
+                # CTC projection fused with the per-frame argmax: the [rows, 25055] logits are never written
+                ops.gemm_argmax(enc_split, self.nparts, self.ctc.w, self.nparts, r, v, self.ctc.k, frame_ids, bias=bias)
+            else:
+                ld = (v + 3) // 4 * 4
+                logits = torch.empty(min(r, self.LOGIT_ROWS), ld, dtype=torch.float32, device=self.device)
+                for r0 in range(0, r, self.LOGIT_ROWS):
+                    n = min(self.LOGIT_ROWS, r - r0)
+                    ops.gemm(enc_split[r0: r0 + n], self.nparts, self.ctc.w, self.nparts, n, v, self.ctc.k, bias=bias,
+                             out_f32=logits[:n])
+                    ops.argmax_logprob(logits[:n], v, frame_ids[r0: r0 + n], rows=n)
             out_ids = torch.empty(r, dtype=torch.int32, device=self.device)
             out_len = torch.empty(len(lens), dtype=torch.int32, device=self.device)
             ops.ctc_collapse(frame_ids, cu_rows, 1 << self.blank_id, True, out_ids, out_len)

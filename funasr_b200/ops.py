@@ -334,6 +334,21 @@ def argmax_logprob(logits, vocab, ids, score=None, rows=None):
     _lib.call("fb200_argmax_logprob", _p(logits), logits.stride(0), rows, vocab, _p(ids), _p(score), _stream())
 
 
+def gemm_argmax(a_split, a_parts, w_split, w_parts, m, n, k, ids, score=None, bias=None, workspace=None, a_rows=None):
+    """ids[r] = argmax over the n columns of A . W^T + bias (first index on ties), score[r] = the log-softmax there; the
+    [m, n] matrix is never written (fused epilogue + a small second pass).  Returns the workspace for reuse."""
+    _chk(a_split, torch.bfloat16, "gemm_argmax")
+    _chk(w_split, torch.bfloat16, "gemm_argmax")
+    need = ctypes.c_longlong()
+    _lib.call("fb200_gemm_argmax_workspace", m, n, ctypes.byref(need))
+    if workspace is None or workspace.numel() * workspace.element_size() < need.value:
+        workspace = torch.empty(max(need.value // 4, 4), dtype=torch.float32, device=a_split.device)
+    a_rows = a_split.shape[0] if a_rows is None else a_rows
+    _lib.call("fb200_gemm_argmax", _p(a_split), a_rows, a_parts, _p(w_split), w_parts, m, n, k, _p(bias), _p(workspace),
+              workspace.numel() * workspace.element_size(), _p(ids), _p(score), _stream())
+    return workspace
+
+
 def ctc_collapse(ids, cu_rows, drop_mask, collapse, out_ids, out_len):
     _lib.call("fb200_ctc_collapse", _p(ids), _p(cu_rows), cu_rows.numel() - 1, drop_mask, 1 if collapse else 0,
               _p(out_ids), _p(out_len), _stream())

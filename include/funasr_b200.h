@@ -375,6 +375,19 @@ int fb200_asf_scores(const float* q, int ld_q, const float* k, int ld_k, const i
 int fb200_argmax_logprob(const float* logits, int ld, int rows, int vocab, int32_t* ids, float* score,
                          void* stream);
 
+/* The vocabulary / CTC projection FUSED with that greedy pick: ids[r] = argmax_c (a . w^T + bias)[r, c] (first index on
+ * ties), score[r] = max log_softmax, without the [rows, vocab] logits matrix ever being written (SenseVoiceSmall: 410 MB
+ * per 4096 rows).  The tcgen05 GEMM's epilogue keeps, per row and column tile, a running (max, first column, sum of
+ * exponentials); a second small kernel folds the tiles.  Replaces `decoder.output_layer` + `log_softmax` + `argmax`
+ * (funasr/models/paraformer/model.py:527-546) and `ctc_lo` + `CTC.argmax` (funasr/models/ctc/ctc.py:173-197).
+ *   a, w      bf16 split operands as for fb200_gemm (1 or 2 parts); bias f32 [n] or NULL (-inf entries ban an id)
+ *   workspace device memory of fb200_gemm_argmax_workspace(m, n) bytes, 16-byte aligned
+ *   score     f32 [m] or NULL */
+int fb200_gemm_argmax_workspace(int m, int n, long long* bytes);
+int fb200_gemm_argmax(const void* a, int a_rows, int a_parts, const void* w, int w_parts, int m, int n, int k,
+                      const float* bias, void* workspace, long long workspace_bytes, int32_t* ids, float* score,
+                      void* stream);
+
 /* CTC greedy collapse per utterance: unique_consecutive then drop ids < n_drop... drop set is
  * {blank} (SenseVoiceSmall, funasr/models/sense_voice/model.py:895-906) or {0,1,2} given as a
  * bit mask over ids 0..31 (funasr/models/ctc/model.py:243-247).  out_ids packed at cu_rows[b],

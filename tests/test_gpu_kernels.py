@@ -341,3 +341,36 @@ def test_ctc_collapse(drop, collapse):
         ref = [int(t) for t in seq if int(t) not in drop]
         assert out[o: o + int(n_out[i])].cpu().tolist() == ref
         o += n
+
+
+@pytest.mark.parametrize("m,n,k", [(5000, 8404, 512), (71, 8404, 512), (4096, 25055, 512), (300, 4234, 256), (1, 100, 512)])
+def test_gemm_argmax_equals_gemm_then_argmax(m, n, k):
+    """fb200_gemm_argmax (projection fused with the greedy pick, logits never written) against fb200_gemm + fb200_argmax_logprob:
+    ids identical -- ties included: duplicated weight rows give equal logits and the FIRST index must win -- scores to 1e-5."""
+    g = torch.Generator().manual_seed(m + n)
+    a = torch.randn(m, k, generator=g).to(DEV)
+    w = (torch.randn(n, k, generator=g) * k ** -0.5)
+    w[n // 2] = w[3]                      # a tie inside one row of logits ...
+    w[n - 1] = w[n - 2]                   # ... and one in the last, partial column tile
+    w = w.to(DEV)
+    bias = torch.randn(n, generator=g).to(DEV)
+    bias[n // 2] = bias[3]
+    bias[n - 1] = bias[n - 2]
+    bias[7] = float("-inf")               # a banned id (SenseVoice's ban_emo_unk)
+    a_s, w_s = ops.split_rows(a, 2), ops.split_rows(w, 2)
+    logits = torch.empty(m, (n + 3) // 4 * 4, dtype=torch.float32, device=DEV)
+    ops.gemm(a_s, 2, w_s, 2, m, n, k, bias=bias, out_f32=logits)
+    want_ids = torch.empty(m, dtype=torch.int32, device=DEV)
+    want_lp = torch.empty(m, dtype=torch.float32, device=DEV)
+    ops.argmax_logprob(logits, n, want_ids, want_lp)
+    got_ids = torch.full((m,), -1, dtype=torch.int32, device=DEV)
+    got_lp = torch.empty(m, dtype=torch.float32, device=DEV)
+    ops.gemm_argmax(a_s, 2, w_s, 2, m, n, k, got_ids, got_lp, bias=bias)
+    torch.cuda.synchronize()
+    assert torch.equal(want_ids, got_ids)
+    assert float((want_lp - got_lp).abs().max()) < 1e-5
+    # rows whose maximum sits on a tie pick the first of the equal columns
+    lg = logits[:, :n]
+    tied = (lg[:, 3] == lg.max(dim=1).values) | (lg[:, n - 2] == lg.max(dim=1).values)
+    if bool(tied.any()):
+        assert bool(((got_ids[tied] == 3) | (got_ids[tied] == n - 2)).all())
