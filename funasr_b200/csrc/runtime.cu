@@ -196,10 +196,10 @@ class Recognizer {
   bool use_graphs_ = true;
   template <typename F>
   int run_graphed(const GraphKey& key, bool allowed, F&& issue);
-  // Small requests (<= kStackBatch utterances, <= kStackRows encoder rows: BASELINE configs[0]): the encoder and decoder
+  // Small requests (<= kStackBatch utterances, <= kStackRows encoder rows -- one 30 s utterance; BASELINE configs[0]): the encoder and decoder
   // stretches run as two persistent cooperative kernels (fb200_stack_*, csrc/stack_sm100.cu) recorded once over
   // capacity-sized buffers of their own; FB200_STACK=0 keeps the per-op launches.
-  static constexpr int kStackRows = 256, kStackTokens = 192, kStackBatch = 8;
+  static constexpr int kStackRows = 512, kStackTokens = 384, kStackBatch = 8;
   struct EncBufs {
     float* feats; bf16 *xs0, *xs, *h, *qkv; float *v, *mem, *x0, *x1, *enc; bf16 *halo, *encs; int32_t *d_cur, *plan;
   };

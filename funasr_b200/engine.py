@@ -483,7 +483,11 @@ class ParaformerEngine:
             self.decoder = DecoderPack(state_dict, self.device, heads=heads, nparts=self.nparts)
 
     # ---- small requests: encoder and decoder stretches as ONE persistent kernel each (csrc/stack_sm100.cu) -----------
-    STACK_ROWS, STACK_TOKENS, STACK_BATCH = 256, 192, 8  # capacities the two programs are recorded with
+    # capacities the two programs are recorded with (encoder rows, tokens, utterances of a request): up to one 30 s utterance
+    # the path beats the per-op launches (tools/stack_capacity_sweep.py: 3.6 / 4.0 / 5.3 ms at 2 / 10 / 30 s against 6.5)
+    STACK_ROWS = int(os.environ.get("FB200_STACK_ROWS", "512"))
+    STACK_TOKENS = int(os.environ.get("FB200_STACK_TOKENS", "384"))
+    STACK_BATCH = 8
 
     def small_path(self):
         """Buffers and programs of the request-stack path, recorded on first use (FB200_STACK=0 switches it off)."""

@@ -148,8 +148,8 @@ def test_launch_counter_counts_kernels(eng_fp32):
     eng_fp32.forward_packed(wave, lens)
     n = _lib.launch_count()
     assert 0 < n < 40 if eng_fp32.small_path() is not None else n > 400
-    # ... a 30 s one (500 encoder rows) the per-op path: 50 encoder layers x 8 kernels + predictor + 16 decoder layers
-    wave, lens = eng_fp32.upload([synth.synth_waveform(10, 480000)])
+    # ... two 30 s ones (1000 encoder rows) the per-op path: 50 encoder layers x 8 kernels + predictor + 16 decoder layers
+    wave, lens = eng_fp32.upload([synth.synth_waveform(10, 480000), synth.synth_waveform(12, 480000)])
     _lib.launch_count(reset=True)
     eng_fp32.forward_packed(wave, lens)
     assert _lib.launch_count() > 400

@@ -206,3 +206,9 @@ def test_engine_small_request_ids_equal_reference_golden(golden_dir, paraformer_
     batch = [synth.synth_waveform(20 + i, n) for i, n in enumerate((32000, 48000, 64000))]
     assert eng.recognize(batch) == eng0.recognize(batch)
     assert eng.recognize(waves) == ref
+    # the capacity edge: one 30 s utterance (500 rows of the 512 recorded) and 8 utterances at once
+    for req in ([synth.synth_waveform(40, 480000)], [synth.synth_waveform(50 + i, 16000 * (2 + i % 3)) for i in range(8)]):
+        _lib.launch_count(reset=True)
+        got = eng.recognize(req)
+        assert _lib.launch_count() < 40
+        assert got == eng0.recognize(req)
