@@ -254,7 +254,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     // (rv[i] = element (row i, column `lane`), a whole 128-byte line per load) while the current chunk is
     // processed, then turns it through the (otherwise unused) split staging box so that each lane gets its
     // own row.  Used when no split output is produced (the residual GEMMs write fp32 only).
-    const bool res_coal = res1 != nullptr && !has_split;
+    const bool direct = p.direct_store != 0;
+    const bool res_coal = res1 != nullptr && !has_split && !direct;
     float rv[32];
     auto load_res = [&](int tile, int c) {
       const int r0 = ((tile / p.tiles_n) * CL + cta_rank) * BM + lg * 32, col = (tile % p.tiles_n) * BN + c + lane;
@@ -413,6 +414,45 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             if (col0 + j >= n) y[j] = 0.f;
         }
         if (warp == 2 && lane == 0) GTRACE(2, 23);
+        if (direct) {
+          // Plain stores: the thread owns 32 consecutive columns of its row (one 128-byte line of fp32, 64 bytes per bf16
+          // part).  No staging box, no cross-proxy fence, no wait for the previous boxes, no ~200-cycle UTMASTG per box.
+          if (row_ok) {
+            if (has_f32 && col0 >= f32_col0) {
+              float* dst = p.out_f32 + (size_t)row * p.ld_out + (col0 - f32_col0);
+              if (full) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) reinterpret_cast<float4*>(dst)[j] = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (col0 + j < n) dst[j] = y[j];
+              }
+            }
+            if (has_split) {
+              __nv_bfloat16* dst = p.out_split + (size_t)row * (out_parts * out_kp) + col0;
+#pragma unroll
+              for (int pp = 0; pp < 2; ++pp) {
+                if (pp < out_parts) {
+#pragma unroll
+                  for (int q = 0; q < 4; ++q) {
+                    uint32_t w[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                      const int j = q * 8 + u * 2;
+                      const __nv_bfloat162 h = __floats2bfloat162_rn(y[j], y[j + 1]);
+                      w[u] = *reinterpret_cast<const uint32_t*>(&h);
+                      y[j] -= __low2float(h);
+                      y[j + 1] -= __high2float(h);
+                    }
+                    reinterpret_cast<uint4*>(dst + (size_t)pp * out_kp)[q] = make_uint4(w[0], w[1], w[2], w[3]);
+                  }
+                }
+              }
+            }
+          }
+          continue;
+        }
         // the boxes of the previous chunk must have been read by the TMA engine before they are overwritten
         if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         __syncwarp();

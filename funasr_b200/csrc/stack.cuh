@@ -32,6 +32,7 @@ struct GemmParams {
   // fused greedy pick (fb200_gemm_argmax): no matrix is written; every column tile leaves, per row, its maximum, the first
   // column that reaches it and sum(exp(y - max)) in amax_part[row * tiles_n + tile] = (max, sum, column as bits, -)
   float4* amax_part;
+  int direct_store;  // epilogue writes its rows with plain 16-byte stores instead of staging boxes + TMA stores
 };
 
 // true while fb200_stack_begin() ... fb200_stack_end() is open on this thread
