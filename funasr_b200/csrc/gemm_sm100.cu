@@ -24,7 +24,7 @@ namespace fb200 {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // bf16 elements = 128 bytes = one swizzle row
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 192;  // 2 + 4 epilogue warps; EW = 8 adds four more (64 + 32 * EW threads)
 constexpr int kEpiWarpBytes = 8192;  // per epilogue warp: fp32 box 32x32 (4 KB, SW128) + 2 bf16 part boxes 32x32 (2 KB each, SW64)
 // swish y * sigmoid(y) on the SFU (ex2.approx + rcp.approx: ~2 ulp, far inside the 16-bit-mantissa operand rounding that
 // follows); the IEEE expf + division made the epilogue of the K = 256 FFN contractions longer than their mainloop
@@ -72,15 +72,19 @@ __device__ long long g_gemm_trace[3][1024];
 // both halves, and each CTA's tensor memory receives its 128 accumulator rows.  A CTA then takes in
 // NP * (16 KB + BN / 2 * 128 B) per k-block instead of NP * (16 KB + BN * 128 B): the mainloop was bound by
 // the ~41 B/clk an SM can take in, not by the tensor pipe -- and the smaller stage buys a third stage.
-template <int NP, int BN, int STAGES, int CL>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// EW = 8: EIGHT epilogue warps, two per tensor-memory lane group (warp % 4), each taking one half of the tile's columns.
+// The epilogue of a K = 512 product is longer than its mainloop and LATENCY-bound per warp (one epilogue warp per
+// scheduler: tcgen05.ld -> bias -> convert -> st.shared -> fence -> UTMASTG each wait for the previous step); two warps per
+// scheduler overlap those chains.  Costs 32 KB more staging, i.e. one ring stage less.
+template <int NP, int BN, int STAGES, int CL, int EW = 4>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     const __grid_constant__ CUtensorMap map_f32, const __grid_constant__ CUtensorMap map_split,
                     const GemmParams p) {
   constexpr uint32_t kAPart = BM * BK * 2;
   constexpr uint32_t kBPart = (BN / CL) * BK * 2;  // this CTA's share of the weight rows
   constexpr uint32_t kStageBytes = NP * (kAPart + kBPart);
-  constexpr uint32_t kEpiBytes = 4 * kEpiWarpBytes;
+  constexpr uint32_t kEpiBytes = EW * kEpiWarpBytes;
   constexpr uint32_t kTmemCols = 2 * BN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B needs 1024 B alignment
@@ -121,7 +125,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       }
       for (int a = 0; a < 2; ++a) {
         mbar_init(tfull_bar(a), 1);
-        mbar_init(tempty_bar(a), 4 * CL);  // one arrival per epilogue warp (of both CTAs, on the leader's)
+        mbar_init(tempty_bar(a), EW * CL);  // one arrival per epilogue warp (of both CTAs, on the leader's)
       }
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -240,6 +244,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     // The TMA engine does the address generation, coalescing and edge clipping; the warp only
     // touches each value once, which keeps this issue-bound branch short.
     const int lg = warp & 3;
+    // columns of the tile this warp handles: all of them (EW = 4) or one half (EW = 8: warps 2..5 the first, 6..9 the second)
+    constexpr int kColsPerWarp = BN / (EW / 4);
+    static_assert(EW == 4 || (EW == 8 && BN % 64 == 0), "eight epilogue warps split the tile's columns in two halves of whole chunks");
+    const int c_lo = ((warp - 2) >> 2) * kColsPerWarp, c_hi = c_lo + kColsPerWarp;
     const uint32_t fbuf = epi_base + (uint32_t)(warp - 2) * kEpiWarpBytes;  // 32 rows x 128 B, SWIZZLE_128B
     const uint32_t sbuf = fbuf + 4096u;                                     // per part: 32 rows x 64 B, SWIZZLE_64B
     const int m = p.m, n = p.n, f32_col0 = p.f32_col0, out_parts = p.out_parts, out_kp = p.out_kp;
@@ -268,8 +276,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     // into registers a whole tile early) and every chunk reads its 32 values with 8 broadcast LDS.128.  Fetched from global
     // memory where they are used -- 8 broadcast LDG.128 per chunk and warp -- they kept the load/store unit busy for ~300 of
     // the ~1350 cycles a chunk takes, and the epilogue, not the MMAs, bounds the K = 512 products (profiles/r02_gemm_epilogue.md).
-    constexpr int kBiasPerThread = BN / 128 > 0 ? BN / 128 : 1;
-    const int et = (warp - 2) * 32 + lane;  // 0..127
+    constexpr int kEpiThreads = EW * 32;
+    constexpr int kBiasPerThread = BN / kEpiThreads > 0 ? BN / kEpiThreads : 1;
+    const int et = (warp - 2) * 32 + lane;  // 0..kEpiThreads-1
     float bnext[kBiasPerThread];
     auto fetch_bias = [&](int tile) {
       const int n0 = (tile % p.tiles_n) * BN;
@@ -279,10 +288,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         bnext[u] = (bias != nullptr && cc < BN && n0 + cc < n) ? __ldg(bias + n0 + cc) : 0.f;
       }
     };
-    auto epi_sync = [&]() { asm volatile("bar.sync 1, 128;" ::: "memory"); };
+    auto epi_sync = [&]() { asm volatile("bar.sync 1, %0;" ::"n"(kEpiThreads) : "memory"); };
     int tl = 0;
     if (unit0 < total_tiles) fetch_bias(unit0);
-    if (res_coal && unit0 < total_tiles) load_res(unit0, 0);
+    if (res_coal && unit0 < total_tiles) load_res(unit0, c_lo);
     for (int tile = unit0; tile < total_tiles; tile += unit_step, ++tl) {
       const int acc = tl & 1;
       const int m0 = ((tile / p.tiles_n) * CL + cta_rank) * BM, n0 = (tile % p.tiles_n) * BN;
@@ -304,7 +313,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
       float am = -INFINITY, asum = 0.f;  // fused greedy pick: this row's running maximum / sum(exp(y - max)) / first column
       int ai = 0x7fffffff;
 #pragma unroll 1
-      for (int c = 0; c < BN; c += 32) {
+      for (int c = c_lo; c < c_hi; c += 32) {
         const int col0 = n0 + c;
         const bool live = col0 < ncols;    // warp-uniform
         const bool full = col0 + 32 <= n;  // warp-uniform: no column guard needed
@@ -316,7 +325,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           for (int j = 0; j < 32; ++j) y[j] = __uint_as_float(r[j]);
         }
         if (warp == 2 && lane == 0) GTRACE(2, 22);
-        if (c + 32 >= BN) {  // accumulator fully read: hand the TMEM buffer back to the MMA warp
+        if (c + 32 >= c_hi) {  // this warp's columns of the accumulator are read: hand the TMEM buffer back to the MMA warp
           tcgen05_fence_before();
           __syncwarp();
           if (lane == 0) {
@@ -359,9 +368,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           for (int j = 0; j < 32; ++j)
             if (full || col0 + j < n) cs += __expf(y[j] - am);
           asum += cs;
-          if (c + 32 >= BN || col0 + 32 >= ncols) {
-            if (row_ok) p.amax_part[(size_t)row * p.tiles_n + (tile % p.tiles_n)] = make_float4(am, asum, __int_as_float(ai), 0.f);
-          }
           continue;
         }
 #pragma unroll
@@ -390,10 +396,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           }
           __syncwarp();
           // next chunk of this tile that is live, else the first chunk of this CTA's next tile
-          if (c + 32 < BN && col0 + 32 < ncols)
+          if (c + 32 < c_hi && col0 + 32 < ncols)
             load_res(tile, c + 32);
           else if (tile + unit_step < total_tiles)
-            load_res(tile + unit_step, 0);
+            load_res(tile + unit_step, c_lo);
         } else if (res1 != nullptr && row_ok) {
           const float* rp = res1 + (size_t)row * p.ld_res1 + col0;
           if (full && (p.ld_res1 & 3) == 0) {
@@ -500,6 +506,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           if (warp == 2) GTRACE(2, 21);
         }
+      }
+      if (p.amax_part != nullptr && row_ok) {  // one (max, sum, first column) triple per row, column tile and column half
+        constexpr int kHalves = EW / 4;
+        p.amax_part[((size_t)row * p.tiles_n + (tile % p.tiles_n)) * kHalves + ((warp - 2) >> 2)] = make_float4(am, asum, __int_as_float(ai), 0.f);
       }
     }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
