@@ -76,7 +76,9 @@ __device__ long long g_gemm_trace[3][1024];
 // The epilogue of a K = 512 product is longer than its mainloop and LATENCY-bound per warp (one epilogue warp per
 // scheduler: tcgen05.ld -> bias -> convert -> st.shared -> fence -> UTMASTG each wait for the previous step); two warps per
 // scheduler overlap those chains.  Costs 32 KB more staging, i.e. one ring stage less.
-template <int NP, int BN, int STAGES, int CL, int EW = 4>
+// EPIB = 4096: the fp32 box and the split boxes of an epilogue warp share ONE 4 KB staging area -- for products with a single
+// kind of output (or outputs in disjoint column ranges that never meet in a chunk); eight warps then fit the 32 KB of four.
+template <int NP, int BN, int STAGES, int CL, int EW = 4, int EPIB = kEpiWarpBytes>
 __global__ void __launch_bounds__(64 + 32 * EW, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_w,
                     const __grid_constant__ CUtensorMap map_f32, const __grid_constant__ CUtensorMap map_split,
@@ -84,7 +86,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   constexpr uint32_t kAPart = BM * BK * 2;
   constexpr uint32_t kBPart = (BN / CL) * BK * 2;  // this CTA's share of the weight rows
   constexpr uint32_t kStageBytes = NP * (kAPart + kBPart);
-  constexpr uint32_t kEpiBytes = EW * kEpiWarpBytes;
+  constexpr uint32_t kEpiBytes = EW * EPIB;
   constexpr uint32_t kTmemCols = 2 * BN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B needs 1024 B alignment
@@ -248,8 +250,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     constexpr int kColsPerWarp = BN / (EW / 4);
     static_assert(EW == 4 || (EW == 8 && BN % 64 == 0), "eight epilogue warps split the tile's columns in two halves of whole chunks");
     const int c_lo = ((warp - 2) >> 2) * kColsPerWarp, c_hi = c_lo + kColsPerWarp;
-    const uint32_t fbuf = epi_base + (uint32_t)(warp - 2) * kEpiWarpBytes;  // 32 rows x 128 B, SWIZZLE_128B
-    const uint32_t sbuf = fbuf + 4096u;                                     // per part: 32 rows x 64 B, SWIZZLE_64B
+    const uint32_t fbuf = epi_base + (uint32_t)(warp - 2) * EPIB;           // 32 rows x 128 B, SWIZZLE_128B
+    const uint32_t sbuf = fbuf + (EPIB >= 8192 ? 4096u : 0u);               // per part: 32 rows x 64 B, SWIZZLE_64B
     const int m = p.m, n = p.n, f32_col0 = p.f32_col0, out_parts = p.out_parts, out_kp = p.out_kp;
     const float* __restrict__ bias = p.bias;
     const float* __restrict__ res1 = p.res1;
@@ -377,6 +379,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           for (int j = 0; j < 32; ++j) y[j] = swish_fast(y[j]);
         }
         if (res_coal) {
+          if (EPIB < 8192) {  // shared staging area: the previous chunk's output box must have been read before it is reused
+            if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            __syncwarp();
+          }
           // rv -> box (128-byte swizzle, like the fp32 output box) -> this lane's row
 #pragma unroll
           for (int i = 0; i < 32; ++i)
