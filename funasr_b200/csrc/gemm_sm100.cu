@@ -476,6 +476,16 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(fbuf + (uint32_t)lane * 128u + ((uint32_t)j ^ sw128) * 16u),
                          "f"(y[4 * j]), "f"(y[4 * j + 1]), "f"(y[4 * j + 2]), "f"(y[4 * j + 3])
                          : "memory");
+          if (EPIB < 8192 && has_split) {  // shared staging area and both outputs in this chunk: the fp32 box leaves first
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&map_f32, fbuf, col0 - f32_col0, m0 + lg * 32);
+              asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+              asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+            }
+            __syncwarp();
+          }
         }
         if (has_split) {
 #pragma unroll
@@ -504,7 +514,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         if (warp == 2 && lane == 0) GTRACE(2, 25);
         if (lane == 0) {
           const int r0 = m0 + lg * 32;
-          if (do_f32) tma_store_2d(&map_f32, fbuf, col0 - f32_col0, r0);
+          if (do_f32 && !(EPIB < 8192 && has_split)) tma_store_2d(&map_f32, fbuf, col0 - f32_col0, r0);
           if (has_split) {
             tma_store_2d(&map_split, sbuf, col0, r0);
             if (out_parts > 1) tma_store_2d(&map_split, sbuf + 2048u, out_kp + col0, r0);
