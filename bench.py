@@ -245,7 +245,7 @@ class ShardedSet:
 def sharded_steps(job, eng, data, stats):
     def run(waves):
         t0 = time.perf_counter()
-        out = schedule.recognize_sharded(eng, waves, job.rank, job.world, stats=stats)
+        out = schedule.recognize_sharded(eng, waves, job.rank, job.world, stats=stats, as_arrays=True)  # ids as int32 arrays
         stats["step_ms"].append((time.perf_counter() - t0) * 1e3)
         return out
 
@@ -464,7 +464,7 @@ def main():
     else:
         work = "configs[1]: ONE set of %d synthetic utterances U(2,30) s (%.0f s audio) sharded over %d GPUs (LPT plan, ~%d " \
                "utterances per GPU, packed var-len batches <= %d rows), transcripts gathered on rank 0 by one NCCL all_gather " \
-               "inside every step" % (args.utts, secs, world, args.utts // world, args.max_rows)
+               "inside every step (ids returned as one int32 array per utterance)" % (args.utts, secs, world, args.utts // world, args.max_rows)
     line = {
         "metric": METRIC, "value": value, "unit": "audio_s/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_res / args.steps, "higher_is_better": True,

@@ -4,6 +4,7 @@ tests/test_schedule.py covers the same logic with gloo)."""
 import os
 import socket
 
+import numpy as np
 import pytest
 import torch
 import torch.multiprocessing as mp
@@ -31,11 +32,14 @@ def _worker(rank, world, port, out_path):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     waves = [synth.synth_waveform(400 + i, n) for i, n in enumerate(LENS)]
     stats = {}
-    got = schedule.recognize_sharded(_engine(rank), waves, rank, world, stats=stats)
+    eng = _engine(rank)
+    got = schedule.recognize_sharded(eng, waves, rank, world, stats=stats)
+    arr = schedule.recognize_sharded(eng, waves, rank, world, as_arrays=True)  # same ids as int32 arrays (what bench.py times)
     if rank == 0:
+        assert [a.tolist() for a in arr] == got and all(a.dtype == np.int32 for a in arr)
         torch.save((got, stats), out_path)
     else:
-        assert got is None
+        assert got is None and arr is None
     dist.barrier()
     dist.destroy_process_group()
 

@@ -28,6 +28,27 @@ def test_shards_partition_and_balance():
         assert schedule.shard(lens, world) == parts  # deterministic: every rank derives the same plan
 
 
+def test_shard_plan_is_the_greedy_lpt_and_cached():
+    """schedule.shard keeps a heap of (load, rank) and caches the plan per length list; the result is the plain greedy
+    longest-first assignment (least-loaded rank, ties by rank), and the capacity follows from the same plan."""
+    lens = synth.synth_durations(300, seed=3).tolist() + [0, 399, 400, 16000, 16000]
+    for world in (1, 2, 3, 8):
+        rows = [schedule.encoder_rows(n) for n in lens]
+        loads, want = [0.0] * world, [[] for _ in range(world)]
+        for i in sorted(range(len(rows)), key=lambda i: (-rows[i], i)):
+            r = min(range(world), key=lambda k: (loads[k], k))
+            want[r].append(i)
+            loads[r] += schedule.cost(rows[i])
+        assert schedule.shard(lens, world) == want
+        for stamped, per_tok in ((False, 1), (True, 3)):
+            cap = max([1] + [1 + sum(3 + per_tok * (rows[i] + 1) for i in mine) for mine in want])
+            assert schedule.payload_capacity(lens, world, stamped) == cap
+    a = schedule.shard(lens, 2)
+    a[0].append(-1)  # callers own the lists they get: the cached plan is not touched
+    assert schedule.shard(lens, 2)[0][-1] != -1
+    assert schedule.shard([], 2) == [[], []] and schedule.payload_capacity([], 2) == 1
+
+
 def test_batches_respect_row_budget_and_drop_empty():
     lens = [399, 16000, 480000, 32000, 100, 160000]
     b = schedule.batches(lens, range(len(lens)), max_rows=600)
@@ -60,10 +81,16 @@ def _worker(rank, world, port, lens, out_path):
     waves = [synth.synth_waveform(i, n) for i, n in enumerate(lens)]
     got = schedule.recognize_sharded(_FakeEngine(), waves, rank, world)
     got2 = schedule.recognize_sharded(_FakeStampEngine(), waves, rank, world)
+    arr = schedule.recognize_sharded(_FakeEngine(), waves, rank, world, as_arrays=True)
+    arr2 = schedule.recognize_sharded(_FakeStampEngine(), waves, rank, world, as_arrays=True)
     if rank == 0:
+        assert all(isinstance(a, np.ndarray) and a.dtype == np.int32 for a in arr)
+        assert [a.tolist() for a in arr] == got  # same ids, int32 arrays instead of lists
+        assert [a.tolist() for a in arr2[0]] == got2[0] and [a.tolist() for a in arr2[1]] == got2[1]
+        assert all(a.ndim == 2 and a.shape[1] == 2 for a in arr2[1])
         torch.save((got, got2), out_path)
     else:
-        assert got is None and got2 is None
+        assert got is None and got2 is None and arr is None and arr2 is None
     dist.barrier()
     dist.destroy_process_group()
 
@@ -89,6 +116,9 @@ def test_transcript_payload_round_trip_and_capacity():
     assert schedule._decode_items(schedule._encode_items(local)) == local
     paired = {2: ([5, 6], [[0, 120], [130, 300]]), 9: ([], [])}
     assert schedule._decode_items(schedule._encode_items(paired)) == paired
+    arr = schedule._decode_items(schedule._encode_items(paired), as_arrays=True)
+    assert arr[2][0].tolist() == [5, 6] and arr[2][1].tolist() == [[0, 120], [130, 300]] and arr[9][0].size == 0 and arr[9][1].shape == (0, 2)
+    assert {k: v.tolist() for k, v in schedule._decode_items(schedule._encode_items(local), as_arrays=True).items()} == local
     lens = [16000, 24000, 700, 52000, 8000, 31000, 399]
     for world in (1, 2, 3):
         for stamped in (False, True):
