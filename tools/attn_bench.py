@@ -7,7 +7,10 @@ import sys
 import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from funasr_b200 import ops  # noqa: E402
+from funasr_b200 import _lib, ops  # noqa: E402
+
+if os.environ.get("FB200_LIB"):  # an experimental build of the library next to the shipped one (tools only)
+    _lib.LIB_PATH = os.path.join(os.path.dirname(_lib.LIB_PATH), os.environ["FB200_LIB"])
 
 DEV = "cuda:0"
 NP = int(sys.argv[1]) if len(sys.argv) > 1 else 2
