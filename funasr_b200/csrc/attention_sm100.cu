@@ -37,15 +37,19 @@ namespace fb200 {
 constexpr int TQ = 128;   // query rows per item
 constexpr int TK = 64;    // key/value rows per tile
 constexpr int HD = 128;   // head dim
-constexpr int KS = 3;     // shared-memory stages of the K tiles
-constexpr int VS = 2;     // ... of the V tiles
+constexpr int VS = 2;     // shared-memory stages of the V tiles
+// ... of the K tiles: 3 with single-part operands, 2 with hi + mid parts (32 KB per stage) -- the third stage's 32 KB hold the
+// output boxes there, so that the Q staging area is free for the NEXT item's Q tile while an item's output is written
+__host__ __device__ constexpr int attn_k_stages(int np) { return np == 1 ? 3 : 2; }
 constexpr int kAttnThreads = 384;  // 3 warpgroups (register budgets are set per warpgroup)
 constexpr float kRescaleThreshold = 8.0f;  // log2 units
 // tensor-memory columns
 constexpr uint32_t kTmemS = 0, kTmemP = 128, kTmemO = 256, kTmemQ = 384, kTmemCols = 512;
-// staging area of the Q / output warps: the Q tile of the next item (NP parts x 2 column blocks of
-// [128 rows x 128 B]), later two [32 x 64] output boxes per warp
-__host__ __device__ constexpr uint32_t attn_stage_bytes(int np) { return np * 2 * TQ * 128 > 32768 ? np * 2 * TQ * 128 : 32768; }
+// staging areas of the Q / output warps: the Q tile of the next item (NP parts x 2 column blocks of [128 rows x 128 B]),
+// then two [32 x 64] output boxes per warp (separate areas: the next item's Q is fetched a whole item ahead)
+__host__ __device__ constexpr uint32_t attn_qstage_bytes(int np) { return np * 2 * TQ * 128; }
+constexpr uint32_t kAttnOutBytes = 4 * 8192;
+__host__ __device__ constexpr uint32_t attn_stage_bytes(int np) { return attn_qstage_bytes(np) + kAttnOutBytes; }
 
 #ifdef FB200_TRACE
 __device__ long long g_attn_trace[8][512];
@@ -151,7 +155,9 @@ attention_tcgen05_kernel(const __grid_constant__ CUtensorMap map_q, const __grid
   constexpr uint32_t kKBytes = NP * 2 * kKBlk;   // one stage: all parts, both column blocks
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = smem_u32(smem_raw);
+  constexpr int KS = attn_k_stages(NP);
   const uint32_t k_sm = base, v_sm = k_sm + KS * kKBytes, stage_sm = v_sm + VS * kKBytes;
+  const uint32_t outbox_sm = stage_sm + attn_qstage_bytes(NP);
   const uint32_t l_sm = stage_sm + attn_stage_bytes(NP);  // row sums of four items
   const uint32_t bar_base = l_sm + 4 * TQ * 4;
   const uint32_t tmem_slot = bar_base;
