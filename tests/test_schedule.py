@@ -75,6 +75,31 @@ class _FakeStampEngine(_FakeEngine):
         return ids, [[[i, i + 10] for i in row] for row in ids]
 
 
+
+class _ArrayEngine(_FakeEngine):
+    """An engine that can hand its ids over as int32 arrays (ParaformerEngine.RETURNS_ARRAYS)."""
+
+    RETURNS_ARRAYS = True
+
+    def recognize(self, waves, as_arrays=False):
+        ids = super().recognize(waves)
+        return [np.asarray(r, np.int32) for r in ids] if as_arrays else ids
+
+
+def test_recognize_sharded_one_rank_lists_and_arrays():
+    """world_size 1 (no process group): lists by default even when the engine produced arrays, arrays on request."""
+    lens = [16000, 700, 52000, 399]
+    waves = [synth.synth_waveform(i, n) for i, n in enumerate(lens)]
+    want = _FakeEngine().recognize(waves)
+    got = schedule.recognize_sharded(_ArrayEngine(), waves, 0, 1)
+    assert got == want and all(isinstance(r, list) and all(isinstance(t, int) for t in r) for r in got)
+    arr = schedule.recognize_sharded(_ArrayEngine(), waves, 0, 1, as_arrays=True)
+    assert all(isinstance(a, np.ndarray) and a.dtype == np.int32 for a in arr) and [a.tolist() for a in arr] == want
+    arr2 = schedule.recognize_sharded(_FakeStampEngine(), waves, 0, 1, as_arrays=True)
+    want2 = _FakeStampEngine().recognize(waves)
+    assert [a.tolist() for a in arr2[0]] == want2[0] and [a.tolist() for a in arr2[1]] == want2[1]
+
+
 def _worker(rank, world, port, lens, out_path):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     dist.init_process_group("gloo", rank=rank, world_size=world)
