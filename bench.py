@@ -65,7 +65,8 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default="fp32", choices=["fp32", "fp32x6", "bf16"])
     ap.add_argument("--utts", type=int, default=1024)
-    ap.add_argument("--max-rows", type=int, default=18944, help="packed rows per batch (148 SMs x 128-row tiles)")
+    ap.add_argument("--max-rows", type=int, default=56832,
+                    help="packed rows per batch (3 waves of 148 SMs x 128-row tiles; 18944 = one wave was the default until the end of round 2)")
     ap.add_argument("--cpu-utts", type=int, default=96, help="utterances of the workload timed on the host cores (~10 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the sub-results for the other BASELINE configs")

@@ -231,7 +231,7 @@ class ConformerCTCEngine:
     DROP_MASK = 0b111  # ids 0, 1, 2 (model.py:243-247)
 
     def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp32",
-                 window: str = "hamming", max_rows: int = 18944):
+                 window: str = "hamming", max_rows: int = 56832):
         if precision not in ParaformerEngine.PRECISIONS:
             raise ValueError("precision must be one of %s" % sorted(ParaformerEngine.PRECISIONS))
         if not torch.cuda.is_available():

@@ -159,7 +159,7 @@ class Recognizer {
   int stage(const std::vector<int>& batch, int slot, const float* const* waves, const int* lens);
   int reserve_wave(size_t samples);
 
-  int device_ = 0, np_ = 2, max_rows_ = 18944, heads_ = 4;
+  int device_ = 0, np_ = 2, max_rows_ = 56832, heads_ = 4;
   int d_ = 512, din_ = 560, ff_ = 2048, vocab_ = 0, n_mels_ = 80, lfr_m_ = 7, lfr_n_ = 6;
   int frame_len_ = 400, frame_shift_ = 160, nfft_ = 512;
   float eps_ = 1e-12f, tail_ = 0.45f;
@@ -1046,7 +1046,7 @@ RT_API void* fb200_offline_init(const char* model_dir, int device, int precision
   Recognizer* r = nullptr;
   try {
     r = new Recognizer();
-    if (r->init(model_dir, device, precision == 0 ? 2 : 1, max_rows > 0 ? max_rows : 18944) != FB200_OK) {
+    if (r->init(model_dir, device, precision == 0 ? 2 : 1, max_rows > 0 ? max_rows : 56832) != FB200_OK) {
       delete r;
       return nullptr;
     }

@@ -37,6 +37,15 @@ def _dev(t: torch.Tensor, device) -> torch.Tensor:
     return t.detach().to(device=device, dtype=torch.float32).contiguous()
 
 
+
+# Packed encoder rows per batch: three waves of 148 SMs x 128-row GEMM tiles.  Measured on the 1024-utterance set
+# (`tools/max_rows_sweep.sh`): 18 944 rows (one wave) 397 ms per step, 37 888 373.6, 56 832 356.7-365.2, 75 776 353.9,
+# 136 192 348.3 -- every launch has fixed costs (a GEMM's last epilogue, the attention's pipeline fill and the tail round of
+# its items, launch tails of the row-wise kernels) that larger batches spread over more rows; 56 832 keeps element offsets of
+# the widest matrix (the decoder's [rows, 2 x 16384] K / V projection) below 2^31 and still leaves ~5 batches per 1024
+# utterances for the upload of batch k + 1 to hide under batch k.
+DEFAULT_MAX_ROWS = 3 * 148 * 128
+
 class _Linear:
     """A Linear (or k-tap Conv1d) as a bf16 split operand + fp32 bias."""
 
@@ -463,7 +472,7 @@ class ParaformerEngine:
 
     def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp32",
                  cmvn: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, window: str = "hamming", heads: int = 4,
-                 max_rows: int = 16384):
+                 max_rows: int = DEFAULT_MAX_ROWS):
         if precision not in self.PRECISIONS:
             raise ValueError("precision must be one of %s" % sorted(self.PRECISIONS))
         if not torch.cuda.is_available():
@@ -651,7 +660,7 @@ class SenseVoiceEngine:
 
     def __init__(self, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp32",
                  cmvn: Optional[Tuple[torch.Tensor, torch.Tensor]] = None, window: str = "hamming", heads: int = 4,
-                 max_rows: int = 16384, blank_id: int = 0):
+                 max_rows: int = DEFAULT_MAX_ROWS, blank_id: int = 0):
         if precision not in ParaformerEngine.PRECISIONS:
             raise ValueError("precision must be one of %s" % sorted(ParaformerEngine.PRECISIONS))
         if not torch.cuda.is_available():

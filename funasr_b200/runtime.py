@@ -59,7 +59,7 @@ def export_model(state_dict: Dict[str, "np.ndarray"], model_dir: str, cmvn=None,
 class OfflineRecognizer:
     """`fb200_offline_init` / `_infer` / `_uninit` behind a Python object (tests and examples)."""
 
-    def __init__(self, model_dir: str, device: int = 0, precision: str = "fp32", max_rows: int = 18944):
+    def __init__(self, model_dir: str, device: int = 0, precision: str = "fp32", max_rows: int = 56832):
         self._lib = _lib.load()
         self._h = self._lib.fb200_offline_init(model_dir.encode("utf-8"), device, {"fp32": 0, "bf16": 1}[precision], max_rows)
         if not self._h:

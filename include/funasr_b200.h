@@ -446,8 +446,9 @@ int fb200_stack_profile_read(void* handle, int32_t* kinds, int32_t* barrier_afte
  * model_dir holds model.fb200 (tools/export_model.py, reference state_dict names), optionally am.mvn (Kaldi-nnet CMVN,
  * parsed as paraformer.cpp:314-349) and tokens.json (JSON array of token strings).  precision: 0 = fp32 parity
  * (hi + mid bf16 operands), 1 = bf16.  waves are HOST float32 in [-1, 1] (16 kHz); every utterance is computed with
- * batch-1 semantics.  NULL is returned on failure (text in fb200_last_error()).  Handles are not thread-safe: one
- * handle per thread / GPU. */
+ * batch-1 semantics.  max_rows = packed encoder rows per batch (<= 0: 56832 = three waves of 148 x 128-row tiles; the
+ * activation arena takes ~180 KB per row).  NULL is returned on failure (text in fb200_last_error()).  Handles are not
+ * thread-safe: one handle per thread / GPU. */
 void* fb200_offline_init(const char* model_dir, int device, int precision, int max_rows);
 void* fb200_offline_infer(void* handle, const float* const* h_waves, const int32_t* h_lens, int count);
 void* fb200_offline_infer_buffer(void* handle, const char* h_pcm16, int n_bytes, int sampling_rate);
