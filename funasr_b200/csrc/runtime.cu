@@ -1009,6 +1009,17 @@ int Recognizer::recognize(const float* const* waves, const int* lens, int n, Res
     cur_rows += rows[i];
   }
   if (!cur.empty()) batches.push_back(cur);
+  if (batches.size() >= 2) {
+    // nothing overlaps the upload of the first batch: cut it at a third of the row budget, the rest arrives under its kernels
+    size_t k = 0;
+    int acc = 0;
+    while (k < batches[0].size() && (k == 0 || acc + rows[batches[0][k]] <= max_rows_ / 3)) acc += rows[batches[0][k++]];
+    if (k < batches[0].size()) {
+      std::vector<int> rest(batches[0].begin() + (long)k, batches[0].end());
+      batches[0].resize(k);
+      batches.insert(batches.begin() + 1, rest);
+    }
+  }
   size_t need = 0;
   for (const auto& b : batches) {
     size_t smp = 0;

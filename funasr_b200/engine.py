@@ -568,7 +568,22 @@ class ParaformerEngine:
             cur_rows += rows[i]
         if cur:
             batches.append(cur)
-        return batches
+        return self._ramp(batches, rows)
+
+    def _ramp(self, batches: List[List[int]], rows: Sequence[int]) -> List[List[int]]:
+        """With several batches the FIRST one is cut at a third of the row budget: nothing can overlap its upload (218 MB of
+        waveforms for a full batch), so the kernels start after a third of that and the rest arrives under them."""
+        if len(batches) < 2:
+            return batches
+        head, acc = [], 0
+        for i in batches[0]:
+            if head and acc + rows[i] > self.max_rows // 3:
+                break
+            head.append(i)
+            acc += rows[i]
+        if len(head) == len(batches[0]):
+            return batches
+        return [head, batches[0][len(head):]] + batches[1:]
 
     # utterances per batch (None: the row budget alone); engines with a time-stamp head set it to the LSTM launch's limit
     max_utts = None
