@@ -403,6 +403,10 @@ int Recognizer::make_linear(const std::string& wname, const std::string& bname, 
 int Recognizer::init(const std::string& dir, int device, int nparts, int max_rows) {
   device_ = device;
   np_ = nparts;
+  if (max_rows < 1 || max_rows > 65536) {  // element offsets of the [rows, 2 x 16384] K / V projection stay below 2^31
+    set_error("runtime: max_rows %d outside [1, 65536]", max_rows);
+    return FB200_EINVAL;
+  }
   max_rows_ = max_rows;
   const char* genv = getenv("FB200_RT_GRAPHS");  // FB200_RT_GRAPHS=0: always launch kernel by kernel
   use_graphs_ = genv == nullptr || atoi(genv) != 0;

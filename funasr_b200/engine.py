@@ -45,6 +45,7 @@ def _dev(t: torch.Tensor, device) -> torch.Tensor:
 # the widest matrix (the decoder's [rows, 2 x 16384] K / V projection) below 2^31 and still leaves ~5 batches per 1024
 # utterances for the upload of batch k + 1 to hide under batch k.
 DEFAULT_MAX_ROWS = 3 * 148 * 128
+MAX_ROWS_LIMIT = 65536  # larger budgets ran in the sweep but their results were never checked: refused
 
 class _Linear:
     """A Linear (or k-tap Conv1d) as a bf16 split operand + fp32 bias."""
@@ -477,6 +478,9 @@ class ParaformerEngine:
             raise ValueError("precision must be one of %s" % sorted(self.PRECISIONS))
         if not torch.cuda.is_available():
             raise RuntimeError("funasr_b200: no CUDA device -- this path has no CPU fallback")
+        if not 1 <= max_rows <= MAX_ROWS_LIMIT:
+            raise ValueError("max_rows must be in [1, %d] (element offsets of the [rows, 2 x 16384] K / V projection stay below 2^31)"
+                             % MAX_ROWS_LIMIT)
         self.device = torch.device(device)
         self.precision = precision
         self.nparts = self.PRECISIONS[precision]

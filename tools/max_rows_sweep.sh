@@ -1,4 +1,4 @@
-for MR in ${SWEEP:-18944 37888 56832 18944}; do
+for MR in ${SWEEP:-18944 37888 56832 65536 18944}; do
   echo "== max_rows=$MR"
   python bench.py --max-rows $MR --steps 4 --warmup 3 --no-cpu-baseline --no-configs 2>/dev/null | tail -1 | python -c "
 import json,sys
