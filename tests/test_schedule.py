@@ -198,3 +198,25 @@ def test_recognize_segments_with_stamps_shifts_by_segment_start():
     assert eng.lens == [800 * 16, 16000 * 3 - 1500 * 16]  # the second segment is clipped to the recording
     assert ids == [10, 20, 11, 21]
     assert stamps == [[105, 150], [150, 190], [1505, 1550], [1550, 1591]]
+
+
+def test_default_row_budget_is_whole_waves_and_ramp_splits_only_the_first_batch():
+    """engine.DEFAULT_MAX_ROWS = whole waves of 148 x 128-row tiles below the offset limit; ParaformerEngine._ramp (host logic,
+    no GPU needed) cuts the first of several batches at a third of the budget and leaves everything else alone."""
+    from funasr_b200 import engine
+
+    assert engine.DEFAULT_MAX_ROWS % (148 * 128) == 0 and engine.DEFAULT_MAX_ROWS <= engine.MAX_ROWS_LIMIT
+
+    class _Planner:
+        max_rows = 900
+        _ramp = engine.ParaformerEngine._ramp
+
+    rows = [500, 400, 300, 200, 100, 90, 80]
+    one = [[0, 1]]
+    assert _Planner()._ramp(one, rows) == one  # a single batch is never split
+    got = _Planner()._ramp([[0, 1], [2, 3, 4, 5, 6]], rows)
+    assert got == [[0], [1], [2, 3, 4, 5, 6]]  # 500 rows already exceed a third of 900: the head is one utterance
+    got = _Planner()._ramp([[4, 5, 6], [0]], rows)
+    assert got == [[4, 5, 6], [0]]  # the whole first batch fits into the third: unchanged
+    got = _Planner()._ramp([[3, 4, 5, 6], [0, 1]], rows)
+    assert got == [[3, 4], [5, 6], [0, 1]] and sorted(sum(got, [])) == [0, 1, 3, 4, 5, 6]
