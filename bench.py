@@ -454,8 +454,12 @@ def main():
         try:
             with open(os.path.join(ROOT, "profiles", name)) as f:
                 _t = json.load(f)
-            gemm_traffic = _t["dram_bytes_per_launch"]
-            gemm_traffic_src = "profiles/%s (ncu dram__bytes_read+write.sum, avg over %d launches)" % (name, _t["launches"])
+            if int(_t.get("max_rows", 18944)) == args.max_rows:
+                gemm_traffic = _t["dram_bytes_per_launch"]
+                gemm_traffic_src = "profiles/%s (ncu dram__bytes_read+write.sum, avg over %d launches)" % (name, _t["launches"])
+            else:  # per launch like `achieved`: a capture at another rows-per-launch does not apply
+                gemm_traffic_src = "none at %d-row batches; profiles/%s holds %.0f MB per launch for %d-row batches" % (
+                    args.max_rows, name, _t["dram_bytes_per_launch"] / 1e6, int(_t.get("max_rows", 18944)))
             break
         except (OSError, KeyError, ValueError):
             continue
