@@ -450,17 +450,17 @@ def main():
     d2h = int(n_tok * 4 + len(durs) * 4)
     # DRAM bytes per GEMM launch: one ncu pass over the same command, summarised under profiles/ (bytes, or None)
     gemm_traffic, gemm_traffic_src = None, None
-    for name in ("r02_gemm_dram.json", "r01_gemm_dram.json"):
+    for name in ("r02_gemm_dram_56832.json", "r02_gemm_dram.json", "r01_gemm_dram.json"):
         try:
             with open(os.path.join(ROOT, "profiles", name)) as f:
                 _t = json.load(f)
-            if int(_t.get("max_rows", 18944)) == args.max_rows:
+            if int(_t.get("max_rows", 18944)) == args.max_rows:  # per launch like `achieved`: same rows per launch only
                 gemm_traffic = _t["dram_bytes_per_launch"]
                 gemm_traffic_src = "profiles/%s (ncu dram__bytes_read+write.sum, avg over %d launches)" % (name, _t["launches"])
-            else:  # per launch like `achieved`: a capture at another rows-per-launch does not apply
+                break
+            if gemm_traffic_src is None:
                 gemm_traffic_src = "none at %d-row batches; profiles/%s holds %.0f MB per launch for %d-row batches" % (
                     args.max_rows, name, _t["dram_bytes_per_launch"] / 1e6, int(_t.get("max_rows", 18944)))
-            break
         except (OSError, KeyError, ValueError):
             continue
     if world == 1:
